@@ -71,3 +71,110 @@ extern "C" int fqlpop_gemm_test(const fqlpop_gemm_test_t* d, void* stream) {
   if (e != cudaSuccess) return fail(std::string("launch: ") + cudaGetErrorString(e));
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// population
+// ---------------------------------------------------------------------------------------------------------
+#include "pop.h"
+
+#define POP(h)                                   \
+  fqlpop::Population* P = (fqlpop::Population*)(h); \
+  if (!P) return fail("null handle")
+
+extern "C" int fqlpop_create(const fqlpop_config_t* c, const float* alphas, const uint64_t* seeds, void** out) {
+  if (!c || !alphas || !seeds || !out) return fail("null argument");
+  fqlpop::PopParams p{};
+  p.O = c->ob_dim; p.A = c->action_dim; p.H_actor = c->hidden_actor; p.H_value = c->hidden_value;
+  p.n_hidden_actor = c->n_hidden_actor; p.n_hidden_value = c->n_hidden_value; p.E = c->num_ensembles;
+  p.F = c->flow_steps; p.B = c->batch_size; p.P = c->population;
+  p.lr = c->lr; p.discount = c->discount; p.tau = c->tau; p.adam_b1 = c->adam_b1; p.adam_b2 = c->adam_b2;
+  p.adam_eps = c->adam_eps; p.ln_eps = c->ln_eps;
+  p.q_agg_min = c->q_agg_min; p.normalize_q_loss = c->normalize_q_loss; p.layer_norm = c->layer_norm;
+  p.actor_layer_norm = c->actor_layer_norm;
+  fqlpop::Population* P = nullptr;
+  std::string err;
+  if (fqlpop::pop_create_impl(p, alphas, (const unsigned long long*)seeds, &P, &err)) return fail(err);
+  *out = P;
+  return 0;
+}
+extern "C" int fqlpop_destroy(void* h) {
+  fqlpop::pop_destroy_impl((fqlpop::Population*)h);
+  return 0;
+}
+extern "C" int fqlpop_set_dataset(void* h, const float* obs, const float* act, const float* next_obs,
+                                  const float* rew, const float* mask, int64_t n) {
+  POP(h);
+  if (!obs || !act || !next_obs || !rew || !mask || n <= 0 || n >= (1ll << 32)) return fail("bad dataset");
+  fqlpop::pop_invalidate_plan(P);
+  P->ds = fqlpop::Dataset{obs, act, next_obs, rew, mask, (long long)n};
+  return 0;
+}
+extern "C" int fqlpop_set_noise(void* h, const int64_t* indices, const float* z_critic, const float* x0,
+                                const float* t, const float* z_actor, const float* z_mse) {
+  POP(h);
+  fqlpop::pop_invalidate_plan(P);
+  P->noise.indices = (const long long*)indices;
+  P->noise.z_critic = z_critic; P->noise.x0 = x0; P->noise.t = t; P->noise.z_actor = z_actor; P->noise.z_mse = z_mse;
+  return 0;
+}
+extern "C" int fqlpop_set_active(void* h, const int32_t* members, int32_t n) {
+  POP(h);
+  std::string err;
+  if (fqlpop::pop_set_active_impl(P, members, n, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_step(void* h, int32_t n_steps, void* stream) {
+  POP(h);
+  std::string err;
+  if (fqlpop::pop_step_impl(P, n_steps, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_total_loss(void* h, void* stream) {
+  POP(h);
+  std::string err;
+  if (fqlpop::pop_total_loss_impl(P, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_info(void* h, float* out_host, int32_t with_grad_stats, void* stream) {
+  POP(h);
+  if (!out_host) return fail("null output");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (with_grad_stats) fqlpop::launch_grad_stats(P, s);
+  cudaError_t e = cudaMemcpyAsync(out_host, P->info, sizeof(float) * P->c.P * fqlpop::kInfoSlots,
+                                  cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  if (e != cudaSuccess) return fail(std::string("fqlpop_info: ") + cudaGetErrorString(e));
+  return 0;
+}
+extern "C" int fqlpop_leaf(void* h, int32_t net, int32_t layer, int32_t kind, int32_t which, int32_t member,
+                           float* host, int32_t to_host) {
+  POP(h);
+  if (!host) return fail("null host buffer");
+  cudaDeviceSynchronize();
+  std::string err;
+  if (fqlpop::pop_leaf_io(P, net, layer, kind, which, member, host, to_host, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_refresh_shadow(void* h, void* stream) {
+  POP(h);
+  std::string err;
+  if (fqlpop::pop_refresh_shadow_impl(P, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_counters(void* h, int32_t* adam_steps, uint64_t* step_counter, int32_t set) {
+  POP(h);
+  cudaDeviceSynchronize();
+  cudaError_t e = cudaSuccess;
+  const cudaMemcpyKind k = set ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+  if (adam_steps) e = set ? cudaMemcpy(P->adam_step, adam_steps, sizeof(int) * P->c.P, k)
+                          : cudaMemcpy(adam_steps, P->adam_step, sizeof(int) * P->c.P, k);
+  if (e == cudaSuccess && step_counter)
+    e = set ? cudaMemcpy(P->step_counter, step_counter, sizeof(uint64_t), k)
+            : cudaMemcpy(step_counter, P->step_counter, sizeof(uint64_t), k);
+  if (e != cudaSuccess) return fail(std::string("fqlpop_counters: ") + cudaGetErrorString(e));
+  return 0;
+}
+extern "C" int fqlpop_launches_per_step(void* h) {
+  fqlpop::Population* P = (fqlpop::Population*)h;
+  return P ? fqlpop::pop_launches_per_step(P) : 0;
+}

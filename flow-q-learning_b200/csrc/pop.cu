@@ -1,0 +1,651 @@
+// Population engine: arenas, activation buffers, the dependency-ordered multi-stream schedule of one lockstep
+// FQL update (captured once into a CUDA graph and replayed), forward-only loss evaluation, parameter I/O.
+//
+// Schedule of one step (SURVEY.md Appendix A maps each pass to the upstream loss term):
+//   s0: prep -> Euler flow chain (F x [4 GEMM + head]) ------------------------> pi_dout -> PI backward -> Adam(pi)
+//   s1: PI forward (3B rows) -> TQ forward -> QC forward -> QC backward -> [QA done] -> Adam(critic)
+//   s2: BC forward -> BC backward -> QA forward -> QA input-gradient chain -> [Euler done] -> Adam(bc)
+#include "pop.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+#include "philox.cuh"
+
+namespace fqlpop {
+
+#define CK(call)                                                                                  \
+  do {                                                                                            \
+    cudaError_t e_ = (call);                                                                      \
+    if (e_ != cudaSuccess) {                                                                      \
+      if (err) *err = std::string(#call) + ": " + cudaGetErrorString(e_);                         \
+      return 1;                                                                                   \
+    }                                                                                             \
+  } while (0)
+
+struct Plan {
+  cudaStream_t s[3] = {nullptr, nullptr, nullptr};
+  std::vector<cudaEvent_t> ev;
+  cudaGraph_t g_step = nullptr, g_loss = nullptr;
+  cudaGraphExec_t x_step = nullptr, x_loss = nullptr;
+  int launches_per_step = 0;  // kernels of ours inside one replay of the step graph
+};
+
+namespace {
+
+int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+template <class T>
+int dev_alloc(Population* P, T** out, long long count, std::string* err) {
+  void* p = nullptr;
+  const size_t bytes = (size_t)(count > 0 ? count : 1) * sizeof(T);
+  CK(cudaMalloc(&p, bytes));
+  CK(cudaMemset(p, 0, bytes));
+  P->allocs.push_back(p);
+  *out = reinterpret_cast<T*>(p);
+  return 0;
+}
+
+NetLayout make_layout(int nb, int in_dim, int H, int n_hidden, int out_dim, int ln) {
+  NetLayout L;
+  L.nb = nb; L.in_dim = in_dim; L.in_pad = round_up(in_dim, 64); L.H = H; L.n_hidden = n_hidden;
+  L.out_dim = out_dim; L.ln = ln;
+  long long o = 0;
+  for (int l = 0; l <= n_hidden; ++l) {
+    L.offW[l] = o; o += (long long)L.K(l) * L.N(l);
+    L.offb[l] = o; o += L.N(l);
+    if (ln && l < n_hidden) {
+      L.offg[l] = o; o += H;
+      L.offbeta[l] = o; o += H;
+    }
+  }
+  L.S = o;  // every leaf size is a multiple of 64 floats, so S and all offsets are too
+  return L;
+}
+
+int alloc_arena(Population* P, Arena& ar, const NetLayout& L, bool with_target, std::string* err) {
+  ar.L = L;
+  ar.V = P->c.P * L.nb;
+  const long long n = (long long)ar.V * L.S;
+  if (dev_alloc(P, &ar.theta, n, err) || dev_alloc(P, &ar.mu, n, err) || dev_alloc(P, &ar.nu, n, err) ||
+      dev_alloc(P, &ar.grad, n, err) || dev_alloc(P, &ar.shadow, n, err))
+    return 1;
+  if (with_target && (dev_alloc(P, &ar.target, n, err) || dev_alloc(P, &ar.tshadow, n, err))) return 1;
+  return 0;
+}
+
+int alloc_pass(Population* P, PassBuf& pb, const NetLayout& L, int V, int M, bool save, std::string* err) {
+  pb.V = V; pb.M = M; pb.in_pad = L.in_pad; pb.H = L.H; pb.n_hidden = L.n_hidden; pb.save = save; pb.ln = L.ln;
+  const long long act = (long long)V * M * L.H;
+  if (dev_alloc(P, &pb.X0, (long long)V * M * L.in_pad, err)) return 1;
+  const int nh = save ? L.n_hidden : 2;
+  for (int l = 0; l < nh; ++l)
+    if (dev_alloc(P, &pb.h[l], act, err)) return 1;
+  if (save)
+    for (int l = 0; l < L.n_hidden; ++l) {
+      if (dev_alloc(P, &pb.gp[l], act, err)) return 1;
+      if (L.ln && (dev_alloc(P, &pb.xhat[l], act, err) || dev_alloc(P, &pb.rstd[l], (long long)V * M, err))) return 1;
+    }
+  return 0;
+}
+
+int alloc_bwd(Population* P, BwdBuf& bw, const NetLayout& L, int V, int M, bool partials, std::string* err) {
+  bw.V = V; bw.M = M; bw.H = L.H; bw.m_tiles = (M + kBlockM - 1) / kBlockM;
+  if (dev_alloc(P, &bw.dout, (long long)V * M * kHeadPad, err)) return 1;
+  for (int l = 0; l < L.n_hidden; ++l) {
+    if (dev_alloc(P, &bw.dz[l], (long long)V * M * L.H, err)) return 1;
+    if (partials) {
+      const long long n = (long long)V * bw.m_tiles * L.H;
+      if (dev_alloc(P, &bw.dbias_part[l], n, err)) return 1;
+      if (L.ln && (dev_alloc(P, &bw.dgamma_part[l], n, err) || dev_alloc(P, &bw.dbeta_part[l], n, err))) return 1;
+    }
+  }
+  return 0;
+}
+
+// Glorot-uniform kernels (true fan-in / fan-out), zero biases, LayerNorm scale 1; padding stays zero.
+__global__ void init_arena_kernel(float* theta, NetLayout L, int V, const unsigned long long* seeds, int net_id) {
+  const int v = blockIdx.y;
+  const int p = v / L.nb, e = v - p * L.nb;
+  float* th = theta + (long long)v * L.S;
+  for (int l = 0; l <= L.n_hidden; ++l) {
+    const int K = L.K(l), N = L.N(l), Kt = L.K_true(l), Nt = L.N_true(l);
+    const float lim = sqrtf(6.0f / (float)(Kt + Nt));
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < K * N; i += gridDim.x * blockDim.x) {
+      const int k = i / N, n = i - k * N;
+      float w = 0.f;
+      if (k < Kt && n < Nt) {
+        const unsigned long long stream = 0xF00D000000000000ull + (unsigned long long)(net_id * 64 + l * 4 + e);
+        w = (2.f * philox_uniform(seeds[p], stream, (uint32_t)k, (uint32_t)n) - 1.f) * lim;
+      }
+      th[L.offW[l] + i] = w;
+    }
+    if (L.ln && l < L.n_hidden)
+      for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < L.H; i += gridDim.x * blockDim.x) th[L.offg[l] + i] = 1.f;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// GEMM group builders
+// ---------------------------------------------------------------------------------------------------
+struct Builder {
+  Population* P;
+  std::string* err;
+  bool ok = true;
+  GemmLaunch* L = nullptr;  // scratch launch descriptor (heap)
+  int count = 0;            // kernels launched through this builder
+
+  void begin(int nb) {
+    memset(L, 0, sizeof(GemmLaunch));
+    L->P = (int)P->h_members.size() * nb;
+    L->n_active = nullptr;
+    L->member_list = nb == 1 ? P->member_list : P->member_list_e;
+  }
+  GemmGroup& add() { return L->g[L->num_groups++]; }
+  void tmap(CUtensorMap* m, const void* base, long long inner, long long rows, long long batch, long long ld,
+            long long ms, int box_rows) {
+    const int rc = encode_tmap_bf16(m, base, inner, rows, batch, ld, ms, box_rows);
+    if (rc != 0 && ok) {
+      ok = false;
+      if (err) *err = "cuTensorMapEncodeTiled failed rc=" + std::to_string(rc);
+    }
+  }
+  void launch(int n_sub, cudaStream_t s) {
+    const int grid = finalize_launch(L, n_sub);
+    cudaError_t e = launch_gemm(*L, n_sub, grid, s);
+    if (e != cudaSuccess && ok) {
+      ok = false;
+      if (err) *err = std::string("launch_gemm: ") + cudaGetErrorString(e);
+    }
+    ++count;
+  }
+
+  // forward layer l of `pass` on rows [row0, row0 + M): h_l = act(x W_l + b_l) (+ LayerNorm)
+  void fwd_group(PassBuf& pass, const Arena& ar, const float* params, const __nv_bfloat16* wsh, int l, int row0, int M,
+                 bool save) {
+    const NetLayout& N = ar.L;
+    GemmGroup& g = add();
+    const int K = N.K(l);
+    const __nv_bfloat16* X = l == 0 ? pass.X0 : pass.hl(l - 1);
+    g.M = M; g.N = N.H; g.k_blocks = K / 64; g.a_mn = 0; g.b_mn = 1;
+    g.a_row0 = row0;
+    tmap(&g.mapA, X, K, pass.M, pass.V, K, (long long)pass.M * K, 128);
+    tmap(&g.mapB, wsh + N.offW[l], N.H, K, ar.V, N.H, N.S, 64);
+    EpiParams& E = g.epi;
+    E.kind = N.ln ? EPI_FWD_LN : EPI_FWD;
+    E.act = ACT_GELU;
+    E.ln_eps = P->c.ln_eps;
+    const long long ams = (long long)pass.M * N.H, roff = (long long)row0 * N.H;
+    E.bias = {params + N.offb[l], N.S, N.H, 0};
+    if (N.ln) {
+      E.gamma = {params + N.offg[l], N.S, N.H, 0};
+      E.beta = {params + N.offbeta[l], N.S, N.H, 0};
+    }
+    E.out_h = {pass.hl(l) + roff, ams, N.H, 0};
+    if (save) {
+      E.out_gp = {pass.gp[l] + roff, ams, N.H, 0};
+      if (N.ln) {
+        E.out_xhat = {pass.xhat[l] + roff, ams, N.H, 0};
+        E.out_rstd = {pass.rstd[l] + row0, (long long)pass.M, 1, 0};
+      }
+    }
+  }
+
+  // backward through layer l (l >= 1): dz_{l-1} = act'(z_{l-1}) * LNbwd(dz_l W_l^T); dz_{n_hidden} = dout
+  void dgrad_group(PassBuf& pass, BwdBuf& bw, const Arena& ar, int l, int row0, bool partials) {
+    const NetLayout& N = ar.L;
+    GemmGroup& g = add();
+    const int Kd = N.N(l);  // reduction = out features of layer l (64 for the head)
+    const __nv_bfloat16* dZ = l == N.n_hidden ? bw.dout : bw.dz[l];
+    g.M = bw.M; g.N = N.H; g.k_blocks = Kd / 64; g.a_mn = 0; g.b_mn = 0;
+    tmap(&g.mapA, dZ, Kd, bw.M, bw.V, Kd, (long long)bw.M * Kd, 128);
+    tmap(&g.mapB, ar.shadow + N.offW[l], Kd, N.K(l), ar.V, Kd, N.S, 128);
+    EpiParams& E = g.epi;
+    E.kind = N.ln ? EPI_DGRAD_LN : EPI_DGRAD;
+    const long long ams = (long long)pass.M * N.H, roff = (long long)row0 * N.H;
+    E.gp = {pass.gp[l - 1] + roff, ams, N.H, 0};
+    if (N.ln) {
+      E.gamma = {ar.theta + N.offg[l - 1], N.S, N.H, 0};
+      E.xhat = {pass.xhat[l - 1] + roff, ams, N.H, 0};
+      E.rstd = {pass.rstd[l - 1] + row0, (long long)pass.M, 1, 0};
+    }
+    E.out_h = {bw.dz[l - 1], (long long)bw.M * N.H, N.H, 0};
+    if (partials) {
+      const long long pms = (long long)bw.m_tiles * N.H;
+      E.out_dbias_part = {bw.dbias_part[l - 1], pms, N.H, 0};
+      if (N.ln) {
+        E.out_dgamma_part = {bw.dgamma_part[l - 1], pms, N.H, 0};
+        E.out_dbeta_part = {bw.dbeta_part[l - 1], pms, N.H, 0};
+      }
+    }
+  }
+
+  // gradient with respect to the (padded) network input: dx0 = dz_0 W_0^T, fp32
+  void dinput_group(BwdBuf& bw, const Arena& ar, float* out) {
+    const NetLayout& N = ar.L;
+    GemmGroup& g = add();
+    g.M = bw.M; g.N = N.in_pad; g.k_blocks = N.H / 64; g.a_mn = 0; g.b_mn = 0;
+    tmap(&g.mapA, bw.dz[0], N.H, bw.M, bw.V, N.H, (long long)bw.M * N.H, 128);
+    tmap(&g.mapB, ar.shadow + N.offW[0], N.H, N.in_pad, ar.V, N.H, N.S, 128);
+    g.epi.kind = EPI_STORE_F32;
+    g.epi.out_f32 = {out, (long long)bw.M * N.in_pad, N.in_pad, 0};
+  }
+
+  // weight gradient of layer l: dW_l = X_l^T dz_l  (fp32, written straight into the grad arena)
+  void wgrad_group(PassBuf& pass, BwdBuf& bw, const Arena& ar, int l, int row0) {
+    const NetLayout& N = ar.L;
+    GemmGroup& g = add();
+    const int Kin = N.K(l), Nout = N.N(l);
+    const __nv_bfloat16* X = l == 0 ? pass.X0 : pass.hl(l - 1);
+    const __nv_bfloat16* dZ = l == N.n_hidden ? bw.dout : bw.dz[l];
+    g.M = Kin; g.N = Nout; g.k_blocks = bw.M / 64; g.a_mn = 1; g.b_mn = 1;
+    g.a_row0 = row0;
+    tmap(&g.mapA, X, Kin, pass.M, pass.V, Kin, (long long)pass.M * Kin, 64);
+    tmap(&g.mapB, dZ, Nout, bw.M, bw.V, Nout, (long long)bw.M * Nout, 64);
+    g.epi.kind = EPI_STORE_F32;
+    g.epi.out_f32 = {ar.grad + N.offW[l], N.S, Nout, 0};
+  }
+};
+
+void record(Plan* pl, cudaEvent_t* out, cudaStream_t s) {
+  cudaEvent_t e;
+  cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+  pl->ev.push_back(e);
+  cudaEventRecord(e, s);
+  *out = e;
+}
+
+// Issues one lockstep step (train = update; !train = losses only) on the plan's streams. Called under stream
+// capture; s[0] is the origin stream.
+int issue_step(Population* P, bool train, std::string* err) {
+  Plan* pl = P->plan;
+  cudaStream_t s0 = pl->s[0], s1 = pl->s[1], s2 = pl->s[2];
+  const PopParams& c = P->c;
+  Builder b{P, err};
+  b.L = new GemmLaunch;
+  int pw = 0;  // pointwise launches
+  const int B = c.B;
+  const int nsub_q = P->critic.L.ln ? 4 : 1, nsub_a = P->pi.L.ln ? 4 : 1;
+  const int nh_q = P->critic.L.n_hidden, nh_a = P->pi.L.n_hidden;
+
+  cudaEvent_t e_prep, e_pi, e_qa, e_euler, e_s1, e_s2;
+  launch_prep(P, s0, train ? 1 : 0); ++pw;
+  record(pl, &e_prep, s0);
+  cudaStreamWaitEvent(s1, e_prep, 0);
+  cudaStreamWaitEvent(s2, e_prep, 0);
+
+  // ---- s0: Euler flow chain --------------------------------------------------------------------
+  for (int i = 0; i < c.F; ++i) {
+    for (int l = 0; l < nh_a; ++l) {
+      b.begin(1);
+      b.fwd_group(P->EU, P->bc, P->bc.theta, P->bc.shadow, l, 0, B, false);
+      b.launch(nsub_a, s0);
+    }
+    launch_euler_head(P, i, s0); ++pw;
+  }
+  record(pl, &e_euler, s0);
+
+  // ---- s1: one-step policy forward (rows [0,B) kept), TD target, critic forward/backward --------
+  for (int l = 0; l < nh_a; ++l) {
+    b.begin(1);
+    b.fwd_group(P->PI, P->pi, P->pi.theta, P->pi.shadow, l, 0, B, train);
+    b.fwd_group(P->PI, P->pi, P->pi.theta, P->pi.shadow, l, B, 2 * B, false);
+    b.launch(nsub_a, s1);
+  }
+  launch_pi_head(P, s1); ++pw;
+  record(pl, &e_pi, s1);
+  for (int l = 0; l < nh_q; ++l) {
+    b.begin(c.E);
+    b.fwd_group(P->TQ, P->critic, P->critic.target, P->critic.tshadow, l, 0, B, false);
+    b.launch(nsub_q, s1);
+  }
+  launch_tq_head(P, s1); ++pw;
+  for (int l = 0; l < nh_q; ++l) {
+    b.begin(c.E);
+    b.fwd_group(P->QC, P->critic, P->critic.theta, P->critic.shadow, l, 0, B, train);
+    b.launch(nsub_q, s1);
+  }
+  launch_qc_head(P, s1); ++pw;
+  if (train) {
+    for (int l = nh_q; l >= 1; --l) {
+      b.begin(c.E);
+      b.dgrad_group(P->QC, P->bQC, P->critic, l, 0, true);
+      b.launch(nsub_q, s1);
+    }
+    b.begin(c.E);
+    for (int l = 0; l <= nh_q; ++l) b.wgrad_group(P->QC, P->bQC, P->critic, l, 0);
+    b.launch(1, s1);
+  }
+
+  // ---- s2: BC flow forward/backward, then the critic pass on (s, clip(a_pi)) -----------------------
+  for (int l = 0; l < nh_a; ++l) {
+    b.begin(1);
+    b.fwd_group(P->BC, P->bc, P->bc.theta, P->bc.shadow, l, 0, B, train);
+    b.launch(nsub_a, s2);
+  }
+  launch_bc_head(P, s2); ++pw;
+  if (train) {
+    for (int l = nh_a; l >= 1; --l) {
+      b.begin(1);
+      b.dgrad_group(P->BC, P->bBC, P->bc, l, 0, true);
+      b.launch(nsub_a, s2);
+    }
+    b.begin(1);
+    for (int l = 0; l <= nh_a; ++l) b.wgrad_group(P->BC, P->bBC, P->bc, l, 0);
+    b.launch(1, s2);
+  }
+  cudaStreamWaitEvent(s2, e_pi, 0);
+  for (int l = 0; l < nh_q; ++l) {
+    b.begin(c.E);
+    b.fwd_group(P->QA, P->critic, P->critic.theta, P->critic.shadow, l, 0, B, train);
+    b.launch(nsub_q, s2);
+  }
+  launch_qa_head(P, s2); ++pw;
+  if (train) {
+    for (int l = nh_q; l >= 1; --l) {
+      b.begin(c.E);
+      b.dgrad_group(P->QA, P->bQA, P->critic, l, 0, false);
+      b.launch(nsub_q, s2);
+    }
+    b.begin(c.E);
+    b.dinput_group(P->bQA, P->critic, P->dx0_qa);
+    b.launch(1, s2);
+  }
+  record(pl, &e_qa, s2);
+
+  // ---- s0: distillation + policy backward -------------------------------------------------------
+  cudaStreamWaitEvent(s0, e_qa, 0);
+  launch_pi_dout(P, s0); ++pw;
+  if (train) {
+    for (int l = nh_a; l >= 1; --l) {
+      b.begin(1);
+      b.dgrad_group(P->PI, P->bPI, P->pi, l, 0, true);
+      b.launch(nsub_a, s0);
+    }
+    b.begin(1);
+    for (int l = 0; l <= nh_a; ++l) b.wgrad_group(P->PI, P->bPI, P->pi, l, 0);
+    b.launch(1, s0);
+    launch_small_grads(P, 2, s0); ++pw;
+    launch_adam(P, 2, s0); ++pw;
+    // critic optimizer: after every reader of the critic weights (QA chain on s2) is done
+    cudaStreamWaitEvent(s1, e_qa, 0);
+    launch_small_grads(P, 0, s1); ++pw;
+    launch_adam(P, 0, s1); ++pw;
+    // BC flow optimizer: after the Euler chain (s0) has stopped reading the BC weights
+    cudaStreamWaitEvent(s2, e_euler, 0);
+    launch_small_grads(P, 1, s2); ++pw;
+    launch_adam(P, 1, s2); ++pw;
+  }
+  record(pl, &e_s1, s1);
+  record(pl, &e_s2, s2);
+  cudaStreamWaitEvent(s0, e_s1, 0);
+  cudaStreamWaitEvent(s0, e_s2, 0);
+  launch_finish_info(P, train ? 1 : 0, s0); ++pw;
+  delete b.L;
+  if (!b.ok) return 1;
+  CK(cudaGetLastError());
+  if (train) pl->launches_per_step = b.count + pw;
+  return 0;
+}
+
+void destroy_graphs(Plan* pl) {
+  if (pl->x_step) cudaGraphExecDestroy(pl->x_step);
+  if (pl->x_loss) cudaGraphExecDestroy(pl->x_loss);
+  if (pl->g_step) cudaGraphDestroy(pl->g_step);
+  if (pl->g_loss) cudaGraphDestroy(pl->g_loss);
+  pl->x_step = pl->x_loss = nullptr;
+  pl->g_step = pl->g_loss = nullptr;
+  for (cudaEvent_t e : pl->ev) cudaEventDestroy(e);
+  pl->ev.clear();
+}
+
+int build_graph(Population* P, bool train, std::string* err) {
+  Plan* pl = P->plan;
+  CK(cudaStreamBeginCapture(pl->s[0], cudaStreamCaptureModeThreadLocal));
+  const int rc = issue_step(P, train, err);
+  cudaGraph_t g = nullptr;
+  cudaError_t e = cudaStreamEndCapture(pl->s[0], &g);
+  if (rc) {
+    if (g) cudaGraphDestroy(g);
+    return 1;
+  }
+  CK(e);
+  cudaGraphExec_t x = nullptr;
+  CK(cudaGraphInstantiate(&x, g, 0));
+  if (train) { pl->g_step = g; pl->x_step = x; }
+  else { pl->g_loss = g; pl->x_loss = x; }
+  return 0;
+}
+
+}  // namespace
+
+// =======================================================================================================
+// public (pop.h) entry points
+// =======================================================================================================
+static int upload_members(Population* P, std::string* err) {
+  const int n = (int)P->h_members.size();
+  std::vector<int> ve((size_t)n * P->c.E);
+  for (int i = 0; i < n; ++i)
+    for (int e = 0; e < P->c.E; ++e) ve[(size_t)i * P->c.E + e] = P->h_members[i] * P->c.E + e;
+  CK(cudaMemcpy(P->member_list, P->h_members.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(P->member_list_e, ve.data(), sizeof(int) * ve.size(), cudaMemcpyHostToDevice));
+  const int ne = n * P->c.E;
+  CK(cudaMemcpy(P->n_active, &n, sizeof(int), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(P->n_active_e, &ne, sizeof(int), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int pop_create_impl(const PopParams& c, const float* alphas, const unsigned long long* seeds, Population** out,
+                    std::string* err) {
+  auto bad = [&](const char* m) {
+    if (err) *err = m;
+    return 1;
+  };
+  if (c.P <= 0 || c.B <= 0 || c.O <= 0 || c.A <= 0) return bad("P, B, O, A must be positive");
+  if (c.B % 64) return bad("batch_size must be a multiple of 64 (the weight-gradient GEMM reduces over 64-row blocks)");
+  if (c.A > kMaxHeadOut) return bad("action_dim > 8 is not supported by the head kernels");
+  if (c.E < 1 || c.E > 4) return bad("num_ensembles must be in [1, 4]");
+  if (c.H_actor % 64 || c.H_value % 64 || c.H_actor <= 0 || c.H_value <= 0 || c.H_actor > 512 || c.H_value > 512)
+    return bad("hidden widths must be multiples of 64, at most 512");
+  if ((c.layer_norm && c.H_value != 512) || (c.actor_layer_norm && c.H_actor != 512))
+    return bad("LayerNorm networks need hidden width 512 (one CTA owns the full 512-wide row)");
+  if (c.n_hidden_actor < 1 || c.n_hidden_value < 1 || c.n_hidden_actor >= kMaxLayers || c.n_hidden_value >= kMaxLayers)
+    return bad("between 1 and 7 hidden layers are supported");
+  if (c.F < 1) return bad("flow_steps must be >= 1");
+  if (cudaError_t e = gemm_init(); e != cudaSuccess) {
+    if (err) *err = std::string("gemm_init: ") + cudaGetErrorString(e);
+    return 1;
+  }
+  if (int rc = pointwise_init()) {
+    if (err) *err = std::string("pointwise_init: ") + cudaGetErrorString((cudaError_t)rc);
+    return 1;
+  }
+  Population* P = new Population;
+  P->c = c;
+  const int V = c.P * c.E;
+  const NetLayout Lq = make_layout(c.E, c.O + c.A, c.H_value, c.n_hidden_value, 1, c.layer_norm);
+  const NetLayout Lb = make_layout(1, c.O + c.A + 1, c.H_actor, c.n_hidden_actor, c.A, c.actor_layer_norm);
+  const NetLayout Lp = make_layout(1, c.O + c.A, c.H_actor, c.n_hidden_actor, c.A, c.actor_layer_norm);
+  int rc = 0;
+  rc |= alloc_arena(P, P->critic, Lq, true, err);
+  rc |= alloc_arena(P, P->bc, Lb, false, err);
+  rc |= alloc_arena(P, P->pi, Lp, false, err);
+  rc = rc || alloc_pass(P, P->PI, Lp, c.P, 3 * c.B, true, err);
+  rc = rc || alloc_pass(P, P->TQ, Lq, V, c.B, false, err);
+  rc = rc || alloc_pass(P, P->QC, Lq, V, c.B, true, err);
+  rc = rc || alloc_pass(P, P->QA, Lq, V, c.B, true, err);
+  rc = rc || alloc_pass(P, P->BC, Lb, c.P, c.B, true, err);
+  rc = rc || alloc_pass(P, P->EU, Lb, c.P, c.B, false, err);
+  rc = rc || alloc_bwd(P, P->bQC, Lq, V, c.B, true, err);
+  rc = rc || alloc_bwd(P, P->bQA, Lq, V, c.B, false, err);
+  rc = rc || alloc_bwd(P, P->bBC, Lb, c.P, c.B, true, err);
+  rc = rc || alloc_bwd(P, P->bPI, Lp, c.P, c.B, true, err);
+  const long long PB = (long long)c.P * c.B;
+  rc = rc || dev_alloc(P, &P->act_f, PB * c.A, err) || dev_alloc(P, &P->vel, PB * c.A, err) ||
+       dev_alloc(P, &P->xe, PB * c.A, err) || dev_alloc(P, &P->target_a, PB * c.A, err) ||
+       dev_alloc(P, &P->api, PB * c.A, err) || dev_alloc(P, &P->rew, PB, err) || dev_alloc(P, &P->mask, PB, err) ||
+       dev_alloc(P, &P->y, PB, err) || dev_alloc(P, &P->dx0_qa, (long long)V * c.B * Lq.in_pad, err) ||
+       dev_alloc(P, &P->info, (long long)c.P * kInfoSlots, err) ||
+       dev_alloc(P, &P->leaf_stats, (long long)c.P * 64 * 4, err) || dev_alloc(P, &P->adam_bc, 2LL * c.P, err) ||
+       dev_alloc(P, &P->adam_step, c.P, err) || dev_alloc(P, &P->alphas, c.P, err) ||
+       dev_alloc(P, &P->seeds, c.P, err) || dev_alloc(P, &P->step_counter, 1, err) ||
+       dev_alloc(P, &P->member_list, c.P, err) || dev_alloc(P, &P->member_list_e, V, err) ||
+       dev_alloc(P, &P->n_active, 1, err) || dev_alloc(P, &P->n_active_e, 1, err);
+  if (rc) {
+    pop_destroy_impl(P);
+    return 1;
+  }
+  cudaMemcpy(P->alphas, alphas, sizeof(float) * c.P, cudaMemcpyHostToDevice);
+  cudaMemcpy(P->seeds, seeds, sizeof(unsigned long long) * c.P, cudaMemcpyHostToDevice);
+  P->h_members.resize(c.P);
+  for (int i = 0; i < c.P; ++i) P->h_members[i] = i;
+  if (upload_members(P, err)) {
+    pop_destroy_impl(P);
+    return 1;
+  }
+  // parameters: Glorot-uniform kernels, zero biases, LayerNorm scale 1, target = critic
+  int net = 0;
+  for (Arena* ar : {&P->critic, &P->bc, &P->pi}) {
+    init_arena_kernel<<<dim3(64, ar->V), 256>>>(ar->theta, ar->L, ar->V, P->seeds, net++);
+  }
+  cudaMemcpy(P->critic.target, P->critic.theta, sizeof(float) * (size_t)P->critic.V * P->critic.L.S,
+             cudaMemcpyDeviceToDevice);
+  launch_refresh_shadow(P, 0);
+  launch_fill_qa_dout(P, 0);
+  P->plan = new Plan;
+  for (int i = 0; i < 3; ++i) cudaStreamCreateWithFlags(&P->plan->s[i], cudaStreamNonBlocking);
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    if (err) *err = std::string("pop_create: ") + cudaGetErrorString(e);
+    pop_destroy_impl(P);
+    return 1;
+  }
+  *out = P;
+  return 0;
+}
+
+void pop_destroy_impl(Population* P) {
+  if (!P) return;
+  cudaDeviceSynchronize();
+  if (P->plan) {
+    destroy_graphs(P->plan);
+    for (int i = 0; i < 3; ++i)
+      if (P->plan->s[i]) cudaStreamDestroy(P->plan->s[i]);
+    delete P->plan;
+  }
+  for (void* p : P->allocs) cudaFree(p);
+  delete P;
+}
+
+void pop_invalidate_plan(Population* P) {
+  if (P->plan) {
+    cudaDeviceSynchronize();
+    destroy_graphs(P->plan);
+  }
+}
+
+int pop_set_active_impl(Population* P, const int* members, int n, std::string* err) {
+  if (n < 1 || n > P->c.P) {
+    if (err) *err = "active member count out of range";
+    return 1;
+  }
+  std::vector<char> seen(P->c.P, 0);
+  for (int i = 0; i < n; ++i) {
+    if (members[i] < 0 || members[i] >= P->c.P || seen[members[i]]) {
+      if (err) *err = "invalid or duplicate member id";
+      return 1;
+    }
+    seen[members[i]] = 1;
+  }
+  pop_invalidate_plan(P);
+  P->h_members.assign(members, members + n);
+  return upload_members(P, err);
+}
+
+static int run_plan(Population* P, bool train, int n_steps, cudaStream_t stream, std::string* err) {
+  Plan* pl = P->plan;
+  if (!P->ds.obs) {
+    if (err) *err = "no dataset / batch bound (call fqlpop_set_dataset first)";
+    return 1;
+  }
+  const bool eager = getenv("FQLPOP_EAGER") != nullptr;
+  cudaEvent_t e_in, e_out;
+  CK(cudaEventCreateWithFlags(&e_in, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&e_out, cudaEventDisableTiming));
+  CK(cudaEventRecord(e_in, stream));
+  CK(cudaStreamWaitEvent(pl->s[0], e_in, 0));
+  int rc = 0;
+  if (eager) {
+    for (int i = 0; i < n_steps && !rc; ++i) rc = issue_step(P, train, err);
+  } else {
+    cudaGraphExec_t& x = train ? pl->x_step : pl->x_loss;
+    if (!x) rc = build_graph(P, train, err);
+    for (int i = 0; i < n_steps && !rc; ++i) {
+      cudaError_t e = cudaGraphLaunch(x, pl->s[0]);
+      if (e != cudaSuccess) {
+        if (err) *err = std::string("cudaGraphLaunch: ") + cudaGetErrorString(e);
+        rc = 1;
+      }
+    }
+  }
+  if (!rc) {
+    cudaEventRecord(e_out, pl->s[0]);
+    cudaStreamWaitEvent(stream, e_out, 0);
+  }
+  cudaEventDestroy(e_in);
+  cudaEventDestroy(e_out);
+  return rc;
+}
+
+int pop_step_impl(Population* P, int n_steps, cudaStream_t stream, std::string* err) {
+  return run_plan(P, true, n_steps, stream, err);
+}
+int pop_total_loss_impl(Population* P, cudaStream_t stream, std::string* err) {
+  return run_plan(P, false, 1, stream, err);
+}
+int pop_refresh_shadow_impl(Population* P, cudaStream_t stream, std::string* err) {
+  launch_refresh_shadow(P, stream);
+  CK(cudaGetLastError());
+  return 0;
+}
+int pop_launches_per_step(const Population* P) { return P->plan ? P->plan->launches_per_step : 0; }
+
+// leaf I/O: kind 0 kernel [nb][K_true][N_true], 1 bias [nb][N_true], 2 LayerNorm scale, 3 LayerNorm bias [nb][H];
+// which 0 theta, 1 mu, 2 nu, 3 target, 4 grad. Host buffers are unpadded fp32.
+int pop_leaf_io(Population* P, int net, int layer, int kind, int which, int member, float* host, int to_host,
+                std::string* err) {
+  Arena* ar = net == 0 ? &P->critic : (net == 1 ? &P->bc : (net == 2 ? &P->pi : nullptr));
+  if (!ar || layer < 0 || layer > ar->L.n_hidden || member < 0 || member >= P->c.P) {
+    if (err) *err = "leaf_io: bad net/layer/member";
+    return 1;
+  }
+  float* base = which == 0 ? ar->theta : which == 1 ? ar->mu : which == 2 ? ar->nu : which == 3 ? ar->target
+                                                                                 : which == 4 ? ar->grad : nullptr;
+  if (!base) {
+    if (err) *err = "leaf_io: this arena has no such array";
+    return 1;
+  }
+  const NetLayout& L = ar->L;
+  long long off;
+  int rows, cols, ld;
+  if (kind == 0) { off = L.offW[layer]; rows = L.K_true(layer); cols = L.N_true(layer); ld = L.N(layer); }
+  else if (kind == 1) { off = L.offb[layer]; rows = 1; cols = L.N_true(layer); ld = L.N(layer); }
+  else if ((kind == 2 || kind == 3) && L.ln && layer < L.n_hidden) {
+    off = kind == 2 ? L.offg[layer] : L.offbeta[layer]; rows = 1; cols = L.H; ld = L.H;
+  } else {
+    if (err) *err = "leaf_io: no such leaf";
+    return 1;
+  }
+  for (int e = 0; e < L.nb; ++e) {
+    float* d = base + ((long long)member * L.nb + e) * L.S + off;
+    float* h = host + (long long)e * rows * cols;
+    if (to_host) CK(cudaMemcpy2D(h, sizeof(float) * cols, d, sizeof(float) * ld, sizeof(float) * cols, rows,
+                                 cudaMemcpyDeviceToHost));
+    else CK(cudaMemcpy2D(d, sizeof(float) * ld, h, sizeof(float) * cols, sizeof(float) * cols, rows,
+                         cudaMemcpyHostToDevice));
+  }
+  return 0;
+}
+
+}  // namespace fqlpop

@@ -39,6 +39,58 @@ typedef struct {
 } fqlpop_gemm_test_t;
 int fqlpop_gemm_test(const fqlpop_gemm_test_t* desc, void* stream);
 
+/* ---- population of FQL agents --------------------------------------------------------------------------
+ * One handle = P agents (one per BC coefficient alpha) resident on the current CUDA device, stepped in
+ * lockstep. Mirrors AgentConfig (/root/reference/trainer/config.py:6-23); ob_dim/action_dim are the two
+ * fields FQLAgent.create fills from the example batch (/root/reference/trainer/experiment.py:44-49).      */
+typedef struct {
+  int32_t ob_dim, action_dim;
+  int32_t hidden_actor, hidden_value;       /* uniform hidden width (multiple of 64, <= 512)              */
+  int32_t n_hidden_actor, n_hidden_value;   /* number of hidden layers (reference: 4)                     */
+  int32_t num_ensembles;                    /* critic ensemble size (upstream FQL: 2)                     */
+  int32_t flow_steps, batch_size, population;
+  float lr, discount, tau, adam_b1, adam_b2, adam_eps, ln_eps;
+  int32_t q_agg_min;                        /* 0: mean over the ensemble ("mean"), 1: "min"               */
+  int32_t normalize_q_loss, layer_norm, actor_layer_norm;
+} fqlpop_config_t;
+
+/* Replaces FQLAgent.create for every member (trainer/experiment.py:44-49): Glorot-uniform kernels, zero
+ * biases, LayerNorm scale 1, target = critic. alphas/seeds: host [population].                            */
+int fqlpop_create(const fqlpop_config_t* cfg, const float* alphas, const uint64_t* seeds, void** out_handle);
+int fqlpop_destroy(void* handle);
+
+/* Binds the offline dataset the on-device uniform gather reads (replaces Dataset.sample reached through
+ * Task.sample("train", B), task/offline_task_simulated.py:53-58). (dev) row-major fp32, borrowed.         */
+int fqlpop_set_dataset(void* handle, const float* obs, const float* act, const float* next_obs,
+                       const float* rew, const float* mask, int64_t n_rows);
+/* Parity mode: explicit row indices [P][B] and noise tensors [P][B][A] / t [P][B] (dev, borrowed).
+ * Any NULL pointer falls back to the counter-based Philox stream for that tensor.                         */
+int fqlpop_set_noise(void* handle, const int64_t* indices, const float* z_critic, const float* x0,
+                     const float* t, const float* z_actor, const float* z_mse);
+/* Members that keep training (successive-halving survivors, hpo/successive_halving.py:64-100).           */
+int fqlpop_set_active(void* handle, const int32_t* members, int32_t n);
+
+/* n lockstep updates of every active member: gather + FQLAgent.update (trainer/experiment.py:108-109).   */
+int fqlpop_step(void* handle, int32_t n_steps, void* stream);
+/* FQLAgent.total_loss(batch, grad_params=None) on the bound batch, no update (trainer/experiment.py:115). */
+int fqlpop_total_loss(void* handle, void* stream);
+/* Info dict of the last step / loss evaluation: host float [population][16], slots as oracle.INFO_KEYS
+ * (13 used). with_grad_stats != 0 also reduces grad/max, grad/min, grad/norm. Synchronises.               */
+int fqlpop_info(void* handle, float* out_host, int32_t with_grad_stats, void* stream);
+
+/* Parameter / optimizer-state I/O for one member (utils/agent.py:9-41 load_agent, experiment.py:128-141
+ * save_agent). net: 0 critic, 1 actor_bc_flow, 2 actor_onestep_flow; kind: 0 kernel [E][in][out], 1 bias,
+ * 2 LayerNorm scale, 3 LayerNorm bias; which: 0 params, 1 Adam mu, 2 Adam nu, 3 target params, 4 grads.
+ * host: unpadded fp32 (critic leaves carry the leading ensemble axis). Synchronous.                       */
+int fqlpop_leaf(void* handle, int32_t net, int32_t layer, int32_t kind, int32_t which, int32_t member,
+                float* host, int32_t to_host);
+/* Re-derives the bf16 GEMM copies after parameters were written with fqlpop_leaf.                         */
+int fqlpop_refresh_shadow(void* handle, void* stream);
+/* Adam step counts [population] and the lockstep step counter (Philox stream position); set != 0 writes.  */
+int fqlpop_counters(void* handle, int32_t* adam_steps, uint64_t* step_counter, int32_t set);
+/* Number of kernels one replay of the captured step launches (bench.py's gpu_launches).                   */
+int fqlpop_launches_per_step(void* handle);
+
 #ifdef __cplusplus
 }
 #endif

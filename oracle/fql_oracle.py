@@ -187,6 +187,23 @@ class _QBias(torch.autograd.Function):
         return dz, _bf16(dz).sum(dim=tuple(range(dz.dim() - 1)))
 
 
+class _QHead(torch.autograd.Function):
+    """Head layer as the CUDA path computes it: forward on CUDA cores with the bf16 activations as stored
+    and fp32 weights; backward through the tensor-core GEMMs, i.e. bf16(dy) against bf16(W) and bf16(x)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        xq = _bf16(x)
+        ctx.save_for_backward(xq, w)
+        return xq @ w + b
+
+    @staticmethod
+    def backward(ctx, dy):
+        xq, w = ctx.saved_tensors
+        dyq = _bf16(dy)
+        return dyq @ _bf16(w).transpose(-1, -2), xq.transpose(-1, -2) @ dyq, dyq.sum(dim=tuple(range(dy.dim() - 1)))
+
+
 def gelu_tanh(z):
     # flax nn.gelu default approximate=True
     return 0.5 * z * (1.0 + torch.tanh(math.sqrt(2.0 / math.pi) * (z + 0.044715 * z ** 3)))
@@ -208,8 +225,7 @@ def mlp_apply(p, x, n_layers, ln, eps, emulate_bf16=False, head_fp32=True):
         if emulate_bf16 and not last:
             x = _QBias.apply(_QLinear.apply(x, W), b)
         elif emulate_bf16 and last:
-            # the CUDA head runs on CUDA cores: bf16 activations (as stored), fp32 weights
-            x = _bf16_ste(x) @ W + b
+            x = _QHead.apply(x, W, b)
         else:
             x = x @ W + b
         if not last:

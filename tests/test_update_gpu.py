@@ -1,0 +1,179 @@
+"""Parity of the CUDA population step (through the C-ABI) with the CPU oracle on identical synthetic batches,
+parameters and injected noise (GPU only).
+
+Tolerances (stated per quantity; the CUDA path multiplies in bf16 with fp32 accumulation, the reference
+computes in fp32 -- SURVEY.md section 7 "bf16 vs the reference's fp32"):
+  * vs the oracle with emulate_bf16=True (same operand rounding): losses/info rel 5e-3, gradients
+    max-norm relative 2e-2 per leaf (tanh.approx GELU, bf16-stored act'(z)/xhat), Adam mu/nu the same,
+    parameters after one step within 2.2 lr (Adam's first step is +-lr * sign(g); sign flips of ~0 grads).
+  * vs the plain fp32 oracle: losses rel 3e-2, gradient cosine similarity per leaf > 0.99.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import fql_oracle as orc  # noqa: E402  (checker only)
+
+
+def _make_case(P, cfg, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    B, O, A = cfg.batch_size, cfg.ob_dim, cfg.action_dim
+    batches, noises = [], []
+    for _ in range(P):
+        obs = torch.randn(B, O, generator=g)
+        batch = {
+            "observations": obs,
+            "actions": (torch.rand(B, A, generator=g) * 2 - 1) * 0.99,
+            "next_observations": obs + 0.05 * torch.randn(B, O, generator=g),
+            "rewards": -(torch.rand(B, generator=g) < 0.9).float(),
+            "masks": (torch.rand(B, generator=g) < 0.9).float(),
+        }
+        noise = {
+            "z_critic": torch.randn(B, A, generator=g), "x0": torch.randn(B, A, generator=g),
+            "t": torch.rand(B, 1, generator=g), "z_actor": torch.randn(B, A, generator=g),
+            "z_mse": torch.randn(B, A, generator=g),
+        }
+        batches.append(batch)
+        noises.append(noise)
+    return batches, noises
+
+
+def _np_tree(t):
+    return orc.tree_map(lambda x: x.detach().cpu().numpy(), t)
+
+
+def _load_population(pop, states):
+    for p, st in enumerate(states):
+        for net in ("critic", "actor_bc_flow", "actor_onestep_flow"):
+            pop.set_tree(p, net, _np_tree(st["params"][net]), "params")
+            pop.set_tree(p, net, _np_tree(st["mu"][net]), "mu")
+            pop.set_tree(p, net, _np_tree(st["nu"][net]), "nu")
+        pop.set_tree(p, "critic", _np_tree(st["params"]["target_critic"]), "target")
+    pop.refresh_shadow()
+    pop.set_counters(adam_steps=[st["step"] for st in states])
+
+
+def _bind(pop, batches, noises):
+    cat = lambda k: torch.cat([b[k] for b in batches], 0)
+    pop.set_dataset(cat("observations"), cat("actions"), cat("next_observations"), cat("rewards"), cat("masks"))
+    P, B = len(batches), batches[0]["rewards"].shape[0]
+    st = lambda k: torch.stack([n[k] for n in noises], 0)
+    pop.set_noise(indices=torch.arange(P * B).view(P, B), z_critic=st("z_critic"), x0=st("x0"),
+                  t=st("t").squeeze(-1), z_actor=st("z_actor"), z_mse=st("z_mse"))
+
+
+def _leaf_pairs(tree_a, tree_b, prefix=""):
+    for k in tree_b:
+        if isinstance(tree_b[k], dict):
+            yield from _leaf_pairs(tree_a[k], tree_b[k], f"{prefix}/{k}")
+        else:
+            yield f"{prefix}/{k}", np.asarray(tree_a[k]), tree_b[k].detach().cpu().numpy()
+
+
+def _cfg_dict(cfg):
+    return dict(ob_dim=cfg.ob_dim, action_dim=cfg.action_dim, lr=cfg.lr, batch_size=cfg.batch_size,
+                actor_hidden_dims=cfg.actor_hidden_dims, value_hidden_dims=cfg.value_hidden_dims,
+                layer_norm=cfg.layer_norm, actor_layer_norm=cfg.actor_layer_norm, discount=cfg.discount,
+                tau=cfg.tau, q_agg=cfg.q_agg, flow_steps=cfg.flow_steps, normalize_q_loss=cfg.normalize_q_loss,
+                num_ensembles=cfg.num_ensembles)
+
+
+@pytest.mark.parametrize("shape,variant", [((28, 5), "default"), ((42, 8), "min_norm"), ((37, 5), "actor_ln")])
+def test_one_update_matches_oracle(shape, variant):
+    from fqlpop.population import INFO_KEYS, Population
+    O, A = shape
+    cfg = orc.FQLConfig(ob_dim=O, action_dim=A, batch_size=256)
+    if variant == "min_norm":
+        cfg.q_agg, cfg.normalize_q_loss, cfg.discount = "min", True, 0.995
+    if variant == "actor_ln":
+        cfg.actor_layer_norm = True
+    alphas = [3.0, 30.0, 300.0]
+    seeds = [11, 22, 33]
+    P = len(alphas)
+    states = [orc.init_state(s, cfg) for s in seeds]
+    # non-trivial biases / LayerNorm parameters and a target that differs from the critic
+    g = torch.Generator().manual_seed(5)
+    for st in states:
+        for net in st["params"]:
+            for name, leaf in orc.tree_leaves(st["params"][net]):
+                if name.endswith("bias"):
+                    leaf.add_(0.05 * torch.randn(leaf.shape, generator=g))
+                if name.endswith("scale"):
+                    leaf.add_(0.1 * torch.randn(leaf.shape, generator=g))
+        for name, leaf in orc.tree_leaves(st["params"]["target_critic"]):
+            leaf.add_(0.01 * torch.randn(leaf.shape, generator=g))
+    batches, noises = _make_case(P, cfg)
+    pop = Population(_cfg_dict(cfg), alphas, seeds)
+    _load_population(pop, states)
+    _bind(pop, batches, noises)
+    pop.step(1)
+    info = pop.info(with_grad_stats=True)
+
+    for p in range(P):
+        new_e, info_e, grads_e = orc.update(states[p], batches[p], noises[p], cfg, alphas[p], emulate_bf16=True,
+                                            return_grads=True)
+        _, info_f, grads_f = orc.update(states[p], batches[p], noises[p], cfg, alphas[p], emulate_bf16=False,
+                                        return_grads=True)
+        for i, k in enumerate(INFO_KEYS):
+            got, want, want_f = float(info[p, i]), info_e[k], info_f[k]
+            tol = 5e-3 * max(1.0, abs(want)) if not k.startswith("grad/") else 3e-2 * max(1e-3, abs(want))
+            assert abs(got - want) <= tol, f"member {p} {k}: cuda {got} oracle(bf16) {want}"
+            if not k.startswith("grad/"):
+                assert abs(got - want_f) <= 3e-2 * max(1.0, abs(want_f)), f"member {p} {k}: cuda {got} oracle(fp32) {want_f}"
+        for net in ("critic", "actor_bc_flow", "actor_onestep_flow"):
+            g_c = pop.get_tree(p, net, "grad")
+            for name, a, b in _leaf_pairs(g_c, grads_e[net], net):
+                scale = np.abs(b).max() + 1e-12
+                err = np.abs(a - b).max() / scale
+                assert err < 2e-2, f"member {p} grad {name}: max-norm rel err {err:.3e} (scale {scale:.3e})"
+            for name, a, b in _leaf_pairs(g_c, grads_f[net], net):
+                cos = float((a * b).sum() / (np.linalg.norm(a) * np.linalg.norm(b) + 1e-30))
+                assert cos > 0.99, f"member {p} grad {name}: cosine vs fp32 oracle {cos:.4f}"
+            for which, key in (("mu", "mu"), ("nu", "nu")):
+                t_c = pop.get_tree(p, net, which)
+                for name, a, b in _leaf_pairs(t_c, new_e[key][net], net):
+                    scale = np.abs(b).max() + 1e-20
+                    assert np.abs(a - b).max() / scale < 4e-2, f"member {p} {which} {name}"
+            t_c = pop.get_tree(p, net, "params")
+            for name, a, b in _leaf_pairs(t_c, new_e["params"][net], net):
+                assert np.abs(a - b).max() <= 2.2 * cfg.lr, f"member {p} params {name}: {np.abs(a - b).max():.3e}"
+                # the bulk of the entries moves exactly like the oracle
+                frac = float((np.abs(a - b) < 0.2 * cfg.lr).mean())
+                assert frac > 0.97, f"member {p} params {name}: only {frac:.3f} within 0.2 lr"
+        t_c = pop.get_tree(p, "critic", "target")
+        for name, a, b in _leaf_pairs(t_c, new_e["params"]["target_critic"], "target"):
+            assert np.abs(a - b).max() <= 2.2 * cfg.lr * cfg.tau + 1e-7, f"member {p} target {name}"
+    steps, ctr = pop.get_counters()
+    assert list(steps) == [1] * P and ctr == 1
+    pop.close()
+
+
+def test_total_loss_matches_update_info_and_leaves_state_untouched():
+    from fqlpop.population import INFO_KEYS, Population
+    cfg = orc.FQLConfig(ob_dim=28, action_dim=5, batch_size=128)
+    alphas, seeds = [10.0, 100.0], [1, 2]
+    states = [orc.init_state(s, cfg) for s in seeds]
+    batches, noises = _make_case(2, cfg, seed=3)
+    pop = Population(_cfg_dict(cfg), alphas, seeds)
+    _load_population(pop, states)
+    _bind(pop, batches, noises)
+    before = pop.get_tree(0, "critic", "params")
+    pop.total_loss()
+    info = pop.info()
+    after = pop.get_tree(0, "critic", "params")
+    for k in before:
+        for kk in before[k]:
+            assert np.array_equal(before[k][kk], after[k][kk])
+    for p in range(2):
+        with torch.no_grad():
+            pass
+        params = orc.tree_map(lambda x: x.clone(), states[p]["params"])
+        _, info_e = orc.total_loss(params, batches[p], noises[p], cfg, alphas[p], emulate_bf16=True)
+        for i, k in enumerate(INFO_KEYS[:10]):
+            want = float(info_e[k])
+            assert abs(float(info[p, i]) - want) <= 5e-3 * max(1.0, abs(want)), (p, k, float(info[p, i]), want)
+    steps, ctr = pop.get_counters()
+    assert list(steps) == [0, 0] and ctr == 0
+    pop.close()
