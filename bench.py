@@ -1,0 +1,315 @@
+#!/usr/bin/env python
+"""Benchmark of the population FQL hot path (BASELINE.json: alpha-agent FQL updates/sec, whole box).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--population P] [--shape NAME]
+
+A "step" is one lockstep update of the whole population resident on a GPU (P member-updates: on-device batch
+gather + FQLAgent.update for every member). Workload at N=1 = BASELINE.json configs[1]: 16 alpha values,
+cube-single shape (O=28, A=5), batch 256, 4x512 MLPs, 10 flow steps, synthetic 1M-row dataset in HBM.
+N>1: one process per GPU (torchrun), every rank owns its own P members (no data-path collective) -> weak scaling.
+
+Printed JSON line: see the task contract; `value` = member-updates/s with inputs resident in HBM, `e2e` = the
+same metric with every step's batch coming from pinned HOST memory (H2D inside the timed region, info D2H),
+`roofline` = the tcgen05 GEMM kernel on the step's dominant launch shape timed alone with CUDA events,
+`cpu_baseline` = the CPU oracle (torch fp32 restatement of the reference path) on this box's host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "flow-q-learning_b200"))
+sys.path.insert(0, ROOT)
+
+SHAPES = {"cube-single": (28, 5), "antsoccer": (42, 8), "cube-double": (37, 5)}
+# algorithmic FLOP per member-update at B=256 / B=1024 (true unpadded dims)
+HID = 512
+
+
+def flop_per_update(O, A, B, F=10, E=2, H=HID, nh=4):
+    def mlp(i, o):
+        return i * H + (nh - 1) * H * H + H * o
+    q, bc, pi = mlp(O + A, 1), mlp(O + A + 1, A), mlp(O + A, A)
+    fwd = pi + E * q + E * q + bc + F * bc + pi + E * q + pi
+    bwd = 2 * (E * q + bc + pi) + E * q
+    return 2.0 * (fwd + bwd) * B
+
+
+def adam_bytes_per_update(O, A, E=2, H=HID, nh=4):
+    def n(i, o):
+        return i * H + H + (nh - 1) * (H * H + H) + H * o + o
+    q = E * (n(O + A, 1) + nh * 2 * H)
+    tr = q + n(O + A + 1, A) + n(O + A, A)
+    return tr * 30 + q * 10
+
+
+def synth_dataset(n, O, A, device, seed=0):
+    import torch
+    g = torch.Generator(device=device).manual_seed(seed)
+    obs = torch.randn(n, O, device=device, generator=g)
+    nxt = obs + 0.05 * torch.randn(n, O, device=device, generator=g)
+    act = ((torch.rand(n, A, device=device, generator=g) * 2 - 1)).clamp(-1 + 1e-5, 1 - 1e-5)
+    rew = -(torch.rand(n, device=device, generator=g) >= 0.005).float()
+    mask = (rew != 0).float()
+    return obs, act, nxt, rew, mask
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.samples, self.reasons = index, False, [], set()
+        self.max_mhz = None
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                f = [x.strip() for x in out.split(",")]
+                self.samples.append(float(f[0]))
+                self.max_mhz = float(f[1])
+                for nm, v in zip(names, f[2:]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return p, "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+def cpu_oracle_updates_per_sec(O, A, B, n_updates, warm=2):
+    """Times the CPU oracle (oracle/fql_oracle.py, fp32, all host threads) on a bounded sample."""
+    import torch
+    from oracle import fql_oracle as orc
+    cfg = orc.FQLConfig(ob_dim=O, action_dim=A, batch_size=B)
+    st = orc.init_state(0, cfg)
+    g = torch.Generator().manual_seed(0)
+    obs = torch.randn(B, O, generator=g)
+    batch = {"observations": obs, "actions": torch.rand(B, A, generator=g) * 2 - 1,
+             "next_observations": obs + 0.05 * torch.randn(B, O, generator=g),
+             "rewards": -torch.ones(B), "masks": torch.ones(B)}
+    noise = lambda: {"z_critic": torch.randn(B, A, generator=g), "x0": torch.randn(B, A, generator=g),
+                     "t": torch.rand(B, 1, generator=g), "z_actor": torch.randn(B, A, generator=g),
+                     "z_mse": torch.randn(B, A, generator=g)}
+    for _ in range(warm):
+        st, _ = orc.update(st, batch, noise(), cfg, 10.0)
+    t0 = time.perf_counter()
+    for _ in range(n_updates):
+        st, _ = orc.update(st, batch, noise(), cfg, 10.0)
+    dt = time.perf_counter() - t0
+    return n_updates / dt, torch.get_num_threads()
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the reference's own CPU path is not installable (missing fql submodule, no jax); the CPU
+    oracle restating it is timed on the host cores instead. Rank 0 only."""
+    if rank != 0:
+        return
+    O, A = SHAPES[args.shape]
+    per_step = 2  # bounded sample: 2 of the P member-updates of one lockstep step
+    ups, threads = cpu_oracle_updates_per_sec(O, A, args.batch, per_step * args.steps, warm=per_step * min(args.warmup, 2))
+    line = {
+        "impl": "reference", "metric": "fql_member_updates_per_sec", "value": ups, "unit": "updates/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * per_step / ups,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"population of {args.population} alpha-agents, {args.shape} shape, batch {args.batch}, "
+                               "4x512 MLPs, 10 flow steps", "population": args.population, "batch": args.batch},
+        "cpu_baseline": {"value": ups, "unit": "updates/s", "cores": threads, "kind": "port",
+                         "sample": f"{per_step} sequential member-updates per step (of {args.population}), "
+                                   f"{args.steps} steps, torch CPU fp32 oracle"},
+        "e2e": {"value": ups, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def gemm_roofline(torch, P, B, iters=200):
+    """The step's dominant launch: hidden layer forward h = gelu(x W + b), M=B rows, N=K=512, batch P members.
+    Timed alone with CUDA events on the launching (current) stream -> burst tensor peak is the denominator."""
+    from fqlpop import _lib
+    dev = "cuda"
+    A = (torch.randn(P, B, HID, device=dev) * 0.5).to(torch.bfloat16)
+    Wt = (torch.randn(P, HID, HID, device=dev) / HID ** 0.5).to(torch.bfloat16)  # [in][out] -> MN-major B
+    bias = torch.zeros(P, HID, device=dev)
+    out = torch.empty(P, B, HID, device=dev, dtype=torch.bfloat16)
+    kw = dict(M=B, N=HID, K=HID, P=P, a_mn=0, b_mn=1, n_sub=1, A=A, a_ld=HID, a_ms=B * HID, B=Wt, b_ld=HID,
+              b_ms=HID * HID, ln_eps=1e-6, epi_kind=_lib.EPI_FWD, act=_lib.ACT_GELU, bias=bias, out_h=out)
+    for _ in range(10):
+        _lib.gemm_test(**kw)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        _lib.gemm_test(**kw)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    flop = 2.0 * P * B * HID * HID
+    return flop / (ms * 1e-3) / 1e12, ms, flop
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--population", type=int, default=16)
+    ap.add_argument("--shape", default="cube-single", choices=sorted(SHAPES))
+    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--rows", type=int, default=1_000_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from fqlpop.population import Population
+    O, A = SHAPES[args.shape]
+    P, B = args.population, args.batch
+    dev = torch.device("cuda", local)
+    import random
+    alphas_all = np.logspace(np.log10(3), np.log10(1000), P * world)   # tune_alpha.py:43-45
+    seeds_all = random.Random(0).sample(range(10000), P * world)       # tune_alpha.py:40,46
+    alphas = alphas_all[rank::world]                                    # member i -> GPU i mod G
+    seeds = seeds_all[rank::world]
+    cfg = dict(ob_dim=O, action_dim=A, batch_size=B, discount=0.995 if args.shape == "antsoccer" else 0.99)
+    pop = Population(cfg, alphas, seeds, device=dev)
+    ds = synth_dataset(args.rows, O, A, dev, seed=0)
+    pop.set_dataset(*ds)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput -------------------------------------------------------------------
+    pop.step(args.warmup)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    pop.step(args.steps)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    info_last = pop.info()
+
+    # ---- end to end: host batches (pinned) -> H2D -> step -> info D2H, every step ---------------------------
+    row = 2 * O + A + 2
+    host = torch.empty(P * B, row, dtype=torch.float32).pin_memory()
+    g = torch.Generator().manual_seed(1)
+    host.normal_(generator=g)
+    host[:, 2 * O:2 * O + A].clamp_(-1, 1)
+    host[:, -2] = -1.0
+    host[:, -1] = 1.0
+    stage = torch.empty(P * B, row, device=dev)
+    d_obs, d_nxt = torch.empty(P * B, O, device=dev), torch.empty(P * B, O, device=dev)
+    d_act, d_rew, d_mask = torch.empty(P * B, A, device=dev), torch.empty(P * B, device=dev), torch.empty(P * B, device=dev)
+    pop.set_dataset(d_obs, d_act, d_nxt, d_rew, d_mask)
+    pop.set_noise(indices=torch.arange(P * B).view(P, B))
+    info_host = np.zeros((P, 16), np.float32)
+
+    def e2e_step():
+        stage.copy_(host, non_blocking=True)
+        d_obs.copy_(stage[:, :O]); d_nxt.copy_(stage[:, O:2 * O]); d_act.copy_(stage[:, 2 * O:2 * O + A])
+        d_rew.copy_(stage[:, -2]); d_mask.copy_(stage[:, -1])
+        pop.step(1)
+        return pop.info()  # D2H + sync
+
+    for _ in range(args.warmup):
+        e2e_step()
+    barrier()
+    e2e_steps = max(10, args.steps // 2)
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(e2e_steps):
+        info_host = e2e_step()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t.item())
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    pk, pk_src = peaks()
+    value = P * world * args.steps / (ms_total * 1e-3)
+    ms_step = ms_total / args.steps
+    flop_upd = flop_per_update(O, A, B)
+    tf_gemm, gemm_ms, gemm_flop = gemm_roofline(torch, P, B)
+    step_tflops = flop_upd * P / (ms_step * 1e-3) / 1e12
+    adam_b = adam_bytes_per_update(O, A)
+    line = {
+        "metric": "fql_member_updates_per_sec", "value": value, "unit": "updates/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": f"lockstep population of {P} alpha-agents per GPU, {args.shape} shape (O={O}, A={A}), "
+                               f"batch {B}, 4x512 MLPs, E=2 critics, 10 flow steps; dataset {args.rows} rows in HBM",
+                   "population_per_gpu": P, "batch": B, "l2": "working set (params+Adam state+dataset, >1 GB) exceeds L2"},
+        "e2e": {"value": P * world * e2e_steps / (e2e_ms * 1e-3), "unit": "updates/s",
+                "h2d_bytes_per_step": int(host.numel() * 4), "d2h_bytes_per_step": int(info_host.nbytes)},
+        "gpu_launches": pop.launches_per_step * args.steps,
+        "roofline": {"bound": "tensor", "achieved": tf_gemm, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
+                     "frac": tf_gemm / pk["bf16_tflops"], "traffic": None, "peak_source": pk_src + " (burst)",
+                     "kernel": "fql_gemm_kernel<1> hidden-layer forward, M=%d N=K=512 x %d members, timed alone" % (B, P),
+                     "launch_ms": gemm_ms, "flop_per_launch": gemm_flop},
+        "step_roofline": {"algorithmic_tflops": step_tflops, "frac_of_sustained_tensor_peak": step_tflops / pk["bf16_tflops_sustained"],
+                          "flop_per_member_update": flop_upd, "adam_bytes_per_member_update": adam_b,
+                          "adam_hbm_floor_ms_per_step": adam_b * P / (pk["hbm_gbs"] * 1e9) * 1e3},
+        "clocks": sampler.summary(),
+        "last_info_member0": {k: float(v) for k, v in zip(("critic_loss", "q_mean"), info_last[0][:2])},
+    }
+    if not args.no_cpu_baseline:
+        n_upd = 30
+        ups, threads = cpu_oracle_updates_per_sec(O, A, B, n_upd)
+        line["cpu_baseline"] = {"value": ups, "unit": "updates/s", "cores": threads, "kind": "port",
+                                "sample": f"{n_upd} single-agent updates (alpha=10, batch {B}, {args.shape} shape), torch CPU fp32 oracle"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -353,7 +353,7 @@ def update(state, batch, noise, cfg: FQLConfig, alpha: Optional[float] = None, e
     gmax = max([g.max() for g in grads_flat] + [torch.zeros(())])
     gmin = min([g.min() for g in grads_flat] + [torch.zeros(())])
     gnorm = sum(torch.linalg.vector_norm(g) for g in grads_flat)
-    info = {k: float(v) for k, v in info.items()}
+    info = {k: float(v.detach()) for k, v in info.items()}
     info.update({"grad/max": float(gmax), "grad/min": float(gmin), "grad/norm": float(gnorm)})
     # optax.adam
     step = state["step"] + 1
