@@ -174,7 +174,82 @@ extern "C" int fqlpop_counters(void* h, int32_t* adam_steps, uint64_t* step_coun
   if (e != cudaSuccess) return fail(std::string("fqlpop_counters: ") + cudaGetErrorString(e));
   return 0;
 }
+extern "C" int fqlpop_last_batch(void* h, float* rewards_host, float* masks_host) {
+  POP(h);
+  cudaDeviceSynchronize();
+  const size_t bytes = sizeof(float) * (size_t)P->c.P * P->c.B;
+  cudaError_t e = cudaSuccess;
+  if (rewards_host) e = cudaMemcpy(rewards_host, P->rew, bytes, cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess && masks_host) e = cudaMemcpy(masks_host, P->mask, bytes, cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) return fail(std::string("fqlpop_last_batch: ") + cudaGetErrorString(e));
+  return 0;
+}
+extern "C" int fqlpop_philox_fill(uint64_t seed, uint64_t step, int32_t rows, int32_t slots, int32_t kind, uint32_t n,
+                                  void* out_host) {
+  if (!out_host || rows < 1 || slots < 1 || kind < 0 || kind > 3) return fail("philox_fill: bad arguments");
+  if (fqlpop::philox_fill(seed, step, rows, slots, kind, n, out_host)) return fail("philox_fill: CUDA error");
+  return 0;
+}
 extern "C" int fqlpop_launches_per_step(void* h) {
   fqlpop::Population* P = (fqlpop::Population*)h;
   return P ? fqlpop::pop_launches_per_step(P) : 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// world model + fused rollout
+// ---------------------------------------------------------------------------------------------------------
+#include "rollout.h"
+
+extern "C" int fqlpop_envmodel_create(const fqlpop_envmodel_config_t* c, const float* const* state_kernels,
+                                      const float* const* state_biases, const float* ln_scale, const float* ln_bias,
+                                      const float* const* term_kernels, const float* const* term_biases, void** out) {
+  if (!c || !state_kernels || !state_biases || !ln_scale || !ln_bias || !term_kernels || !term_biases || !out)
+    return fail("null argument");
+  if (c->n_state_hidden < 1 || c->n_state_hidden > 6 || c->n_term_hidden < 1 || c->n_term_hidden > 6)
+    return fail("world model: between 1 and 6 hidden layers per network");
+  fqlpop::EnvModel* m = nullptr;
+  std::string err;
+  if (fqlpop::envmodel_create_impl(c->ob_dim, c->action_dim, c->n_state_hidden, c->state_hidden, c->n_term_hidden,
+                                   c->term_hidden, c->ln_eps, state_kernels, state_biases, ln_scale, ln_bias,
+                                   term_kernels, term_biases, &m, &err))
+    return fail(err);
+  *out = m;
+  return 0;
+}
+extern "C" int fqlpop_envmodel_destroy(void* m) {
+  fqlpop::envmodel_destroy_impl((fqlpop::EnvModel*)m);
+  return 0;
+}
+extern "C" int fqlpop_rollout(void* h, void* envmodel, const fqlpop_rollout_t* a, void* stream) {
+  POP(h);
+  if (!envmodel || !a) return fail("null argument");
+  fqlpop::RolloutArgs r;
+  r.n_episodes = a->n_episodes; r.max_episode_steps = a->max_episode_steps; r.horizon = a->horizon;
+  r.init_obs = a->init_obs; r.init_obs_ms = a->init_obs_member_stride;
+  r.noise = a->noise; r.noise_ms = a->noise_member_stride;
+  r.eval_seed = a->eval_seed;
+  r.success = a->out_success; r.length = a->out_length;
+  r.success_rate = a->out_success_rate; r.return_mean = a->out_return_mean; r.steps_run = a->out_steps;
+  r.traj_obs = a->traj_obs; r.traj_act = a->traj_act; r.traj_logit = a->traj_logit;
+  std::string err;
+  if (fqlpop::rollout_impl(P, (fqlpop::EnvModel*)envmodel, r, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_sample_actions(void* h, int32_t member, const float* obs, int32_t n, const float* noise,
+                                     uint64_t seed, float* out, void* stream) {
+  POP(h);
+  std::string err;
+  if (fqlpop::sample_actions_impl(P, member, obs, n, noise, seed, out, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_env_step(void* envmodel, const float* obs, const float* actions, int32_t n, float* next_obs,
+                               float* logits, void* stream) {
+  std::string err;
+  if (fqlpop::env_step_impl((fqlpop::EnvModel*)envmodel, obs, actions, n, next_obs, logits, (cudaStream_t)stream, &err))
+    return fail(err);
+  return 0;
+}
+extern "C" int64_t fqlpop_rollout_launches(void* h) {
+  fqlpop::Population* P = (fqlpop::Population*)h;
+  return P ? P->ro.launches : 0;
 }

@@ -778,6 +778,34 @@ void launch_fill_qa_dout(Population* P, cudaStream_t s) {
   fill_col0_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(P->bQA.dout, rows, v);
 }
 
+// device Philox stream exposed for the bit-exact parity test against oracle/philox_oracle.py
+__global__ void philox_fill_kernel(unsigned long long seed, unsigned long long step, int rows, int slots, int kind,
+                                   unsigned int n, float* out_f, unsigned int* out_u) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * slots) return;
+  const uint32_t row = (uint32_t)(i / slots), slot = (uint32_t)(i % slots);
+  if (kind == 0) {
+    const Philox4 r = philox4x32_10(seed, step, row, slot);
+    out_u[4 * i + 0] = r.x; out_u[4 * i + 1] = r.y; out_u[4 * i + 2] = r.z; out_u[4 * i + 3] = r.w;
+  } else if (kind == 1) {
+    out_f[i] = philox_uniform(seed, step, row, slot);
+  } else if (kind == 2) {
+    out_u[i] = philox_index(seed, step, row, slot, n);
+  } else {
+    out_f[i] = philox_normal(seed, step, row, slot);
+  }
+}
+int philox_fill(unsigned long long seed, unsigned long long step, int rows, int slots, int kind, unsigned int n,
+                void* out_host) {
+  const size_t count = (size_t)rows * slots * (kind == 0 ? 4 : 1);
+  void* d = nullptr;
+  if (cudaMalloc(&d, count * 4) != cudaSuccess) return 1;
+  philox_fill_kernel<<<(rows * slots + 255) / 256, 256>>>(seed, step, rows, slots, kind, n, (float*)d, (unsigned int*)d);
+  cudaError_t e = cudaMemcpy(out_host, d, count * 4, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  return e == cudaSuccess ? 0 : 1;
+}
+
 int pointwise_init() {
   // head kernels stage up to nb*out*H floats; raise the dynamic shared-memory limit once
   const int bytes = 64 * 1024;

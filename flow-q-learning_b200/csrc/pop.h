@@ -101,6 +101,19 @@ struct NoisePtrs {
 
 struct Plan;  // captured step (streams, events, CUDA graph)
 
+// Device scratch of the fused rollout / sample_actions kernels (rollout.cu), allocated on first use.
+struct RolloutScratch {
+  __nv_bfloat16* head_w = nullptr;  // [P][H][64] one-step-policy head, action j in column O + j
+  float* head_b = nullptr;          // [P][64]
+  float *obs_work = nullptr, *success_sum = nullptr, *return_sum = nullptr;
+  int* steps_run = nullptr;
+  unsigned char* success = nullptr;
+  int* length = nullptr;
+  int* identity = nullptr;  // [P] = 0..P-1 (a one-entry member list for single-member launches)
+  long long ep_cap = 0;
+  long long launches = 0;   // kernels launched by rollout / sample_actions calls so far
+};
+
 struct Population {
   PopParams c{};
   Arena critic, bc, pi;
@@ -121,6 +134,7 @@ struct Population {
   Dataset ds;
   NoisePtrs noise;
   Plan* plan = nullptr;
+  RolloutScratch ro;
   std::vector<void*> allocs;
 };
 
@@ -153,5 +167,7 @@ void launch_finish_info(Population* p, int bump_step, cudaStream_t s);
 void launch_refresh_shadow(Population* p, cudaStream_t s);
 void launch_fill_qa_dout(Population* p, cudaStream_t s);
 int pointwise_init();
+int philox_fill(unsigned long long seed, unsigned long long step, int rows, int slots, int kind, unsigned int n,
+                void* out_host);
 
 }  // namespace fqlpop

@@ -53,6 +53,11 @@ lib.fqlpop_leaf.argtypes = [_vp] + [ctypes.c_int32] * 5 + [_vp, ctypes.c_int32]
 lib.fqlpop_refresh_shadow.argtypes = [_vp, _vp]
 lib.fqlpop_counters.argtypes = [_vp, _vp, _vp, ctypes.c_int32]
 lib.fqlpop_launches_per_step.argtypes = [_vp]
+lib.fqlpop_last_batch.argtypes = [_vp, _vp, _vp]
+lib.fqlpop_last_batch.restype = ctypes.c_int
+lib.fqlpop_philox_fill.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                   ctypes.c_uint32, _vp]
+lib.fqlpop_philox_fill.restype = ctypes.c_int
 for _f in ("create", "destroy", "set_dataset", "set_noise", "set_active", "step", "total_loss", "info", "leaf",
            "refresh_shadow", "counters", "launches_per_step"):
     getattr(lib, "fqlpop_" + _f).restype = ctypes.c_int
@@ -170,6 +175,21 @@ class Population:
         n = len(INFO_KEYS) if with_grad_stats else 10
         return {k: float(row[i]) for i, k in enumerate(INFO_KEYS[:n])}
 
+    def last_batch(self):
+        """(rewards, masks) [P,B] of the batch the last step gathered (test hook for the on-device gather)."""
+        r = np.zeros((self.P, self.B), np.float32)
+        m = np.zeros((self.P, self.B), np.float32)
+        check(lib.fqlpop_last_batch(self._h, r.ctypes.data, m.ctypes.data), "fqlpop_last_batch")
+        return r, m
+
+    def rollout(self, envmodel, init_obs, max_episode_steps, **kw):
+        from . import envmodel as _em
+        return _em.rollout(self, envmodel, init_obs, max_episode_steps, **kw)
+
+    def sample_actions(self, member, observations, noise=None, seed=0):
+        from . import envmodel as _em
+        return _em.sample_actions(self, member, observations, noise, seed)
+
     @property
     def launches_per_step(self) -> int:
         return int(lib.fqlpop_launches_per_step(self._h))
@@ -243,3 +263,15 @@ class Population:
         ctr = None if step_counter is None else np.asarray([step_counter], np.uint64)
         check(lib.fqlpop_counters(self._h, None if steps is None else steps.ctypes.data,
                                   None if ctr is None else ctr.ctypes.data, 1), "fqlpop_counters")
+
+
+def philox_fill(seed: int, step: int, rows: int, slots: int, kind: int, n: int = 0) -> np.ndarray:
+    """Device Philox stream (see include/fqlpop.h fqlpop_philox_fill)."""
+    if kind == 0:
+        out = np.zeros((rows, slots, 4), np.uint32)
+    elif kind == 2:
+        out = np.zeros((rows, slots), np.uint32)
+    else:
+        out = np.zeros((rows, slots), np.float32)
+    check(lib.fqlpop_philox_fill(seed, step, rows, slots, kind, n, out.ctypes.data), "fqlpop_philox_fill")
+    return out

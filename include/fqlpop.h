@@ -88,8 +88,67 @@ int fqlpop_leaf(void* handle, int32_t net, int32_t layer, int32_t kind, int32_t 
 int fqlpop_refresh_shadow(void* handle, void* stream);
 /* Adam step counts [population] and the lockstep step counter (Philox stream position); set != 0 writes.  */
 int fqlpop_counters(void* handle, int32_t* adam_steps, uint64_t* step_counter, int32_t set);
+/* Rewards / masks [population][batch] (host) of the batch the last step gathered: lets a test recover the row
+ * indices the on-device uniform gather drew (Dataset.sample, task/offline_task_simulated.py:53-58).         */
+int fqlpop_last_batch(void* handle, float* rewards_host, float* masks_host);
+/* The device's counter-based Philox4x32-10 stream (every random draw of the path), for bit-exact checks
+ * against oracle/philox_oracle.py. kind 0: 4 uint32 words per (row, slot); 1: uniform fp32; 2: index in
+ * [0, n) as uint32; 3: normal fp32. out_host: [rows][slots] (x4 words for kind 0).                           */
+int fqlpop_philox_fill(uint64_t seed, uint64_t step, int32_t rows, int32_t slots, int32_t kind, uint32_t n,
+                       void* out_host);
 /* Number of kernels one replay of the captured step launches (bench.py's gpu_launches).                   */
 int fqlpop_launches_per_step(void* handle);
+
+/* ---- learned world model + fused simulated evaluation ----------------------------------------------------
+ * Replaces load_model(...)->apply_fn for the state predictor and the termination predictor
+ * (utils/envmodel.py:9-56; modules envmodel/baseline.py:25-37, envmodel/termination_predictor.py:14-21).
+ * Kernels are flax layout [in][out] fp32 on the HOST, one pointer per Dense layer (hidden..., output);
+ * ln_scale / ln_bias: the state predictor's input LayerNorm over concat(obs, action), [ob_dim+action_dim].  */
+typedef struct {
+  int32_t ob_dim, action_dim;
+  int32_t n_state_hidden, state_hidden[6];
+  int32_t n_term_hidden, term_hidden[6];
+  float ln_eps;                               /* flax LayerNorm default 1e-6                               */
+} fqlpop_envmodel_config_t;
+int fqlpop_envmodel_create(const fqlpop_envmodel_config_t* cfg, const float* const* state_kernels,
+                           const float* const* state_biases, const float* ln_scale, const float* ln_bias,
+                           const float* const* term_kernels, const float* const* term_biases, void** out_handle);
+int fqlpop_envmodel_destroy(void* envmodel);
+
+/* One simulated evaluation of every ACTIVE member: evaluate_actor_fn (evaluator/evaluation.py:67-114) driving
+ * OfflineTaskWithSimulatedEvaluations.step (task/offline_task_simulated.py:85-107) with the member's one-step
+ * policy (FQLAgent.sample_actions). All episodes of all members advance in ONE kernel launch.
+ * Arrays marked [P] / [P][n] are indexed by member id (population order), inactive members are left untouched. */
+typedef struct {
+  int32_t n_episodes;           /* n: parallel episodes per member (num_evaluation_envs)                    */
+  int32_t max_episode_steps;    /* truncation (offline_task_simulated.py:23,96-97)                          */
+  int32_t horizon;              /* > 0: stop after this many lockstep steps even if episodes are unfinished */
+  const float* init_obs;        /* (dev) [n][ob_dim] (+ member * init_obs_member_stride elements)           */
+  int64_t init_obs_member_stride;
+  const float* noise;           /* (dev) [T][n][action_dim] policy noise (+ member * stride) or NULL=Philox */
+  int64_t noise_member_stride;
+  uint64_t eval_seed;           /* Philox stream of this evaluation when noise == NULL                      */
+  uint8_t* out_success;         /* (dev, optional) [P][n] terminated at the first done step                 */
+  int32_t* out_length;          /* (dev, optional) [P][n] step index of the first done step, 0 = none       */
+  float* out_success_rate;      /* (dev, optional) [P]  == stats["success"] of evaluate_actor_fn            */
+  float* out_return_mean;       /* (dev, optional) [P]  mean of -(length) + success                         */
+  int32_t* out_steps;           /* (dev, optional) [P]  lockstep steps executed (max over the member's CTAs)*/
+  float* traj_obs;              /* (dev, optional) [P][T][n][ob_dim] observation fed to the policy          */
+  float* traj_act;              /* (dev, optional) [P][T][n][action_dim] clipped action                     */
+  float* traj_logit;            /* (dev, optional) [P][T][n] termination logit                              */
+} fqlpop_rollout_t;             /* T = horizon if 0 < horizon < max_episode_steps else max_episode_steps     */
+int fqlpop_rollout(void* handle, void* envmodel, const fqlpop_rollout_t* args, void* stream);
+
+/* FQLAgent.sample_actions(observations, seed) of one member (evaluator/evaluation.py:58-63,94):
+ * out[n][action_dim] = clip(pi(obs, z), -1, 1); z = noise[n][action_dim] (dev) or Philox(seed) when NULL.    */
+int fqlpop_sample_actions(void* handle, int32_t member, const float* obs, int32_t n, const float* noise,
+                          uint64_t seed, float* out, void* stream);
+/* Task.step of the simulated task (task/offline_task_simulated.py:85-91): next_obs[n][ob_dim] and the
+ * termination logits[n] (terminated = logit > 0) for obs[n][ob_dim], actions[n][action_dim] (all dev).       */
+int fqlpop_env_step(void* envmodel, const float* obs, const float* actions, int32_t n, float* next_obs,
+                    float* logits, void* stream);
+/* Kernels launched so far by fqlpop_rollout / fqlpop_sample_actions on this handle (bench.py's gpu_launches). */
+int64_t fqlpop_rollout_launches(void* handle);
 
 #ifdef __cplusplus
 }

@@ -217,12 +217,14 @@ def layer_norm(x, scale, bias, eps):
     return (x - mean) * torch.rsqrt(var + eps) * scale + bias
 
 
-def mlp_apply(p, x, n_layers, ln, eps, emulate_bf16=False, head_fp32=True):
-    """MLP: [Dense -> GELU -> (LayerNorm)] x hidden, then Dense. x: [B, in]; params without ensemble axis."""
+def mlp_apply(p, x, n_layers, ln, eps, emulate_bf16=False, head_bf16=False):
+    """MLP: [Dense -> GELU -> (LayerNorm)] x hidden, then Dense. x: [B, in]; params without ensemble axis.
+    head_bf16: the fused rollout kernel runs the head on the tensor cores too (bf16 weights); the training
+    step runs it on CUDA cores with fp32 weights."""
     for i in range(n_layers):
         W, b = p[f"Dense_{i}"]["kernel"], p[f"Dense_{i}"]["bias"]
         last = i == n_layers - 1
-        if emulate_bf16 and not last:
+        if emulate_bf16 and (not last or head_bf16):
             x = _QBias.apply(_QLinear.apply(x, W), b)
         elif emulate_bf16 and last:
             x = _QHead.apply(x, W, b)
@@ -262,16 +264,17 @@ def critic_apply(p, obs, act, cfg: FQLConfig, emulate_bf16=False):
     return torch.stack(outs, 0)
 
 
-def actor_apply(p, obs, act, t, cfg: FQLConfig, emulate_bf16=False):
+def actor_apply(p, obs, act, t, cfg: FQLConfig, emulate_bf16=False, head_bf16=False):
     xs = [obs, act] if t is None else [obs, act, t]
     n = len(cfg.actor_hidden_dims) + 1
-    return mlp_apply(p, torch.cat(xs, -1), n, cfg.actor_layer_norm, cfg.ln_eps, emulate_bf16)
+    return mlp_apply(p, torch.cat(xs, -1), n, cfg.actor_layer_norm, cfg.ln_eps, emulate_bf16, head_bf16)
 
 
-def sample_actions(params, obs, noise, cfg: FQLConfig, emulate_bf16=False):
+def sample_actions(params, obs, noise, cfg: FQLConfig, emulate_bf16=False, head_bf16=False):
     """FQLAgent.sample_actions: clip(pi_omega(obs, z), -1, 1); temperature is accepted upstream and unused."""
     with torch.no_grad():
-        return torch.clamp(actor_apply(params["actor_onestep_flow"], obs, noise, None, cfg, emulate_bf16), -1, 1)
+        return torch.clamp(actor_apply(params["actor_onestep_flow"], obs, noise, None, cfg, emulate_bf16, head_bf16),
+                           -1, 1)
 
 
 def compute_flow_actions(params, obs, noise, cfg: FQLConfig, emulate_bf16=False):
@@ -396,32 +399,39 @@ def init_envmodel(seed: int, ob_dim: int, action_dim: int, hidden=(128, 256, 128
     return {"state": state, "termination": term}
 
 
-def state_predictor_apply(p, obs, act, eps=1e-6):
+def _dense(x, d, emulate_bf16):
+    if emulate_bf16:  # bf16 operands, wide accumulation, fp32 bias -- as the tensor-core path
+        return _bf16(x) @ _bf16(d["kernel"]) + d["bias"]
+    return x @ d["kernel"] + d["bias"]
+
+
+def state_predictor_apply(p, obs, act, eps=1e-6, emulate_bf16=False):
     """BaselineStatePredictor.__call__ (/root/reference/envmodel/baseline.py:25-37)."""
     x = torch.cat([obs, act], -1)
     x = layer_norm(x, p["LayerNorm_0"]["scale"], p["LayerNorm_0"]["bias"], eps)
     n = sum(1 for k in p if k.startswith("Dense_"))
     for i in range(n - 1):
-        x = torch.relu(x @ p[f"Dense_{i}"]["kernel"] + p[f"Dense_{i}"]["bias"])
-    return x @ p[f"Dense_{n - 1}"]["kernel"] + p[f"Dense_{n - 1}"]["bias"] + obs
+        x = torch.relu(_dense(x, p[f"Dense_{i}"], emulate_bf16))
+    return _dense(x, p[f"Dense_{n - 1}"], emulate_bf16) + obs
 
 
-def termination_predictor_apply(p, obs):
+def termination_predictor_apply(p, obs, emulate_bf16=False):
     """TerminationPredictor.__call__ with train=False (dropout is the identity)
     (/root/reference/envmodel/termination_predictor.py:14-21)."""
     x = obs
     n = sum(1 for k in p if k.startswith("Dense_"))
     for i in range(n - 1):
-        x = torch.relu(x @ p[f"Dense_{i}"]["kernel"] + p[f"Dense_{i}"]["bias"])
-    return (x @ p[f"Dense_{n - 1}"]["kernel"] + p[f"Dense_{n - 1}"]["bias"]).squeeze(-1)
+        x = torch.relu(_dense(x, p[f"Dense_{i}"], emulate_bf16))
+    return _dense(x, p[f"Dense_{n - 1}"], emulate_bf16).squeeze(-1)
 
 
 def rollout(agent_params, envmodel, init_obs, policy_noise, cfg: FQLConfig, max_episode_steps: int,
-            emulate_bf16=False, return_trajectory=False):
+            emulate_bf16=False, return_trajectory=False, horizon: int = 0):
     """Simulated evaluation: evaluate_actor_fn (/root/reference/evaluator/evaluation.py:67-114) driving
     OfflineTaskWithSimulatedEvaluations.step (/root/reference/task/offline_task_simulated.py:85-107).
 
-    init_obs [n,O]; policy_noise [T,n,A] (one draw per lockstep step). Returns dict with per-episode
+    init_obs [n,O]; policy_noise [T,n,A] (one draw per lockstep step); horizon > 0 stops after that many
+    lockstep steps (fixed-horizon parity tests; unfinished episodes keep length 0). Returns dict with per-episode
     success (bool), length (int, the step of the first termination/truncation), the scalar success rate
     (= stats['success'] of the reference) and the number of lockstep steps executed.
     """
@@ -434,10 +444,10 @@ def rollout(agent_params, envmodel, init_obs, policy_noise, cfg: FQLConfig, max_
     steps = 0
     with torch.no_grad():
         while True:
-            a = sample_actions(agent_params, obs, policy_noise[steps], cfg, emulate_bf16)
+            a = sample_actions(agent_params, obs, policy_noise[steps], cfg, emulate_bf16, head_bf16=True)
             a = torch.clamp(a, -1, 1)  # evaluation.py:96
-            nxt = state_predictor_apply(envmodel["state"], obs, a)
-            logit = termination_predictor_apply(envmodel["termination"], nxt)
+            nxt = state_predictor_apply(envmodel["state"], obs, a, emulate_bf16=emulate_bf16)
+            logit = termination_predictor_apply(envmodel["termination"], nxt, emulate_bf16=emulate_bf16)
             term = logit > 0
             steps += 1
             trunc = torch.full_like(term, steps >= max_episode_steps)
@@ -445,14 +455,15 @@ def rollout(agent_params, envmodel, init_obs, policy_noise, cfg: FQLConfig, max_
             success |= first & term
             length = torch.where(first, torch.full_like(length, steps), length)
             if return_trajectory:
-                traj.append((obs.clone(), a.clone(), done_once.clone()))
+                traj.append((obs.clone(), a.clone(), done_once.clone(), logit.clone()))
             done_now = term | trunc | done_once  # evaluation.py:100
             done_once |= term | trunc            # offline_task_simulated.py:102-105
             obs = nxt                            # offline_task_simulated.py:93 (all envs, finished or not)
-            if bool(done_now.all()):
+            if bool(done_now.all()) or (horizon and steps >= horizon):
                 break
+    run_len = torch.where(length > 0, length, torch.full_like(length, steps))
     out = {"success": success, "length": length, "success_rate": float(success.float().mean()),
-           "steps": steps, "returns": -length.to(torch.float32) + success.to(torch.float32)}
+           "steps": steps, "returns": -run_len.to(torch.float32) + success.to(torch.float32)}
     if return_trajectory:
         out["trajectory"] = traj
     return out

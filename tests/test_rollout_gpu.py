@@ -1,0 +1,239 @@
+"""Parity of the fused world-model rollout kernel, sample_actions and env_step (through the C-ABI) with the CPU
+oracle (GPU only).
+
+Tolerances (the kernel multiplies in bf16 with fp32 accumulation; the reference computes in fp32):
+  * vs the oracle with emulate_bf16=True (same operand rounding): actions max-abs 2e-2 and mean-abs 2e-3
+    (tanh.approx GELU inside a 4x512 MLP flips individual bf16 roundings; LayerNorm amplifies them), next observations atol 5e-3 * max(1, |obs|), termination logits atol 2e-2.
+  * vs the plain fp32 oracle: actions atol 6e-2, next observations atol 3e-2 * max(1, |obs|).
+  * success flags / episode lengths are discrete: they must match EXACTLY for every episode whose oracle logits
+    stay at least `margin` away from the decision threshold 0 up to the episode's end (the others are counted and
+    bounded).
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import fql_oracle as orc  # noqa: E402  (checker only)
+from oracle import philox_oracle as phx  # noqa: E402
+
+
+def _np_tree(t):
+    return orc.tree_map(lambda x: x.detach().cpu().numpy(), t)
+
+
+def _cfg_dict(cfg):
+    return dict(ob_dim=cfg.ob_dim, action_dim=cfg.action_dim, lr=cfg.lr, batch_size=cfg.batch_size,
+                actor_hidden_dims=cfg.actor_hidden_dims, value_hidden_dims=cfg.value_hidden_dims,
+                layer_norm=cfg.layer_norm, actor_layer_norm=cfg.actor_layer_norm, discount=cfg.discount,
+                tau=cfg.tau, q_agg=cfg.q_agg, flow_steps=cfg.flow_steps, normalize_q_loss=cfg.normalize_q_loss,
+                num_ensembles=cfg.num_ensembles)
+
+
+def _population(cfg, alphas, seeds, bias_noise=0.05):
+    from fqlpop.population import Population
+    states = [orc.init_state(s, cfg) for s in seeds]
+    g = torch.Generator().manual_seed(99)
+    for st in states:
+        for name, leaf in orc.tree_leaves(st["params"]["actor_onestep_flow"]):
+            if name.endswith("bias") or name.endswith("scale"):
+                leaf.add_(bias_noise * torch.randn(leaf.shape, generator=g))
+    pop = Population(_cfg_dict(cfg), alphas, seeds)
+    for p, st in enumerate(states):
+        for net in ("critic", "actor_bc_flow", "actor_onestep_flow"):
+            pop.set_tree(p, net, _np_tree(st["params"][net]))
+    pop.refresh_shadow()
+    return pop, states
+
+
+def _envmodel(O, A, seed=3, hidden=(128, 256, 128), out_scale=0.05, term_bias=0.0):
+    em = orc.init_envmodel(seed, O, A, hidden)
+    g = torch.Generator().manual_seed(seed + 100)
+    n = len(hidden)
+    # a trained dynamics model predicts small residuals; keep the synthetic one contractive so that rounding
+    # differences do not amplify along the trajectory
+    em["state"][f"Dense_{n}"]["kernel"].mul_(out_scale)
+    for net in ("state", "termination"):
+        for name, leaf in orc.tree_leaves(em[net]):
+            if name.endswith("bias"):
+                leaf.add_(0.05 * torch.randn(leaf.shape, generator=g))
+    em["state"]["LayerNorm_0"]["scale"].add_(0.1 * torch.randn(O + A, generator=g))
+    em["termination"][f"Dense_{n}"]["bias"].add_(term_bias)
+    return em
+
+
+def _device_envmodel(em, O, A):
+    from fqlpop.envmodel import EnvModel
+    return EnvModel(_np_tree(em["state"]), _np_tree(em["termination"]), O, A)
+
+
+@pytest.mark.parametrize("shape,actor_ln", [((28, 5), False), ((42, 8), False), ((37, 5), True)])
+def test_sample_actions_matches_oracle(shape, actor_ln):
+    O, A = shape
+    cfg = orc.FQLConfig(ob_dim=O, action_dim=A, batch_size=128, actor_layer_norm=actor_ln)
+    pop, states = _population(cfg, [3.0, 30.0], [5, 6])
+    g = torch.Generator().manual_seed(1)
+    for n in (1, 50, 200):  # ragged row tiles
+        obs = torch.randn(n, O, generator=g)
+        z = torch.randn(n, A, generator=g)
+        for p in range(2):
+            got = pop.sample_actions(p, obs, z).cpu()
+            want = orc.sample_actions(states[p]["params"], obs, z, cfg, emulate_bf16=True, head_bf16=True)
+            want32 = orc.sample_actions(states[p]["params"], obs, z, cfg)
+            assert got.shape == (n, A)
+            assert float((got - want).abs().max()) < 2e-2, (n, p, float((got - want).abs().max()))
+            assert float((got - want).abs().mean()) < 2e-3
+            assert float((got - want32).abs().max()) < 6e-2
+            assert float(got.abs().max()) <= 1.0
+    # Philox noise: deterministic per seed, equal to the oracle's stream restatement
+    obs = torch.randn(64, O, generator=g)
+    a1 = pop.sample_actions(0, obs, None, seed=17).cpu()
+    a2 = pop.sample_actions(0, obs, None, seed=17).cpu()
+    a3 = pop.sample_actions(0, obs, None, seed=18).cpu()
+    assert torch.equal(a1, a2) and not torch.equal(a1, a3)
+    ctr = 0xC000000000000000 | ((17 & 0x3FFFFFFF) << 32)
+    z = torch.from_numpy(phx.normal(np.uint64(5), np.uint64(ctr), np.arange(64)[:, None], np.arange(A)[None, :]))
+    want = orc.sample_actions(states[0]["params"], obs, z, cfg, emulate_bf16=True, head_bf16=True)
+    assert float((a1 - want).abs().max()) < 2e-2
+    pop.close()
+
+
+@pytest.mark.parametrize("shape,hidden", [((42, 8), (128, 256, 128)), ((28, 5), (128, 128)), ((37, 5), (100, 72))])
+def test_env_step_matches_oracle(shape, hidden):
+    O, A = shape
+    em = _envmodel(O, A, hidden=hidden, out_scale=1.0)
+    dem = _device_envmodel(em, O, A)
+    g = torch.Generator().manual_seed(2)
+    for n in (3, 128, 300):
+        obs = torch.randn(n, O, generator=g) * 2
+        act = torch.rand(n, A, generator=g) * 2 - 1
+        nxt, logit = dem.step(obs, act)
+        nxt, logit = nxt.cpu(), logit.cpu()
+        w_n = orc.state_predictor_apply(em["state"], obs, act, emulate_bf16=True)
+        w_l = orc.termination_predictor_apply(em["termination"], w_n, emulate_bf16=True)
+        f_n = orc.state_predictor_apply(em["state"], obs, act)
+        scale = torch.clamp(w_n.abs(), min=1.0)
+        assert float(((nxt - w_n).abs() / scale).max()) < 5e-3
+        assert float(((nxt - f_n).abs() / scale).max()) < 3e-2
+        assert float((logit - w_l).abs().max()) < 2e-2 * max(1.0, float(w_l.abs().max()))
+    dem.close()
+
+
+@pytest.mark.parametrize("shape", [(42, 8), (28, 5)])
+def test_rollout_matches_oracle_fixed_horizon(shape):
+    O, A = shape
+    cfg = orc.FQLConfig(ob_dim=O, action_dim=A, batch_size=128)
+    alphas, seeds = [3.0, 30.0, 300.0], [5, 6, 7]
+    pop, states = _population(cfg, alphas, seeds)
+    em = _envmodel(O, A, term_bias=-0.6)
+    dem = _device_envmodel(em, O, A)
+    n, T = 200, 12
+    g = torch.Generator().manual_seed(4)
+    init = torch.randn(n, O, generator=g)
+    noise = torch.randn(3, T, n, A, generator=g)
+    out = pop.rollout(dem, init, max_episode_steps=50, horizon=T, noise=noise, trajectory=True)
+    torch.cuda.synchronize()
+    margin = 0.05
+    for p in range(3):
+        ref = orc.rollout(states[p]["params"], em, init, noise[p], cfg, 50, emulate_bf16=True,
+                          return_trajectory=True, horizon=T)
+        # the oracle stops when every episode is done; the kernel may run one lockstep step longer
+        t_cmp = ref["steps"]
+        assert t_cmp <= int(out["steps"][p]) <= min(T, t_cmp + 1)
+        r_obs = torch.stack([t[0] for t in ref["trajectory"]])
+        r_act = torch.stack([t[1] for t in ref["trajectory"]])
+        r_logit = torch.stack([t[3] for t in ref["trajectory"]])
+        g_obs, g_act = out["traj_obs"][p, :t_cmp].cpu(), out["traj_act"][p, :t_cmp].cpu()
+        g_logit = out["traj_logit"][p, :t_cmp].cpu()
+        assert float(((g_obs - r_obs).abs() / torch.clamp(r_obs.abs(), min=1.0)).max()) < 2e-2
+        assert float((g_act - r_act).abs().max()) < 3e-2
+        assert float((g_logit - r_logit).abs().max()) < 6e-2
+        # discrete outcomes: exact wherever the oracle's decision is not within `margin` of the threshold
+        length_ref = ref["length"]
+        end = torch.where(length_ref > 0, length_ref, torch.full_like(length_ref, t_cmp))
+        steps_idx = torch.arange(t_cmp)[:, None]
+        relevant = steps_idx < end[None, :]
+        min_abs = torch.where(relevant, r_logit.abs(), torch.full_like(r_logit, 1e9)).min(0).values
+        clear = min_abs > margin
+        assert float(clear.float().mean()) > 0.8
+        succ, length = out["success"][p].cpu().bool(), out["length"][p].cpu().long()
+        assert torch.equal(succ[clear], ref["success"][clear])
+        assert torch.equal(length[clear], length_ref[clear])
+        n_amb = int((~clear).sum())
+        assert abs(float(out["success_rate"][p]) - ref["success_rate"]) <= n_amb / n + 1e-6
+        want_ret = float((-torch.where(length > 0, length, torch.full_like(length, int(out["steps"][p]))).float()
+                          + succ.float()).mean())
+        assert abs(float(out["return_mean"][p]) - want_ret) < 1e-3
+    pop.close()
+    dem.close()
+
+
+def test_rollout_truncation_early_exit_and_active_members():
+    O, A = 28, 5
+    cfg = orc.FQLConfig(ob_dim=O, action_dim=A, batch_size=128)
+    pop, states = _population(cfg, [3.0, 30.0, 300.0], [1, 2, 3])
+    n, T = 300, 9
+    init = torch.randn(n, O, generator=torch.Generator().manual_seed(8))
+    # nobody terminates: every episode is truncated at max_episode_steps, success 0
+    dem = _device_envmodel(_envmodel(O, A, term_bias=-50.0), O, A)
+    out = pop.rollout(dem, init, max_episode_steps=T, eval_seed=1)
+    assert int(out["success"].sum()) == 0
+    assert bool((out["length"] == T).all()) and bool((out["steps"] == T).all())
+    assert torch.allclose(out["return_mean"].cpu(), torch.full((3,), -float(T)))
+    dem.close()
+    # everybody terminates at the first step: success 1, the kernel leaves the loop early
+    dem = _device_envmodel(_envmodel(O, A, term_bias=50.0), O, A)
+    pop.set_active([2, 0])
+    out = pop.rollout(dem, init, max_episode_steps=1000, eval_seed=1)
+    assert bool((out["success"][[0, 2]] == 1).all()) and bool((out["length"][[0, 2]] == 1).all())
+    assert bool((out["steps"][[0, 2]] <= 2).all())
+    assert torch.allclose(out["success_rate"][[0, 2]].cpu(), torch.ones(2))
+    assert torch.allclose(out["return_mean"][[0, 2]].cpu(), torch.zeros(2))
+    # the inactive member is untouched
+    assert int(out["success"][1].sum()) == 0 and int(out["steps"][1]) == 0
+    dem.close()
+    # device Philox policy noise: same eval_seed -> identical evaluation, other seed -> different actions
+    dem = _device_envmodel(_envmodel(O, A, term_bias=-0.5), O, A)
+    pop.set_active([0, 1, 2])
+    o1 = pop.rollout(dem, init, max_episode_steps=T, eval_seed=5, trajectory=True)
+    o2 = pop.rollout(dem, init, max_episode_steps=T, eval_seed=5, trajectory=True)
+    o3 = pop.rollout(dem, init, max_episode_steps=T, eval_seed=6, trajectory=True)
+    assert torch.equal(o1["traj_act"], o2["traj_act"]) and torch.equal(o1["length"], o2["length"])
+    assert not torch.equal(o1["traj_act"], o3["traj_act"])
+    lengths = o1["length"].cpu()
+    assert int(lengths.min()) >= 1 and int(lengths.max()) <= T
+    trunc = (lengths == T) & (o1["success"].cpu() == 0)
+    assert bool(((o1["success"].cpu() == 1) | trunc).all())
+    pop.close()
+    dem.close()
+
+
+def test_device_philox_stream_is_bit_exact_and_gather_uses_it():
+    from fqlpop.population import Population, philox_fill
+    seed, step = 0x1234567890ABCDEF, 77
+    rows, slots = 257, 23
+    r, s = np.arange(rows)[:, None], np.arange(slots)[None, :]
+    words = philox_fill(seed, step, rows, slots, 0)
+    want = np.stack(phx.philox4x32_10(np.uint64(seed), np.uint64(step), r, s), -1)
+    assert np.array_equal(words, want)
+    assert np.array_equal(philox_fill(seed, step, rows, slots, 1), phx.uniform(np.uint64(seed), np.uint64(step), r, s))
+    assert np.array_equal(philox_fill(seed, step, rows, slots, 2, n=1_000_003).astype(np.int64),
+                          phx.index(np.uint64(seed), np.uint64(step), r, s, 1_000_003))
+    assert np.allclose(philox_fill(seed, step, rows, slots, 3), phx.normal(np.uint64(seed), np.uint64(step), r, s),
+                       atol=2e-6, rtol=1e-5)
+    # the on-device uniform gather: rewards carry the row id, so the gathered batch reveals the drawn indices
+    O, A, B, N = 28, 5, 128, 100_000
+    seeds = [3, 2**40 + 9]
+    pop = Population(dict(ob_dim=O, action_dim=A, batch_size=B), [10.0, 20.0], seeds)
+    g = torch.Generator().manual_seed(0)
+    obs = torch.randn(N, O, generator=g)
+    pop.set_dataset(obs, torch.rand(N, A, generator=g) * 2 - 1, obs, torch.arange(N, dtype=torch.float32),
+                    torch.ones(N))
+    for k in range(3):
+        pop.step(1)
+        rew, _ = pop.last_batch()
+        for p in range(2):
+            want_idx = phx.batch_indices(np.uint64(seeds[p]), np.uint64(k), B, A, N)
+            assert np.array_equal(rew[p].astype(np.int64), want_idx), (k, p)
+    pop.close()
