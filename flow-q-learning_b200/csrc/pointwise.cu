@@ -687,7 +687,7 @@ static int add_small_jobs(SmallGradArgs& a, int n, const Arena& ar, const BwdBuf
   const NetLayout& L = ar.L;
   for (int l = 0; l < L.n_hidden; ++l) {
     SmallGradJob j{};
-    j.dst_ms = L.S; j.part_ms = (long long)bw.m_tiles * L.H; j.m_tiles = bw.m_tiles; j.N = L.H; j.nb = L.nb;
+    j.dst_ms = L.S; j.part_ms = (long long)bw.part_rows * L.H; j.m_tiles = bw.part_rows; j.N = L.H; j.nb = L.nb;
     j.dst = ar.grad + L.offb[l]; j.part = bw.dbias_part[l];
     a.j[n++] = j;
     if (L.ln) {

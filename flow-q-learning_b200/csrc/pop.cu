@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstring>
 
+#include "chain.h"
 #include "philox.cuh"
 
 namespace fqlpop {
@@ -96,7 +97,7 @@ int alloc_bwd(Population* P, BwdBuf& bw, const NetLayout& L, int V, int M, bool 
   for (int l = 0; l < L.n_hidden; ++l) {
     if (dev_alloc(P, &bw.dz[l], (long long)V * M * L.H, err)) return 1;
     if (partials) {
-      const long long n = (long long)V * bw.m_tiles * L.H;
+      const long long n = (long long)V * bw.m_tiles * 4 * L.H;  // chain kernels write one row per TMEM lane quarter
       if (dev_alloc(P, &bw.dbias_part[l], n, err)) return 1;
       if (L.ln && (dev_alloc(P, &bw.dgamma_part[l], n, err) || dev_alloc(P, &bw.dbeta_part[l], n, err))) return 1;
     }
@@ -248,6 +249,133 @@ struct Builder {
   }
 };
 
+// ---------------------------------------------------------------------------------------------------
+// layer-chain job builders (chain.cu): one launch = a whole forward pass / Euler flow / input-gradient chain
+// ---------------------------------------------------------------------------------------------------
+struct ChainBuilder {
+  Population* P;
+  std::string* err;
+  bool ok = true;
+  ChainLaunch* L = nullptr;
+  int count = 0;
+
+  void begin(int nb) {
+    memset(L, 0, sizeof(ChainLaunch));
+    L->n_virtual = (int)P->h_members.size() * nb;
+    L->member_list = nb == 1 ? P->member_list : P->member_list_e;
+  }
+  ChainJob& add() { return L->job[L->num_jobs++]; }
+  void tmap(CUtensorMap* m, const void* base, long long inner, long long rows, long long batch, long long ld,
+            long long ms, int box_rows) {
+    const int rc = encode_tmap_bf16(m, base, inner, rows, batch, ld, ms, box_rows);
+    if (rc != 0 && ok) {
+      ok = false;
+      if (err) *err = "cuTensorMapEncodeTiled failed rc=" + std::to_string(rc);
+    }
+  }
+  void launch(int mode, cudaStream_t s) {
+    finalize_chain(L);
+    cudaError_t e = launch_chain(*L, mode, s);
+    if (e != cudaSuccess && ok) {
+      ok = false;
+      if (err) *err = std::string("launch_chain: ") + cudaGetErrorString(e);
+    }
+    ++count;
+  }
+  ChainJob& common(PassBuf& pass, const Arena& ar, const float* params, int row0, int M) {
+    const NetLayout& N = ar.L;
+    ChainJob& j = add();
+    j.M = M; j.row0 = row0; j.iters = 1; j.ln = N.ln; j.H = N.H; j.ln_eps = P->c.ln_eps;
+    j.params = params; j.S = N.S;
+    j.pass_ms = (long long)pass.M * N.H; j.pass_rs = pass.M;
+    return j;
+  }
+
+  // forward pass over rows [row0, row0 + M): every hidden layer; the last hidden activations always go to HBM
+  // (the head kernels read them), the others only when the backward pass needs them
+  ChainJob& fwd_job(PassBuf& pass, const Arena& ar, const float* params, const __nv_bfloat16* wsh, int row0, int M,
+                    bool save) {
+    const NetLayout& N = ar.L;
+    ChainJob& j = common(pass, ar, params, row0, M);
+    j.n_layers = N.n_hidden;
+    tmap(&j.mapA0, pass.X0, N.in_pad, pass.M, pass.V, N.in_pad, (long long)pass.M * N.in_pad, 128);
+    const long long roff = (long long)row0 * N.H;
+    for (int l = 0; l < N.n_hidden; ++l) {
+      tmap(&j.mapW[l], wsh + N.offW[l], N.H, N.K(l), ar.V, N.H, N.S, 64);
+      ChainLayer& y = j.layer[l];
+      y.kind = CL_HIDDEN; y.k_blocks = N.K(l) / 64; y.n_pad = N.H; y.a_from_x0 = l == 0;
+      y.off_b = N.offb[l]; y.off_g = N.offg[l]; y.off_beta = N.offbeta[l];
+      if (save || l == N.n_hidden - 1) y.out_h = pass.hl(l) + roff;
+      if (save) {
+        y.out_gp = pass.gp[l] + roff;
+        if (N.ln) {
+          y.out_xhat = pass.xhat[l] + roff;
+          y.out_rstd = pass.rstd[l] + row0;
+        }
+      }
+    }
+    return j;
+  }
+
+  // the F Euler steps of compute_flow_actions: hidden layers + the head as a 64-column GEMM, iterated on chip
+  void euler_job() {
+    const Arena& ar = P->bc;
+    const NetLayout& N = ar.L;
+    ChainJob& j = fwd_job(P->EU, ar, ar.theta, ar.shadow, 0, P->c.B, false);
+    j.layer[N.n_hidden - 1].out_h = nullptr;
+    const int l = N.n_hidden;
+    tmap(&j.mapW[l], ar.shadow + N.offW[l], kHeadPad, N.H, ar.V, kHeadPad, N.S, 64);
+    ChainLayer& y = j.layer[l];
+    y.kind = CL_EULER_HEAD; y.k_blocks = N.H / 64; y.n_pad = kHeadPad; y.a_from_x0 = 0;
+    y.off_b = N.offb[l];
+    j.n_layers = N.n_hidden + 1;
+    j.iters = P->c.F;
+    j.O = P->c.O; j.A = P->c.A; j.F = P->c.F; j.B = P->c.B;
+    j.xe = P->xe; j.target_a = P->target_a;
+  }
+
+  // input-gradient chain: dz_{l-1} = act'(z_{l-1}) * LNbwd(dz_l W_l^T) for l = n_hidden .. 1 (dz_{n_hidden} = dout),
+  // optionally followed by the gradient with respect to the network input (fp32)
+  void bwd_job(PassBuf& pass, BwdBuf& bw, const Arena& ar, int row0, bool partials, float* dinput_out) {
+    const NetLayout& N = ar.L;
+    ChainJob& j = common(pass, ar, ar.theta, 0, bw.M);
+    j.dz_ms = (long long)bw.M * N.H;
+    j.part_ms = (long long)bw.part_rows * N.H;
+    tmap(&j.mapA0, bw.dout, kHeadPad, bw.M, bw.V, kHeadPad, (long long)bw.M * kHeadPad, 128);
+    const long long roff = (long long)row0 * N.H;
+    int s = 0;
+    for (int l = N.n_hidden; l >= 1; --l, ++s) {
+      const int Kd = N.N(l);
+      tmap(&j.mapW[s], ar.shadow + N.offW[l], Kd, N.K(l), ar.V, Kd, N.S, 128);
+      ChainLayer& y = j.layer[s];
+      y.kind = CL_HIDDEN; y.k_blocks = Kd / 64; y.n_pad = N.H; y.a_from_x0 = s == 0;
+      y.off_g = N.offg[l - 1];
+      y.gp = pass.gp[l - 1] + roff;
+      if (N.ln) {
+        y.xhat = pass.xhat[l - 1] + roff;
+        y.rstd = pass.rstd[l - 1] + row0;
+      }
+      y.out_dz = bw.dz[l - 1];
+      if (partials) {
+        y.dbias_part = bw.dbias_part[l - 1];
+        if (N.ln) {
+          y.dgamma_part = bw.dgamma_part[l - 1];
+          y.dbeta_part = bw.dbeta_part[l - 1];
+        }
+      }
+    }
+    if (dinput_out) {
+      tmap(&j.mapW[s], ar.shadow + N.offW[0], N.H, N.in_pad, ar.V, N.H, N.S, 64);
+      ChainLayer& y = j.layer[s];
+      y.kind = CL_DINPUT; y.k_blocks = N.H / 64; y.n_pad = N.in_pad; y.a_from_x0 = 0;
+      y.out_f32 = dinput_out; y.out_ld = N.in_pad;
+      j.f32_ms = (long long)bw.M * N.in_pad;
+      ++s;
+    }
+    j.n_layers = s;
+  }
+};
+
 void record(Plan* pl, cudaEvent_t* out, cudaStream_t s) {
   cudaEvent_t e;
   cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
@@ -275,94 +403,100 @@ int issue_step(Population* P, bool train, std::string* err) {
   cudaStreamWaitEvent(s1, e_prep, 0);
   cudaStreamWaitEvent(s2, e_prep, 0);
 
-  // ---- s0: Euler flow chain --------------------------------------------------------------------
-  for (int i = 0; i < c.F; ++i) {
-    for (int l = 0; l < nh_a; ++l) {
-      b.begin(1);
-      b.fwd_group(P->EU, P->bc, P->bc.theta, P->bc.shadow, l, 0, B, false);
-      b.launch(nsub_a, s0);
+  ChainBuilder cb{P, err};
+  cb.L = new ChainLaunch;
+  const bool chain = P->use_chain;
+  // forward pass of one network over [row0, row0 + M) (+ a second, unsaved row range)
+  auto fwd_pass = [&](PassBuf& pass, const Arena& ar, const float* params, const __nv_bfloat16* wsh, int nsub, int M0,
+                      bool save0, int M1, cudaStream_t s) {
+    const int nh = ar.L.n_hidden;
+    if (chain) {
+      cb.begin(ar.L.nb);
+      cb.fwd_job(pass, ar, params, wsh, 0, M0, save0);
+      if (M1 > 0) cb.fwd_job(pass, ar, params, wsh, M0, M1, false);
+      cb.launch(0, s);
+    } else {
+      for (int l = 0; l < nh; ++l) {
+        b.begin(ar.L.nb);
+        b.fwd_group(pass, ar, params, wsh, l, 0, M0, save0);
+        if (M1 > 0) b.fwd_group(pass, ar, params, wsh, l, M0, M1, false);
+        b.launch(nsub, s);
+      }
     }
-    launch_euler_head(P, i, s0); ++pw;
+  };
+  auto bwd_pass = [&](PassBuf& pass, BwdBuf& bw, const Arena& ar, int nsub, bool partials, float* dinput,
+                      cudaStream_t s) {
+    const int nh = ar.L.n_hidden;
+    if (chain) {
+      cb.begin(ar.L.nb);
+      cb.bwd_job(pass, bw, ar, 0, partials, dinput);
+      cb.launch(1, s);
+    } else {
+      for (int l = nh; l >= 1; --l) {
+        b.begin(ar.L.nb);
+        b.dgrad_group(pass, bw, ar, l, 0, partials);
+        b.launch(nsub, s);
+      }
+      if (dinput) {
+        b.begin(ar.L.nb);
+        b.dinput_group(bw, ar, dinput);
+        b.launch(1, s);
+      }
+    }
+  };
+
+  // ---- s0: Euler flow chain --------------------------------------------------------------------
+  if (chain) {
+    cb.begin(1);
+    cb.euler_job();
+    cb.launch(0, s0);
+  } else {
+    for (int i = 0; i < c.F; ++i) {
+      for (int l = 0; l < nh_a; ++l) {
+        b.begin(1);
+        b.fwd_group(P->EU, P->bc, P->bc.theta, P->bc.shadow, l, 0, B, false);
+        b.launch(nsub_a, s0);
+      }
+      launch_euler_head(P, i, s0); ++pw;
+    }
   }
   record(pl, &e_euler, s0);
 
   // ---- s1: one-step policy forward (rows [0,B) kept), TD target, critic forward/backward --------
-  for (int l = 0; l < nh_a; ++l) {
-    b.begin(1);
-    b.fwd_group(P->PI, P->pi, P->pi.theta, P->pi.shadow, l, 0, B, train);
-    b.fwd_group(P->PI, P->pi, P->pi.theta, P->pi.shadow, l, B, 2 * B, false);
-    b.launch(nsub_a, s1);
-  }
+  fwd_pass(P->PI, P->pi, P->pi.theta, P->pi.shadow, nsub_a, B, train, 2 * B, s1);
   launch_pi_head(P, s1); ++pw;
   record(pl, &e_pi, s1);
-  for (int l = 0; l < nh_q; ++l) {
-    b.begin(c.E);
-    b.fwd_group(P->TQ, P->critic, P->critic.target, P->critic.tshadow, l, 0, B, false);
-    b.launch(nsub_q, s1);
-  }
+  fwd_pass(P->TQ, P->critic, P->critic.target, P->critic.tshadow, nsub_q, B, false, 0, s1);
   launch_tq_head(P, s1); ++pw;
-  for (int l = 0; l < nh_q; ++l) {
-    b.begin(c.E);
-    b.fwd_group(P->QC, P->critic, P->critic.theta, P->critic.shadow, l, 0, B, train);
-    b.launch(nsub_q, s1);
-  }
+  fwd_pass(P->QC, P->critic, P->critic.theta, P->critic.shadow, nsub_q, B, train, 0, s1);
   launch_qc_head(P, s1); ++pw;
   if (train) {
-    for (int l = nh_q; l >= 1; --l) {
-      b.begin(c.E);
-      b.dgrad_group(P->QC, P->bQC, P->critic, l, 0, true);
-      b.launch(nsub_q, s1);
-    }
+    bwd_pass(P->QC, P->bQC, P->critic, nsub_q, true, nullptr, s1);
     b.begin(c.E);
     for (int l = 0; l <= nh_q; ++l) b.wgrad_group(P->QC, P->bQC, P->critic, l, 0);
     b.launch(1, s1);
   }
 
   // ---- s2: BC flow forward/backward, then the critic pass on (s, clip(a_pi)) -----------------------
-  for (int l = 0; l < nh_a; ++l) {
-    b.begin(1);
-    b.fwd_group(P->BC, P->bc, P->bc.theta, P->bc.shadow, l, 0, B, train);
-    b.launch(nsub_a, s2);
-  }
+  fwd_pass(P->BC, P->bc, P->bc.theta, P->bc.shadow, nsub_a, B, train, 0, s2);
   launch_bc_head(P, s2); ++pw;
   if (train) {
-    for (int l = nh_a; l >= 1; --l) {
-      b.begin(1);
-      b.dgrad_group(P->BC, P->bBC, P->bc, l, 0, true);
-      b.launch(nsub_a, s2);
-    }
+    bwd_pass(P->BC, P->bBC, P->bc, nsub_a, true, nullptr, s2);
     b.begin(1);
     for (int l = 0; l <= nh_a; ++l) b.wgrad_group(P->BC, P->bBC, P->bc, l, 0);
     b.launch(1, s2);
   }
   cudaStreamWaitEvent(s2, e_pi, 0);
-  for (int l = 0; l < nh_q; ++l) {
-    b.begin(c.E);
-    b.fwd_group(P->QA, P->critic, P->critic.theta, P->critic.shadow, l, 0, B, train);
-    b.launch(nsub_q, s2);
-  }
+  fwd_pass(P->QA, P->critic, P->critic.theta, P->critic.shadow, nsub_q, B, train, 0, s2);
   launch_qa_head(P, s2); ++pw;
-  if (train) {
-    for (int l = nh_q; l >= 1; --l) {
-      b.begin(c.E);
-      b.dgrad_group(P->QA, P->bQA, P->critic, l, 0, false);
-      b.launch(nsub_q, s2);
-    }
-    b.begin(c.E);
-    b.dinput_group(P->bQA, P->critic, P->dx0_qa);
-    b.launch(1, s2);
-  }
+  if (train) bwd_pass(P->QA, P->bQA, P->critic, nsub_q, false, P->dx0_qa, s2);
   record(pl, &e_qa, s2);
 
   // ---- s0: distillation + policy backward -------------------------------------------------------
   cudaStreamWaitEvent(s0, e_qa, 0);
   launch_pi_dout(P, s0); ++pw;
   if (train) {
-    for (int l = nh_a; l >= 1; --l) {
-      b.begin(1);
-      b.dgrad_group(P->PI, P->bPI, P->pi, l, 0, true);
-      b.launch(nsub_a, s0);
-    }
+    bwd_pass(P->PI, P->bPI, P->pi, nsub_a, true, nullptr, s0);
     b.begin(1);
     for (int l = 0; l <= nh_a; ++l) b.wgrad_group(P->PI, P->bPI, P->pi, l, 0);
     b.launch(1, s0);
@@ -383,9 +517,10 @@ int issue_step(Population* P, bool train, std::string* err) {
   cudaStreamWaitEvent(s0, e_s2, 0);
   launch_finish_info(P, train ? 1 : 0, s0); ++pw;
   delete b.L;
-  if (!b.ok) return 1;
+  delete cb.L;
+  if (!b.ok || !cb.ok) return 1;
   CK(cudaGetLastError());
-  if (train) pl->launches_per_step = b.count + pw;
+  if (train) pl->launches_per_step = b.count + cb.count + pw;
   return 0;
 }
 
@@ -457,6 +592,10 @@ int pop_create_impl(const PopParams& c, const float* alphas, const unsigned long
     if (err) *err = std::string("gemm_init: ") + cudaGetErrorString(e);
     return 1;
   }
+  if (cudaError_t e = chain_init(); e != cudaSuccess) {
+    if (err) *err = std::string("chain_init: ") + cudaGetErrorString(e);
+    return 1;
+  }
   if (int rc = pointwise_init()) {
     if (err) *err = std::string("pointwise_init: ") + cudaGetErrorString((cudaError_t)rc);
     return 1;
@@ -481,6 +620,11 @@ int pop_create_impl(const PopParams& c, const float* alphas, const unsigned long
   rc = rc || alloc_bwd(P, P->bQA, Lq, V, c.B, false, err);
   rc = rc || alloc_bwd(P, P->bBC, Lb, c.P, c.B, true, err);
   rc = rc || alloc_bwd(P, P->bPI, Lp, c.P, c.B, true, err);
+  // The layer-chain kernels need every network input to fit one 64-wide block (true for all OGBench shapes the
+  // reference uses) and at most kChainMaxLayers GEMMs per chain; otherwise the per-layer kernels are used.
+  P->use_chain = Lq.in_pad == 64 && Lb.in_pad == 64 && Lp.in_pad == 64 && c.n_hidden_actor + 1 <= kChainMaxLayers &&
+                 c.n_hidden_value + 1 <= kChainMaxLayers && getenv("FQLPOP_NO_CHAIN") == nullptr;
+  for (BwdBuf* bw : {&P->bQC, &P->bQA, &P->bBC, &P->bPI}) bw->part_rows = bw->m_tiles * (P->use_chain ? 4 : 1);
   const long long PB = (long long)c.P * c.B;
   rc = rc || dev_alloc(P, &P->act_f, PB * c.A, err) || dev_alloc(P, &P->vel, PB * c.A, err) ||
        dev_alloc(P, &P->xe, PB * c.A, err) || dev_alloc(P, &P->target_a, PB * c.A, err) ||

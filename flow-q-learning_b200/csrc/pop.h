@@ -75,6 +75,7 @@ struct PassBuf {
 // Backward scratch of one trainable pass.
 struct BwdBuf {
   int V = 0, M = 0, H = 0, m_tiles = 0;
+  int part_rows = 0;  // rows of the partial-sum buffers actually written (m_tiles, or 4 * m_tiles by the chain kernels)
   __nv_bfloat16* dout = nullptr;   // [V][M][64]   head output gradient (bf16, zero padded)
   __nv_bfloat16* dz[kMaxLayers] = {nullptr};   // [V][M][H] per hidden layer (wgrad reads them later)
   float* dbias_part[kMaxLayers] = {nullptr};   // [V][m_tiles][H]
@@ -134,6 +135,7 @@ struct Population {
   Dataset ds;
   NoisePtrs noise;
   Plan* plan = nullptr;
+  bool use_chain = false;  // layer-chain kernels (chain.cu) instead of one launch per layer
   RolloutScratch ro;
   std::vector<void*> allocs;
 };
