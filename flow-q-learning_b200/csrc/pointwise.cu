@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(256) prep_kernel(const PrepArgs a) {
   const int b = blockIdx.x * 8 + warp;
   if (b >= a.B) return;
   const int O = a.O, A = a.A, B = a.B, E = a.E;
-  const unsigned long long step = *a.step_counter;
+  const unsigned long long step = a.step_counter[p];
   const unsigned long long seed = a.seeds[p];
   const long long pb = (long long)p * B + b;
 
@@ -579,9 +579,9 @@ struct FinishArgs {
 };
 __global__ void finish_info_kernel(const FinishArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0 && a.bump) *a.step_counter += 1ull;
   if (i >= a.n_active) return;
   const int p = a.member_list[i];
+  if (a.bump) a.step_counter[p] += 1ull;
   float* f = a.info + p * kInfoSlots;
   const float s = a.normalize_q ? 1.f / f[I_QABS] : 1.f;
   f[I_Q_LOSS] = -f[I_Q] * s;
@@ -609,7 +609,7 @@ HeadArgs head_args(const Population* P, const PassBuf& pass, const Arena& ar, co
   a.q_agg_min = P->c.q_agg_min;
   a.normalize_q = P->c.normalize_q_loss;
   a.discount = P->c.discount;
-  a.member_list = P->member_list;
+  a.member_list = P->cur_list();
   a.act_f = P->act_f; a.vel = P->vel; a.rew = P->rew; a.mask = P->mask; a.alphas = P->alphas;
   a.api = P->api; a.y = P->y; a.xe = P->xe; a.target_a = P->target_a; a.info = P->info;
   a.y_in = P->y;
@@ -618,7 +618,7 @@ HeadArgs head_args(const Population* P, const PassBuf& pass, const Arena& ar, co
 }
 size_t head_smem(const HeadArgs& a) { return (size_t)(a.nb * a.out * a.H + a.nb * a.out) * sizeof(float); }
 dim3 head_grid(const Population* P, int rows) {
-  return dim3((rows + kRowsPerBlock - 1) / kRowsPerBlock, (unsigned)P->h_members.size());
+  return dim3((rows + kRowsPerBlock - 1) / kRowsPerBlock, (unsigned)P->cur_n());
 }
 
 }  // namespace
@@ -633,7 +633,7 @@ void launch_prep(Population* P, cudaStream_t s, int bump_adam) {
   a.z_mse = P->noise.z_mse;
   a.seeds = P->seeds;
   a.step_counter = P->step_counter;
-  a.member_list = P->member_list;
+  a.member_list = P->cur_list();
   a.O = P->c.O; a.A = P->c.A; a.B = P->c.B; a.E = P->c.E;
   a.pad_q = P->PI.in_pad; a.pad_bc = P->BC.in_pad;
   a.b1 = P->c.adam_b1; a.b2 = P->c.adam_b2;
@@ -642,7 +642,7 @@ void launch_prep(Population* P, cudaStream_t s, int bump_adam) {
   a.adam_bc = P->adam_bc;
   a.adam_step = P->adam_step;
   a.bump_adam = bump_adam;
-  prep_kernel<<<dim3((P->c.B + 7) / 8, (unsigned)P->h_members.size()), 256, 0, s>>>(a);
+  prep_kernel<<<dim3((P->c.B + 7) / 8, (unsigned)P->cur_n()), 256, 0, s>>>(a);
 }
 
 void launch_pi_head(Population* P, cudaStream_t s) {
@@ -677,10 +677,10 @@ void launch_pi_dout(Population* P, cudaStream_t s) {
   PiDoutArgs a{};
   a.api = P->api; a.target_a = P->target_a; a.dx0 = P->dx0_qa; a.alphas = P->alphas; a.info = P->info;
   a.dout = P->bPI.dout;
-  a.member_list = P->member_list;
+  a.member_list = P->cur_list();
   a.B = P->c.B; a.A = P->c.A; a.E = P->c.E; a.O = P->c.O; a.pad_in = P->QA.in_pad;
   a.normalize_q = P->c.normalize_q_loss;
-  pi_dout_kernel<<<dim3((P->c.B * P->c.A + 255) / 256, (unsigned)P->h_members.size()), 256, 0, s>>>(a);
+  pi_dout_kernel<<<dim3((P->c.B * P->c.A + 255) / 256, (unsigned)P->cur_n()), 256, 0, s>>>(a);
 }
 
 static int add_small_jobs(SmallGradArgs& a, int n, const Arena& ar, const BwdBuf& bw) {
@@ -709,8 +709,8 @@ void launch_small_grads(Population* P, int which, cudaStream_t s) {
   if (which == 0) n = add_small_jobs(a, n, P->critic, P->bQC);
   else if (which == 1) n = add_small_jobs(a, n, P->bc, P->bBC);
   else n = add_small_jobs(a, n, P->pi, P->bPI);
-  a.member_list = P->member_list;
-  small_grads_kernel<<<dim3(n, (unsigned)P->h_members.size()), 256, 0, s>>>(a);
+  a.member_list = P->cur_list();
+  small_grads_kernel<<<dim3(n, (unsigned)P->cur_n()), 256, 0, s>>>(a);
 }
 
 static int add_leaves(StatsArgs& a, int n, const Arena& ar) {
@@ -735,10 +735,10 @@ void launch_grad_stats(Population* P, cudaStream_t s) {
   n = add_leaves(a, n, P->critic);
   n = add_leaves(a, n, P->bc);
   n = add_leaves(a, n, P->pi);
-  a.member_list = P->member_list;
+  a.member_list = P->cur_list();
   a.leaf_stats = P->leaf_stats;
-  grad_stats_kernel<<<dim3(n, (unsigned)P->h_members.size()), 256, 0, s>>>(a);
-  grad_stats_final_kernel<<<(unsigned)P->h_members.size(), 32, 0, s>>>(P->leaf_stats, n, P->member_list, P->info);
+  grad_stats_kernel<<<dim3(n, (unsigned)P->cur_n()), 256, 0, s>>>(a);
+  grad_stats_final_kernel<<<(unsigned)P->cur_n(), 32, 0, s>>>(P->leaf_stats, n, P->cur_list(), P->info);
 }
 
 static void launch_adam_one(Population* P, Arena& ar, cudaStream_t s) {
@@ -746,12 +746,12 @@ static void launch_adam_one(Population* P, Arena& ar, cudaStream_t s) {
   a.theta = ar.theta; a.mu = ar.mu; a.nu = ar.nu; a.grad = ar.grad; a.shadow = ar.shadow;
   a.target = ar.target; a.tshadow = ar.tshadow;
   a.S = ar.L.S; a.nb = ar.L.nb;
-  a.member_list = P->member_list;
+  a.member_list = P->cur_list();
   a.adam_bc = P->adam_bc;
   a.lr = P->c.lr; a.b1 = P->c.adam_b1; a.b2 = P->c.adam_b2; a.eps = P->c.adam_eps; a.tau = P->c.tau;
   const long long n4 = ar.L.S / 4;
   const int gx = (int)((n4 + 256 * 4 - 1) / (256 * 4));  // 4 float4 per thread
-  adam_kernel<<<dim3(gx, (unsigned)(P->h_members.size() * ar.L.nb)), 256, 0, s>>>(a);
+  adam_kernel<<<dim3(gx, (unsigned)(P->cur_n() * ar.L.nb)), 256, 0, s>>>(a);
 }
 void launch_adam(Population* P, int which, cudaStream_t s) {
   launch_adam_one(P, which == 0 ? P->critic : (which == 1 ? P->bc : P->pi), s);
@@ -759,8 +759,8 @@ void launch_adam(Population* P, int which, cudaStream_t s) {
 
 void launch_finish_info(Population* P, int bump, cudaStream_t s) {
   FinishArgs a{};
-  a.info = P->info; a.alphas = P->alphas; a.member_list = P->member_list; a.step_counter = P->step_counter;
-  a.n_active = (int)P->h_members.size(); a.normalize_q = P->c.normalize_q_loss; a.bump = bump;
+  a.info = P->info; a.alphas = P->alphas; a.member_list = P->cur_list(); a.step_counter = P->step_counter;
+  a.n_active = P->cur_n(); a.normalize_q = P->c.normalize_q_loss; a.bump = bump;
   finish_info_kernel<<<(a.n_active + 127) / 128, 128, 0, s>>>(a);
 }
 

@@ -9,6 +9,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "chain.h"
@@ -25,12 +26,20 @@ namespace fqlpop {
     }                                                                                             \
   } while (0)
 
-struct Plan {
+// One member group: a window [off, off + n) of the active list that steps on its own three streams, independently
+// of the other groups (members share nothing but read-only data), so one group's long dependent chain -- the F
+// Euler steps -- overlaps the other groups' wide passes instead of leaving the SMs idle behind a step barrier.
+struct GroupPlan {
+  int off = 0, n = 0;
   cudaStream_t s[3] = {nullptr, nullptr, nullptr};
-  std::vector<cudaEvent_t> ev;
   cudaGraph_t g_step = nullptr, g_loss = nullptr;
   cudaGraphExec_t x_step = nullptr, x_loss = nullptr;
-  int launches_per_step = 0;  // kernels of ours inside one replay of the step graph
+  cudaEvent_t done = nullptr;
+};
+struct Plan {
+  std::vector<GroupPlan> groups;
+  std::vector<cudaEvent_t> ev;
+  int launches_per_step = 0;  // kernels of ours inside one replay of every group's step graph
 };
 
 namespace {
@@ -139,9 +148,9 @@ struct Builder {
 
   void begin(int nb) {
     memset(L, 0, sizeof(GemmLaunch));
-    L->P = (int)P->h_members.size() * nb;
+    L->P = P->cur_n() * nb;
     L->n_active = nullptr;
-    L->member_list = nb == 1 ? P->member_list : P->member_list_e;
+    L->member_list = nb == 1 ? P->cur_list() : P->cur_list_e();
   }
   GemmGroup& add() { return L->g[L->num_groups++]; }
   void tmap(CUtensorMap* m, const void* base, long long inner, long long rows, long long batch, long long ld,
@@ -261,8 +270,8 @@ struct ChainBuilder {
 
   void begin(int nb) {
     memset(L, 0, sizeof(ChainLaunch));
-    L->n_virtual = (int)P->h_members.size() * nb;
-    L->member_list = nb == 1 ? P->member_list : P->member_list_e;
+    L->n_virtual = P->cur_n() * nb;
+    L->member_list = nb == 1 ? P->cur_list() : P->cur_list_e();
   }
   ChainJob& add() { return L->job[L->num_jobs++]; }
   void tmap(CUtensorMap* m, const void* base, long long inner, long long rows, long long batch, long long ld,
@@ -384,11 +393,11 @@ void record(Plan* pl, cudaEvent_t* out, cudaStream_t s) {
   *out = e;
 }
 
-// Issues one lockstep step (train = update; !train = losses only) on the plan's streams. Called under stream
-// capture; s[0] is the origin stream.
-int issue_step(Population* P, bool train, std::string* err) {
+// Issues one step (train = update; !train = losses only) of the members in P's current window on the group's
+// streams. Called under stream capture; s[0] is the origin stream.
+int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   Plan* pl = P->plan;
-  cudaStream_t s0 = pl->s[0], s1 = pl->s[1], s2 = pl->s[2];
+  cudaStream_t s0 = gp.s[0], s1 = gp.s[1], s2 = gp.s[2];
   const PopParams& c = P->c;
   Builder b{P, err};
   b.L = new GemmLaunch;
@@ -520,27 +529,68 @@ int issue_step(Population* P, bool train, std::string* err) {
   delete cb.L;
   if (!b.ok || !cb.ok) return 1;
   CK(cudaGetLastError());
-  if (train) pl->launches_per_step = b.count + cb.count + pw;
+  if (train) pl->launches_per_step += b.count + cb.count + pw;
   return 0;
 }
 
 void destroy_graphs(Plan* pl) {
-  if (pl->x_step) cudaGraphExecDestroy(pl->x_step);
-  if (pl->x_loss) cudaGraphExecDestroy(pl->x_loss);
-  if (pl->g_step) cudaGraphDestroy(pl->g_step);
-  if (pl->g_loss) cudaGraphDestroy(pl->g_loss);
-  pl->x_step = pl->x_loss = nullptr;
-  pl->g_step = pl->g_loss = nullptr;
+  for (GroupPlan& g : pl->groups) {
+    if (g.x_step) cudaGraphExecDestroy(g.x_step);
+    if (g.x_loss) cudaGraphExecDestroy(g.x_loss);
+    if (g.g_step) cudaGraphDestroy(g.g_step);
+    if (g.g_loss) cudaGraphDestroy(g.g_loss);
+    g.x_step = g.x_loss = nullptr;
+    g.g_step = g.g_loss = nullptr;
+  }
   for (cudaEvent_t e : pl->ev) cudaEventDestroy(e);
   pl->ev.clear();
+  pl->launches_per_step = 0;
 }
 
-int build_graph(Population* P, bool train, std::string* err) {
+void destroy_groups(Plan* pl) {
+  destroy_graphs(pl);
+  for (GroupPlan& g : pl->groups) {
+    for (int i = 0; i < 3; ++i)
+      if (g.s[i]) cudaStreamDestroy(g.s[i]);
+    if (g.done) cudaEventDestroy(g.done);
+  }
+  pl->groups.clear();
+}
+
+// Splits the active list into member groups of FQLPOP_GROUP_SIZE members (default 4; 0 = one lockstep group).
+int make_groups(Population* P, std::string* err) {
   Plan* pl = P->plan;
-  CK(cudaStreamBeginCapture(pl->s[0], cudaStreamCaptureModeThreadLocal));
-  const int rc = issue_step(P, train, err);
+  destroy_groups(pl);
+  const int n = (int)P->h_members.size();
+  int gs = 4;
+  if (const char* e = getenv("FQLPOP_GROUP_SIZE")) gs = atoi(e);
+  if (gs <= 0 || gs > n) gs = n;
+  const int G = (n + gs - 1) / gs;
+  pl->groups.resize(G);
+  for (int g = 0; g < G; ++g) {
+    GroupPlan& gp = pl->groups[g];
+    // spread the remainder so group sizes differ by at most one
+    gp.off = (int)((long long)n * g / G);
+    gp.n = (int)((long long)n * (g + 1) / G) - gp.off;
+    for (int i = 0; i < 3; ++i) CK(cudaStreamCreateWithFlags(&gp.s[i], cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&gp.done, cudaEventDisableTiming));
+  }
+  return 0;
+}
+
+struct Window {  // RAII: narrows the population's launch window to one group
+  Population* P;
+  int off, n;
+  Window(Population* p, const GroupPlan& g) : P(p), off(p->g_off), n(p->g_n) { P->g_off = g.off; P->g_n = g.n; }
+  ~Window() { P->g_off = off; P->g_n = n; }
+};
+
+int build_graph(Population* P, bool train, GroupPlan& gp, std::string* err) {
+  Window w(P, gp);
+  CK(cudaStreamBeginCapture(gp.s[0], cudaStreamCaptureModeThreadLocal));
+  const int rc = issue_step(P, train, gp, err);
   cudaGraph_t g = nullptr;
-  cudaError_t e = cudaStreamEndCapture(pl->s[0], &g);
+  cudaError_t e = cudaStreamEndCapture(gp.s[0], &g);
   if (rc) {
     if (g) cudaGraphDestroy(g);
     return 1;
@@ -548,8 +598,8 @@ int build_graph(Population* P, bool train, std::string* err) {
   CK(e);
   cudaGraphExec_t x = nullptr;
   CK(cudaGraphInstantiate(&x, g, 0));
-  if (train) { pl->g_step = g; pl->x_step = x; }
-  else { pl->g_loss = g; pl->x_loss = x; }
+  if (train) { gp.g_step = g; gp.x_step = x; }
+  else { gp.g_loss = g; gp.x_loss = x; }
   return 0;
 }
 
@@ -568,6 +618,9 @@ static int upload_members(Population* P, std::string* err) {
   const int ne = n * P->c.E;
   CK(cudaMemcpy(P->n_active, &n, sizeof(int), cudaMemcpyHostToDevice));
   CK(cudaMemcpy(P->n_active_e, &ne, sizeof(int), cudaMemcpyHostToDevice));
+  P->g_off = 0;
+  P->g_n = n;
+  if (P->plan) return make_groups(P, err);
   return 0;
 }
 
@@ -633,7 +686,7 @@ int pop_create_impl(const PopParams& c, const float* alphas, const unsigned long
        dev_alloc(P, &P->info, (long long)c.P * kInfoSlots, err) ||
        dev_alloc(P, &P->leaf_stats, (long long)c.P * 64 * 4, err) || dev_alloc(P, &P->adam_bc, 2LL * c.P, err) ||
        dev_alloc(P, &P->adam_step, c.P, err) || dev_alloc(P, &P->alphas, c.P, err) ||
-       dev_alloc(P, &P->seeds, c.P, err) || dev_alloc(P, &P->step_counter, 1, err) ||
+       dev_alloc(P, &P->seeds, c.P, err) || dev_alloc(P, &P->step_counter, c.P, err) ||
        dev_alloc(P, &P->member_list, c.P, err) || dev_alloc(P, &P->member_list_e, V, err) ||
        dev_alloc(P, &P->n_active, 1, err) || dev_alloc(P, &P->n_active_e, 1, err);
   if (rc) {
@@ -658,7 +711,10 @@ int pop_create_impl(const PopParams& c, const float* alphas, const unsigned long
   launch_refresh_shadow(P, 0);
   launch_fill_qa_dout(P, 0);
   P->plan = new Plan;
-  for (int i = 0; i < 3; ++i) cudaStreamCreateWithFlags(&P->plan->s[i], cudaStreamNonBlocking);
+  if (make_groups(P, err)) {
+    pop_destroy_impl(P);
+    return 1;
+  }
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) {
     if (err) *err = std::string("pop_create: ") + cudaGetErrorString(e);
@@ -673,9 +729,7 @@ void pop_destroy_impl(Population* P) {
   if (!P) return;
   cudaDeviceSynchronize();
   if (P->plan) {
-    destroy_graphs(P->plan);
-    for (int i = 0; i < 3; ++i)
-      if (P->plan->s[i]) cudaStreamDestroy(P->plan->s[i]);
+    destroy_groups(P->plan);
     delete P->plan;
   }
   for (void* p : P->allocs) cudaFree(p);
@@ -714,31 +768,39 @@ static int run_plan(Population* P, bool train, int n_steps, cudaStream_t stream,
     return 1;
   }
   const bool eager = getenv("FQLPOP_EAGER") != nullptr;
-  cudaEvent_t e_in, e_out;
+  cudaEvent_t e_in;
   CK(cudaEventCreateWithFlags(&e_in, cudaEventDisableTiming));
-  CK(cudaEventCreateWithFlags(&e_out, cudaEventDisableTiming));
   CK(cudaEventRecord(e_in, stream));
-  CK(cudaStreamWaitEvent(pl->s[0], e_in, 0));
   int rc = 0;
-  if (eager) {
-    for (int i = 0; i < n_steps && !rc; ++i) rc = issue_step(P, train, err);
-  } else {
-    cudaGraphExec_t& x = train ? pl->x_step : pl->x_loss;
-    if (!x) rc = build_graph(P, train, err);
-    for (int i = 0; i < n_steps && !rc; ++i) {
-      cudaError_t e = cudaGraphLaunch(x, pl->s[0]);
-      if (e != cudaSuccess) {
-        if (err) *err = std::string("cudaGraphLaunch: ") + cudaGetErrorString(e);
-        rc = 1;
+  if (!eager && !(train ? pl->groups[0].x_step : pl->groups[0].x_loss)) {
+    if (train) pl->launches_per_step = 0;
+    for (GroupPlan& gp : pl->groups)
+      if (!rc) rc = build_graph(P, train, gp, err);
+  }
+  // every group runs its n_steps back to back on its own streams; the groups only meet again on `stream`
+  for (GroupPlan& gp : pl->groups) {
+    if (rc) break;
+    cudaStreamWaitEvent(gp.s[0], e_in, 0);
+    if (eager) {
+      Window w(P, gp);
+      if (train) pl->launches_per_step = 0;
+      for (int i = 0; i < n_steps && !rc; ++i) rc = issue_step(P, train, gp, err);
+    } else {
+      cudaGraphExec_t x = train ? gp.x_step : gp.x_loss;
+      for (int i = 0; i < n_steps && !rc; ++i) {
+        cudaError_t e = cudaGraphLaunch(x, gp.s[0]);
+        if (e != cudaSuccess) {
+          if (err) *err = std::string("cudaGraphLaunch: ") + cudaGetErrorString(e);
+          rc = 1;
+        }
       }
     }
-  }
-  if (!rc) {
-    cudaEventRecord(e_out, pl->s[0]);
-    cudaStreamWaitEvent(stream, e_out, 0);
+    if (!rc) {
+      cudaEventRecord(gp.done, gp.s[0]);
+      cudaStreamWaitEvent(stream, gp.done, 0);
+    }
   }
   cudaEventDestroy(e_in);
-  cudaEventDestroy(e_out);
   return rc;
 }
 

@@ -129,9 +129,15 @@ struct Population {
   int* adam_step = nullptr;  // [P]
   float* alphas = nullptr;   // [P]
   unsigned long long* seeds = nullptr;  // [P]
-  unsigned long long* step_counter = nullptr;  // device scalar: lockstep step index (Philox counter)
+  unsigned long long* step_counter = nullptr;  // (dev) [P] per-member step index (Philox counter)
   int *member_list = nullptr, *member_list_e = nullptr, *n_active = nullptr, *n_active_e = nullptr;
   std::vector<int> h_members;  // host copy of the active member ids
+  // Window of the active list the launchers cover: the whole list, or one member group while a group's step is
+  // being issued (groups step independently of each other, see pop.cu).
+  int g_off = 0, g_n = 0;
+  int cur_n() const { return g_n; }
+  const int* cur_list() const { return member_list + g_off; }
+  const int* cur_list_e() const { return member_list_e + (long long)g_off * c.E; }
   Dataset ds;
   NoisePtrs noise;
   Plan* plan = nullptr;

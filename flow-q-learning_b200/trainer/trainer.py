@@ -1,0 +1,262 @@
+"""Trainer: the reference's population loop (/root/reference/trainer/trainer.py:11-120) -- train every candidate for
+`eval_interval` steps, evaluate, `strategy.update`, `strategy.sample`, create / stop experiments, `max_evaluations`
+budget, `state_dict` -- with the candidate loop turned into ONE lockstep device population:
+
+  reference                                   here
+  for config in candidates: train(...)   ->   population.set_active(slots); population.step(n)   (all at once)
+  experiment.evaluate() per candidate    ->   task.rollout_population(population)                (one fused launch)
+  strategy.update(experiment, score)     ->   strategy.update(config, score)   (keyed by config, as
+                                              /root/reference/evaluator/strategy_evaluator.py:55 does; the reference
+                                              trainer passes the Experiment object, which breaks SuccessiveHalving)
+
+Multi-GPU (one process per GPU, torch.distributed initialised by the launcher): candidate i of the initial population
+lives on rank i mod world_size for its whole life -- members never communicate while training -- and the only
+collective is the all-gather of the evaluation scores, after which every rank runs the same strategy update.
+"""
+from __future__ import annotations
+
+import random
+import time
+from dataclasses import asdict
+from typing import Callable, Dict, List, Optional
+
+import numpy as np
+
+from hpo.strategy import HpoStrategy
+from task.task import Task
+from trainer.config import TrainerConfig
+from trainer.experiment import Experiment, resolve_agent_config
+
+
+def _default_population_factory(agent_config: dict, alphas, seeds, device):
+    from fqlpop.population import Population  # CUDA library; no CPU fallback
+    return Population(agent_config, alphas, seeds, device=device)
+
+
+def _dist():
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            return dist
+    except ImportError:
+        pass
+    return None
+
+
+class Trainer:
+    def __init__(self, task: Task, strategy: HpoStrategy, config: TrainerConfig, state_dict: Optional[dict] = None,
+                 population_factory: Optional[Callable] = None):
+        self.task = task
+        self.strategy = strategy
+        self.config = config
+        self.experiments: Dict = {}
+        dist = _dist()
+        self.rank = dist.get_rank() if dist else 0
+        self.world = dist.get_world_size() if dist else 1
+        self._factory = population_factory or _default_population_factory
+
+        if state_dict is not None:
+            self.candidates = state_dict["candidates"]
+            initial = list(state_dict["experiments"].keys())
+        else:
+            self.candidates = self.strategy.sample()
+            initial = list(self.candidates)
+        # every candidate keeps the slot (and the GPU) it is given here for its whole life
+        self._order = {c: i for i, c in enumerate(initial)}
+        mine = [c for c in initial if self.owns(c)]
+        self._slot = {c: s for s, c in enumerate(mine)}
+        self.population = None
+        if mine:
+            cfgs = [resolve_agent_config(config, c)[0] for c in mine]
+            example = task.sample("train", 1)
+            base = asdict(cfgs[0])
+            base["ob_dims"] = tuple(np.shape(example["observations"])[-1:])
+            base["action_dim"] = int(np.shape(example["actions"])[-1])
+            self.population = self._factory(base, [float(c.alpha) for c in cfgs], [int(c.seed) for c in cfgs],
+                                            getattr(task, "device", "cuda:0"))
+
+        if state_dict is not None:
+            for c, st in state_dict["experiments"].items():
+                self.create_experiment(c, state_dict=st)
+            self.untrained_candidates = state_dict["untrained_candidates"]
+            self.finished_candidates = state_dict["finished_candidates"]
+            random.setstate(state_dict["random_rng_state"])
+            np.random.set_state(state_dict["np_rng_state"])
+        else:
+            self.untrained_candidates = []
+            self.finished_candidates = []
+            for c in self.candidates:
+                self.create_experiment(c)
+
+    # ---- placement -----------------------------------------------------------------------------------------------
+    def owns(self, candidate) -> bool:
+        return self._order[candidate] % self.world == self.rank
+
+    def _ordered(self, candidates) -> List:
+        return sorted(candidates, key=lambda c: self._order[c])
+
+    def state_dict(self) -> dict:
+        return {
+            "experiments": {c: e.state_dict() for c, e in self.experiments.items()},
+            "candidates": self.candidates,
+            "random_rng_state": random.getstate(),
+            "np_rng_state": np.random.get_state(),
+            "untrained_candidates": self.untrained_candidates,
+            "finished_candidates": self.finished_candidates,
+        }
+
+    def create_experiment(self, experiment_config, **kwargs) -> None:
+        if experiment_config not in self._order:
+            raise KeyError(f"{experiment_config} is not part of the initial population; slots are fixed at start")
+        if self.owns(experiment_config):
+            self.experiments[experiment_config] = Experiment(
+                self.task, self.config, experiment_config, population=self.population,
+                slot=self._slot[experiment_config], **kwargs)
+
+    # ---- lockstep pieces ---------------------------------------------------------------------------------------
+    def _train_lockstep(self, mine: List, num_steps: int) -> None:
+        groups: Dict = {}
+        for c in mine:
+            e = self.experiments[c]
+            n = min(num_steps, e.steps - e.current_step)
+            if n > 0:
+                groups.setdefault((e.current_step, n), []).append(c)
+        pop = self.population
+        for (start, n), members in groups.items():
+            slots = [self._slot[c] for c in members]
+            pop.set_active(slots)
+            on_device = hasattr(self.task, "device_dataset")
+            step, end = start, start + n
+            log_every = self.config.log_interval
+            bound = False
+            while step < end:
+                chunk = min(end - step, log_every - step % log_every)
+                if on_device:
+                    if not bound:
+                        pop.set_dataset(*self.task.device_dataset("train"))
+                        pop.set_noise()
+                        bound = True
+                    pop.step(chunk)
+                else:
+                    for _ in range(chunk):
+                        self._step_host_batches(members, slots)
+                step += chunk
+                for c in members:
+                    self.experiments[c].current_step = step
+                if step % log_every == 0:
+                    info = pop.info(with_grad_stats=True)
+                    keys = self._info_keys()
+                    for c, s in zip(members, slots):
+                        self.experiments[c].logger.log({k: float(info[s, i]) for i, k in enumerate(keys)}, step=step,
+                                                       group="train")
+                    self._log_validation(members, slots, step)
+                    bound = False
+
+    def _info_keys(self):
+        from fqlpop.population import INFO_KEYS
+        return INFO_KEYS
+
+    def _bind_host_batches(self, split: str, slots: List[int]) -> None:
+        import torch
+        pop = self.population
+        B = pop.B
+        batches = [self.task.sample(split, B) for _ in slots]
+        cat = lambda k: np.concatenate([np.asarray(b[k], np.float32).reshape(B, -1) for b in batches])
+        idx = torch.zeros(pop.P, B, dtype=torch.int64)
+        for j, s in enumerate(slots):
+            idx[s] = torch.arange(j * B, (j + 1) * B)
+        pop.set_dataset(cat("observations"), cat("actions"), cat("next_observations"), cat("rewards").reshape(-1),
+                        cat("masks").reshape(-1))
+        pop.set_noise(indices=idx)
+
+    def _step_host_batches(self, members, slots) -> None:
+        self._bind_host_batches("train", slots)
+        self.population.step(1)
+
+    def _log_validation(self, members, slots, step) -> None:
+        self._bind_host_batches("val", slots)
+        self.population.total_loss()
+        info = self.population.info()
+        for c, s in zip(members, slots):
+            self.experiments[c].logger.log({k: float(info[s, i]) for i, k in enumerate(self._info_keys()[:10])},
+                                           step=step, group="val")
+
+    def _evaluate(self, mine: List) -> Dict:
+        if not mine:
+            return {}
+        if hasattr(self.task, "rollout_population"):
+            slots = [self._slot[c] for c in mine]
+            self.population.set_active(slots)
+            rate = self.task.rollout_population(self.population)["success_rate"]
+            rate = rate.cpu().numpy() if hasattr(rate, "cpu") else np.asarray(rate)
+            scores = {c: float(rate[s]) for c, s in zip(mine, slots)}
+            for c in mine:
+                e = self.experiments[c]
+                e.logger.log({"success": scores[c]}, step=e.current_step, group="eval")
+            return scores
+        return {c: self.experiments[c].evaluate() for c in mine}
+
+    def _gather_scores(self, now: List, local: Dict) -> Dict:
+        """All-gather of the evaluation scores (the one collective of the whole job)."""
+        dist = _dist()
+        if dist is None or self.world == 1:
+            return dict(local)
+        import torch
+        per_rank = [[c for c in now if self._order[c] % self.world == r] for r in range(self.world)]
+        width = max(1, max(len(x) for x in per_rank))
+        device = "cuda" if dist.get_backend() == "nccl" else "cpu"
+        send = torch.full((width,), float("nan"), dtype=torch.float32, device=device)
+        for j, c in enumerate(per_rank[self.rank]):
+            send[j] = local[c]
+        recv = [torch.empty_like(send) for _ in range(self.world)]
+        dist.all_gather(recv, send)
+        return {c: float(recv[r][j]) for r in range(self.world) for j, c in enumerate(per_rank[r])}
+
+    # ---- the loop (control flow of reference lines 69-120) -------------------------------------------------------
+    def train(self, max_evaluations: int) -> None:
+        while max_evaluations > 0:
+            todo = self._ordered(self.untrained_candidates if len(self.untrained_candidates) > 0 else self.candidates)
+            now, later = todo[:max_evaluations], todo[max_evaluations:]
+            start_time = time.perf_counter()
+            mine = [c for c in now if self.owns(c)]
+            if mine:
+                self._train_lockstep(mine, self.config.eval_interval)
+            scores = self._gather_scores(now, self._evaluate(mine))
+            for c in now:
+                if self.owns(c):
+                    e = self.experiments[c]
+                    if e.current_step == e.steps and c not in self.finished_candidates:
+                        e.save_agent()
+                done_steps = min(self.config.steps, self._steps_of(c))
+                if done_steps == self.config.steps and c not in self.finished_candidates:
+                    self.finished_candidates.append(c)
+                self.strategy.update(c, scores[c])
+                max_evaluations -= 1
+            print(f"Elapsed time: {time.perf_counter() - start_time:.6f} seconds ({len(now)} candidates in lockstep)")
+
+            if later:
+                self.untrained_candidates = later
+                break
+            self.untrained_candidates = []
+            if all(c in self.finished_candidates for c in self.candidates):
+                break
+            new_candidates = self.strategy.sample()
+            for c in new_candidates:
+                if c not in self.experiments and self.owns(c):
+                    self.create_experiment(c)
+            for c in self.candidates:
+                if c not in new_candidates and c in self.experiments:
+                    self.experiments[c].stop()
+            self.candidates = new_candidates
+
+        for e in self.experiments.values():
+            e.stop()
+
+    def _steps_of(self, candidate) -> int:
+        """Training steps a candidate has done; every rank can compute it (lockstep: evaluations x eval_interval)."""
+        if candidate in self.experiments:
+            return self.experiments[candidate].current_step
+        self._remote_steps = getattr(self, "_remote_steps", {})
+        self._remote_steps[candidate] = min(self.config.steps,
+                                            self._remote_steps.get(candidate, 0) + self.config.eval_interval)
+        return self._remote_steps[candidate]
