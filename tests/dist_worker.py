@@ -1,0 +1,39 @@
+"""Worker of tests/test_dist_cpu.py: one rank of a world_size-2 gloo job running the Trainer over fake device populations."""
+import json
+import os
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+for p in (os.path.join(ROOT, "flow-q-learning_b200"), ROOT, HERE):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def main(rank, world, port, out_dir):
+    import numpy as np
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from pathlib import Path
+
+    from fakes import FakePopulation, FakeTask
+    from hpo.successive_halving import SuccessiveHalving
+    from trainer.config import AgentConfig, ExperimentConfig, TrainerConfig
+    from trainer.trainer import Trainer
+    cfg = TrainerConfig(steps=40, eval_interval=10, log_interval=5, save_directory=Path(out_dir) / f"rank{rank}",
+                        env_name="cube-test", agent=AgentConfig(batch_size=8))
+    pop = [ExperimentConfig(seed=i, alpha=a) for i, a in enumerate(np.logspace(np.log10(3), 3, 8).tolist())]
+    sh = SuccessiveHalving(set(pop), total_evaluations=4, fraction=0.5, history_length=1)
+    tr = Trainer(FakeTask(), sh, cfg, population_factory=FakePopulation)
+    tr.train(max_evaluations=100)
+    out = {"rank": rank, "local_members": len(tr.experiments), "candidates": sorted(c.alpha for c in tr.candidates),
+           "scores": {str(c.alpha): v for c, v in sh.candidate_scores.items()},
+           "steps": {str(c.alpha): e.current_step for c, e in tr.experiments.items()}}
+    with open(os.path.join(out_dir, f"rank{rank}.json"), "w") as f:
+        json.dump(out, f)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main(int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3]), sys.argv[4])

@@ -1,0 +1,31 @@
+"""N > 1 host path on the CPU: two gloo ranks, members placed i mod world, the evaluation-score all-gather as the only
+collective, identical successive-halving decisions on every rank."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_two_rank_trainer_agrees_on_pruning(tmp_path):
+    port = _free_port()
+    worker = os.path.join(os.path.dirname(__file__), "dist_worker.py")
+    procs = [subprocess.Popen([sys.executable, worker, str(r), "2", str(port), str(tmp_path)]) for r in range(2)]
+    for p in procs:
+        assert p.wait(timeout=240) == 0
+    r0, r1 = (json.load(open(tmp_path / f"rank{r}.json")) for r in range(2))
+    assert r0["local_members"] == 4 and r1["local_members"] == 4          # member i -> rank i mod 2
+    assert r0["candidates"] == r1["candidates"] and len(r0["candidates"]) == 2
+    assert r0["scores"] == r1["scores"] and len(r0["scores"]) == 8        # every rank saw every score
+    assert not set(r0["steps"]) & set(r1["steps"])                          # no member trained twice
+    trained = {**r0["steps"], **r1["steps"]}
+    assert sorted(trained.values()) == [10, 10, 10, 10, 20, 20, 40, 40]
+    # same decisions as the single-process run
+    best = sorted((float(a) for a in trained), key=lambda a: abs(__import__("math").log10(a) - 2))[:2]
+    assert sorted(best) == r0["candidates"]
