@@ -81,6 +81,142 @@ __device__ __forceinline__ void st_act_half_row(uint8_t* block, int r, int c0, c
         make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Forward hidden layer epilogue (MODE 0): h = LayerNorm?(gelu(acc + b)).
+// Pass 1 runs sub-tile by sub-tile behind the tensor core (packed FFMA2 math, double-buffered tcgen05.ld): the bf16
+// activations cannot go to ACT yet -- the MMAs of the later sub-tiles still read it -- so they are PARKED in the TMEM
+// columns they were just drained from (16 packed columns per 32 accumulator columns). Pass 2, once every MMA of the
+// layer has retired (and, for LayerNorm, the row statistics are complete), moves them TMEM -> registers -> ACT / HBM.
+// Without LayerNorm the last sub-tile skips the detour.
+// ---------------------------------------------------------------------------------------------------------------
+struct EpiCtx {
+  uint32_t tmem_row;
+  uint64_t* tmem_full;
+  uint32_t fullph;
+  uint8_t* act;
+  const float* params;
+  int r, half, q, lane, H;
+  bool row_ok;
+  long long prow;    // element offset of this row in the pass buffers
+  long long rs_off;  // offset of this row in the rstd buffers
+  float ln_eps;
+};
+
+template <bool LN, bool SAVE>
+__device__ __forceinline__ void fwd_hidden_layer(EpiCtx& C, const ChainLayer& Ly) {
+  const int n_pad = Ly.n_pad;
+  const int n_sub = (n_pad + 127) >> 7;
+  const int my0 = C.half * 64;  // first column of this thread inside every 128-column sub-tile
+  f32x2 s1 = pk2(0.f, 0.f), s2 = pk2(0.f, 0.f);
+  const float* bias = C.params + Ly.off_b;
+
+#pragma unroll 1
+  for (int sub = 0; sub < n_sub; ++sub) {
+    mbar_wait(&C.tmem_full[sub], (C.fullph >> sub) & 1u);
+    C.fullph ^= 1u << sub;
+    tc_fence_after();
+    if (sub * 128 + my0 >= n_pad) continue;
+    const bool direct = !LN && sub == n_sub - 1;  // every MMA of the layer has retired: ACT is free
+    const int col0 = sub * 128 + my0;
+    uint32_t rr[2][32];
+    tmem_ld32(C.tmem_row + col0, rr[0]);
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const int col = col0 + c * 32;
+      float4 b4[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) b4[i] = __ldg(reinterpret_cast<const float4*>(bias + col) + i);
+      tmem_ld_wait();
+      if (c == 0) tmem_ld32(C.tmem_row + col0 + 32, rr[1]);
+      uint32_t pk[16], gpk[16];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        f32x2 g0, g1, p0, p1;
+        gelu2<SAVE>(add2(pk2u(rr[c][4 * i + 0], rr[c][4 * i + 1]), pk2(b4[i].x, b4[i].y)), g0, p0);
+        gelu2<SAVE>(add2(pk2u(rr[c][4 * i + 2], rr[c][4 * i + 3]), pk2(b4[i].z, b4[i].w)), g1, p1);
+        if (LN) {
+          s1 = add2(s1, add2(g0, g1));
+          s2 = fma2(g0, g0, fma2(g1, g1, s2));
+        }
+        pk[2 * i] = pack_bf16x2_v(g0);
+        pk[2 * i + 1] = pack_bf16x2_v(g1);
+        if (SAVE) {
+          gpk[2 * i] = pack_bf16x2_v(p0);
+          gpk[2 * i + 1] = pack_bf16x2_v(p1);
+        }
+      }
+      if (SAVE && C.row_ok) st_global_packed32(Ly.out_gp + C.prow + col, gpk);
+      if (direct) {
+        st_act_half_row(C.act + (sub * 2 + C.half) * kActBlockBytes, C.r, c * 4, pk);
+        if (C.row_ok && Ly.out_h) st_global_packed32(Ly.out_h + C.prow + col, pk);
+      } else {
+        tmem_st16(C.tmem_row + col0 + c * 16, pk);
+      }
+    }
+  }
+  tmem_st_wait();
+
+  float mean = 0.f, rstd = 1.f;
+  if (LN) {
+    // exchange the half-row statistics through the (now free) first bytes of ACT
+    float a0, a1, q0, q1;
+    upk2(s1, a0, a1);
+    upk2(s2, q0, q1);
+    float t1 = a0 + a1, t2 = q0 + q1;
+    float2* ex = reinterpret_cast<float2*>(C.act);
+    ex[C.half * 128 + C.r] = make_float2(t1, t2);
+    epi_bar_sync();
+    const float2 o = ex[(C.half ^ 1) * 128 + C.r];
+    epi_bar_sync();
+    t1 += o.x;
+    t2 += o.y;
+    const float inv_n = 1.0f / (float)C.H;
+    mean = t1 * inv_n;
+    const float var = fmaxf(t2 * inv_n - mean * mean, 0.f);  // flax LayerNorm: E[x^2] - E[x]^2
+    rstd = rsqrtf(var + C.ln_eps);
+    if (C.row_ok && C.half == 0 && Ly.out_rstd) Ly.out_rstd[C.rs_off] = rstd;
+  }
+  const int n_park = LN ? n_sub : n_sub - 1;
+  const f32x2 rstd2 = pk2(rstd, rstd), shift2 = pk2(-mean * rstd, -mean * rstd);
+#pragma unroll 1
+  for (int sub = 0; sub < n_park; ++sub) {
+    if (sub * 128 + my0 >= n_pad) continue;
+    const int col0 = sub * 128 + my0;
+    uint32_t pr[2][16];
+    tmem_ld16(C.tmem_row + col0, pr[0]);
+    tmem_ld16(C.tmem_row + col0 + 16, pr[1]);
+    tmem_ld_wait();
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const int col = col0 + c * 32;
+      if (LN) {
+        const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + col);
+        const float4* e4 = reinterpret_cast<const float4*>(C.params + Ly.off_beta + col);
+        uint32_t hk[16], xk[16];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 ga = __ldg(g4 + i), be = __ldg(e4 + i);
+          const uint32_t w0 = pr[c][2 * i], w1 = pr[c][2 * i + 1];
+          const f32x2 x0 = fma2(pk2u(w0 << 16, w0 & 0xFFFF0000u), rstd2, shift2);
+          const f32x2 x1 = fma2(pk2u(w1 << 16, w1 & 0xFFFF0000u), rstd2, shift2);
+          xk[2 * i] = pack_bf16x2_v(x0);
+          xk[2 * i + 1] = pack_bf16x2_v(x1);
+          hk[2 * i] = pack_bf16x2_v(fma2(x0, pk2(ga.x, ga.y), pk2(be.x, be.y)));
+          hk[2 * i + 1] = pack_bf16x2_v(fma2(x1, pk2(ga.z, ga.w), pk2(be.z, be.w)));
+        }
+        st_act_half_row(C.act + (sub * 2 + C.half) * kActBlockBytes, C.r, c * 4, hk);
+        if (C.row_ok) {
+          if (Ly.out_h) st_global_packed32(Ly.out_h + C.prow + col, hk);
+          if (SAVE && Ly.out_xhat) st_global_packed32(Ly.out_xhat + C.prow + col, xk);
+        }
+      } else {
+        st_act_half_row(C.act + (sub * 2 + C.half) * kActBlockBytes, C.r, c * 4, pr[c]);
+        if (C.row_ok && Ly.out_h) st_global_packed32(Ly.out_h + C.prow + col, pr[c]);
+      }
+    }
+  }
+}
+
 template <int MODE>  // 0 = forward / Euler flow, 1 = backward (input-gradient chain)
 __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_constant__ ChainLaunch L) {
   extern __shared__ uint8_t smem_raw[];
@@ -232,7 +368,19 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
       for (int li = 0; li < n_layers; ++li) {
         const ChainLayer& Ly = J.layer[li];
         const int n_pad = Ly.n_pad;
-        if (Ly.kind == CL_HIDDEN && !J.ln) {
+        if (MODE == 0 && Ly.kind == CL_HIDDEN) {
+          EpiCtx C{tmem_row, tmem_full, fullph, act, params, r, half, q, lane, H, row_ok, prow,
+                   (long long)v * J.pass_rs + grow, J.ln_eps};
+          const bool save = Ly.out_gp != nullptr;
+          if (J.ln) {
+            if (save) fwd_hidden_layer<true, true>(C, Ly);
+            else fwd_hidden_layer<true, false>(C, Ly);
+          } else {
+            if (save) fwd_hidden_layer<false, true>(C, Ly);
+            else fwd_hidden_layer<false, false>(C, Ly);
+          }
+          fullph = C.fullph;
+        } else if (MODE == 1 && Ly.kind == CL_HIDDEN && !J.ln) {
           // ------------------------------------------------------------------------------------------
           // bias + GELU (forward) / act'(z) product (backward); sub-tiles 0..2 are kept in registers while the
           // tensor core still reads ACT
@@ -321,7 +469,7 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
                 for (int c = 0; c < 2; ++c) dst[sub * 128 + half * 64 + c * 32 + lane] = csum[sub][c];
               }
           }
-        } else if (Ly.kind == CL_HIDDEN) {
+        } else if (MODE == 1 && Ly.kind == CL_HIDDEN) {
           // ------------------------------------------------------------------------------------------
           // LayerNorm layers: pass 1 (overlapped with the MMAs of later sub-tiles) parks per-element values in
           // TMEM and accumulates the row statistics; pass 2 normalises into ACT.

@@ -136,6 +136,24 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
       : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+      "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
 
 // ----------------------------------------------------------------------------------------------
 // UMMA descriptors (bit layouts follow cute/arch/mma_sm100_desc.hpp: SmemDescriptor / InstrDescriptor)
@@ -186,6 +204,61 @@ __device__ __forceinline__ void gelu_fwd(float z, float& g, float& gp) {
   g = z * hp;
   gp = hp + 0.5f * z * (1.0f - t * t) * k0 * fmaf(3.0f * k1, z2, 1.0f);
 }
+// ---- packed fp32 pairs (FFMA2 / FMUL2 / FADD2: the full-rate fp32 path of sm_100) ----------------------------------
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float a, float b) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 pk2u(uint32_t a, uint32_t b) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ void upk2(f32x2 v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint32_t pack_bf16x2_v(f32x2 v) {
+  float a, b;
+  upk2(v, a, b);
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+// tanh-GELU of a pair: g = z hp, hp = (1 + tanh u)/2, u = k0 z (1 + k1 z^2); GP also returns
+// g' = hp + z (du/dz) (1 - tanh^2 u)/2 = hp + z (2 k0 + 6 k0 k1 z^2) hp (1 - hp).   6 (+5) packed ops + 2 MUFU.
+template <bool GP>
+__device__ __forceinline__ void gelu2(f32x2 z, f32x2& g, f32x2& gp) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  const f32x2 z2 = mul2(z, z);
+  const f32x2 u = mul2(z, fma2(pk2(k0 * k1, k0 * k1), z2, pk2(k0, k0)));
+  float u0, u1;
+  upk2(u, u0, u1);
+  const f32x2 t = pk2(tanh_fast(u0), tanh_fast(u1));
+  const f32x2 hp = fma2(pk2(0.5f, 0.5f), t, pk2(0.5f, 0.5f));
+  g = mul2(z, hp);
+  if (GP) {
+    const f32x2 hn = fma2(pk2(-0.5f, -0.5f), t, pk2(0.5f, 0.5f));
+    const f32x2 w = mul2(z, fma2(pk2(6.f * k0 * k1, 6.f * k0 * k1), z2, pk2(2.f * k0, 2.f * k0)));
+    gp = fma2(w, mul2(hp, hn), hp);
+  }
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);

@@ -209,11 +209,15 @@ def gelu_tanh(z):
     return 0.5 * z * (1.0 + torch.tanh(math.sqrt(2.0 / math.pi) * (z + 0.044715 * z ** 3)))
 
 
-def layer_norm(x, scale, bias, eps):
+def layer_norm(x, scale, bias, eps, park_bf16=False):
     # flax LayerNorm(use_fast_variance=True): var = E[x^2] - E[x]^2
+    # park_bf16 (bf16 emulation of the CUDA chain kernels): the row statistics come from the fp32 activations, the
+    # values that get normalised were parked as bf16 while the tensor core finished the layer.
     mean = x.mean(-1, keepdim=True)
     var = (x * x).mean(-1, keepdim=True) - mean * mean
     var = torch.clamp(var, min=0.0)
+    if park_bf16:
+        x = _bf16_ste(x)
     return (x - mean) * torch.rsqrt(var + eps) * scale + bias
 
 
@@ -233,7 +237,8 @@ def mlp_apply(p, x, n_layers, ln, eps, emulate_bf16=False, head_bf16=False):
         if not last:
             x = gelu_tanh(x)
             if ln:
-                x = layer_norm(x, p[f"LayerNorm_{i}"]["scale"], p[f"LayerNorm_{i}"]["bias"], eps)
+                x = layer_norm(x, p[f"LayerNorm_{i}"]["scale"], p[f"LayerNorm_{i}"]["bias"], eps,
+                               park_bf16=emulate_bf16 and not head_bf16)  # the rollout kernel normalises fp32
     return x
 
 
