@@ -197,6 +197,14 @@ extern "C" int fqlpop_philox_fill(uint64_t seed, uint64_t step, int32_t rows, in
   if (fqlpop::philox_fill(seed, step, rows, slots, kind, n, out_host)) return fail("philox_fill: CUDA error");
   return 0;
 }
+extern "C" int fqlpop_debug_chain_trace(void* h, long long* host_out, int32_t n) {
+  POP(h);
+  if (!P->chain_trace) return fail("chain trace disabled (set FQLPOP_CHAIN_TRACE=1 before fqlpop_create)");
+  cudaDeviceSynchronize();
+  if (cudaMemcpy(host_out, P->chain_trace, sizeof(long long) * (n < 8192 ? n : 8192), cudaMemcpyDeviceToHost) != cudaSuccess)
+    return fail("chain trace copy failed");
+  return 0;
+}
 extern "C" int fqlpop_launches_per_step(void* h) {
   fqlpop::Population* P = (fqlpop::Population*)h;
   return P ? fqlpop::pop_launches_per_step(P) : 0;

@@ -100,6 +100,8 @@ struct EpiCtx {
   long long prow;    // element offset of this row in the pass buffers
   long long rs_off;  // offset of this row in the rstd buffers
   float ln_eps;
+  long long* trace;  // non-null on the one traced thread
+  int tr;
 };
 
 template <bool LN, bool SAVE>
@@ -115,6 +117,7 @@ __device__ __forceinline__ void fwd_hidden_layer(EpiCtx& C, const ChainLayer& Ly
     mbar_wait(&C.tmem_full[sub], (C.fullph >> sub) & 1u);
     C.fullph ^= 1u << sub;
     tc_fence_after();
+    if (C.trace && C.tr < 4000) C.trace[4096 + C.tr++] = clock64();
     if (sub * 128 + my0 >= n_pad) continue;
     const bool direct = !LN && sub == n_sub - 1;  // every MMA of the layer has retired: ACT is free
     const int col0 = sub * 128 + my0;
@@ -155,6 +158,7 @@ __device__ __forceinline__ void fwd_hidden_layer(EpiCtx& C, const ChainLayer& Ly
     }
   }
   tmem_st_wait();
+  if (C.trace && C.tr < 4000) C.trace[4096 + C.tr++] = clock64();
 
   float mean = 0.f, rstd = 1.f;
   if (LN) {
@@ -303,38 +307,46 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
     }
   } else if (warp == 1) {
     // ========================================= MMA issuer ===========================================
-    if (lane == 0) {
+    // The whole warp walks the loop (waits are warp-uniform); one elected lane issues the MMAs and commits.
+    {
       int stage = 0;
       uint32_t phase = 0;
       uint32_t itc = 0;
+      int tr = 0;
       const uint32_t act_addr = smem_u32(act), x0_addr = smem_u32(x0s);
+      const uint64_t bdesc0 = MODE == 0 ? make_smem_desc_sw128(smem_u32(stage_base), kBoxBytes, 1024)
+                                        : make_smem_desc_sw128(smem_u32(stage_base), 16, 1024);
+      constexpr uint32_t kBStep = (MODE == 0 ? 2048u : 32u) >> 4;  // descriptor units (16 B) per K = 16 step
       for (int it = 0; it < iters; ++it) {
         for (int li = 0; li < n_layers; ++li, ++itc) {
           const ChainLayer& Ly = J.layer[li];
           if (itc == 0) mbar_wait(a0_full, 0);
           else mbar_wait(act_ready, (itc - 1) & 1);
           tc_fence_after();
-          const uint32_t a_base = Ly.a_from_x0 ? x0_addr : act_addr;
+          if (L.trace && blockIdx.x == 0 && lane == 0 && tr < 4000) L.trace[tr++] = clock64();
+          const uint64_t adesc0 = make_smem_desc_sw128(Ly.a_from_x0 ? x0_addr : act_addr, 16, 1024);
+          const int k_blocks = Ly.k_blocks;
           int sub = 0;
           for (int n0 = 0; n0 < Ly.n_pad; n0 += 128, ++sub) {
             const int ncols = min(128, Ly.n_pad - n0);
             const uint32_t idesc = make_idesc_bf16(128, (uint32_t)ncols, 0, MODE == 0 ? 1 : 0);
-            for (int kb = 0; kb < Ly.k_blocks; ++kb) {
+            const uint32_t tmem_d = tmem_base + n0;
+            for (int kb = 0; kb < k_blocks; ++kb) {
               mbar_wait(&full_bar[stage], phase);
               tc_fence_after();
-              const uint32_t sa = a_base + kb * kActBlockBytes;
-              const uint32_t sb = smem_u32(stage_base + stage * kStageBytes);
+              if (elect_one()) {
+                const uint64_t ad = adesc0 + (uint64_t)(kb * (kActBlockBytes >> 4));
+                const uint64_t bd = bdesc0 + (uint64_t)(stage * (kStageBytes >> 4));
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                const uint64_t adesc = make_smem_desc_sw128(sa + k * 32, 16, 1024);
-                const uint64_t bdesc = MODE == 0 ? make_smem_desc_sw128(sb + k * 2048, kBoxBytes, 1024)
-                                                 : make_smem_desc_sw128(sb + k * 32, 16, 1024);
-                umma_bf16(tmem_base + n0, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                for (int k = 0; k < 4; ++k)
+                  umma_bf16(tmem_d, ad + 2 * k, bd + kBStep * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                umma_commit(&empty_bar[stage]);
+                if (kb == k_blocks - 1) umma_commit(&tmem_full[sub]);
               }
-              umma_commit(&empty_bar[stage]);
+              __syncwarp();
               if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
-            umma_commit(&tmem_full[sub]);
+            if (L.trace && blockIdx.x == 0 && lane == 0 && tr < 4000) L.trace[tr++] = clock64();
           }
         }
       }
@@ -357,6 +369,7 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
       tc_fence_after();
     };
 
+    int etr = 0;
     float xs[8];  // Euler flow: the action iterate of this row (fp32)
     if (MODE == 0 && J.xe) {
 #pragma unroll
@@ -370,7 +383,8 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
         const int n_pad = Ly.n_pad;
         if (MODE == 0 && Ly.kind == CL_HIDDEN) {
           EpiCtx C{tmem_row, tmem_full, fullph, act, params, r, half, q, lane, H, row_ok, prow,
-                   (long long)v * J.pass_rs + grow, J.ln_eps};
+                   (long long)v * J.pass_rs + grow, J.ln_eps,
+                   (L.trace && blockIdx.x == 0 && threadIdx.x == 64) ? L.trace : nullptr, etr};
           const bool save = Ly.out_gp != nullptr;
           if (J.ln) {
             if (save) fwd_hidden_layer<true, true>(C, Ly);
@@ -380,6 +394,7 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
             else fwd_hidden_layer<false, false>(C, Ly);
           }
           fullph = C.fullph;
+          etr = C.tr;
         } else if (MODE == 1 && Ly.kind == CL_HIDDEN && !J.ln) {
           // ------------------------------------------------------------------------------------------
           // bias + GELU (forward) / act'(z) product (backward); sub-tiles 0..2 are kept in registers while the
@@ -700,6 +715,7 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
         tc_fence_before();
         fence_proxy_async_smem();
         mbar_arrive(act_ready);
+        if (L.trace && blockIdx.x == 0 && threadIdx.x == 64 && etr < 4000) L.trace[4096 + etr++] = clock64();
       }
     }
   }

@@ -74,6 +74,7 @@ struct ChainLaunch {
   int num_jobs;
   int n_virtual;            // active virtual members (grid = sum_jobs m_tiles * n_virtual)
   const int* member_list;   // (dev) [n_virtual] virtual member ids
+  long long* trace;         // (dev, debug) clock64 stamps of CTA 0: [0,4096) MMA thread, [4096,8192) epilogue thread 0
   ChainJob job[kChainMaxJobs];
 };
 

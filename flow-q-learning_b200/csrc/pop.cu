@@ -458,6 +458,7 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   if (chain) {
     cb.begin(1);
     cb.euler_job();
+    cb.L->trace = P->chain_trace;
     cb.launch(0, s0);
   } else {
     for (int i = 0; i < c.F; ++i) {
@@ -677,6 +678,7 @@ int pop_create_impl(const PopParams& c, const float* alphas, const unsigned long
   // reference uses) and at most kChainMaxLayers GEMMs per chain; otherwise the per-layer kernels are used.
   P->use_chain = Lq.in_pad == 64 && Lb.in_pad == 64 && Lp.in_pad == 64 && c.n_hidden_actor + 1 <= kChainMaxLayers &&
                  c.n_hidden_value + 1 <= kChainMaxLayers && getenv("FQLPOP_NO_CHAIN") == nullptr;
+  if (getenv("FQLPOP_CHAIN_TRACE")) rc = rc || dev_alloc(P, &P->chain_trace, 8192, err);
   for (BwdBuf* bw : {&P->bQC, &P->bQA, &P->bBC, &P->bPI}) bw->part_rows = bw->m_tiles * (P->use_chain ? 4 : 1);
   const long long PB = (long long)c.P * c.B;
   rc = rc || dev_alloc(P, &P->act_f, PB * c.A, err) || dev_alloc(P, &P->vel, PB * c.A, err) ||

@@ -96,6 +96,9 @@ int fqlpop_last_batch(void* handle, float* rewards_host, float* masks_host);
  * [0, n) as uint32; 3: normal fp32. out_host: [rows][slots] (x4 words for kind 0).                           */
 int fqlpop_philox_fill(uint64_t seed, uint64_t step, int32_t rows, int32_t slots, int32_t kind, uint32_t n,
                        void* out_host);
+/* Debug: clock64 stamps of CTA 0 of the Euler layer-chain kernel (needs FQLPOP_CHAIN_TRACE=1 at create time):
+ * [0,4096) MMA thread (layer start, after each sub-tile's last MMA issue), [4096,8192) first epilogue thread.  */
+int fqlpop_debug_chain_trace(void* handle, long long* host_out, int32_t n);
 /* Number of kernels one replay of the captured step launches (bench.py's gpu_launches).                   */
 int fqlpop_launches_per_step(void* handle);
 
