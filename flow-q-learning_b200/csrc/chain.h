@@ -32,6 +32,8 @@ struct ChainLayer {
   int k_blocks;    // reduction length / 64
   int n_pad;       // output columns (multiple of 64, <= 512)
   int a_from_x0;   // A operand = the 128 x 64 input block instead of the activation buffer
+  int b_box_rows;  // backward: rows of the weight TMA box (min(256, output columns)); forward: unused
+  int _pad0;
   long long off_b, off_g, off_beta;  // element offsets of bias / LayerNorm scale / LayerNorm bias in `params`
   // forward outputs (nullptr = not stored). Row-major [V][pass rows][H] bf16, already offset to the job's row 0.
   __nv_bfloat16* out_h;
@@ -53,8 +55,8 @@ struct ChainLayer {
 
 struct ChainJob {
   CUtensorMap mapA0;                   // first A operand: dims (64, pass rows, V), box 64 x 128
-  CUtensorMap mapW[kChainMaxLayers];   // forward: [K][N] n-contiguous, box 64n x 64k; backward: same array read
-                                       // as B^T, box 64n(k of the GEMM) x 128 rows
+  CUtensorMap mapW[kChainMaxLayers];   // forward: [K][N] n-contiguous, box 64n x 32k; backward: same array read
+                                       // as B^T, 64-byte swizzle, box 32 k x min(256, n) rows
   ChainLayer layer[kChainMaxLayers];
   int tile_begin, m_tiles, M, row0;    // rows [row0, row0 + M) of the pass buffers
   int n_layers, iters, ln, H;
@@ -74,6 +76,8 @@ struct ChainLaunch {
   int num_jobs;
   int n_virtual;            // active virtual members (grid = sum_jobs m_tiles * n_virtual)
   const int* member_list;   // (dev) [n_virtual] virtual member ids
+  int debug_flags;          // (debug) bit 0: no weight TMA / no stage waits (timing of the bare MMA stream; results are garbage)
+  int _pad_dbg;
   long long* trace;         // (dev, debug) clock64 stamps of CTA 0: [0,4096) MMA thread, [4096,8192) epilogue thread 0
   ChainJob job[kChainMaxJobs];
 };

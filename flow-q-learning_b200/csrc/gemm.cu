@@ -502,6 +502,21 @@ int encode_tmap_bf16(CUtensorMap* out, const void* base, long long inner, long l
   return r == CUDA_SUCCESS ? 0 : (int)r;
 }
 
+int encode_tmap_bf16_sw64(CUtensorMap* out, const void* base, long long inner, long long rows, long long batch,
+                          long long ld, long long batch_stride, int box_rows) {
+  PFN_encodeTiled fn = get_encode_fn();
+  if (!fn) return -1;
+  cuuint64_t dims[3] = {(cuuint64_t)inner, (cuuint64_t)rows, (cuuint64_t)batch};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)batch_stride * 2};
+  cuuint32_t box[3] = {32, (cuuint32_t)box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  if (batch <= 1) strides[1] = (cuuint64_t)ld * 2 * (cuuint64_t)rows;
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : (int)r;
+}
+
 int finalize_launch(GemmLaunch* L, int n_sub) {
   int t = 0;
   for (int i = 0; i < L->num_groups; ++i) {

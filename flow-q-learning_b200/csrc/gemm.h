@@ -96,6 +96,10 @@ struct GemmLaunch {
 int encode_tmap_bf16(CUtensorMap* out, const void* base, long long inner, long long rows, long long batch,
                      long long ld, long long batch_stride, int box_rows);
 
+// Same tensor, 64-byte swizzle and a (32, box_rows, 1) box: K-major operand stages of 32 reduction elements per row.
+int encode_tmap_bf16_sw64(CUtensorMap* out, const void* base, long long inner, long long rows, long long batch,
+                          long long ld, long long batch_stride, int box_rows);
+
 // Fills tile_begin of every group (tiles are ordered group-major, then member, m-tile, n-tile) and
 // returns the grid size. n_sub is 1 or 4 (4 = full 512-wide rows per CTA, needed by the *_LN epilogues).
 int finalize_launch(GemmLaunch* L, int n_sub);

@@ -282,6 +282,14 @@ struct ChainBuilder {
       if (err) *err = "cuTensorMapEncodeTiled failed rc=" + std::to_string(rc);
     }
   }
+  void tmap64(CUtensorMap* m, const void* base, long long inner, long long rows, long long batch, long long ld,
+              long long ms, int box_rows) {
+    const int rc = encode_tmap_bf16_sw64(m, base, inner, rows, batch, ld, ms, box_rows);
+    if (rc != 0 && ok) {
+      ok = false;
+      if (err) *err = "cuTensorMapEncodeTiled (64B swizzle) failed rc=" + std::to_string(rc);
+    }
+  }
   void launch(int mode, cudaStream_t s) {
     finalize_chain(L);
     cudaError_t e = launch_chain(*L, mode, s);
@@ -310,7 +318,7 @@ struct ChainBuilder {
     tmap(&j.mapA0, pass.X0, N.in_pad, pass.M, pass.V, N.in_pad, (long long)pass.M * N.in_pad, 128);
     const long long roff = (long long)row0 * N.H;
     for (int l = 0; l < N.n_hidden; ++l) {
-      tmap(&j.mapW[l], wsh + N.offW[l], N.H, N.K(l), ar.V, N.H, N.S, 64);
+      tmap(&j.mapW[l], wsh + N.offW[l], N.H, N.K(l), ar.V, N.H, N.S, 32);
       ChainLayer& y = j.layer[l];
       y.kind = CL_HIDDEN; y.k_blocks = N.K(l) / 64; y.n_pad = N.H; y.a_from_x0 = l == 0;
       y.off_b = N.offb[l]; y.off_g = N.offg[l]; y.off_beta = N.offbeta[l];
@@ -333,7 +341,7 @@ struct ChainBuilder {
     ChainJob& j = fwd_job(P->EU, ar, ar.theta, ar.shadow, 0, P->c.B, false);
     j.layer[N.n_hidden - 1].out_h = nullptr;
     const int l = N.n_hidden;
-    tmap(&j.mapW[l], ar.shadow + N.offW[l], kHeadPad, N.H, ar.V, kHeadPad, N.S, 64);
+    tmap(&j.mapW[l], ar.shadow + N.offW[l], kHeadPad, N.H, ar.V, kHeadPad, N.S, 32);
     ChainLayer& y = j.layer[l];
     y.kind = CL_EULER_HEAD; y.k_blocks = N.H / 64; y.n_pad = kHeadPad; y.a_from_x0 = 0;
     y.off_b = N.offb[l];
@@ -355,8 +363,9 @@ struct ChainBuilder {
     int s = 0;
     for (int l = N.n_hidden; l >= 1; --l, ++s) {
       const int Kd = N.N(l);
-      tmap(&j.mapW[s], ar.shadow + N.offW[l], Kd, N.K(l), ar.V, Kd, N.S, 128);
       ChainLayer& y = j.layer[s];
+      y.b_box_rows = N.K(l) < 256 ? N.K(l) : 256;
+      tmap64(&j.mapW[s], ar.shadow + N.offW[l], Kd, N.K(l), ar.V, Kd, N.S, y.b_box_rows);
       y.kind = CL_HIDDEN; y.k_blocks = Kd / 64; y.n_pad = N.H; y.a_from_x0 = s == 0;
       y.off_g = N.offg[l - 1];
       y.gp = pass.gp[l - 1] + roff;
@@ -374,8 +383,9 @@ struct ChainBuilder {
       }
     }
     if (dinput_out) {
-      tmap(&j.mapW[s], ar.shadow + N.offW[0], N.H, N.in_pad, ar.V, N.H, N.S, 64);
       ChainLayer& y = j.layer[s];
+      y.b_box_rows = N.in_pad < 256 ? N.in_pad : 256;
+      tmap64(&j.mapW[s], ar.shadow + N.offW[0], N.H, N.in_pad, ar.V, N.H, N.S, y.b_box_rows);
       y.kind = CL_DINPUT; y.k_blocks = N.H / 64; y.n_pad = N.in_pad; y.a_from_x0 = 0;
       y.out_f32 = dinput_out; y.out_ld = N.in_pad;
       j.f32_ms = (long long)bw.M * N.in_pad;
@@ -459,6 +469,7 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
     cb.begin(1);
     cb.euler_job();
     cb.L->trace = P->chain_trace;
+    if (const char* e = getenv("FQLPOP_CHAIN_DEBUG")) cb.L->debug_flags = atoi(e);
     cb.launch(0, s0);
   } else {
     for (int i = 0; i < c.F; ++i) {

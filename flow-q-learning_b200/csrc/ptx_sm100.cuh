@@ -147,6 +147,17 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
       : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+               ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
@@ -173,15 +184,20 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16
 //   K-major : rows of 128 B (64 bf16 of K); 8-row atoms of 1024 B; sbo = 1024; lbo unused (1 unit).
 //   MN-major: rows of 128 B (64 bf16 of M/N), one row per k; 8-row atoms of 1024 B (sbo = 1024);
 //             the next 64 M/N elements start lbo bytes further (one TMA box).
-__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes,
-                                                         uint32_t sbo_bytes) {
+// layout: cute LayoutType -- 2 = SWIZZLE_128B, 4 = SWIZZLE_64B (K-major rows of 64 B: 8-row atoms of 512 B)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout) {
   uint64_t d = 0;
   d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
   d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
   d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
   d |= static_cast<uint64_t>(1) << 46;  // descriptor version 1 (Blackwell)
-  d |= static_cast<uint64_t>(2) << 61;  // LayoutType::SWIZZLE_128B
+  d |= static_cast<uint64_t>(layout) << 61;
   return d;
+}
+__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes,
+                                                         uint32_t sbo_bytes) {
+  return make_smem_desc(smem_addr, lbo_bytes, sbo_bytes, 2);
 }
 // kind::f16, A=B=bf16, D=f32, dense, no negate. M in {64,128}, N multiple of 16 (M=128).
 __device__ __forceinline__ uint32_t make_idesc_bf16(uint32_t M, uint32_t N, uint32_t a_mn_major,
@@ -267,6 +283,22 @@ __device__ __forceinline__ void gelu2(f32x2 z, f32x2& g, f32x2& gp) {
     const f32x2 hn = fma2(pk2(-0.5f, -0.5f), t, pk2(0.5f, 0.5f));
     const f32x2 w = mul2(z, fma2(pk2(6.f * k0 * k1, 6.f * k0 * k1), z2, pk2(2.f * k0, 2.f * k0)));
     gp = fma2(w, mul2(hp, hn), hp);
+  }
+}
+
+// Scalar tanh-GELU with the fewest fp32 operations (measured on B200: FFMA with an immediate runs at 125 lanes/clk/SM,
+// three-register FFMA and packed FFMA2 both at ~84 FMA lanes/clk/SM, so packing buys nothing but register pressure):
+// g = z hp, hp = (1 + tanh u)/2, u = z (k0 + k0 k1 z^2);  g' = hp + z (2 k0 + 6 k0 k1 z^2) hp (1 - hp).
+template <bool GP>
+__device__ __forceinline__ void gelu1(float z, float& g, float& gp) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  const float z2 = z * z;
+  const float t = tanh_fast(z * fmaf(z2, k0 * k1, k0));
+  const float hp = fmaf(t, 0.5f, 0.5f);
+  g = z * hp;
+  if (GP) {
+    const float hn = fmaf(t, -0.5f, 0.5f);
+    gp = fmaf(z * fmaf(z2, 6.f * k0 * k1, 2.f * k0), hp * hn, hp);
   }
 }
 

@@ -20,12 +20,13 @@ lib.fqlpop_debug_chain_trace.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctype
 check(lib.fqlpop_debug_chain_trace(pop._h, buf.ctypes.data, 8192))
 mma, epi = buf[:4096], buf[4096:]
 t0 = mma[0]
-# Euler: 5 layers per step; MMA stamps per layer: 1 + n_sub (4,4,4,4,1); epilogue: hidden: n_sub + 1 (pass-1 end) + 1 (release); head: 1
+# Euler: 5 layers per step. MMA stamps per layer: start + one per 256-column tile (2,2,2,2,1).
+# Epilogue stamps: hidden layer: tile 0 ready, tile 1 ready, act_lo released, act_hi released; head: ready, lo, hi.
 mi = ei = 0
-for it in range(2):
+for it in range(3):
     for l in range(5):
-        ns = 4 if l < 4 else 1
-        m = mma[mi:mi + 1 + ns] - t0; mi += 1 + ns
-        ne = ns + 2 if l < 4 else 1
+        nt = 2 if l < 4 else 1
+        m = mma[mi:mi + 1 + nt] - t0; mi += 1 + nt
+        ne = 4 if l < 4 else 3
         e = epi[ei:ei + ne] - t0; ei += ne
-        print(f"it{it} L{l}: mma start {m[0]:7d} issued {[int(x - m[0]) for x in m[1:]]}  | epi sub-ready {[int(x - m[0]) for x in e[:ns]] if l < 4 else []} pass1-end/release {[int(x - m[0]) for x in e[ns:]]}")
+        print(f"it{it} L{l}: mma start {m[0]:7d} tiles issued {[int(x - m[0]) for x in m[1:]]} | epi: tiles ready {[int(x - m[0]) for x in e[:nt]]} released lo/hi {[int(x - m[0]) for x in e[nt:]]}")
