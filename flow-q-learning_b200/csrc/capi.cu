@@ -205,6 +205,20 @@ extern "C" int fqlpop_debug_chain_trace(void* h, long long* host_out, int32_t n)
     return fail("chain trace copy failed");
   return 0;
 }
+extern "C" int fqlpop_debug_timeline(void* h, long long* host_out, int32_t max_records, int32_t* n_out) {
+  POP(h);
+  if (!P->timeline) return fail("timeline disabled (set FQLPOP_TIMELINE=1 before fqlpop_create)");
+  cudaDeviceSynchronize();
+  long long n = 0;
+  if (cudaMemcpy(&n, P->timeline, sizeof(long long), cudaMemcpyDeviceToHost) != cudaSuccess) return fail("timeline copy failed");
+  if (n > 65536) n = 65536;
+  if (n > max_records) n = max_records;
+  if (n > 0 && cudaMemcpy(host_out, P->timeline + 8, sizeof(long long) * 4 * n, cudaMemcpyDeviceToHost) != cudaSuccess)
+    return fail("timeline copy failed");
+  cudaMemset(P->timeline, 0, sizeof(long long));
+  if (n_out) *n_out = (int32_t)n;
+  return 0;
+}
 extern "C" int fqlpop_launches_per_step(void* h) {
   fqlpop::Population* P = (fqlpop::Population*)h;
   return P ? fqlpop::pop_launches_per_step(P) : 0;

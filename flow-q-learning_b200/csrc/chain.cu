@@ -18,6 +18,15 @@
 // parked in the TMEM columns they were drained from. Once T1 has landed, T0 is flushed to the low half of ACT and
 // `act_lo` lets the next layer's MMAs start on it while T1's epilogue fills the high half. LayerNorm layers need the
 // whole row before normalising: both tiles are parked, then flushed low half first.
+//
+// Global traffic of the epilogue (saved h / act'(z) / xhat of a forward pass, dz and the saved tensors of a backward
+// pass): a thread owns a ROW, so a direct 16-byte access per lane touches 32 different 128-byte lines per warp
+// instruction. Everything therefore goes through shared memory: h / dz are copied out of ACT (they are there anyway,
+// as the next layer's A operand), the other tensors through a warp-private 4 KB staging block (32 rows x 128 bytes,
+// same XOR swizzle as ACT, so no cross-warp synchronisation is needed), and the global side is always 4 rows x 128
+// contiguous bytes per warp instruction (stores: ld.shared + st.global; loads: cp.async, issued a block ahead). The
+// per-column sums of dz (bias gradients) fall out of the copy-out loop. Launches that need the staging area run on 3
+// weight stages instead of 5 (the Euler chain keeps 5).
 #include "chain.h"
 
 #include "gemm.h"
@@ -28,7 +37,9 @@ namespace fqlpop {
 namespace {
 
 constexpr int kThreads = 320;
-constexpr int kStages = 5;
+constexpr int kStages = 5;          // weight stages of a launch without saved tensors (Euler chain, target critic)
+constexpr int kStagesStaged = 3;    // ... of a launch whose epilogue stages tensors through shared memory
+constexpr int kStagingBytes = 4096; // per epilogue warp: 32 rows x 128 bytes (overlays weight stages 3 and 4)
 constexpr int kActBlockBytes = 128 * 64 * 2;   // one 64-wide k-block of the A operand = 16 KB
 constexpr int kActBytes = 8 * kActBlockBytes;  // 128 KB
 constexpr int kStageBytes = 16384;             // 32 k x 256 n bf16
@@ -97,7 +108,105 @@ struct EpiCtx {
   long long dzrow;       // element offset of this row in the dz buffers
   long long part_off;    // offset of this (tile, lane quarter) row in the partial-sum buffers
   float ln_eps;
+  // warp-level view for the staged global traffic
+  uint8_t* stg;          // this warp's 4 KB staging block (nullptr in launches that keep all 5 weight stages)
+  long long wrow;        // element offset of the warp's first row in the pass buffers
+  long long wdz;         // ... in the dz buffers
+  int rows_valid;        // how many of the warp's 32 rows exist (0 .. 32)
 };
+
+// ---------------------------------------------------------------------------------------------------------------
+// Staged global traffic. A "block" is 32 rows x 64 bf16 columns = 32 x 128 bytes in shared memory, 16-byte chunk c
+// of row r at r * 128 + ((c ^ (r & 7)) << 4) -- the layout of a warp's 32 rows inside a 64-column block of ACT, and
+// of the warp-private staging block. Row-wise accesses (lane = row) and the coalesced sweep below (a quarter-warp per
+// row) are both bank-conflict free.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_stage16(uint8_t* stg, int lane, int cw, const uint32_t* w) {
+  uint8_t* row = stg + lane * 128;
+  const int c0 = cw >> 3;
+  *reinterpret_cast<uint4*>(row + ((c0 ^ (lane & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+  *reinterpret_cast<uint4*>(row + (((c0 + 1) ^ (lane & 7)) << 4)) = make_uint4(w[4], w[5], w[6], w[7]);
+}
+__device__ __forceinline__ void ld_stage16(const uint8_t* stg, int lane, int cw, uint32_t* w) {
+  const uint8_t* row = stg + lane * 128;
+  const int c0 = cw >> 3;
+  const uint4 a = *reinterpret_cast<const uint4*>(row + ((c0 ^ (lane & 7)) << 4));
+  const uint4 b = *reinterpret_cast<const uint4*>(row + (((c0 + 1) ^ (lane & 7)) << 4));
+  w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
+  w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
+}
+// block -> global rows (row stride ld elements); 4 rows x 128 contiguous bytes per warp instruction
+__device__ __forceinline__ void copy_out_block(const uint8_t* blk, __nv_bfloat16* g, int ld, int lane, int rows_valid) {
+  const int ch = lane & 7, rsub = lane >> 3;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int r = i * 4 + rsub;
+    const uint4 v = *reinterpret_cast<const uint4*>(blk + r * 128 + ((ch ^ (r & 7)) << 4));
+    if (r < rows_valid) *reinterpret_cast<uint4*>(g + (long long)r * ld + ch * 8) = v;
+  }
+}
+// the same sweep, also summing every column over the warp's 32 rows (rows that do not exist hold zeros):
+// lanes 0..7 write 8 column sums each
+__device__ __forceinline__ void copy_out_block_colsum(const uint8_t* blk, __nv_bfloat16* g, int ld, int lane,
+                                                      int rows_valid, float* part) {
+  const int ch = lane & 7, rsub = lane >> 3;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int r = i * 4 + rsub;
+    const uint4 v = *reinterpret_cast<const uint4*>(blk + r * 128 + ((ch ^ (r & 7)) << 4));
+    if (r < rows_valid) *reinterpret_cast<uint4*>(g + (long long)r * ld + ch * 8) = v;
+    acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x);
+    acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
+    acc[4] += bf16_lo(v.z); acc[5] += bf16_hi(v.z);
+    acc[6] += bf16_lo(v.w); acc[7] += bf16_hi(v.w);
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 8);
+    acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 16);
+  }
+  if (lane < 8) {
+    float4* p4 = reinterpret_cast<float4*>(part + ch * 8);
+    p4[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    p4[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  }
+}
+// global rows -> block, asynchronously (cp.async; rows that do not exist are zero-filled). One commit group.
+__device__ __forceinline__ void stage_in_block(uint8_t* blk, const __nv_bfloat16* g, int ld, int lane, int rows_valid) {
+  const int ch = lane & 7, rsub = lane >> 3;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int r = i * 4 + rsub;
+    uint8_t* dst = blk + r * 128 + ((ch ^ (r & 7)) << 4);
+    if (r < rows_valid) cp_async16(dst, g + (long long)r * ld + ch * 8);
+    else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+  }
+  cp_async_commit();
+}
+// Half blocks (32 rows x 32 columns = 32 x 64 bytes, 2 KB): chunk c (0..3) of row r at r * 64 + ((c ^ ((r >> 1) & 3))
+// << 4). Used where two tensors have to be resident at once (LayerNorm backward).
+__device__ __forceinline__ void stage_in_half(uint8_t* blk, const __nv_bfloat16* g, int ld, int lane, int rows_valid) {
+  const int ch = lane & 3, rsub = lane >> 2;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = i * 8 + rsub;
+    uint8_t* dst = blk + r * 64 + ((ch ^ ((r >> 1) & 3)) << 4);
+    if (r < rows_valid) cp_async16(dst, g + (long long)r * ld + ch * 8);
+    else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+  }
+  cp_async_commit();
+}
+__device__ __forceinline__ void ld_half16(const uint8_t* blk, int lane, int cw, uint32_t* w) {
+  const uint8_t* row = blk + lane * 64;
+  const int c0 = cw >> 3, sw = (lane >> 1) & 3;
+  const uint4 a = *reinterpret_cast<const uint4*>(row + ((c0 ^ sw) << 4));
+  const uint4 b = *reinterpret_cast<const uint4*>(row + (((c0 + 1) ^ sw) << 4));
+  w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
+  w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
+}
 
 __device__ __forceinline__ void wait_tile(const EpiCtx& C, uint32_t& fullph, int t) {
   mbar_wait(&C.tmem_full[t], (fullph >> t) & 1u);  // bit t of fullph: parity to wait for on tmem_full[t]
@@ -165,11 +274,27 @@ __device__ __forceinline__ void store_colsum16(float* part, const EpiCtx& C, int
   if (C.lane < 16) part[C.part_off + col + C.lane] = cs;
 }
 
+// This warp's part of accumulator tile `tile` (its 32 rows x its 128 columns = two 64-column blocks of ACT) -> global
+// rows of `dst` ([rows][H] bf16, already offset to the job's row 0 of virtual member 0), optionally with the per-column
+// sums over the warp's rows -> part[part_off + column].
+__device__ __forceinline__ void copy_out_act(const EpiCtx& C, int tile, int n_pad, __nv_bfloat16* dst, long long wofs,
+                                             float* part) {
+  const int nblk = tile_chunks16(C, tile, n_pad) >> 2;
+  const int col0 = tile * kTileN + C.half * 128;
+  for (int b = 0; b < nblk; ++b) {
+    const int col = col0 + b * 64;
+    const uint8_t* blk = C.act + (col >> 6) * kActBlockBytes + C.q * (32 * 128);
+    if (part) copy_out_block_colsum(blk, dst + wofs + col, C.H, C.lane, C.rows_valid, part + C.part_off + col);
+    else copy_out_block(blk, dst + wofs + col, C.H, C.lane, C.rows_valid);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // forward hidden layer: h = LayerNorm?(gelu(acc + b))
 // ---------------------------------------------------------------------------------------------------------------
-// Pass 1 over this thread's chunks of one accumulator tile: bias + GELU (+ act'(z) for the backward pass) in packed
-// fp32, bf16 result parked in the drained TMEM columns or -- `direct` -- written to ACT / HBM.
+// Pass 1 over this thread's chunks of one accumulator tile: bias + GELU (+ act'(z) for the backward pass, staged and
+// copied out per 64-column block); the bf16 result is parked in the drained TMEM columns or -- `direct` -- written
+// to ACT (the caller copies h out of ACT once the layer has been handed to the tensor core).
 template <bool LN, bool SAVE>
 __device__ __forceinline__ void fwd_pass1(const EpiCtx& C, const ChainLayer& Ly, int tile, bool direct, float& s1, float& s2) {
   const int nch = tile_chunks16(C, tile, Ly.n_pad);
@@ -178,10 +303,10 @@ __device__ __forceinline__ void fwd_pass1(const EpiCtx& C, const ChainLayer& Ly,
   const float* bias = C.params + Ly.off_b;
   uint32_t rr[16];
 #pragma unroll 1
-  for (int cp = 0; cp < nch; cp += 2) {
+  for (int cb = 0; cb < nch; cb += 4) {
 #pragma unroll 1
-    for (int ch = 0; ch < 2; ++ch) {
-      const int c = cp + ch;
+    for (int c4 = 0; c4 < 4; ++c4) {
+      const int c = cb + c4;
       const int col = col0 + c * 16;
       float4 b4[4];
 #pragma unroll
@@ -207,30 +332,33 @@ __device__ __forceinline__ void fwd_pass1(const EpiCtx& C, const ChainLayer& Ly,
           gpk[2 * i + 1] = pack_bf16x2(p2, p3);
         }
       }
-      if (SAVE && C.row_ok) st_global_packed16(Ly.out_gp + C.prow + col, gpk);
-      if (direct) {
-        st_act16(C.act, C.r, col, pk);
-        if (C.row_ok && Ly.out_h) st_global_packed16(Ly.out_h + C.prow + col, pk);
-      } else {
-        tmem_st8(C.tmem_row + col0 + c * 8, pk);
-      }
+      if (SAVE) st_stage16(C.stg, C.lane, c4 * 16, gpk);
+      if (direct) st_act16(C.act, C.r, col, pk);
+      else tmem_st8(C.tmem_row + col0 + c * 8, pk);
+    }
+    if (SAVE) {
+      __syncwarp();
+      copy_out_block(C.stg, Ly.out_gp + C.wrow + col0 + cb * 16, C.H, C.lane, C.rows_valid);
+      __syncwarp();
     }
   }
 }
 
-// Parked tile -> ACT (+ HBM); LayerNorm layers normalise on the way: x = (g - mean) rstd, h = x gamma + beta.
+// Parked tile -> ACT; LayerNorm layers normalise on the way: x = (g - mean) rstd, h = x gamma + beta (xhat staged and
+// copied out per 64-column block).
 template <bool LN, bool SAVE>
 __device__ __forceinline__ void fwd_flush(const EpiCtx& C, const ChainLayer& Ly, int tile, float mean, float rstd) {
   const int nch = tile_chunks16(C, tile, Ly.n_pad);
   if (nch == 0) return;
   const int col0 = tile * kTileN + C.half * 128;
   const float shift = -mean * rstd;
+  const bool save_x = LN && SAVE && Ly.out_xhat != nullptr;
   uint32_t pr[8];
 #pragma unroll 1
-  for (int cp = 0; cp < nch; cp += 2) {
+  for (int cb = 0; cb < nch; cb += 4) {
 #pragma unroll 1
-    for (int ch = 0; ch < 2; ++ch) {
-      const int c = cp + ch;
+    for (int c4 = 0; c4 < 4; ++c4) {
+      const int c = cb + c4;
       const int col = col0 + c * 16;
       tmem_ld8(C.tmem_row + col0 + c * 8, pr);
       tmem_ld_wait();
@@ -250,14 +378,15 @@ __device__ __forceinline__ void fwd_flush(const EpiCtx& C, const ChainLayer& Ly,
           hk[2 * i + 1] = pack_bf16x2(fmaf(x2, ga.z, be.z), fmaf(x3, ga.w, be.w));
         }
         st_act16(C.act, C.r, col, hk);
-        if (C.row_ok) {
-          if (Ly.out_h) st_global_packed16(Ly.out_h + C.prow + col, hk);
-          if (SAVE && Ly.out_xhat) st_global_packed16(Ly.out_xhat + C.prow + col, xk);
-        }
+        if (save_x) st_stage16(C.stg, C.lane, c4 * 16, xk);
       } else {
         st_act16(C.act, C.r, col, pr);
-        if (C.row_ok && Ly.out_h) st_global_packed16(Ly.out_h + C.prow + col, pr);
       }
+    }
+    if (save_x) {
+      __syncwarp();
+      copy_out_block(C.stg, Ly.out_xhat + C.wrow + col0 + cb * 16, C.H, C.lane, C.rows_valid);
+      __syncwarp();
     }
   }
 }
@@ -292,6 +421,11 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
       fwd_pass1<false, SAVE>(C, Ly, 1, true, s1, s2);
     }
     release(C.act_hi);
+    // h -> HBM out of ACT, off the hand-off path: these rows of ACT are next written by this very warp
+    if (Ly.out_h) {
+      __syncwarp();
+      for (int t = 0; t < n_tiles; ++t) copy_out_act(C, t, Ly.n_pad, Ly.out_h, C.wrow, nullptr);
+    }
   } else {
     wait_tile(C, fullph, 0);
     fwd_pass1<true, SAVE>(C, Ly, 0, false, s1, s2);
@@ -307,9 +441,15 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
     const float var = fmaxf(t2 * inv_n - mean * mean, 0.f);  // flax LayerNorm: E[x^2] - E[x]^2
     const float rstd = rsqrtf(var + C.ln_eps);
     if (C.row_ok && C.half == 0 && Ly.out_rstd) Ly.out_rstd[C.rs_off] = rstd;
+    // LayerNorm layers copy h out BEFORE the hand-off: the next layer's row-sum exchange reuses the head of ACT and
+    // must not overtake a slower warp's copy
     fwd_flush<true, SAVE>(C, Ly, 0, mean, rstd);
+    if (Ly.out_h) { __syncwarp(); copy_out_act(C, 0, Ly.n_pad, Ly.out_h, C.wrow, nullptr); }
     release(C.act_lo);
-    if (n_tiles > 1) fwd_flush<true, SAVE>(C, Ly, 1, mean, rstd);
+    if (n_tiles > 1) {
+      fwd_flush<true, SAVE>(C, Ly, 1, mean, rstd);
+      if (Ly.out_h) { __syncwarp(); copy_out_act(C, 1, Ly.n_pad, Ly.out_h, C.wrow, nullptr); }
+    }
     release(C.act_hi);
   }
 }
@@ -317,20 +457,33 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
 // ---------------------------------------------------------------------------------------------------------------
 // backward hidden layer: dz = act'(z) * LNbwd?(acc), acc = dz_next W^T
 // ---------------------------------------------------------------------------------------------------------------
-// no LayerNorm: one pass, parked or direct exactly like the forward layer
-__device__ __forceinline__ void bwd_pass1(const EpiCtx& C, const ChainLayer& Ly, int tile, bool direct) {
+// act'(z) of block `blk` (64 columns) of this warp's part of tile `tile` -> staging (asynchronous)
+__device__ __forceinline__ void bwd_prefetch_gp(const EpiCtx& C, const ChainLayer& Ly, int tile, int blk) {
+  if (!Ly.gp) return;
+  if (blk * 4 >= tile_chunks16(C, tile, Ly.n_pad)) return;
+  stage_in_block(C.stg, Ly.gp + C.wrow + tile * kTileN + C.half * 128 + blk * 64, C.H, C.lane, C.rows_valid);
+}
+
+// no LayerNorm: one pass, parked or direct exactly like the forward layer. The first block of act'(z) has been
+// prefetched by the caller; `next_tile` >= 0 prefetches that tile's first block on the way out.
+__device__ __forceinline__ void bwd_pass1(const EpiCtx& C, const ChainLayer& Ly, int tile, bool direct, int next_tile) {
   const int nch = tile_chunks16(C, tile, Ly.n_pad);
   if (nch == 0) return;
   const int col0 = tile * kTileN + C.half * 128;
+  const bool has_gp = Ly.gp != nullptr;
   uint32_t rr[16];
 #pragma unroll 1
-  for (int cp = 0; cp < nch; cp += 2) {
+  for (int cb = 0; cb < nch; cb += 4) {
+    if (has_gp) {
+      cp_async_wait_all();
+      __syncwarp();
+    }
 #pragma unroll 1
-    for (int ch = 0; ch < 2; ++ch) {
-      const int c = cp + ch;
+    for (int c4 = 0; c4 < 4; ++c4) {
+      const int c = cb + c4;
       const int col = col0 + c * 16;
       uint32_t gw[8];
-      if (Ly.gp && C.row_ok) ld_global_packed16(Ly.gp + C.prow + col, gw);
+      if (has_gp) ld_stage16(C.stg, C.lane, c4 * 16, gw);
       else {
 #pragma unroll
         for (int i = 0; i < 8; ++i) gw[i] = C.row_ok ? 0x3F803F80u : 0u;  // bf16 (1, 1) / (0, 0)
@@ -342,10 +495,13 @@ __device__ __forceinline__ void bwd_pass1(const EpiCtx& C, const ChainLayer& Ly,
       for (int i = 0; i < 8; ++i)
         pk[i] = pack_bf16x2(__uint_as_float(rr[2 * i]) * bf16_lo(gw[i]),
                             __uint_as_float(rr[2 * i + 1]) * bf16_hi(gw[i]));
-      if (C.row_ok) st_global_packed16(Ly.out_dz + C.dzrow + col, pk);
       if (direct) st_act16(C.act, C.r, col, pk);
       else tmem_st8(C.tmem_row + col0 + c * 8, pk);
-      if (Ly.dbias_part) store_colsum16(Ly.dbias_part, C, col, pk);
+    }
+    if (has_gp) {
+      __syncwarp();
+      if (cb + 4 < nch) bwd_prefetch_gp(C, Ly, tile, (cb >> 2) + 1);
+      else if (next_tile >= 0) bwd_prefetch_gp(C, Ly, next_tile, 0);
     }
   }
 }
@@ -364,26 +520,35 @@ __device__ __forceinline__ void bwd_flush(const EpiCtx& C, const ChainLayer& Ly,
   }
 }
 
+// LayerNorm backward works on half blocks (32 columns): the staging block holds two of them.
+// sub-block `sb` (0 .. 3 within the tile's 128 columns of this warp) of a saved tensor -> staging slot `slot`
+__device__ __forceinline__ void ln_prefetch(const EpiCtx& C, const __nv_bfloat16* src, int n_pad, int tile, int sb, int slot) {
+  if (sb * 2 >= tile_chunks16(C, tile, n_pad)) return;
+  stage_in_half(C.stg + slot * 2048, src + C.wrow + tile * kTileN + C.half * 128 + sb * 32, C.H, C.lane, C.rows_valid);
+}
+
 // LayerNorm, statistics pass (overlaps the MMAs of the other tile; the accumulator stays in TMEM untouched):
 // h = xhat gamma + beta, acc = dL/dh  ->  dxhat = acc gamma; s1 = sum dxhat, s2 = sum dxhat xhat;
-// partial column sums dbeta = colsum(acc), dgamma = colsum(acc xhat).
-__device__ __forceinline__ void bwd_ln_stats(const EpiCtx& C, const ChainLayer& Ly, int tile, float& s1, float& s2) {
+// partial column sums dbeta = colsum(acc), dgamma = colsum(acc xhat). xhat is double-buffered through the two
+// staging slots; sub-block 0 has been prefetched into slot 0 by the caller.
+__device__ __forceinline__ void bwd_ln_stats(const EpiCtx& C, const ChainLayer& Ly, int tile, int next_tile, float& s1, float& s2) {
   const int nch = tile_chunks16(C, tile, Ly.n_pad);
   if (nch == 0) return;
   const int col0 = tile * kTileN + C.half * 128;
+  const int nsb = nch >> 1;
   uint32_t rr[16];
 #pragma unroll 1
-  for (int cp = 0; cp < nch; cp += 2) {
+  for (int sb = 0; sb < nsb; ++sb) {
+    cp_async_wait_all();
+    __syncwarp();
+    if (sb + 1 < nsb) ln_prefetch(C, Ly.xhat, Ly.n_pad, tile, sb + 1, (sb + 1) & 1);
+    else if (next_tile >= 0) ln_prefetch(C, Ly.xhat, Ly.n_pad, next_tile, 0, (sb + 1) & 1);
+    const uint8_t* slot = C.stg + (sb & 1) * 2048;
 #pragma unroll 1
     for (int ch = 0; ch < 2; ++ch) {
-      const int c = cp + ch;
-      const int col = col0 + c * 16;
+      const int col = col0 + sb * 32 + ch * 16;
       uint32_t xw[8];
-      if (C.row_ok) ld_global_packed16(Ly.xhat + C.prow + col, xw);
-      else {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) xw[i] = 0u;
-      }
+      ld_half16(slot, C.lane, ch * 16, xw);
       const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + col);
       tmem_ld16(C.tmem_row + col, rr);
       tmem_ld_wait();
@@ -417,30 +582,32 @@ __device__ __forceinline__ void bwd_ln_stats(const EpiCtx& C, const ChainLayer& 
     }
   }
 }
-// LayerNorm, output pass: dg = rstd (dxhat - mean(dxhat) - xhat mean(dxhat xhat)); dz = act'(z) dg -> ACT, HBM
+// LayerNorm, output pass: dg = rstd (dxhat - mean(dxhat) - xhat mean(dxhat xhat)); dz = act'(z) dg -> ACT.
+// Slot 0 = xhat, slot 1 = act'(z) of the current 32-column sub-block.
 __device__ __forceinline__ void bwd_ln_out(const EpiCtx& C, const ChainLayer& Ly, int tile, float c1, float c2, float rstd) {
   const int nch = tile_chunks16(C, tile, Ly.n_pad);
   if (nch == 0) return;
   const int col0 = tile * kTileN + C.half * 128;
   const float k1 = -c1 * rstd, k2 = -c2 * rstd;
+  const int nsb = nch >> 1;
+  const bool has_gp = Ly.gp != nullptr;
   uint32_t rr[16];
 #pragma unroll 1
-  for (int cp = 0; cp < nch; cp += 2) {
+  for (int sb = 0; sb < nsb; ++sb) {
+    __syncwarp();  // the previous sub-block has been read by every lane
+    ln_prefetch(C, Ly.xhat, Ly.n_pad, tile, sb, 0);
+    if (has_gp) ln_prefetch(C, Ly.gp, Ly.n_pad, tile, sb, 1);
+    cp_async_wait_all();
+    __syncwarp();
 #pragma unroll 1
     for (int ch = 0; ch < 2; ++ch) {
-      const int c = cp + ch;
-      const int col = col0 + c * 16;
+      const int col = col0 + sb * 32 + ch * 16;
       uint32_t xw[8], gw[8];
-      if (C.row_ok) {
-        ld_global_packed16(Ly.xhat + C.prow + col, xw);
-        if (Ly.gp) ld_global_packed16(Ly.gp + C.prow + col, gw);
-        else {
+      ld_half16(C.stg, C.lane, ch * 16, xw);
+      if (has_gp) ld_half16(C.stg + 2048, C.lane, ch * 16, gw);
+      else {
 #pragma unroll
-          for (int i = 0; i < 8; ++i) gw[i] = 0x3F803F80u;
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) { xw[i] = 0u; gw[i] = 0u; }
+        for (int i = 0; i < 8; ++i) gw[i] = C.row_ok ? 0x3F803F80u : 0u;
       }
       const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + col);
       tmem_ld16(C.tmem_row + col, rr);
@@ -463,8 +630,6 @@ __device__ __forceinline__ void bwd_ln_out(const EpiCtx& C, const ChainLayer& Ly
         pk[2 * i + 1] = pack_bf16x2(dz[2], dz[3]);
       }
       st_act16(C.act, C.r, col, pk);
-      if (C.row_ok) st_global_packed16(Ly.out_dz + C.dzrow + col, pk);
-      if (Ly.dbias_part) store_colsum16(Ly.dbias_part, C, col, pk);
     }
   }
 }
@@ -473,34 +638,46 @@ template <bool LN>
 __device__ __forceinline__ void bwd_hidden_layer(const EpiCtx& C, uint32_t& fullph, const ChainLayer& Ly) {
   const int n_tiles = (Ly.n_pad + kTileN - 1) / kTileN;
   if (!LN) {
+    bwd_prefetch_gp(C, Ly, 0, 0);
     wait_tile(C, fullph, 0);
     if (n_tiles == 1) {
-      bwd_pass1(C, Ly, 0, true);
+      bwd_pass1(C, Ly, 0, true, -1);
       release(C.act_lo);
     } else {
-      bwd_pass1(C, Ly, 0, false);
+      bwd_pass1(C, Ly, 0, false, 1);
       tmem_st_wait();
       wait_tile(C, fullph, 1);
       bwd_flush(C, Ly, 0);
       release(C.act_lo);
-      bwd_pass1(C, Ly, 1, true);
+      bwd_pass1(C, Ly, 1, true, -1);
     }
     release(C.act_hi);
+    // dz -> HBM (+ bias-gradient partial sums) out of ACT, off the hand-off path
+    __syncwarp();
+    for (int t = 0; t < n_tiles; ++t) copy_out_act(C, t, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
   } else {
     float s1 = 0.f, s2 = 0.f;
+    ln_prefetch(C, Ly.xhat, Ly.n_pad, 0, 0, 0);
     wait_tile(C, fullph, 0);
-    bwd_ln_stats(C, Ly, 0, s1, s2);
+    bwd_ln_stats(C, Ly, 0, n_tiles > 1 ? 1 : -1, s1, s2);
     if (n_tiles > 1) {
       wait_tile(C, fullph, 1);
-      bwd_ln_stats(C, Ly, 1, s1, s2);
+      bwd_ln_stats(C, Ly, 1, -1, s1, s2);
     }
     float t1 = s1, t2 = s2;
     exchange_row_sums(C, t1, t2);
     const float inv_n = 1.0f / (float)C.H;
     const float rstd = C.row_ok ? __ldg(Ly.rstd + C.rs_off) : 0.f;
+    // copies happen before the hand-off (see fwd_hidden_layer)
     bwd_ln_out(C, Ly, 0, t1 * inv_n, t2 * inv_n, rstd);
+    __syncwarp();
+    copy_out_act(C, 0, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
     release(C.act_lo);
-    if (n_tiles > 1) bwd_ln_out(C, Ly, 1, t1 * inv_n, t2 * inv_n, rstd);
+    if (n_tiles > 1) {
+      bwd_ln_out(C, Ly, 1, t1 * inv_n, t2 * inv_n, rstd);
+      __syncwarp();
+      copy_out_act(C, 1, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
+    }
     release(C.act_hi);
   }
 }
@@ -523,6 +700,8 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  long long tl_t0 = 0;
+  if (L.timeline && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
 
   // ---- tile decode ---------------------------------------------------------------------------------
   int ji = 0;
@@ -536,6 +715,7 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
   const int v = L.member_list ? __ldg(L.member_list + bidx) : bidx;
   const int n_layers = J.n_layers;
   const int iters = J.iters;
+  const int n_stages = L.stages;  // 5, or 3 when stages 3 and 4 serve as the epilogue's staging area
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&J.mapA0);
@@ -587,7 +767,7 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
                 mbar_arrive_expect_tx(&full_bar[stage], Ly.b_box_rows * kStageK * 2);
                 tma_load_3d(sb, &J.mapW[li], &full_bar[stage], ks * kStageK, n0, v);
               }
-              if (++stage == kStages) { stage = 0; phase ^= 1; }
+              if (++stage == n_stages) { stage = 0; phase ^= 1; }
             }
           }
         }
@@ -639,7 +819,7 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
               if (ks == k_steps - 1) umma_commit(&tmem_full[tile]);
             }
             __syncwarp();
-            if (++stage == kStages) { stage = 0; phase ^= 1; }
+            if (++stage == n_stages) { stage = 0; phase ^= 1; }
           }
           if (L.trace && blockIdx.x == 0 && lane == 0 && tr < 4000) L.trace[tr++] = clock64();
         }
@@ -668,6 +848,11 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
     C.dzrow = (long long)v * J.dz_ms + (long long)grow * J.H;
     C.part_off = (long long)v * J.part_ms + (long long)(mt * 4 + q) * J.H;
     C.ln_eps = J.ln_eps;
+    C.stg = n_stages == kStages ? nullptr : stage_base + kStagesStaged * kStageBytes + (warp - 2) * kStagingBytes;
+    const int grow0 = mt * 128 + q * 32;
+    C.wrow = (long long)v * J.pass_ms + (long long)grow0 * J.H;
+    C.wdz = (long long)v * J.dz_ms + (long long)grow0 * J.H;
+    C.rows_valid = min(32, max(0, J.M - grow0));
     uint32_t fullph = 0;
     int etr = 0;
     const bool traced = L.trace && blockIdx.x == 0 && threadIdx.x == 64;
@@ -761,6 +946,17 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
+  if (L.timeline && threadIdx.x == 0) {
+    long long t1;
+    unsigned smid;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    const unsigned long long slot = atomicAdd(reinterpret_cast<unsigned long long*>(L.timeline), 1ull);
+    if (slot < 65536ull) {
+      long long* rec = L.timeline + 8 + 4 * slot;
+      rec[0] = tl_t0; rec[1] = t1; rec[2] = smid; rec[3] = L.tag | ((long long)blockIdx.x << 32);
+    }
+  }
 }
 
 }  // namespace
@@ -782,10 +978,16 @@ cudaError_t chain_init() {
   return cudaFuncSetAttribute(fql_chain_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
 }
 
-cudaError_t launch_chain(const ChainLaunch& L, int mode, cudaStream_t stream) {
+cudaError_t launch_chain(ChainLaunch& L, int mode, cudaStream_t stream) {
   int grid = 0;
   for (int i = 0; i < L.num_jobs; ++i) grid += L.job[i].m_tiles * L.n_virtual;
   if (grid <= 0) return cudaSuccess;
+  // the staging area (tensors saved for / read by the backward pass) takes the place of weight stages 3 and 4
+  bool staged = mode == 1;
+  for (int i = 0; i < L.num_jobs; ++i)
+    for (int l = 0; l < L.job[i].n_layers; ++l)
+      if (L.job[i].layer[l].out_gp || L.job[i].layer[l].out_xhat) staged = true;
+  L.stages = staged ? kStagesStaged : kStages;
   if (mode == 0) fql_chain_kernel<0><<<grid, kThreads, kSmemBytes, stream>>>(L);
   else fql_chain_kernel<1><<<grid, kThreads, kSmemBytes, stream>>>(L);
   return cudaGetLastError();

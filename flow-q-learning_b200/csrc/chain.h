@@ -77,13 +77,15 @@ struct ChainLaunch {
   int n_virtual;            // active virtual members (grid = sum_jobs m_tiles * n_virtual)
   const int* member_list;   // (dev) [n_virtual] virtual member ids
   int debug_flags;          // (debug) bit 0: no weight TMA / no stage waits (timing of the bare MMA stream; results are garbage)
-  int _pad_dbg;
+  int stages;               // weight stages (set by launch_chain: 5, or 3 when the epilogue stages tensors through smem)
   long long* trace;         // (dev, debug) clock64 stamps of CTA 0: [0,4096) MMA thread, [4096,8192) epilogue thread 0
+  long long* timeline;      // (dev, debug) [0] = record counter; records of 4 words from [8]: start ns, end ns, smid, tag
+  long long tag;            // (debug) launch index within the step | first member of the group << 8 | blockIdx << 32
   ChainJob job[kChainMaxJobs];
 };
 
 // mode 0: forward / Euler, 1: backward. Returns the launch status.
-cudaError_t launch_chain(const ChainLaunch& L, int mode, cudaStream_t stream);
+cudaError_t launch_chain(ChainLaunch& L, int mode, cudaStream_t stream);
 cudaError_t chain_init();
 // Fills tile_begin of every job; returns the grid size.
 int finalize_chain(ChainLaunch* L);

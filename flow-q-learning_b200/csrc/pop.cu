@@ -292,6 +292,8 @@ struct ChainBuilder {
   }
   void launch(int mode, cudaStream_t s) {
     finalize_chain(L);
+    L->timeline = P->timeline;
+    L->tag = (long long)count | ((long long)P->g_off << 8);
     cudaError_t e = launch_chain(*L, mode, s);
     if (e != cudaSuccess && ok) {
       ok = false;
@@ -690,6 +692,7 @@ int pop_create_impl(const PopParams& c, const float* alphas, const unsigned long
   P->use_chain = Lq.in_pad == 64 && Lb.in_pad == 64 && Lp.in_pad == 64 && c.n_hidden_actor + 1 <= kChainMaxLayers &&
                  c.n_hidden_value + 1 <= kChainMaxLayers && getenv("FQLPOP_NO_CHAIN") == nullptr;
   if (getenv("FQLPOP_CHAIN_TRACE")) rc = rc || dev_alloc(P, &P->chain_trace, 8192, err);
+  if (getenv("FQLPOP_TIMELINE")) rc = rc || dev_alloc(P, &P->timeline, 8 + 4 * 65536, err);
   for (BwdBuf* bw : {&P->bQC, &P->bQA, &P->bBC, &P->bPI}) bw->part_rows = bw->m_tiles * (P->use_chain ? 4 : 1);
   const long long PB = (long long)c.P * c.B;
   rc = rc || dev_alloc(P, &P->act_f, PB * c.A, err) || dev_alloc(P, &P->vel, PB * c.A, err) ||

@@ -141,6 +141,7 @@ struct Population {
   Dataset ds;
   NoisePtrs noise;
   Plan* plan = nullptr;
+  long long* timeline = nullptr;     // (dev, debug) FQLPOP_TIMELINE=1: per-CTA start/end stamps of every chain launch
   long long* chain_trace = nullptr;  // (dev, debug) FQLPOP_CHAIN_TRACE=1: clock stamps of the Euler chain's CTA 0
   bool use_chain = false;  // layer-chain kernels (chain.cu) instead of one launch per layer
   RolloutScratch ro;

@@ -99,6 +99,10 @@ int fqlpop_philox_fill(uint64_t seed, uint64_t step, int32_t rows, int32_t slots
 /* Debug: clock64 stamps of CTA 0 of the Euler layer-chain kernel (needs FQLPOP_CHAIN_TRACE=1 at create time):
  * [0,4096) MMA thread (layer start, after each sub-tile's last MMA issue), [4096,8192) first epilogue thread.  */
 int fqlpop_debug_chain_trace(void* handle, long long* host_out, int32_t n);
+/* Debug: per-CTA records of every layer-chain launch since the last call (needs FQLPOP_TIMELINE=1 at create time):
+ * 4 words each -- start ns, end ns (globaltimer), SM id, tag (launch index in the step | first member of the group
+ * << 8 | blockIdx << 32). *n_out = number of records copied; the log is reset.                                    */
+int fqlpop_debug_timeline(void* handle, long long* host_out, int32_t max_records, int32_t* n_out);
 /* Number of kernels one replay of the captured step launches (bench.py's gpu_launches).                   */
 int fqlpop_launches_per_step(void* handle);
 

@@ -1,0 +1,41 @@
+"""Per-CTA timeline of the layer-chain launches of one graph-replayed population step (FQLPOP_TIMELINE=1): for every
+chain launch (tag = launch index within the step) the first start / last end relative to the step's first CTA, the
+CTA count and the mean CTA duration; then SM occupancy by chain CTAs over the step.
+Usage: python profiles/ubench/timeline.py [members] [group_size]"""
+import ctypes, os, sys
+os.environ["FQLPOP_TIMELINE"] = "1"
+if len(sys.argv) > 2:
+    os.environ["FQLPOP_GROUP_SIZE"] = sys.argv[2]
+sys.path.insert(0, "flow-q-learning_b200"); sys.path.insert(0, ".")
+import numpy as np, torch
+from fqlpop.population import Population
+from fqlpop._lib import lib, check
+from bench import synth_dataset
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 16
+pop = Population(dict(ob_dim=28, action_dim=5, batch_size=256), np.logspace(0.5, 3, n), list(range(n)))
+pop.set_dataset(*synth_dataset(1000000, 28, 5, "cuda"))
+lib.fqlpop_debug_timeline.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p]
+buf = np.zeros((65536, 4), np.int64)
+cnt = ctypes.c_int32(0)
+pop.step(20)
+torch.cuda.synchronize()
+check(lib.fqlpop_debug_timeline(pop._h, buf.ctypes.data, 65536, ctypes.byref(cnt)))
+pop.step(1)
+torch.cuda.synchronize()
+check(lib.fqlpop_debug_timeline(pop._h, buf.ctypes.data, 65536, ctypes.byref(cnt)))
+r = buf[:cnt.value]
+t0 = r[:, 0].min()
+names = ["euler", "pi_fwd", "tq_fwd", "qc_fwd", "qc_bwd", "bc_fwd", "bc_bwd", "qa_fwd", "qa_bwd", "pi_bwd"]
+print(f"records {len(r)}  step span {(r[:, 1].max() - t0) / 1e3:.1f} us")
+tag = r[:, 3] & 0xFF
+grp = (r[:, 3] >> 8) & 0xFFFF
+for g in sorted(set(grp)):
+    for k in range(10):
+        m = (tag == k) & (grp == g)
+        if not m.any():
+            continue
+        s, e = r[m, 0], r[m, 1]
+        print(f"group@{g:3d} {names[k]:7s} ctas {m.sum():3d} start {(s.min() - t0) / 1e3:7.1f} .. {(s.max() - t0) / 1e3:7.1f}"
+              f"  end {(e.max() - t0) / 1e3:7.1f}  mean cta {np.mean(e - s) / 1e3:6.1f} us")
+busy = (r[:, 1] - r[:, 0]).sum() / 1e3
+print(f"chain CTA-us total {busy:.0f}; / 148 SMs = {busy / 148:.1f} us; SMs used {len(set(r[:, 2]))}")
