@@ -113,7 +113,20 @@ struct EpiCtx {
   long long wrow;        // element offset of the warp's first row in the pass buffers
   long long wdz;         // ... in the dz buffers
   int rows_valid;        // how many of the warp's 32 rows exist (0 .. 32)
+  long long* tr;         // (debug) stamp log of the traced epilogue thread: tr[0] = count, stamps (clock, id) from tr[2]
 };
+
+// (debug) clock stamp with a site id; only the traced thread has C.tr != nullptr
+__device__ __forceinline__ void stamp(const EpiCtx& C, int id) {
+  if (C.tr) {
+    const long long i = C.tr[0];
+    if (i < 1900) {
+      C.tr[2 + 2 * i] = clock64();
+      C.tr[3 + 2 * i] = id;
+      C.tr[0] = i + 1;
+    }
+  }
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // Staged global traffic. A "block" is 32 rows x 64 bf16 columns = 32 x 128 bytes in shared memory, 16-byte chunk c
@@ -409,18 +422,27 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
   float s1 = 0.f, s2 = 0.f;
   if (!LN) {
     wait_tile(C, fullph, 0);
+    stamp(C, 10);
     if (n_tiles == 1) {
       fwd_pass1<false, SAVE>(C, Ly, 0, true, s1, s2);
+      stamp(C, 11);
       release(C.act_lo);
+      stamp(C, 12);
     } else {
       fwd_pass1<false, SAVE>(C, Ly, 0, false, s1, s2);
+      stamp(C, 13);
       tmem_st_wait();
+      stamp(C, 14);
       wait_tile(C, fullph, 1);  // every MMA of the layer has retired: ACT may be overwritten
       fwd_flush<false, SAVE>(C, Ly, 0, 0.f, 1.f);
+      stamp(C, 15);
       release(C.act_lo);
+      stamp(C, 16);
       fwd_pass1<false, SAVE>(C, Ly, 1, true, s1, s2);
+      stamp(C, 17);
     }
     release(C.act_hi);
+    stamp(C, 18);
     // h -> HBM out of ACT, off the hand-off path: these rows of ACT are next written by this very warp
     if (Ly.out_h) {
       __syncwarp();
@@ -428,14 +450,20 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
     }
   } else {
     wait_tile(C, fullph, 0);
+    stamp(C, 19);
     fwd_pass1<true, SAVE>(C, Ly, 0, false, s1, s2);
+    stamp(C, 20);
     if (n_tiles > 1) {
       wait_tile(C, fullph, 1);
+      stamp(C, 21);
       fwd_pass1<true, SAVE>(C, Ly, 1, false, s1, s2);
+      stamp(C, 22);
     }
     tmem_st_wait();
+    stamp(C, 23);
     float t1 = s1, t2 = s2;
     exchange_row_sums(C, t1, t2);
+    stamp(C, 24);
     const float inv_n = 1.0f / (float)C.H;
     const float mean = t1 * inv_n;
     const float var = fmaxf(t2 * inv_n - mean * mean, 0.f);  // flax LayerNorm: E[x^2] - E[x]^2
@@ -444,13 +472,17 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
     // LayerNorm layers copy h out BEFORE the hand-off: the next layer's row-sum exchange reuses the head of ACT and
     // must not overtake a slower warp's copy
     fwd_flush<true, SAVE>(C, Ly, 0, mean, rstd);
+    stamp(C, 25);
     if (Ly.out_h) { __syncwarp(); copy_out_act(C, 0, Ly.n_pad, Ly.out_h, C.wrow, nullptr); }
     release(C.act_lo);
+    stamp(C, 26);
     if (n_tiles > 1) {
       fwd_flush<true, SAVE>(C, Ly, 1, mean, rstd);
+      stamp(C, 27);
       if (Ly.out_h) { __syncwarp(); copy_out_act(C, 1, Ly.n_pad, Ly.out_h, C.wrow, nullptr); }
     }
     release(C.act_hi);
+    stamp(C, 28);
   }
 }
 
@@ -640,18 +672,28 @@ __device__ __forceinline__ void bwd_hidden_layer(const EpiCtx& C, uint32_t& full
   if (!LN) {
     bwd_prefetch_gp(C, Ly, 0, 0);
     wait_tile(C, fullph, 0);
+    stamp(C, 10);
     if (n_tiles == 1) {
       bwd_pass1(C, Ly, 0, true, -1);
+      stamp(C, 11);
       release(C.act_lo);
+      stamp(C, 12);
     } else {
       bwd_pass1(C, Ly, 0, false, 1);
+      stamp(C, 13);
       tmem_st_wait();
+      stamp(C, 14);
       wait_tile(C, fullph, 1);
+      stamp(C, 15);
       bwd_flush(C, Ly, 0);
+      stamp(C, 16);
       release(C.act_lo);
+      stamp(C, 17);
       bwd_pass1(C, Ly, 1, true, -1);
+      stamp(C, 18);
     }
     release(C.act_hi);
+    stamp(C, 19);
     // dz -> HBM (+ bias-gradient partial sums) out of ACT, off the hand-off path
     __syncwarp();
     for (int t = 0; t < n_tiles; ++t) copy_out_act(C, t, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
@@ -659,26 +701,35 @@ __device__ __forceinline__ void bwd_hidden_layer(const EpiCtx& C, uint32_t& full
     float s1 = 0.f, s2 = 0.f;
     ln_prefetch(C, Ly.xhat, Ly.n_pad, 0, 0, 0);
     wait_tile(C, fullph, 0);
+    stamp(C, 20);
     bwd_ln_stats(C, Ly, 0, n_tiles > 1 ? 1 : -1, s1, s2);
+    stamp(C, 21);
     if (n_tiles > 1) {
       wait_tile(C, fullph, 1);
+      stamp(C, 22);
       bwd_ln_stats(C, Ly, 1, -1, s1, s2);
+      stamp(C, 23);
     }
     float t1 = s1, t2 = s2;
     exchange_row_sums(C, t1, t2);
+    stamp(C, 24);
     const float inv_n = 1.0f / (float)C.H;
     const float rstd = C.row_ok ? __ldg(Ly.rstd + C.rs_off) : 0.f;
     // copies happen before the hand-off (see fwd_hidden_layer)
     bwd_ln_out(C, Ly, 0, t1 * inv_n, t2 * inv_n, rstd);
+    stamp(C, 25);
     __syncwarp();
     copy_out_act(C, 0, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
     release(C.act_lo);
+    stamp(C, 26);
     if (n_tiles > 1) {
       bwd_ln_out(C, Ly, 1, t1 * inv_n, t2 * inv_n, rstd);
+      stamp(C, 27);
       __syncwarp();
       copy_out_act(C, 1, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
     }
     release(C.act_hi);
+    stamp(C, 28);
   }
 }
 
@@ -853,9 +904,10 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
     C.wrow = (long long)v * J.pass_ms + (long long)grow0 * J.H;
     C.wdz = (long long)v * J.dz_ms + (long long)grow0 * J.H;
     C.rows_valid = min(32, max(0, J.M - grow0));
-    uint32_t fullph = 0;
-    int etr = 0;
     const bool traced = L.trace && blockIdx.x == 0 && threadIdx.x == 64;
+    C.tr = traced ? L.trace + 4096 : nullptr;
+    if (traced) L.trace[4096] = 0;
+    uint32_t fullph = 0;
 
     float xs[8];  // Euler flow: the action iterate of this row (fp32)
     if (MODE == 0 && J.xe) {
@@ -935,7 +987,7 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
           release(act_lo);
           release(act_hi);
         }
-        if (traced && etr < 4000) L.trace[4096 + etr++] = clock64();
+        stamp(C, 99);
       }
     }
   }

@@ -16,8 +16,8 @@ namespace fqlpop {
 namespace {
 
 constexpr int kHeadThreads = 256;
-constexpr int kRowsPerWarp = 8;
-constexpr int kRowsPerBlock = (kHeadThreads / 32) * kRowsPerWarp;  // 64
+constexpr int kRowsPerWarp = 2;  // short serial chains: the heads sit on the step's critical path between two layer-chain launches
+constexpr int kRowsPerBlock = (kHeadThreads / 32) * kRowsPerWarp;  // 16
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -31,7 +31,7 @@ namespace fqlpop {
 // Euler steps -- overlaps the other groups' wide passes instead of leaving the SMs idle behind a step barrier.
 struct GroupPlan {
   int off = 0, n = 0;
-  cudaStream_t s[3] = {nullptr, nullptr, nullptr};
+  cudaStream_t s[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
   cudaGraph_t g_step = nullptr, g_loss = nullptr;
   cudaGraphExec_t x_step = nullptr, x_loss = nullptr;
   cudaEvent_t done = nullptr;
@@ -294,6 +294,10 @@ struct ChainBuilder {
     finalize_chain(L);
     L->timeline = P->timeline;
     L->tag = (long long)count | ((long long)P->g_off << 8);
+    {  // (debug) FQLPOP_CHAIN_TRACE=1: clock stamps of CTA 0 of chain launch FQLPOP_TRACE_LAUNCH (default 0 = Euler)
+      const char* tl = getenv("FQLPOP_TRACE_LAUNCH");
+      L->trace = (P->chain_trace && count == (tl ? atoi(tl) : 0) && P->g_off == 0) ? P->chain_trace : nullptr;
+    }
     cudaError_t e = launch_chain(*L, mode, s);
     if (e != cudaSuccess && ok) {
       ok = false;
@@ -409,7 +413,7 @@ void record(Plan* pl, cudaEvent_t* out, cudaStream_t s) {
 // streams. Called under stream capture; s[0] is the origin stream.
 int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   Plan* pl = P->plan;
-  cudaStream_t s0 = gp.s[0], s1 = gp.s[1], s2 = gp.s[2];
+  cudaStream_t s0 = gp.s[0], s1 = gp.s[1], s2 = gp.s[2], s3 = gp.s[3], s4 = gp.s[4];
   const PopParams& c = P->c;
   Builder b{P, err};
   b.L = new GemmLaunch;
@@ -418,11 +422,12 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   const int nsub_q = P->critic.L.ln ? 4 : 1, nsub_a = P->pi.L.ln ? 4 : 1;
   const int nh_q = P->critic.L.n_hidden, nh_a = P->pi.L.n_hidden;
 
-  cudaEvent_t e_prep, e_pi, e_qa, e_euler, e_s1, e_s2;
+  cudaEvent_t e_prep, e_pi, e_qa, e_euler, e_s1, e_s2, e_qcf;
   launch_prep(P, s0, train ? 1 : 0); ++pw;
   record(pl, &e_prep, s0);
   cudaStreamWaitEvent(s1, e_prep, 0);
   cudaStreamWaitEvent(s2, e_prep, 0);
+  cudaStreamWaitEvent(s3, e_prep, 0);
 
   ChainBuilder cb{P, err};
   cb.L = new ChainLaunch;
@@ -470,7 +475,6 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   if (chain) {
     cb.begin(1);
     cb.euler_job();
-    cb.L->trace = P->chain_trace;
     if (const char* e = getenv("FQLPOP_CHAIN_DEBUG")) cb.L->debug_flags = atoi(e);
     cb.launch(0, s0);
   } else {
@@ -491,7 +495,11 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   record(pl, &e_pi, s1);
   fwd_pass(P->TQ, P->critic, P->critic.target, P->critic.tshadow, nsub_q, B, false, 0, s1);
   launch_tq_head(P, s1); ++pw;
-  fwd_pass(P->QC, P->critic, P->critic.theta, P->critic.shadow, nsub_q, B, train, 0, s1);
+  // (the critic's own forward pass needs nothing from the policy / target passes: it runs beside them on s3 and
+  // joins s1 at the loss head)
+  fwd_pass(P->QC, P->critic, P->critic.theta, P->critic.shadow, nsub_q, B, train, 0, s3);
+  record(pl, &e_qcf, s3);
+  cudaStreamWaitEvent(s1, e_qcf, 0);
   launch_qc_head(P, s1); ++pw;
   if (train) {
     bwd_pass(P->QC, P->bQC, P->critic, nsub_q, true, nullptr, s1);
@@ -509,11 +517,12 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
     for (int l = 0; l <= nh_a; ++l) b.wgrad_group(P->BC, P->bBC, P->bc, l, 0);
     b.launch(1, s2);
   }
-  cudaStreamWaitEvent(s2, e_pi, 0);
-  fwd_pass(P->QA, P->critic, P->critic.theta, P->critic.shadow, nsub_q, B, train, 0, s2);
-  launch_qa_head(P, s2); ++pw;
-  if (train) bwd_pass(P->QA, P->bQA, P->critic, nsub_q, false, P->dx0_qa, s2);
-  record(pl, &e_qa, s2);
+  // critic pass on (s, clip(a_pi)): its own stream, as soon as the policy head is out
+  cudaStreamWaitEvent(s4, e_pi, 0);
+  fwd_pass(P->QA, P->critic, P->critic.theta, P->critic.shadow, nsub_q, B, train, 0, s4);
+  launch_qa_head(P, s4); ++pw;
+  if (train) bwd_pass(P->QA, P->bQA, P->critic, nsub_q, false, P->dx0_qa, s4);
+  record(pl, &e_qa, s4);
 
   // ---- s0: distillation + policy backward -------------------------------------------------------
   cudaStreamWaitEvent(s0, e_qa, 0);
@@ -564,7 +573,7 @@ void destroy_graphs(Plan* pl) {
 void destroy_groups(Plan* pl) {
   destroy_graphs(pl);
   for (GroupPlan& g : pl->groups) {
-    for (int i = 0; i < 3; ++i)
+    for (int i = 0; i < 5; ++i)
       if (g.s[i]) cudaStreamDestroy(g.s[i]);
     if (g.done) cudaEventDestroy(g.done);
   }
@@ -586,7 +595,7 @@ int make_groups(Population* P, std::string* err) {
     // spread the remainder so group sizes differ by at most one
     gp.off = (int)((long long)n * g / G);
     gp.n = (int)((long long)n * (g + 1) / G) - gp.off;
-    for (int i = 0; i < 3; ++i) CK(cudaStreamCreateWithFlags(&gp.s[i], cudaStreamNonBlocking));
+    for (int i = 0; i < 5; ++i) CK(cudaStreamCreateWithFlags(&gp.s[i], cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&gp.done, cudaEventDisableTiming));
   }
   return 0;
