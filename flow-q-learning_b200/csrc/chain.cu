@@ -37,6 +37,7 @@ namespace fqlpop {
 namespace {
 
 constexpr int kThreads = 320;
+constexpr int kThreads2 = 352;  // cluster kernel: + one warp that forwards finished ACT blocks to the peer CTA
 constexpr int kStages = 5;          // weight stages of a launch without saved tensors (Euler chain, target critic)
 constexpr int kStagesStaged = 3;    // ... of a launch whose epilogue stages tensors through shared memory
 constexpr int kStagingBytes = 4096; // per epilogue warp: 32 rows x 128 bytes (overlays weight stages 3 and 4)
@@ -46,7 +47,7 @@ constexpr int kStageBytes = 16384;             // 32 k x 256 n bf16
 constexpr int kStageK = 32;
 constexpr int kTileN = 256;
 constexpr int kFwdBoxBytes = 64 * kStageK * 2;  // forward weight box: 64 n x 32 k (MN-major, 128-byte swizzle)
-constexpr int kBarBytes = 256;
+constexpr int kBarBytes = 256 + 1024;  // mbarriers + the cluster kernel's cross-CTA row-sum buffer (128 x float2)
 constexpr int kSmemBytes = kActBytes + kActBlockBytes + kStages * kStageBytes + kBarBytes + 1024;
 
 __device__ __forceinline__ float clip1(float x) { return fminf(fmaxf(x, -1.f), 1.f); }
@@ -113,6 +114,13 @@ struct EpiCtx {
   long long wrow;        // element offset of the warp's first row in the pass buffers
   long long wdz;         // ... in the dz buffers
   int rows_valid;        // how many of the warp's 32 rows exist (0 .. 32)
+  // 2-CTA cluster variant (chain2): this CTA owns output columns [g_off, g_off + 256) of every hidden layer and
+  // alternates between two 256-column accumulators (tm_off = 0 / 256); the single-CTA kernel keeps both at 0
+  int tm_off, g_off;
+  bool cl;               // cluster variant: publish every finished 64-column block of ACT (local barrier + copy to the peer)
+  bool publish;          // ... unless nobody consumes this layer's output on chip
+  uint64_t* blk_full;    // [8] local barriers: k-block j of ACT holds the next layer's A operand
+  uint32_t peer_act, peer_blk_full;  // shared::cluster addresses of the peer's ACT / blk_full[0]
   long long* tr;         // (debug) stamp log of the traced epilogue thread: tr[0] = count, stamps (clock, id) from tr[2]
 };
 
@@ -287,6 +295,8 @@ __device__ __forceinline__ void store_colsum16(float* part, const EpiCtx& C, int
   if (C.lane < 16) part[C.part_off + col + C.lane] = cs;
 }
 
+__device__ __forceinline__ void publish_block(const EpiCtx& C, int gblk);
+
 // This warp's part of accumulator tile `tile` (its 32 rows x its 128 columns = two 64-column blocks of ACT) -> global
 // rows of `dst` ([rows][H] bf16, already offset to the job's row 0 of virtual member 0), optionally with the per-column
 // sums over the warp's rows -> part[part_off + column].
@@ -295,7 +305,7 @@ __device__ __forceinline__ void copy_out_act(const EpiCtx& C, int tile, int n_pa
   const int nblk = tile_chunks16(C, tile, n_pad) >> 2;
   const int col0 = tile * kTileN + C.half * 128;
   for (int b = 0; b < nblk; ++b) {
-    const int col = col0 + b * 64;
+    const int col = C.g_off + col0 + b * 64;
     const uint8_t* blk = C.act + (col >> 6) * kActBlockBytes + C.q * (32 * 128);
     if (part) copy_out_block_colsum(blk, dst + wofs + col, C.H, C.lane, C.rows_valid, part + C.part_off + col);
     else copy_out_block(blk, dst + wofs + col, C.H, C.lane, C.rows_valid);
@@ -309,51 +319,63 @@ __device__ __forceinline__ void copy_out_act(const EpiCtx& C, int tile, int n_pa
 // copied out per 64-column block); the bf16 result is parked in the drained TMEM columns or -- `direct` -- written
 // to ACT (the caller copies h out of ACT once the layer has been handed to the tensor core).
 template <bool LN, bool SAVE>
+__device__ __forceinline__ void fwd_chunk(const EpiCtx& C, const float* bias, const uint32_t (&rr)[16], int col0, int c,
+                                          bool direct, float& s1, float& s2) {
+  const int col = col0 + c * 16;
+  float4 b4[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) b4[i] = __ldg(reinterpret_cast<const float4*>(bias + col) + i);
+  uint32_t pk[8], gpk[8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float g0, g1, g2, g3, p0, p1, p2, p3;
+    gelu1<SAVE>(__uint_as_float(rr[4 * i + 0]) + b4[i].x, g0, p0);
+    gelu1<SAVE>(__uint_as_float(rr[4 * i + 1]) + b4[i].y, g1, p1);
+    gelu1<SAVE>(__uint_as_float(rr[4 * i + 2]) + b4[i].z, g2, p2);
+    gelu1<SAVE>(__uint_as_float(rr[4 * i + 3]) + b4[i].w, g3, p3);
+    if (LN) {
+      s1 += (g0 + g1) + (g2 + g3);
+      s2 = fmaf(g0, g0, fmaf(g1, g1, fmaf(g2, g2, fmaf(g3, g3, s2))));
+    }
+    pk[2 * i] = pack_bf16x2(g0, g1);
+    pk[2 * i + 1] = pack_bf16x2(g2, g3);
+    if (SAVE) {
+      gpk[2 * i] = pack_bf16x2(p0, p1);
+      gpk[2 * i + 1] = pack_bf16x2(p2, p3);
+    }
+  }
+  if (SAVE) st_stage16(C.stg, C.lane, (c & 3) * 16, gpk);
+  if (direct) st_act16(C.act, C.r, C.g_off + col, pk);
+  else tmem_st8(C.tmem_row + C.tm_off + col0 + c * 8, pk);
+}
+// The accumulator chunks are double-buffered in registers: the TMEM load of chunk c + 1 is in flight while chunk c is
+// being computed (tcgen05.wait::ld waits for every outstanding load, so the next one is issued right after the wait).
+template <bool LN, bool SAVE>
 __device__ __forceinline__ void fwd_pass1(const EpiCtx& C, const ChainLayer& Ly, int tile, bool direct, float& s1, float& s2) {
-  const int nch = tile_chunks16(C, tile, Ly.n_pad);
+  const int nch = tile_chunks16(C, tile, Ly.n_pad);  // a multiple of 4
   if (nch == 0) return;
   const int col0 = tile * kTileN + C.half * 128;
-  const float* bias = C.params + Ly.off_b;
-  uint32_t rr[16];
+  const float* bias = C.params + Ly.off_b + C.g_off;
+  const uint32_t tbase = C.tmem_row + C.tm_off + col0;
+  uint32_t ra[16], rb[16];
+  tmem_ld16(tbase, ra);
 #pragma unroll 1
   for (int cb = 0; cb < nch; cb += 4) {
 #pragma unroll 1
-    for (int c4 = 0; c4 < 4; ++c4) {
-      const int c = cb + c4;
-      const int col = col0 + c * 16;
-      float4 b4[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) b4[i] = __ldg(reinterpret_cast<const float4*>(bias + col) + i);
-      tmem_ld16(C.tmem_row + col, rr);
+    for (int c = cb; c < cb + 4; c += 2) {
       tmem_ld_wait();
-      uint32_t pk[8], gpk[8];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        float g0, g1, g2, g3, p0, p1, p2, p3;
-        gelu1<SAVE>(__uint_as_float(rr[4 * i + 0]) + b4[i].x, g0, p0);
-        gelu1<SAVE>(__uint_as_float(rr[4 * i + 1]) + b4[i].y, g1, p1);
-        gelu1<SAVE>(__uint_as_float(rr[4 * i + 2]) + b4[i].z, g2, p2);
-        gelu1<SAVE>(__uint_as_float(rr[4 * i + 3]) + b4[i].w, g3, p3);
-        if (LN) {
-          s1 += (g0 + g1) + (g2 + g3);
-          s2 = fmaf(g0, g0, fmaf(g1, g1, fmaf(g2, g2, fmaf(g3, g3, s2))));
-        }
-        pk[2 * i] = pack_bf16x2(g0, g1);
-        pk[2 * i + 1] = pack_bf16x2(g2, g3);
-        if (SAVE) {
-          gpk[2 * i] = pack_bf16x2(p0, p1);
-          gpk[2 * i + 1] = pack_bf16x2(p2, p3);
-        }
-      }
-      if (SAVE) st_stage16(C.stg, C.lane, c4 * 16, gpk);
-      if (direct) st_act16(C.act, C.r, col, pk);
-      else tmem_st8(C.tmem_row + col0 + c * 8, pk);
+      tmem_ld16(tbase + (c + 1) * 16, rb);
+      fwd_chunk<LN, SAVE>(C, bias, ra, col0, c, direct, s1, s2);
+      tmem_ld_wait();
+      if (c + 2 < nch) tmem_ld16(tbase + (c + 2) * 16, ra);
+      fwd_chunk<LN, SAVE>(C, bias, rb, col0, c + 1, direct, s1, s2);
     }
     if (SAVE) {
       __syncwarp();
-      copy_out_block(C.stg, Ly.out_gp + C.wrow + col0 + cb * 16, C.H, C.lane, C.rows_valid);
+      copy_out_block(C.stg, Ly.out_gp + C.wrow + C.g_off + col0 + cb * 16, C.H, C.lane, C.rows_valid);
       __syncwarp();
     }
+    if (direct && C.cl) publish_block(C, (C.g_off + col0 + cb * 16) >> 6);
   }
 }
 
@@ -373,11 +395,11 @@ __device__ __forceinline__ void fwd_flush(const EpiCtx& C, const ChainLayer& Ly,
     for (int c4 = 0; c4 < 4; ++c4) {
       const int c = cb + c4;
       const int col = col0 + c * 16;
-      tmem_ld8(C.tmem_row + col0 + c * 8, pr);
+      tmem_ld8(C.tmem_row + C.tm_off + col0 + c * 8, pr);
       tmem_ld_wait();
       if (LN) {
-        const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + col);
-        const float4* e4 = reinterpret_cast<const float4*>(C.params + Ly.off_beta + col);
+        const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + C.g_off + col);
+        const float4* e4 = reinterpret_cast<const float4*>(C.params + Ly.off_beta + C.g_off + col);
         uint32_t hk[8], xk[8];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -390,17 +412,18 @@ __device__ __forceinline__ void fwd_flush(const EpiCtx& C, const ChainLayer& Ly,
           hk[2 * i] = pack_bf16x2(fmaf(x0, ga.x, be.x), fmaf(x1, ga.y, be.y));
           hk[2 * i + 1] = pack_bf16x2(fmaf(x2, ga.z, be.z), fmaf(x3, ga.w, be.w));
         }
-        st_act16(C.act, C.r, col, hk);
+        st_act16(C.act, C.r, C.g_off + col, hk);
         if (save_x) st_stage16(C.stg, C.lane, c4 * 16, xk);
       } else {
-        st_act16(C.act, C.r, col, pr);
+        st_act16(C.act, C.r, C.g_off + col, pr);
       }
     }
     if (save_x) {
       __syncwarp();
-      copy_out_block(C.stg, Ly.out_xhat + C.wrow + col0 + cb * 16, C.H, C.lane, C.rows_valid);
+      copy_out_block(C.stg, Ly.out_xhat + C.wrow + C.g_off + col0 + cb * 16, C.H, C.lane, C.rows_valid);
       __syncwarp();
     }
+    if (C.cl) publish_block(C, (C.g_off + col0 + cb * 16) >> 6);
   }
 }
 
@@ -493,7 +516,7 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
 __device__ __forceinline__ void bwd_prefetch_gp(const EpiCtx& C, const ChainLayer& Ly, int tile, int blk) {
   if (!Ly.gp) return;
   if (blk * 4 >= tile_chunks16(C, tile, Ly.n_pad)) return;
-  stage_in_block(C.stg, Ly.gp + C.wrow + tile * kTileN + C.half * 128 + blk * 64, C.H, C.lane, C.rows_valid);
+  stage_in_block(C.stg, Ly.gp + C.wrow + C.g_off + tile * kTileN + C.half * 128 + blk * 64, C.H, C.lane, C.rows_valid);
 }
 
 // no LayerNorm: one pass, parked or direct exactly like the forward layer. The first block of act'(z) has been
@@ -520,21 +543,22 @@ __device__ __forceinline__ void bwd_pass1(const EpiCtx& C, const ChainLayer& Ly,
 #pragma unroll
         for (int i = 0; i < 8; ++i) gw[i] = C.row_ok ? 0x3F803F80u : 0u;  // bf16 (1, 1) / (0, 0)
       }
-      tmem_ld16(C.tmem_row + col, rr);
+      tmem_ld16(C.tmem_row + C.tm_off + col, rr);
       tmem_ld_wait();
       uint32_t pk[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i)
         pk[i] = pack_bf16x2(__uint_as_float(rr[2 * i]) * bf16_lo(gw[i]),
                             __uint_as_float(rr[2 * i + 1]) * bf16_hi(gw[i]));
-      if (direct) st_act16(C.act, C.r, col, pk);
-      else tmem_st8(C.tmem_row + col0 + c * 8, pk);
+      if (direct) st_act16(C.act, C.r, C.g_off + col, pk);
+      else tmem_st8(C.tmem_row + C.tm_off + col0 + c * 8, pk);
     }
     if (has_gp) {
       __syncwarp();
       if (cb + 4 < nch) bwd_prefetch_gp(C, Ly, tile, (cb >> 2) + 1);
       else if (next_tile >= 0) bwd_prefetch_gp(C, Ly, next_tile, 0);
     }
+    if (direct && C.cl) publish_block(C, (C.g_off + col0 + cb * 16) >> 6);
   }
 }
 __device__ __forceinline__ void bwd_flush(const EpiCtx& C, const ChainLayer& Ly, int tile) {
@@ -545,10 +569,10 @@ __device__ __forceinline__ void bwd_flush(const EpiCtx& C, const ChainLayer& Ly,
   for (int cp = 0; cp < nch; cp += 4) {
     uint32_t pr[4][8];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) tmem_ld8(C.tmem_row + col0 + (cp + j) * 8, pr[j]);
+    for (int j = 0; j < 4; ++j) tmem_ld8(C.tmem_row + C.tm_off + col0 + (cp + j) * 8, pr[j]);
     tmem_ld_wait();
 #pragma unroll
-    for (int j = 0; j < 4; ++j) st_act16(C.act, C.r, col0 + (cp + j) * 16, pr[j]);
+    for (int j = 0; j < 4; ++j) st_act16(C.act, C.r, C.g_off + col0 + (cp + j) * 16, pr[j]);
   }
 }
 
@@ -556,7 +580,7 @@ __device__ __forceinline__ void bwd_flush(const EpiCtx& C, const ChainLayer& Ly,
 // sub-block `sb` (0 .. 3 within the tile's 128 columns of this warp) of a saved tensor -> staging slot `slot`
 __device__ __forceinline__ void ln_prefetch(const EpiCtx& C, const __nv_bfloat16* src, int n_pad, int tile, int sb, int slot) {
   if (sb * 2 >= tile_chunks16(C, tile, n_pad)) return;
-  stage_in_half(C.stg + slot * 2048, src + C.wrow + tile * kTileN + C.half * 128 + sb * 32, C.H, C.lane, C.rows_valid);
+  stage_in_half(C.stg + slot * 2048, src + C.wrow + C.g_off + tile * kTileN + C.half * 128 + sb * 32, C.H, C.lane, C.rows_valid);
 }
 
 // LayerNorm, statistics pass (overlaps the MMAs of the other tile; the accumulator stays in TMEM untouched):
@@ -581,8 +605,8 @@ __device__ __forceinline__ void bwd_ln_stats(const EpiCtx& C, const ChainLayer& 
       const int col = col0 + sb * 32 + ch * 16;
       uint32_t xw[8];
       ld_half16(slot, C.lane, ch * 16, xw);
-      const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + col);
-      tmem_ld16(C.tmem_row + col, rr);
+      const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + C.g_off + col);
+      tmem_ld16(C.tmem_row + C.tm_off + col, rr);
       tmem_ld_wait();
       float t0[16], t1[16];
 #pragma unroll
@@ -607,8 +631,8 @@ __device__ __forceinline__ void bwd_ln_stats(const EpiCtx& C, const ChainLayer& 
         const float cb = warp_colsum16(t0, C.lane);
         const float cg = warp_colsum16(t1, C.lane);
         if (C.lane < 16) {
-          Ly.dbeta_part[C.part_off + col + C.lane] = cb;
-          Ly.dgamma_part[C.part_off + col + C.lane] = cg;
+          Ly.dbeta_part[C.part_off + C.g_off + col + C.lane] = cb;
+          Ly.dgamma_part[C.part_off + C.g_off + col + C.lane] = cg;
         }
       }
     }
@@ -641,8 +665,8 @@ __device__ __forceinline__ void bwd_ln_out(const EpiCtx& C, const ChainLayer& Ly
 #pragma unroll
         for (int i = 0; i < 8; ++i) gw[i] = C.row_ok ? 0x3F803F80u : 0u;
       }
-      const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + col);
-      tmem_ld16(C.tmem_row + col, rr);
+      const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + C.g_off + col);
+      tmem_ld16(C.tmem_row + C.tm_off + col, rr);
       tmem_ld_wait();
       uint32_t pk[8];
 #pragma unroll
@@ -661,8 +685,9 @@ __device__ __forceinline__ void bwd_ln_out(const EpiCtx& C, const ChainLayer& Ly
         pk[2 * i] = pack_bf16x2(dz[0], dz[1]);
         pk[2 * i + 1] = pack_bf16x2(dz[2], dz[3]);
       }
-      st_act16(C.act, C.r, col, pk);
+      st_act16(C.act, C.r, C.g_off + col, pk);
     }
+    if (C.cl && (sb & 1)) publish_block(C, (C.g_off + col0 + sb * 32) >> 6);
   }
 }
 
@@ -730,6 +755,447 @@ __device__ __forceinline__ void bwd_hidden_layer(const EpiCtx& C, uint32_t& full
     }
     release(C.act_hi);
     stamp(C, 28);
+  }
+}
+
+// ===============================================================================================================
+// chain2: the same layer chains on a CLUSTER OF TWO CTAs per 128-row tile. Every hidden layer's 512 output columns are
+// split: CTA `rank` computes columns [256 rank, 256 rank + 256) -- one 128 x 256 accumulator, double-buffered in TMEM
+// (layer parity), so the next layer's MMAs never wait for the epilogue to drain it. The epilogue writes finished
+// 64-column blocks straight into ACT (no parking, no flush pass), publishes each block to the local tensor core
+// (mbarrier) and copies it into the peer's ACT (cp.async.bulk shared::cta -> shared::cluster, completion counted on
+// the PEER's block barrier), and the next layer's MMAs start on whichever K blocks have landed. Per-layer latency:
+// max(MMA of 128 x 256 x 512, epilogue of 128 columns per thread) instead of their sum over 512 columns; two SMs'
+// fp32 pipes work on every row tile. Layers narrower than 257 columns (Euler head, input gradient) are computed by
+// both CTAs redundantly (each patches its own copy of the layer-0 operand; rank 0 stores).
+//
+// Cross-CTA ordering: peer_done = "the peer's MMAs of this layer have retired" (remote arrive once per layer): nobody
+// writes into the other CTA's ACT -- nor rewrites a block of its own ACT that an outgoing copy may still be reading
+// -- before that. LayerNorm row statistics cross the cluster through st.shared::cluster + a remote mbarrier.
+// ===============================================================================================================
+struct Cl2 {
+  uint64_t *tmem_full, *peer_done, *layer_ready, *ln_x;
+  uint32_t peer_peer_done, peer_ln_x, peer_ex2;  // shared::cluster addresses in the peer CTA
+  const float2* ex2;                             // [128] row sums written by the peer
+  bool ln;
+};
+
+__device__ __forceinline__ void publish_block(const EpiCtx& C, int gblk) {
+  if (!C.publish) return;
+  // this thread has written its row of the block (generic proxy) and is done with the accumulator columns behind
+  // it; the block barrier completes when all 128 threads of the half-group have arrived. The local tensor core and
+  // the copy warp (which forwards the block to the peer) both wait on it.
+  tc_fence_before();
+  fence_proxy_async_smem();
+  mbar_arrive(&C.blk_full[gblk]);
+}
+
+// wait for this layer's accumulator, tell the peer our ACT is free, wait until the peer's is
+__device__ __forceinline__ void c2_begin_layer(EpiCtx& C, const Cl2& X, int lc) {
+  const int p = lc & 1;
+  mbar_wait(&X.tmem_full[p], (lc >> 1) & 1);
+  tc_fence_after();
+  // LayerNorm chains reuse the head of ACT for the row-sum exchange: every warp must be done copying the previous
+  // layer out of ACT before the peer may write there
+  if (X.ln) epi_bar_sync();
+  if (threadIdx.x == 64) mbar_arrive_cluster(X.peer_peer_done);
+  mbar_wait_cluster(X.peer_done, lc & 1);
+  C.tm_off = p * 256;
+}
+
+// row sums over all 512 columns: the other half-group through the head of ACT, the other CTA through its ex2 area
+__device__ __forceinline__ void exchange_row_sums2(const EpiCtx& C, const Cl2& X, int lnc, float& t1, float& t2) {
+  float2* ex = reinterpret_cast<float2*>(C.act);
+  const float2* ex2 = X.ex2;
+  ex[C.half * 128 + C.r] = make_float2(t1, t2);
+  epi_bar_sync();
+  const float2 o = ex[(C.half ^ 1) * 128 + C.r];
+  t1 += o.x;
+  t2 += o.y;
+  if (C.half == 0) {
+    st_cluster_f32x2(X.peer_ex2 + C.r * 8, t1, t2);
+    mbar_arrive_cluster_release(X.peer_ln_x);
+  }
+  mbar_wait_cluster(X.ln_x, lnc & 1);
+  const float2 w = ex2[C.r];
+  t1 += w.x;
+  t2 += w.y;
+  epi_bar_sync();  // the exchange area has been read: ACT may be rewritten
+}
+
+template <bool LN, bool SAVE>
+__device__ __forceinline__ void fwd2_hidden_layer(EpiCtx& C, const Cl2& X, const ChainLayer& Ly, int lc, int lnc) {
+  c2_begin_layer(C, X, lc);
+  stamp(C, 40);
+  float s1 = 0.f, s2 = 0.f;
+  if (!LN) {
+    fwd_pass1<false, SAVE>(C, Ly, 0, true, s1, s2);
+  } else {
+    fwd_pass1<true, SAVE>(C, Ly, 0, false, s1, s2);
+    tmem_st_wait();
+    float t1 = s1, t2 = s2;
+    exchange_row_sums2(C, X, lnc, t1, t2);
+    const float inv_n = 1.0f / (float)C.H;
+    const float mean = t1 * inv_n;
+    const float var = fmaxf(t2 * inv_n - mean * mean, 0.f);
+    const float rstd = rsqrtf(var + C.ln_eps);
+    if (C.row_ok && C.half == 0 && C.g_off == 0 && Ly.out_rstd) Ly.out_rstd[C.rs_off] = rstd;
+    fwd_flush<true, SAVE>(C, Ly, 0, mean, rstd);
+  }
+  stamp(C, 41);
+  if (Ly.out_h) {
+    __syncwarp();
+    copy_out_act(C, 0, Ly.n_pad, Ly.out_h, C.wrow, nullptr);
+  }
+  stamp(C, 42);
+}
+
+template <bool LN>
+__device__ __forceinline__ void bwd2_hidden_layer(EpiCtx& C, const Cl2& X, const ChainLayer& Ly, int lc, int lnc) {
+  if (!LN) bwd_prefetch_gp(C, Ly, 0, 0);
+  else ln_prefetch(C, Ly.xhat, Ly.n_pad, 0, 0, 0);
+  c2_begin_layer(C, X, lc);
+  stamp(C, 50);
+  if (!LN) {
+    bwd_pass1(C, Ly, 0, true, -1);
+  } else {
+    float s1 = 0.f, s2 = 0.f;
+    bwd_ln_stats(C, Ly, 0, -1, s1, s2);
+    float t1 = s1, t2 = s2;
+    exchange_row_sums2(C, X, lnc, t1, t2);
+    const float inv_n = 1.0f / (float)C.H;
+    const float rstd = C.row_ok ? __ldg(Ly.rstd + C.rs_off) : 0.f;
+    bwd_ln_out(C, Ly, 0, t1 * inv_n, t2 * inv_n, rstd);
+  }
+  stamp(C, 51);
+  __syncwarp();
+  copy_out_act(C, 0, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
+  stamp(C, 52);
+}
+
+// K-block order of a 512-deep layer in CTA `r`: first the blocks each half-group (here and in the peer) finishes
+// first, own blocks ahead of the peer's
+__device__ __forceinline__ int c2_kb_order(int i, int r) {
+  const int j = i & 3;
+  const int cta = (j < 2) ? r : (r ^ 1);
+  return cta * 4 + (j & 1) * 2 + (i >> 2);
+}
+
+template <int MODE>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1) fql_chain2_kernel(const __grid_constant__ ChainLaunch L) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* act = smem;
+  uint8_t* x0s = smem + kActBytes;
+  uint8_t* stage_base = x0s + kActBlockBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stage_base + kStages * kStageBytes);
+  uint64_t* full_bar = bars;                // [kStages]
+  uint64_t* empty_bar = bars + kStages;     // [kStages]
+  uint64_t* tmem_full = bars + 2 * kStages; // [2] one per accumulator buffer
+  uint64_t* blk_full = tmem_full + 2;       // [8] ACT k-blocks
+  uint64_t* peer_done = blk_full + 8;
+  uint64_t* layer_ready = peer_done + 1;    // after a narrow (unsplit) layer: 256 arrivals
+  uint64_t* a0_full = layer_ready + 1;
+  uint64_t* ln_x = a0_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(ln_x + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int rank = (int)cluster_ctarank();
+  long long tl_t0 = 0;
+  if (L.timeline && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
+
+  const int pair = (int)blockIdx.x >> 1;
+  int ji = 0;
+#pragma unroll 1
+  for (int i = 1; i < L.num_jobs; ++i)
+    if (pair >= L.job[i].tile_begin) ji = i;
+  const ChainJob& J = L.job[ji];
+  const int rel = pair - J.tile_begin;
+  const int bidx = rel / J.m_tiles;
+  const int mt = rel - bidx * J.m_tiles;
+  const int v = L.member_list ? __ldg(L.member_list + bidx) : bidx;
+  const int n_layers = J.n_layers;
+  const int iters = J.iters;
+  const int n_stages = L.stages;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&J.mapA0);
+    for (int i = 0; i < n_layers; ++i) tma_prefetch_desc(&J.mapW[i]);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(&tmem_full[0], 1);
+    mbar_init(&tmem_full[1], 1);
+    // own blocks: one arrival per producing thread; the peer's blocks: its copy warp's expect_tx + the bytes
+    for (int i = 0; i < 8; ++i) mbar_init(&blk_full[i], (i >> 2) == rank ? 128 : 1);
+    mbar_init(peer_done, 1);
+    mbar_init(layer_ready, 256);
+    mbar_init(a0_full, 1);
+    mbar_init(ln_x, 128);
+    fence_barrier_init();
+    fence_proxy_async_smem();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // the peer's barriers are initialised before anything is sent to them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ========================================= TMA producer =========================================
+    if (lane == 0) {
+      mbar_arrive_expect_tx(a0_full, kActBlockBytes);
+      tma_load_3d(x0s, &J.mapA0, a0_full, 0, J.row0 + mt * 128, v);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int it = 0; it < iters; ++it) {
+        for (int li = 0; li < n_layers; ++li) {
+          const ChainLayer& Ly = J.layer[li];
+          const bool split = Ly.kind == CL_HIDDEN;
+          const int n0 = split ? rank * 256 : 0;
+          const int ncols = split ? 256 : Ly.n_pad;
+          const int nkb = Ly.k_blocks;
+          for (int i = 0; i < nkb; ++i) {
+            const int kb = (nkb == 8 && !Ly.a_from_x0) ? c2_kb_order(i, rank) : i;
+            for (int h = 0; h < 2; ++h) {
+              const int ks = kb * 2 + h;
+              mbar_wait(&empty_bar[stage], phase ^ 1);
+              uint8_t* sb = stage_base + stage * kStageBytes;
+              if (MODE == 0) {
+                mbar_arrive_expect_tx(&full_bar[stage], ncols * kStageK * 2);
+                for (int b = 0; b < ncols / 64; ++b)
+                  tma_load_3d(sb + b * kFwdBoxBytes, &J.mapW[li], &full_bar[stage], n0 + 64 * b, ks * kStageK, v);
+              } else {
+                mbar_arrive_expect_tx(&full_bar[stage], (split ? 256 : Ly.b_box_rows) * kStageK * 2);
+                tma_load_3d(sb, &J.mapW[li], &full_bar[stage], ks * kStageK, n0, v);
+              }
+              if (++stage == n_stages) { stage = 0; phase ^= 1; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ========================================= MMA issuer ===========================================
+    int stage = 0;
+    uint32_t phase = 0;
+    int lc = 0, sc = 0, hc = 0;  // layers, split layers, narrow layers issued so far
+    int tr = 0;
+    const uint32_t act_addr = smem_u32(act), x0_addr = smem_u32(x0s);
+    const uint64_t bdesc0 = MODE == 0 ? make_smem_desc(smem_u32(stage_base), kFwdBoxBytes, 1024, 2)
+                                      : make_smem_desc(smem_u32(stage_base), 16, 512, 4);
+    constexpr uint32_t kBStep = (MODE == 0 ? 2048u : 32u) >> 4;
+    for (int it = 0; it < iters; ++it) {
+      for (int li = 0; li < n_layers; ++li, ++lc) {
+        const ChainLayer& Ly = J.layer[li];
+        const bool split = Ly.kind == CL_HIDDEN;
+        const int ncols = split ? 256 : Ly.n_pad;
+        const int nkb = Ly.k_blocks;
+        const bool from_act = !Ly.a_from_x0;
+        if (!from_act) {
+          if (lc == 0) mbar_wait(a0_full, 0);
+          else mbar_wait(layer_ready, (hc - 1) & 1);
+          tc_fence_after();
+        }
+        const uint64_t adesc0 = make_smem_desc(from_act ? act_addr : x0_addr, 16, 1024, 2);
+        const uint32_t idesc = make_idesc_bf16(128, (uint32_t)ncols, 0, MODE == 0 ? 1 : 0);
+        const uint32_t tmem_d = tmem_base + (lc & 1) * 256;
+        for (int i = 0; i < nkb; ++i) {
+          const int kb = (nkb == 8 && from_act) ? c2_kb_order(i, rank) : i;
+          if (from_act) {
+            mbar_wait(&blk_full[kb], (sc - 1) & 1);
+            tc_fence_after();
+          }
+          if (L.trace && blockIdx.x == 0 && lane == 0 && tr < 4000) L.trace[tr++] = clock64();
+          for (int h = 0; h < 2; ++h) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint64_t ad = adesc0 + (uint64_t)(kb * (kActBlockBytes >> 4) + h * 4);
+              const uint64_t bd = bdesc0 + (uint64_t)(stage * (kStageBytes >> 4));
+              umma_bf16(tmem_d, ad, bd, idesc, (i != 0 || h != 0) ? 1u : 0u);
+              umma_bf16(tmem_d, ad + 2, bd + kBStep, idesc, 1u);
+              umma_commit(&empty_bar[stage]);
+              if (i == nkb - 1 && h == 1) umma_commit(&tmem_full[lc & 1]);
+            }
+            __syncwarp();
+            if (++stage == n_stages) { stage = 0; phase ^= 1; }
+          }
+        }
+        if (split) ++sc; else ++hc;
+      }
+    }
+  } else if (warp == 10) {
+    // ========================================= block forwarder ======================================
+    // finished blocks of this CTA's column range -> the peer's ACT (asynchronous bulk copy; completion is counted on
+    // the peer's block barrier, armed from here)
+    if (lane == 0) {
+      const uint32_t peer = (uint32_t)(rank ^ 1);
+      const uint32_t peer_act = mapa_u32(smem_u32(act), peer);
+      const uint32_t peer_blk = mapa_u32(smem_u32(blk_full), peer);
+      int lc = 0, sc = 0;
+      for (int it = 0; it < iters; ++it) {
+        for (int li = 0; li < n_layers; ++li, ++lc) {
+          if (J.layer[li].kind != CL_HIDDEN) continue;
+          if (it == iters - 1 && li == n_layers - 1) continue;  // nobody consumes the last layer on chip
+          mbar_wait_cluster(peer_done, lc & 1);  // the peer's tensor core has stopped reading its ACT
+          for (int j = 0; j < 4; ++j) {
+            const int gblk = rank * 4 + (j & 1) * 2 + (j >> 1);  // order of completion: block 0 of either half-group first
+            mbar_wait(&blk_full[gblk], sc & 1);
+            const uint32_t pb = peer_blk + gblk * 8;
+            mbar_arrive_expect_tx_cluster(pb, kActBlockBytes);
+            dsmem_bulk_copy(peer_act + gblk * kActBlockBytes, act + gblk * kActBlockBytes, kActBlockBytes, pb);
+          }
+          ++sc;
+        }
+      }
+    }
+  } else {
+    // ========================================= epilogue =============================================
+    const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int r = q * 32 + lane;
+    const int grow = mt * 128 + r;
+    const bool row_ok = grow < J.M;
+    EpiCtx C;
+    C.tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    C.tmem_full = tmem_full; C.act_lo = nullptr; C.act_hi = nullptr;
+    C.act = act;
+    C.params = J.params + (long long)v * J.S;
+    C.r = r; C.half = half; C.q = q; C.lane = lane; C.H = J.H;
+    C.row_ok = row_ok;
+    C.prow = (long long)v * J.pass_ms + (long long)grow * J.H;
+    C.rs_off = (long long)v * J.pass_rs + grow;
+    C.dzrow = (long long)v * J.dz_ms + (long long)grow * J.H;
+    C.part_off = (long long)v * J.part_ms + (long long)(mt * 4 + q) * J.H;
+    C.ln_eps = J.ln_eps;
+    C.stg = n_stages == kStages ? nullptr : stage_base + kStagesStaged * kStageBytes + (warp - 2) * kStagingBytes;
+    const int grow0 = mt * 128 + q * 32;
+    C.wrow = (long long)v * J.pass_ms + (long long)grow0 * J.H;
+    C.wdz = (long long)v * J.dz_ms + (long long)grow0 * J.H;
+    C.rows_valid = min(32, max(0, J.M - grow0));
+    C.tm_off = 0; C.g_off = rank * 256; C.cl = true; C.publish = true;
+    C.blk_full = blk_full;
+    const uint32_t peer = (uint32_t)(rank ^ 1);
+    C.peer_act = mapa_u32(smem_u32(act), peer);
+    C.peer_blk_full = mapa_u32(smem_u32(blk_full), peer);
+    Cl2 X;
+    X.tmem_full = tmem_full; X.peer_done = peer_done; X.layer_ready = layer_ready; X.ln_x = ln_x;
+    X.peer_peer_done = mapa_u32(smem_u32(peer_done), peer);
+    X.peer_ln_x = mapa_u32(smem_u32(ln_x), peer);
+    X.ex2 = reinterpret_cast<const float2*>(reinterpret_cast<uint8_t*>(bars) + 256);
+    X.peer_ex2 = mapa_u32(smem_u32(X.ex2), peer);
+    X.ln = J.ln != 0;
+    const bool traced = L.trace && blockIdx.x == 0 && threadIdx.x == 64;
+    C.tr = traced ? L.trace + 4096 : nullptr;
+    if (traced) L.trace[4096] = 0;
+
+    float xs[8];
+    if (MODE == 0 && J.xe) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        xs[j] = (row_ok && half == 0 && j < J.A) ? J.xe[((long long)v * J.B + grow) * J.A + j] : 0.f;
+    }
+
+    int lc = 0, lnc = 0;
+    for (int it = 0; it < iters; ++it) {
+      for (int li = 0; li < n_layers; ++li, ++lc) {
+        const ChainLayer& Ly = J.layer[li];
+        if (Ly.kind == CL_HIDDEN) {
+          // the last layer's output is consumed by nobody on chip
+          C.publish = !(it == iters - 1 && li == n_layers - 1);
+          if (MODE == 0) {
+            const bool save = Ly.out_gp != nullptr;
+            if (J.ln) {
+              if (save) fwd2_hidden_layer<true, true>(C, X, Ly, lc, lnc);
+              else fwd2_hidden_layer<true, false>(C, X, Ly, lc, lnc);
+              ++lnc;
+            } else {
+              if (save) fwd2_hidden_layer<false, true>(C, X, Ly, lc, lnc);
+              else fwd2_hidden_layer<false, false>(C, X, Ly, lc, lnc);
+            }
+          } else {
+            if (J.ln) { bwd2_hidden_layer<true>(C, X, Ly, lc, lnc); ++lnc; }
+            else bwd2_hidden_layer<false>(C, X, Ly, lc, lnc);
+          }
+        } else if (Ly.kind == CL_EULER_HEAD) {
+          c2_begin_layer(C, X, lc);
+          if (half == 0) {
+            uint32_t rr[16];
+            tmem_ld16(C.tmem_row + C.tm_off, rr);
+            tmem_ld_wait();
+            const float invF = 1.f / (float)J.F;
+            const bool last = it == iters - 1;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              if (j < J.A) {
+                xs[j] = fmaf(__uint_as_float(rr[j]) + __ldg(C.params + Ly.off_b + j), invF, xs[j]);
+                if (last) {
+                  if (row_ok && rank == 0) J.target_a[((long long)v * J.B + grow) * J.A + j] = clip1(xs[j]);
+                } else {
+                  const int col = J.O + j;
+                  *reinterpret_cast<__nv_bfloat16*>(x0s + r * 128 + (((col >> 3) ^ (r & 7)) << 4) + (col & 7) * 2) =
+                      __float2bfloat16_rn(xs[j]);
+                }
+              }
+            }
+            if (!last) {
+              const int col = J.O + J.A;
+              *reinterpret_cast<__nv_bfloat16*>(x0s + r * 128 + (((col >> 3) ^ (r & 7)) << 4) + (col & 7) * 2) =
+                  __float2bfloat16_rn((float)(it + 1) / (float)J.F);
+            }
+          }
+          release(layer_ready);
+        } else {  // CL_DINPUT (both CTAs hold the full result; rank 0 stores)
+          c2_begin_layer(C, X, lc);
+          if (half == 0 && rank == 0) {
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+              if (c * 32 < Ly.n_pad) {
+                uint32_t rr[32];
+                tmem_ld32(C.tmem_row + C.tm_off + c * 32, rr);
+                tmem_ld_wait();
+                if (row_ok) {
+                  float4* d4 = reinterpret_cast<float4*>(Ly.out_f32 + (long long)v * J.f32_ms +
+                                                         (long long)grow * Ly.out_ld + c * 32);
+#pragma unroll
+                  for (int i = 0; i < 8; ++i)
+                    d4[i] = make_float4(__uint_as_float(rr[4 * i]), __uint_as_float(rr[4 * i + 1]),
+                                        __uint_as_float(rr[4 * i + 2]), __uint_as_float(rr[4 * i + 3]));
+                }
+              }
+            }
+          }
+          release(layer_ready);
+        }
+        stamp(C, 99);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // no CTA leaves while its peer may still signal it or copy into it
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+  if (L.timeline && threadIdx.x == 0) {
+    long long t1;
+    unsigned smid;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    const unsigned long long slot = atomicAdd(reinterpret_cast<unsigned long long*>(L.timeline), 1ull);
+    if (slot < 65536ull) {
+      long long* rec = L.timeline + 8 + 4 * slot;
+      rec[0] = tl_t0; rec[1] = t1; rec[2] = smid; rec[3] = L.tag | ((long long)blockIdx.x << 32);
+    }
   }
 }
 
@@ -904,6 +1370,7 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
     C.wrow = (long long)v * J.pass_ms + (long long)grow0 * J.H;
     C.wdz = (long long)v * J.dz_ms + (long long)grow0 * J.H;
     C.rows_valid = min(32, max(0, J.M - grow0));
+    C.tm_off = 0; C.g_off = 0; C.cl = false; C.publish = false; C.blk_full = nullptr; C.peer_act = 0; C.peer_blk_full = 0;
     const bool traced = L.trace && blockIdx.x == 0 && threadIdx.x == 64;
     C.tr = traced ? L.trace + 4096 : nullptr;
     if (traced) L.trace[4096] = 0;
@@ -1027,7 +1494,32 @@ int finalize_chain(ChainLaunch* L) {
 cudaError_t chain_init() {
   cudaError_t e = cudaFuncSetAttribute(fql_chain_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(fql_chain_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  e = cudaFuncSetAttribute(fql_chain_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(fql_chain2_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(fql_chain2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+}
+
+// The cluster kernel covers the production shape: every hidden layer 512 wide, reductions of 64 (first layer) or 512.
+static bool chain2_eligible(const ChainLaunch& L) {
+  static const int mode = [] {
+    const char* e = getenv("FQLPOP_CHAIN2");
+    return e ? atoi(e) : 1;
+  }();
+  if (!mode) return false;
+  if (mode == 2 && L.job[0].iters <= 1) return false;  // 2: only the Euler chain (the step's longest serial path)
+  for (int i = 0; i < L.num_jobs; ++i) {
+    const ChainJob& j = L.job[i];
+    if (j.H != 512) return false;
+    for (int l = 0; l < j.n_layers; ++l) {
+      const ChainLayer& y = j.layer[l];
+      if (y.kind == CL_HIDDEN && y.n_pad != 512) return false;
+      if (y.kind != CL_HIDDEN && y.n_pad > 256) return false;
+      if (y.a_from_x0 ? y.k_blocks != 1 : y.k_blocks != 8) return false;
+    }
+  }
+  return true;
 }
 
 cudaError_t launch_chain(ChainLaunch& L, int mode, cudaStream_t stream) {
@@ -1040,6 +1532,11 @@ cudaError_t launch_chain(ChainLaunch& L, int mode, cudaStream_t stream) {
     for (int l = 0; l < L.job[i].n_layers; ++l)
       if (L.job[i].layer[l].out_gp || L.job[i].layer[l].out_xhat) staged = true;
   L.stages = staged ? kStagesStaged : kStages;
+  if (chain2_eligible(L)) {
+    if (mode == 0) fql_chain2_kernel<0><<<2 * grid, kThreads2, kSmemBytes, stream>>>(L);
+    else fql_chain2_kernel<1><<<2 * grid, kThreads2, kSmemBytes, stream>>>(L);
+    return cudaGetLastError();
+  }
   if (mode == 0) fql_chain_kernel<0><<<grid, kThreads, kSmemBytes, stream>>>(L);
   else fql_chain_kernel<1><<<grid, kThreads, kSmemBytes, stream>>>(L);
   return cudaGetLastError();

@@ -247,7 +247,30 @@ fql_gemm_kernel(const __grid_constant__ GemmLaunch L) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
           if (kind == EPI_STORE_F32) {
-            if (row_ok) store_f32x32(E.out_f32.p + member * E.out_f32.ms + (long long)grow * E.out_f32.ld + col, v);
+            if (N_SUB == 1) {
+              // One tile per CTA: once the accumulator is complete the operand stages are idle. A thread owns a ROW, so
+              // storing its 128 bytes directly costs 32 partial-line requests per warp instruction; transposing the
+              // 32 x 32 block through a warp-private 4 KB slice of stage memory (16-byte chunks XOR-swizzled by row)
+              // makes every store instruction cover 4 rows x 128 contiguous bytes.
+              uint8_t* stg = stage_base + q * 4096;
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                *reinterpret_cast<float4*>(stg + lane * 128 + ((i ^ (lane & 7)) << 4)) =
+                    make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+              __syncwarp();
+              const int rows_valid = G.M - (mt * kBlockM + q * 32);
+              float* dst = E.out_f32.p + member * E.out_f32.ms + (long long)(mt * kBlockM + q * 32) * E.out_f32.ld + col;
+              const int ch = lane & 7, rsub = lane >> 3;
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const int r = i * 4 + rsub;
+                const float4 u = *reinterpret_cast<const float4*>(stg + r * 128 + ((ch ^ (r & 7)) << 4));
+                if (r < rows_valid) *reinterpret_cast<float4*>(dst + (long long)r * E.out_f32.ld + ch * 4) = u;
+              }
+              __syncwarp();
+            } else {
+              if (row_ok) store_f32x32(E.out_f32.p + member * E.out_f32.ms + (long long)grow * E.out_f32.ld + col, v);
+            }
           } else if (kind == EPI_STORE_BF16) {
             if (row_ok) store_bf16x32(E.out_h.p + member * E.out_h.ms + (long long)grow * E.out_h.ld + col, v);
           } else if (kind == EPI_FWD) {

@@ -188,7 +188,22 @@ __global__ void __launch_bounds__(256) prep_kernel(const PrepArgs a) {
 // ------------------------------------------------------------------------------------------------------
 // head layers (H -> out <= 8 on CUDA cores, fp32 weights, bf16 activations) fused with what follows them
 // ------------------------------------------------------------------------------------------------------
+// (debug) one timeline record: start ns, end ns, SM id, tag | blockIdx.x << 32
+__device__ __forceinline__ void tl_record(long long* timeline, long long t0, long long tag) {
+  long long t1;
+  unsigned smid;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+  const unsigned long long slot = atomicAdd(reinterpret_cast<unsigned long long*>(timeline), 1ull);
+  if (slot < 65536ull) {
+    long long* rec = timeline + 8 + 4 * slot;
+    rec[0] = t0; rec[1] = t1; rec[2] = smid; rec[3] = tag | ((long long)blockIdx.x << 32);
+  }
+}
+
 struct HeadArgs {
+  long long* timeline;     // (debug) per-CTA records, see fqlpop_debug_timeline
+  long long tag;
   const __nv_bfloat16* h;  // [V][M][H] last hidden activations of the pass
   const float* theta;      // arena the head weights come from (theta, or target for the TD target)
   long long S, offW, offb;
@@ -202,6 +217,8 @@ struct HeadArgs {
 };
 
 #define HEAD_PROLOGUE()                                                                  \
+  long long tl_t0 = 0;                                                                   \
+  if (a.timeline && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0)); \
   extern __shared__ float sm_head[];                                                     \
   float* wT = sm_head;                                                                   \
   float* bs = sm_head + a.nb * a.out * a.H;                                              \
@@ -209,6 +226,9 @@ struct HeadArgs {
   stage_head(wT, bs, a.theta, a.S, a.offW, a.offb, p * a.nb, a.nb, a.out, a.H);          \
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;                            \
   const int row_begin = blockIdx.x * kRowsPerBlock + warp * kRowsPerWarp;
+
+#define HEAD_EPILOGUE()                                                                  \
+  if (a.timeline && threadIdx.x == 0) tl_record(a.timeline, tl_t0, a.tag);
 
 template <int MAXO>
 __device__ __forceinline__ float pick_lane(const float (&acc)[MAXO], const float* bs, int lane) {
@@ -248,6 +268,7 @@ __global__ void __launch_bounds__(kHeadThreads) pi_head_kernel(const HeadArgs a)
   }
   mse_acc = warp_sum(mse_acc);
   if (lane == 0 && mse_acc != 0.f) atomicAdd(&a.info[p * kInfoSlots + I_MSE], mse_acc / (float)(a.B * a.A));
+  HEAD_EPILOGUE();
 }
 
 // target critic head: y = r + discount * mask * agg_e Qbar_e(s', a')
@@ -270,6 +291,7 @@ __global__ void __launch_bounds__(kHeadThreads) tq_head_kernel(const HeadArgs a)
       a.y[pb] = a.rew[pb] + a.discount * a.mask[pb] * nq;
     }
   }
+  HEAD_EPILOGUE();
 }
 
 // critic head on (s, a): TD loss, its gradient (bf16, column 0 of dout) and the q statistics
@@ -301,6 +323,7 @@ __global__ void __launch_bounds__(kHeadThreads) qc_head_kernel(const HeadArgs a)
     atomic_max_f(&a.info[p * kInfoSlots + I_Q_MAX], qmx);
     atomic_min_f(&a.info[p * kInfoSlots + I_Q_MIN], qmn);
   }
+  HEAD_EPILOGUE();
 }
 
 // critic head on (s, clip(a_pi)): mean_e Q_e -> sums for q_loss / q / the normalisation constant
@@ -324,6 +347,7 @@ __global__ void __launch_bounds__(kHeadThreads) qa_head_kernel(const HeadArgs a)
     atomicAdd(&a.info[p * kInfoSlots + I_Q], qsum / (float)a.B);
     atomicAdd(&a.info[p * kInfoSlots + I_QABS], qabs / (float)a.B);
   }
+  HEAD_EPILOGUE();
 }
 
 // BC flow head on (s, x_t, t): flow-matching loss and its gradient
@@ -346,6 +370,7 @@ __global__ void __launch_bounds__(kHeadThreads) bc_head_kernel(const HeadArgs a)
   }
   loss = warp_sum(loss);
   if (lane == 0 && row_begin < a.B) atomicAdd(&a.info[p * kInfoSlots + I_BC_LOSS], loss * inv);
+  HEAD_EPILOGUE();
 }
 
 // BC flow head inside the Euler rollout: x <- x + v / F, restage the next step's input (bf16) with t = (i+1)/F
@@ -502,6 +527,8 @@ __global__ void grad_stats_final_kernel(const float* leaf_stats, int n_leaves, c
 // + 6 B written for the target and its shadow.
 // ------------------------------------------------------------------------------------------------------
 struct AdamArgs {
+  long long* timeline;
+  long long tag;
   float *theta, *mu, *nu;
   const float* grad;
   __nv_bfloat16* shadow;
@@ -514,6 +541,9 @@ struct AdamArgs {
   float lr, b1, b2, eps, tau;
 };
 __global__ void __launch_bounds__(256) adam_kernel(const AdamArgs a) {
+  long long tl_t0 = 0;
+  const bool tl_on = a.timeline && threadIdx.x == 0 && (blockIdx.x & 31) == 0;
+  if (tl_on) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
   const int am = blockIdx.y / a.nb, e = blockIdx.y - am * a.nb;
   const int p = a.member_list[am];
   const long long base = ((long long)p * a.nb + e) * a.S;
@@ -551,6 +581,7 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamArgs a) {
       *reinterpret_cast<uint2*>(a.tshadow + o) = ts;
     }
   }
+  if (tl_on) tl_record(a.timeline, tl_t0, a.tag);
 }
 
 // theta -> bf16 shadow (after importing parameters)
@@ -647,24 +678,29 @@ void launch_prep(Population* P, cudaStream_t s, int bump_adam) {
 
 void launch_pi_head(Population* P, cudaStream_t s) {
   HeadArgs a = head_args(P, P->PI, P->pi, P->pi.theta);
+  a.timeline = P->timeline; a.tag = 20 | ((long long)P->g_off << 8);
   pi_head_kernel<<<head_grid(P, a.M), kHeadThreads, head_smem(a), s>>>(a);
 }
 void launch_tq_head(Population* P, cudaStream_t s) {
   HeadArgs a = head_args(P, P->TQ, P->critic, P->critic.target);
+  a.timeline = P->timeline; a.tag = 21 | ((long long)P->g_off << 8);
   tq_head_kernel<<<head_grid(P, a.B), kHeadThreads, head_smem(a), s>>>(a);
 }
 void launch_qc_head(Population* P, cudaStream_t s) {
   HeadArgs a = head_args(P, P->QC, P->critic, P->critic.theta);
   a.dout = P->bQC.dout;
+  a.timeline = P->timeline; a.tag = 22 | ((long long)P->g_off << 8);
   qc_head_kernel<<<head_grid(P, a.B), kHeadThreads, head_smem(a), s>>>(a);
 }
 void launch_qa_head(Population* P, cudaStream_t s) {
   HeadArgs a = head_args(P, P->QA, P->critic, P->critic.theta);
+  a.timeline = P->timeline; a.tag = 23 | ((long long)P->g_off << 8);
   qa_head_kernel<<<head_grid(P, a.B), kHeadThreads, head_smem(a), s>>>(a);
 }
 void launch_bc_head(Population* P, cudaStream_t s) {
   HeadArgs a = head_args(P, P->BC, P->bc, P->bc.theta);
   a.dout = P->bBC.dout;
+  a.timeline = P->timeline; a.tag = 24 | ((long long)P->g_off << 8);
   bc_head_kernel<<<head_grid(P, a.B), kHeadThreads, head_smem(a), s>>>(a);
 }
 void launch_euler_head(Population* P, int i, cudaStream_t s) {
@@ -749,6 +785,8 @@ static void launch_adam_one(Population* P, Arena& ar, cudaStream_t s) {
   a.member_list = P->cur_list();
   a.adam_bc = P->adam_bc;
   a.lr = P->c.lr; a.b1 = P->c.adam_b1; a.b2 = P->c.adam_b2; a.eps = P->c.adam_eps; a.tau = P->c.tau;
+  a.timeline = P->timeline;
+  a.tag = (&ar == &P->critic ? 30 : (&ar == &P->bc ? 31 : 32)) | ((long long)P->g_off << 8);
   const long long n4 = ar.L.S / 4;
   const int gx = (int)((n4 + 256 * 4 - 1) / (256 * 4));  // 4 float4 per thread
   adam_kernel<<<dim3(gx, (unsigned)(P->cur_n() * ar.L.nb)), 256, 0, s>>>(a);

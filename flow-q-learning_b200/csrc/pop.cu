@@ -31,7 +31,9 @@ namespace fqlpop {
 // Euler steps -- overlaps the other groups' wide passes instead of leaving the SMs idle behind a step barrier.
 struct GroupPlan {
   int off = 0, n = 0;
-  cudaStream_t s[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  // s[0..4]: compute branches of the step (high priority); s[5..7]: the three optimizer branches (low priority: their
+  // grids flood every free SM and would otherwise delay the small head kernels of the other groups)
+  cudaStream_t s[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   cudaGraph_t g_step = nullptr, g_loss = nullptr;
   cudaGraphExec_t x_step = nullptr, x_loss = nullptr;
   cudaEvent_t done = nullptr;
@@ -413,7 +415,12 @@ void record(Plan* pl, cudaEvent_t* out, cudaStream_t s) {
 // streams. Called under stream capture; s[0] is the origin stream.
 int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   Plan* pl = P->plan;
-  cudaStream_t s0 = gp.s[0], s1 = gp.s[1], s2 = gp.s[2], s3 = gp.s[3], s4 = gp.s[4];
+  // schedule knobs (measured on B200): FQLPOP_SCHED bit 0 = critic forward / actor-critic pass
+  // on their own streams (s3, s4) instead of queued behind s1 / s2; bit 1 = optimizer kernels on separate streams;
+  // FQLPOP_ADAM_PRIO = priority of those streams (0 low, 1 same as compute)
+  static const int sched = [] { const char* e = getenv("FQLPOP_SCHED"); return e ? atoi(e) : 3; }();
+  cudaStream_t s0 = gp.s[0], s1 = gp.s[1], s2 = gp.s[2];
+  cudaStream_t s3 = (sched & 1) ? gp.s[3] : s1, s4 = (sched & 1) ? gp.s[4] : s2;
   const PopParams& c = P->c;
   Builder b{P, err};
   b.L = new GemmLaunch;
@@ -427,7 +434,7 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   record(pl, &e_prep, s0);
   cudaStreamWaitEvent(s1, e_prep, 0);
   cudaStreamWaitEvent(s2, e_prep, 0);
-  cudaStreamWaitEvent(s3, e_prep, 0);
+  if (s3 != s1) cudaStreamWaitEvent(s3, e_prep, 0);
 
   ChainBuilder cb{P, err};
   cb.L = new ChainLaunch;
@@ -532,16 +539,31 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
     b.begin(1);
     for (int l = 0; l <= nh_a; ++l) b.wgrad_group(P->PI, P->bPI, P->pi, l, 0);
     b.launch(1, s0);
-    launch_small_grads(P, 2, s0); ++pw;
-    launch_adam(P, 2, s0); ++pw;
-    // critic optimizer: after every reader of the critic weights (QA chain on s2) is done
-    cudaStreamWaitEvent(s1, e_qa, 0);
-    launch_small_grads(P, 0, s1); ++pw;
-    launch_adam(P, 0, s1); ++pw;
+    // the optimizer branches run on the low-priority streams
+    cudaStream_t a0 = (sched & 2) ? gp.s[5] : s1, a1 = (sched & 2) ? gp.s[6] : s2, a2 = (sched & 2) ? gp.s[7] : s0;
+    cudaEvent_t e_w0, e_w1, e_w2, e_a0, e_a1, e_a2;
+    record(pl, &e_w2, s0);
+    cudaStreamWaitEvent(a2, e_w2, 0);
+    launch_small_grads(P, 2, a2); ++pw;
+    launch_adam(P, 2, a2); ++pw;
+    record(pl, &e_a2, a2);
+    // critic optimizer: after every reader of the critic weights (QA chain on s4) is done
+    record(pl, &e_w0, s1);
+    cudaStreamWaitEvent(a0, e_w0, 0);
+    cudaStreamWaitEvent(a0, e_qa, 0);
+    launch_small_grads(P, 0, a0); ++pw;
+    launch_adam(P, 0, a0); ++pw;
+    record(pl, &e_a0, a0);
     // BC flow optimizer: after the Euler chain (s0) has stopped reading the BC weights
-    cudaStreamWaitEvent(s2, e_euler, 0);
-    launch_small_grads(P, 1, s2); ++pw;
-    launch_adam(P, 1, s2); ++pw;
+    record(pl, &e_w1, s2);
+    cudaStreamWaitEvent(a1, e_w1, 0);
+    cudaStreamWaitEvent(a1, e_euler, 0);
+    launch_small_grads(P, 1, a1); ++pw;
+    launch_adam(P, 1, a1); ++pw;
+    record(pl, &e_a1, a1);
+    cudaStreamWaitEvent(s0, e_a0, 0);
+    cudaStreamWaitEvent(s0, e_a1, 0);
+    cudaStreamWaitEvent(s0, e_a2, 0);
   }
   record(pl, &e_s1, s1);
   record(pl, &e_s2, s2);
@@ -573,7 +595,7 @@ void destroy_graphs(Plan* pl) {
 void destroy_groups(Plan* pl) {
   destroy_graphs(pl);
   for (GroupPlan& g : pl->groups) {
-    for (int i = 0; i < 5; ++i)
+    for (int i = 0; i < 8; ++i)
       if (g.s[i]) cudaStreamDestroy(g.s[i]);
     if (g.done) cudaEventDestroy(g.done);
   }
@@ -595,7 +617,12 @@ int make_groups(Population* P, std::string* err) {
     // spread the remainder so group sizes differ by at most one
     gp.off = (int)((long long)n * g / G);
     gp.n = (int)((long long)n * (g + 1) / G) - gp.off;
-    for (int i = 0; i < 5; ++i) CK(cudaStreamCreateWithFlags(&gp.s[i], cudaStreamNonBlocking));
+    int prio_lo = 0, prio_hi = 0;  // numerically: lowest priority, highest priority
+    const char* ape = getenv("FQLPOP_ADAM_PRIO");
+    const int adam_prio = ape ? atoi(ape) : 0;
+    CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    for (int i = 0; i < 8; ++i)
+      CK(cudaStreamCreateWithPriority(&gp.s[i], cudaStreamNonBlocking, (i < 5 || adam_prio) ? prio_hi : prio_lo));
     CK(cudaEventCreateWithFlags(&gp.done, cudaEventDisableTiming));
   }
   return 0;

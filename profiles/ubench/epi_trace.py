@@ -20,7 +20,7 @@ mma = buf[:4096]
 n = int(buf[4096])
 st = buf[4098:4098 + 2 * n].reshape(-1, 2)
 t0 = min(mma[0], st[0, 0]) if n else mma[0]
-print("MMA issuer stamps (cycles from t0):", [int(x - t0) for x in mma[:24] if x > 0])
+print("MMA issuer stamps (cycles from t0):", [int(x - t0) for x in mma[:int(os.environ.get("NMMA", "24"))] if x > 0])
 lim = int(sys.argv[2]) if len(sys.argv) > 2 else 120
 prev = t0
 for c, i in st[:lim]:

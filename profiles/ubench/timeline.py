@@ -20,22 +20,32 @@ cnt = ctypes.c_int32(0)
 pop.step(20)
 torch.cuda.synchronize()
 check(lib.fqlpop_debug_timeline(pop._h, buf.ctypes.data, 65536, ctypes.byref(cnt)))
-pop.step(1)
+NS = int(os.environ.get('TL_STEPS', '1'))
+pop.step(NS)
 torch.cuda.synchronize()
 check(lib.fqlpop_debug_timeline(pop._h, buf.ctypes.data, 65536, ctypes.byref(cnt)))
 r = buf[:cnt.value]
+if NS > 1:  # keep the last step of every (group, launch): its CTAs are the last ones in time
+    keep = []
+    for key in set(r[:, 3] & 0xFFFFFF):
+        m = np.where((r[:, 3] & 0xFFFFFF) == key)[0]
+        m = m[np.argsort(r[m, 0])]
+        keep.extend(m[-(len(m) // NS):])
+    r = r[np.array(keep)]
 t0 = r[:, 0].min()
-names = ["euler", "pi_fwd", "tq_fwd", "qc_fwd", "qc_bwd", "bc_fwd", "bc_bwd", "qa_fwd", "qa_bwd", "pi_bwd"]
+names = {0: "euler", 1: "pi_fwd", 2: "tq_fwd", 3: "qc_fwd", 4: "qc_bwd", 5: "bc_fwd", 6: "bc_bwd", 7: "qa_fwd", 8: "qa_bwd", 9: "pi_bwd",
+         20: "pi_head", 21: "tq_head", 22: "qc_head", 23: "qa_head", 24: "bc_head", 30: "adam_q", 31: "adam_bc", 32: "adam_pi"}
 print(f"records {len(r)}  step span {(r[:, 1].max() - t0) / 1e3:.1f} us")
 tag = r[:, 3] & 0xFF
 grp = (r[:, 3] >> 8) & 0xFFFF
 for g in sorted(set(grp)):
-    for k in range(10):
+    for k in sorted(names):
         m = (tag == k) & (grp == g)
         if not m.any():
             continue
         s, e = r[m, 0], r[m, 1]
         print(f"group@{g:3d} {names[k]:7s} ctas {m.sum():3d} start {(s.min() - t0) / 1e3:7.1f} .. {(s.max() - t0) / 1e3:7.1f}"
               f"  end {(e.max() - t0) / 1e3:7.1f}  mean cta {np.mean(e - s) / 1e3:6.1f} us")
+r = r[tag < 10]
 busy = (r[:, 1] - r[:, 0]).sum() / 1e3
 print(f"chain CTA-us total {busy:.0f}; / 148 SMs = {busy / 148:.1f} us; SMs used {len(set(r[:, 2]))}")
