@@ -143,28 +143,24 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def gemm_roofline(torch, P, B, iters=200):
-    """The step's dominant launch: hidden layer forward h = gelu(x W + b), M=B rows, N=K=512, batch P members.
-    Timed alone with CUDA events on the launching (current) stream -> burst tensor peak is the denominator."""
-    from fqlpop import _lib
-    dev = "cuda"
-    A = (torch.randn(P, B, HID, device=dev) * 0.5).to(torch.bfloat16)
-    Wt = (torch.randn(P, HID, HID, device=dev) / HID ** 0.5).to(torch.bfloat16)  # [in][out] -> MN-major B
-    bias = torch.zeros(P, HID, device=dev)
-    out = torch.empty(P, B, HID, device=dev, dtype=torch.bfloat16)
-    kw = dict(M=B, N=HID, K=HID, P=P, a_mn=0, b_mn=1, n_sub=1, A=A, a_ld=HID, a_ms=B * HID, B=Wt, b_ld=HID,
-              b_ms=HID * HID, ln_eps=1e-6, epi_kind=_lib.EPI_FWD, act=_lib.ACT_GELU, bias=bias, out_h=out)
-    for _ in range(10):
-        _lib.gemm_test(**kw)
+def chain_roofline(torch, pop, P, O, A, B, iters=50):
+    """The step's dominant kernel, fql_chain_kernel<0>, in its widest launch: the one-step policy forward pass (3B rows
+    of every member through the four hidden layers in one launch, activations on chip, act'(z) / h saved for the
+    backward pass). Launched alone, back to back, on the current stream and bracketed by CUDA events on that stream ->
+    the burst tensor peak is the denominator. FLOP = algorithmic (true input width, not the padded 64)."""
+    import ctypes
+    from fqlpop._lib import lib, check
+    lib.fqlpop_debug_chain_launch.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    check(lib.fqlpop_debug_chain_launch(pop._h, 1, 5, st))
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(iters):
-        _lib.gemm_test(**kw)
+    check(lib.fqlpop_debug_chain_launch(pop._h, 1, iters, st))
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / iters
-    flop = 2.0 * P * B * HID * HID
+    flop = 2.0 * P * 3 * B * ((O + A) * HID + 3 * HID * HID)   # policy input = (obs, noise): O + A wide
     return flop / (ms * 1e-3) / 1e12, ms, flop
 
 
@@ -278,7 +274,7 @@ def main():
     value = P * world * args.steps / (ms_total * 1e-3)
     ms_step = ms_total / args.steps
     flop_upd = flop_per_update(O, A, B)
-    tf_gemm, gemm_ms, gemm_flop = gemm_roofline(torch, P, B)
+    tf_gemm, gemm_ms, gemm_flop = chain_roofline(torch, pop, P, O, A, B)
     step_tflops = flop_upd * P / (ms_step * 1e-3) / 1e12
     adam_b = adam_bytes_per_update(O, A)
     line = {
@@ -293,7 +289,8 @@ def main():
         "gpu_launches": pop.launches_per_step * args.steps,
         "roofline": {"bound": "tensor", "achieved": tf_gemm, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
                      "frac": tf_gemm / pk["bf16_tflops"], "traffic": None, "peak_source": pk_src + " (burst)",
-                     "kernel": "fql_gemm_kernel<1> hidden-layer forward, M=%d N=K=512 x %d members, timed alone" % (B, P),
+                     "kernel": "fql_chain_kernel<0>: one-step policy forward pass, %d rows x 4 hidden layers x %d members in one "
+                               "launch (%d CTAs of 128 rows), timed alone" % (3 * B, P, P * ((3 * B + 127) // 128)),
                      "launch_ms": gemm_ms, "flop_per_launch": gemm_flop},
         "step_roofline": {"algorithmic_tflops": step_tflops, "frac_of_sustained_tensor_peak": step_tflops / pk["bf16_tflops_sustained"],
                           "flop_per_member_update": flop_upd, "adam_bytes_per_member_update": adam_b,

@@ -219,6 +219,12 @@ extern "C" int fqlpop_debug_timeline(void* h, long long* host_out, int32_t max_r
   if (n_out) *n_out = (int32_t)n;
   return 0;
 }
+extern "C" int fqlpop_debug_chain_launch(void* h, int32_t which, int32_t iters, void* stream) {
+  POP(h);
+  std::string err;
+  if (fqlpop::pop_debug_chain_launch(P, which, iters, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
 extern "C" int fqlpop_launches_per_step(void* h) {
   fqlpop::Population* P = (fqlpop::Population*)h;
   return P ? fqlpop::pop_launches_per_step(P) : 0;

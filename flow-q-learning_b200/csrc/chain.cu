@@ -348,9 +348,11 @@ __device__ __forceinline__ void fwd_chunk(const EpiCtx& C, const float* bias, co
   if (direct) st_act16(C.act, C.r, C.g_off + col, pk);
   else tmem_st8(C.tmem_row + C.tm_off + col0 + c * 8, pk);
 }
-// The accumulator chunks are double-buffered in registers: the TMEM load of chunk c + 1 is in flight while chunk c is
-// being computed (tcgen05.wait::ld waits for every outstanding load, so the next one is issued right after the wait).
-template <bool LN, bool SAVE>
+// DB: the accumulator chunks are double-buffered in registers -- the TMEM load of chunk c + 1 is in flight while chunk c
+// is being computed (tcgen05.wait::ld waits for every outstanding load, so the next one is issued right after the
+// wait). Pays off in the cluster kernel (one pass per layer, nothing else to overlap with); the single-CTA kernel,
+// whose passes already overlap the other tile's MMAs, is faster with the plain loop (fewer live registers).
+template <bool LN, bool SAVE, bool DB>
 __device__ __forceinline__ void fwd_pass1(const EpiCtx& C, const ChainLayer& Ly, int tile, bool direct, float& s1, float& s2) {
   const int nch = tile_chunks16(C, tile, Ly.n_pad);  // a multiple of 4
   if (nch == 0) return;
@@ -358,17 +360,26 @@ __device__ __forceinline__ void fwd_pass1(const EpiCtx& C, const ChainLayer& Ly,
   const float* bias = C.params + Ly.off_b + C.g_off;
   const uint32_t tbase = C.tmem_row + C.tm_off + col0;
   uint32_t ra[16], rb[16];
-  tmem_ld16(tbase, ra);
+  if (DB) tmem_ld16(tbase, ra);
 #pragma unroll 1
   for (int cb = 0; cb < nch; cb += 4) {
+    if (DB) {
 #pragma unroll 1
-    for (int c = cb; c < cb + 4; c += 2) {
-      tmem_ld_wait();
-      tmem_ld16(tbase + (c + 1) * 16, rb);
-      fwd_chunk<LN, SAVE>(C, bias, ra, col0, c, direct, s1, s2);
-      tmem_ld_wait();
-      if (c + 2 < nch) tmem_ld16(tbase + (c + 2) * 16, ra);
-      fwd_chunk<LN, SAVE>(C, bias, rb, col0, c + 1, direct, s1, s2);
+      for (int c = cb; c < cb + 4; c += 2) {
+        tmem_ld_wait();
+        tmem_ld16(tbase + (c + 1) * 16, rb);
+        fwd_chunk<LN, SAVE>(C, bias, ra, col0, c, direct, s1, s2);
+        tmem_ld_wait();
+        if (c + 2 < nch) tmem_ld16(tbase + (c + 2) * 16, ra);
+        fwd_chunk<LN, SAVE>(C, bias, rb, col0, c + 1, direct, s1, s2);
+      }
+    } else {
+#pragma unroll 1
+      for (int c = cb; c < cb + 4; ++c) {
+        tmem_ld16(tbase + c * 16, ra);
+        tmem_ld_wait();
+        fwd_chunk<LN, SAVE>(C, bias, ra, col0, c, direct, s1, s2);
+      }
     }
     if (SAVE) {
       __syncwarp();
@@ -447,12 +458,12 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
     wait_tile(C, fullph, 0);
     stamp(C, 10);
     if (n_tiles == 1) {
-      fwd_pass1<false, SAVE>(C, Ly, 0, true, s1, s2);
+      fwd_pass1<false, SAVE, false>(C, Ly, 0, true, s1, s2);
       stamp(C, 11);
       release(C.act_lo);
       stamp(C, 12);
     } else {
-      fwd_pass1<false, SAVE>(C, Ly, 0, false, s1, s2);
+      fwd_pass1<false, SAVE, false>(C, Ly, 0, false, s1, s2);
       stamp(C, 13);
       tmem_st_wait();
       stamp(C, 14);
@@ -461,7 +472,7 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
       stamp(C, 15);
       release(C.act_lo);
       stamp(C, 16);
-      fwd_pass1<false, SAVE>(C, Ly, 1, true, s1, s2);
+      fwd_pass1<false, SAVE, false>(C, Ly, 1, true, s1, s2);
       stamp(C, 17);
     }
     release(C.act_hi);
@@ -474,12 +485,12 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
   } else {
     wait_tile(C, fullph, 0);
     stamp(C, 19);
-    fwd_pass1<true, SAVE>(C, Ly, 0, false, s1, s2);
+    fwd_pass1<true, SAVE, false>(C, Ly, 0, false, s1, s2);
     stamp(C, 20);
     if (n_tiles > 1) {
       wait_tile(C, fullph, 1);
       stamp(C, 21);
-      fwd_pass1<true, SAVE>(C, Ly, 1, false, s1, s2);
+      fwd_pass1<true, SAVE, false>(C, Ly, 1, false, s1, s2);
       stamp(C, 22);
     }
     tmem_st_wait();
@@ -829,9 +840,9 @@ __device__ __forceinline__ void fwd2_hidden_layer(EpiCtx& C, const Cl2& X, const
   stamp(C, 40);
   float s1 = 0.f, s2 = 0.f;
   if (!LN) {
-    fwd_pass1<false, SAVE>(C, Ly, 0, true, s1, s2);
+    fwd_pass1<false, SAVE, true>(C, Ly, 0, true, s1, s2);
   } else {
-    fwd_pass1<true, SAVE>(C, Ly, 0, false, s1, s2);
+    fwd_pass1<true, SAVE, true>(C, Ly, 0, false, s1, s2);
     tmem_st_wait();
     float t1 = s1, t2 = s2;
     exchange_row_sums2(C, X, lnc, t1, t2);
@@ -1504,8 +1515,11 @@ cudaError_t chain_init() {
 // The cluster kernel covers the production shape: every hidden layer 512 wide, reductions of 64 (first layer) or 512.
 static bool chain2_eligible(const ChainLaunch& L) {
   static const int mode = [] {
+    // 0 (default): single-CTA kernel; 1: cluster kernel for every chain; 2: cluster kernel for the Euler chain only.
+    // Measured on B200 (16 members): the cluster kernel cuts a chain's latency 1.4-1.7x but costs
+    // ~20% more SM time, and the step is bound by SM time + optimizer HBM time, so the default stays 0.
     const char* e = getenv("FQLPOP_CHAIN2");
-    return e ? atoi(e) : 1;
+    return e ? atoi(e) : 0;
   }();
   if (!mode) return false;
   if (mode == 2 && L.job[0].iters <= 1) return false;  // 2: only the Euler chain (the step's longest serial path)

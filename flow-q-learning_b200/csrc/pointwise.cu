@@ -536,45 +536,56 @@ struct AdamArgs {
   __nv_bfloat16* tshadow;
   long long S;
   int nb;
+  int n_virtual;  // active members x nb
   const int* member_list;
   const float* adam_bc;
   float lr, b1, b2, eps, tau;
 };
-__global__ void __launch_bounds__(256) adam_kernel(const AdamArgs a) {
+// Persistent, deliberately NARROW grid (a few dozen CTAs of 1024 threads, grid-stride over every active member): the
+// optimizer is HBM-bound and needs bytes in flight, not SMs -- while a grid of thousands of small CTAs keeps every SM
+// partially occupied until it drains, which starves the layer-chain kernels of the other member groups (their CTAs
+// need a whole SM). With ~32 CTAs per launch the three optimizer launches of a group occupy well under 148 SMs and
+// overlap the chains. theta / mu / nu / target are touched once per step: streaming loads and stores (evict-first)
+// keep them from pushing the bf16 shadow weights -- which the next chains stream from L2 -- out of the cache.
+constexpr int kAdamThreads = 1024;
+__global__ void __launch_bounds__(kAdamThreads, 1) adam_kernel(const AdamArgs a) {
   long long tl_t0 = 0;
-  const bool tl_on = a.timeline && threadIdx.x == 0 && (blockIdx.x & 31) == 0;
+  const bool tl_on = a.timeline && threadIdx.x == 0;
   if (tl_on) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
-  const int am = blockIdx.y / a.nb, e = blockIdx.y - am * a.nb;
-  const int p = a.member_list[am];
-  const long long base = ((long long)p * a.nb + e) * a.S;
-  const float ibc1 = 1.f / a.adam_bc[2 * p], ibc2 = 1.f / a.adam_bc[2 * p + 1];
-  const long long n4 = a.S >> 2;
-  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
-    const long long o = base + 4 * i;
+  const int n4 = (int)(a.S >> 2);
+  const long long total = (long long)a.n_virtual * n4;
+  for (long long idx = (long long)blockIdx.x * kAdamThreads + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * kAdamThreads) {
+    const int av = (int)(idx / n4);
+    const int i = (int)(idx - (long long)av * n4);
+    const int am = av / a.nb, e = av - am * a.nb;
+    const int p = a.member_list[am];
+    const long long o = ((long long)p * a.nb + e) * a.S + 4ll * i;
+    const float ibc1 = 1.f / a.adam_bc[2 * p], ibc2 = 1.f / a.adam_bc[2 * p + 1];
     const float4 g = __ldcs(reinterpret_cast<const float4*>(a.grad + o));
-    float4 th = *reinterpret_cast<const float4*>(a.theta + o);
-    float4 m = *reinterpret_cast<const float4*>(a.mu + o);
-    float4 v = *reinterpret_cast<const float4*>(a.nu + o);
+    float4 th = __ldcs(reinterpret_cast<const float4*>(a.theta + o));
+    float4 m = __ldcs(reinterpret_cast<const float4*>(a.mu + o));
+    float4 v = __ldcs(reinterpret_cast<const float4*>(a.nu + o));
 #define ADAM1(c)                                                        \
   m.c = a.b1 * m.c + (1.f - a.b1) * g.c;                                \
   v.c = a.b2 * v.c + (1.f - a.b2) * g.c * g.c;                          \
   th.c = th.c - a.lr * (m.c * ibc1) / (sqrtf(v.c * ibc2) + a.eps);
     ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
 #undef ADAM1
-    *reinterpret_cast<float4*>(a.theta + o) = th;
-    *reinterpret_cast<float4*>(a.mu + o) = m;
-    *reinterpret_cast<float4*>(a.nu + o) = v;
+    __stcs(reinterpret_cast<float4*>(a.theta + o), th);
+    __stcs(reinterpret_cast<float4*>(a.mu + o), m);
+    __stcs(reinterpret_cast<float4*>(a.nu + o), v);
     uint2 s;
     s.x = pack_bf16x2(th.x, th.y);
     s.y = pack_bf16x2(th.z, th.w);
     *reinterpret_cast<uint2*>(a.shadow + o) = s;
     if (a.target) {
-      float4 tg = *reinterpret_cast<const float4*>(a.target + o);
+      float4 tg = __ldcs(reinterpret_cast<const float4*>(a.target + o));
       tg.x = a.tau * th.x + (1.f - a.tau) * tg.x;
       tg.y = a.tau * th.y + (1.f - a.tau) * tg.y;
       tg.z = a.tau * th.z + (1.f - a.tau) * tg.z;
       tg.w = a.tau * th.w + (1.f - a.tau) * tg.w;
-      *reinterpret_cast<float4*>(a.target + o) = tg;
+      __stcs(reinterpret_cast<float4*>(a.target + o), tg);
       uint2 ts;
       ts.x = pack_bf16x2(tg.x, tg.y);
       ts.y = pack_bf16x2(tg.z, tg.w);
@@ -787,9 +798,9 @@ static void launch_adam_one(Population* P, Arena& ar, cudaStream_t s) {
   a.lr = P->c.lr; a.b1 = P->c.adam_b1; a.b2 = P->c.adam_b2; a.eps = P->c.adam_eps; a.tau = P->c.tau;
   a.timeline = P->timeline;
   a.tag = (&ar == &P->critic ? 30 : (&ar == &P->bc ? 31 : 32)) | ((long long)P->g_off << 8);
-  const long long n4 = ar.L.S / 4;
-  const int gx = (int)((n4 + 256 * 4 - 1) / (256 * 4));  // 4 float4 per thread
-  adam_kernel<<<dim3(gx, (unsigned)(P->cur_n() * ar.L.nb)), 256, 0, s>>>(a);
+  a.n_virtual = P->cur_n() * ar.L.nb;
+  static const int ctas = [] { const char* e = getenv("FQLPOP_ADAM_CTAS"); return e ? atoi(e) : 32; }();
+  adam_kernel<<<ctas > 0 ? ctas : 32, kAdamThreads, 0, s>>>(a);
 }
 void launch_adam(Population* P, int which, cudaStream_t s) {
   launch_adam_one(P, which == 0 ? P->critic : (which == 1 ? P->bc : P->pi), s);

@@ -34,6 +34,9 @@ struct GroupPlan {
   // s[0..4]: compute branches of the step (high priority); s[5..7]: the three optimizer branches (low priority: their
   // grids flood every free SM and would otherwise delay the small head kernels of the other groups)
   cudaStream_t s[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  // low-priority twins of s[0..4]: the layer-chain launches (SM-filling, long) run here, so that whenever an SM frees
+  // up the short kernels between them (heads, weight gradients, optimizer) are served first
+  cudaStream_t c[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
   cudaGraph_t g_step = nullptr, g_loss = nullptr;
   cudaGraphExec_t x_step = nullptr, x_loss = nullptr;
   cudaEvent_t done = nullptr;
@@ -263,9 +266,13 @@ struct Builder {
 // ---------------------------------------------------------------------------------------------------
 // layer-chain job builders (chain.cu): one launch = a whole forward pass / Euler flow / input-gradient chain
 // ---------------------------------------------------------------------------------------------------
+void record(Plan* pl, cudaEvent_t* out, cudaStream_t s);
+
 struct ChainBuilder {
   Population* P;
   std::string* err;
+  GroupPlan* gp = nullptr;  // chain launches hop to the low-priority twin of their stream (FQLPOP_SCHED bit 2)
+  Plan* pl = nullptr;
   bool ok = true;
   ChainLaunch* L = nullptr;
   int count = 0;
@@ -300,10 +307,23 @@ struct ChainBuilder {
       const char* tl = getenv("FQLPOP_TRACE_LAUNCH");
       L->trace = (P->chain_trace && count == (tl ? atoi(tl) : 0) && P->g_off == 0) ? P->chain_trace : nullptr;
     }
-    cudaError_t e = launch_chain(*L, mode, s);
+    cudaStream_t run = s;
+    if (gp)
+      for (int i = 0; i < 5; ++i)
+        if (gp->s[i] == s) run = gp->c[i];
+    cudaEvent_t e_in = nullptr, e_out = nullptr;
+    if (run != s) {
+      record(pl, &e_in, s);
+      cudaStreamWaitEvent(run, e_in, 0);
+    }
+    cudaError_t e = launch_chain(*L, mode, run);
     if (e != cudaSuccess && ok) {
       ok = false;
       if (err) *err = std::string("launch_chain: ") + cudaGetErrorString(e);
+    }
+    if (run != s) {
+      record(pl, &e_out, run);
+      cudaStreamWaitEvent(s, e_out, 0);
     }
     ++count;
   }
@@ -418,7 +438,8 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   // schedule knobs (measured on B200): FQLPOP_SCHED bit 0 = critic forward / actor-critic pass
   // on their own streams (s3, s4) instead of queued behind s1 / s2; bit 1 = optimizer kernels on separate streams;
   // FQLPOP_ADAM_PRIO = priority of those streams (0 low, 1 same as compute)
-  static const int sched = [] { const char* e = getenv("FQLPOP_SCHED"); return e ? atoi(e) : 3; }();
+  static const int dbg_skip = [] { const char* e = getenv("FQLPOP_DEBUG_SKIP"); return e ? atoi(e) : 0; }();  // timing experiments only
+  static const int sched = [] { const char* e = getenv("FQLPOP_SCHED"); return e ? atoi(e) : 7; }();
   cudaStream_t s0 = gp.s[0], s1 = gp.s[1], s2 = gp.s[2];
   cudaStream_t s3 = (sched & 1) ? gp.s[3] : s1, s4 = (sched & 1) ? gp.s[4] : s2;
   const PopParams& c = P->c;
@@ -437,6 +458,7 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   if (s3 != s1) cudaStreamWaitEvent(s3, e_prep, 0);
 
   ChainBuilder cb{P, err};
+  if (sched & 4) { cb.gp = &gp; cb.pl = pl; }
   cb.L = new ChainLaunch;
   const bool chain = P->use_chain;
   // forward pass of one network over [row0, row0 + M) (+ a second, unsaved row range)
@@ -512,7 +534,7 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
     bwd_pass(P->QC, P->bQC, P->critic, nsub_q, true, nullptr, s1);
     b.begin(c.E);
     for (int l = 0; l <= nh_q; ++l) b.wgrad_group(P->QC, P->bQC, P->critic, l, 0);
-    b.launch(1, s1);
+    if (!(dbg_skip & 2)) b.launch(1, s1);
   }
 
   // ---- s2: BC flow forward/backward, then the critic pass on (s, clip(a_pi)) -----------------------
@@ -522,7 +544,7 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
     bwd_pass(P->BC, P->bBC, P->bc, nsub_a, true, nullptr, s2);
     b.begin(1);
     for (int l = 0; l <= nh_a; ++l) b.wgrad_group(P->BC, P->bBC, P->bc, l, 0);
-    b.launch(1, s2);
+    if (!(dbg_skip & 2)) b.launch(1, s2);
   }
   // critic pass on (s, clip(a_pi)): its own stream, as soon as the policy head is out
   cudaStreamWaitEvent(s4, e_pi, 0);
@@ -538,28 +560,28 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
     bwd_pass(P->PI, P->bPI, P->pi, nsub_a, true, nullptr, s0);
     b.begin(1);
     for (int l = 0; l <= nh_a; ++l) b.wgrad_group(P->PI, P->bPI, P->pi, l, 0);
-    b.launch(1, s0);
+    if (!(dbg_skip & 2)) b.launch(1, s0);
     // the optimizer branches run on the low-priority streams
     cudaStream_t a0 = (sched & 2) ? gp.s[5] : s1, a1 = (sched & 2) ? gp.s[6] : s2, a2 = (sched & 2) ? gp.s[7] : s0;
     cudaEvent_t e_w0, e_w1, e_w2, e_a0, e_a1, e_a2;
     record(pl, &e_w2, s0);
     cudaStreamWaitEvent(a2, e_w2, 0);
-    launch_small_grads(P, 2, a2); ++pw;
-    launch_adam(P, 2, a2); ++pw;
+    if (!(dbg_skip & 4)) { launch_small_grads(P, 2, a2); ++pw; }
+    if (!(dbg_skip & 1)) { launch_adam(P, 2, a2); ++pw; }
     record(pl, &e_a2, a2);
     // critic optimizer: after every reader of the critic weights (QA chain on s4) is done
     record(pl, &e_w0, s1);
     cudaStreamWaitEvent(a0, e_w0, 0);
     cudaStreamWaitEvent(a0, e_qa, 0);
-    launch_small_grads(P, 0, a0); ++pw;
-    launch_adam(P, 0, a0); ++pw;
+    if (!(dbg_skip & 4)) { launch_small_grads(P, 0, a0); ++pw; }
+    if (!(dbg_skip & 1)) { launch_adam(P, 0, a0); ++pw; }
     record(pl, &e_a0, a0);
     // BC flow optimizer: after the Euler chain (s0) has stopped reading the BC weights
     record(pl, &e_w1, s2);
     cudaStreamWaitEvent(a1, e_w1, 0);
     cudaStreamWaitEvent(a1, e_euler, 0);
-    launch_small_grads(P, 1, a1); ++pw;
-    launch_adam(P, 1, a1); ++pw;
+    if (!(dbg_skip & 4)) { launch_small_grads(P, 1, a1); ++pw; }
+    if (!(dbg_skip & 1)) { launch_adam(P, 1, a1); ++pw; }
     record(pl, &e_a1, a1);
     cudaStreamWaitEvent(s0, e_a0, 0);
     cudaStreamWaitEvent(s0, e_a1, 0);
@@ -597,6 +619,8 @@ void destroy_groups(Plan* pl) {
   for (GroupPlan& g : pl->groups) {
     for (int i = 0; i < 8; ++i)
       if (g.s[i]) cudaStreamDestroy(g.s[i]);
+    for (int i = 0; i < 5; ++i)
+      if (g.c[i]) cudaStreamDestroy(g.c[i]);
     if (g.done) cudaEventDestroy(g.done);
   }
   pl->groups.clear();
@@ -619,10 +643,11 @@ int make_groups(Population* P, std::string* err) {
     gp.n = (int)((long long)n * (g + 1) / G) - gp.off;
     int prio_lo = 0, prio_hi = 0;  // numerically: lowest priority, highest priority
     const char* ape = getenv("FQLPOP_ADAM_PRIO");
-    const int adam_prio = ape ? atoi(ape) : 0;
+    const int adam_prio = ape ? atoi(ape) : 1;
     CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     for (int i = 0; i < 8; ++i)
       CK(cudaStreamCreateWithPriority(&gp.s[i], cudaStreamNonBlocking, (i < 5 || adam_prio) ? prio_hi : prio_lo));
+    for (int i = 0; i < 5; ++i) CK(cudaStreamCreateWithPriority(&gp.c[i], cudaStreamNonBlocking, prio_lo));
     CK(cudaEventCreateWithFlags(&gp.done, cudaEventDisableTiming));
   }
   return 0;
@@ -868,6 +893,35 @@ int pop_refresh_shadow_impl(Population* P, cudaStream_t stream, std::string* err
   return 0;
 }
 int pop_launches_per_step(const Population* P) { return P->plan ? P->plan->launches_per_step : 0; }
+
+// (measurement) `iters` back-to-back launches, on `stream`, of one layer-chain launch of the step covering every
+// active member: which = 0 the Euler flow chain, 1 the one-step policy forward pass (3B rows, first B saved).
+// The pass buffers must hold a step's inputs (call after fqlpop_step). Leaves the population state untouched except
+// for those scratch buffers.
+int pop_debug_chain_launch(Population* P, int which, int iters, cudaStream_t stream, std::string* err) {
+  if (!P->use_chain) {
+    if (err) *err = "layer-chain kernels are not in use for this shape";
+    return 1;
+  }
+  ChainBuilder cb{P, err};
+  cb.L = new ChainLaunch;
+  const int B = P->c.B;
+  for (int i = 0; i < iters && cb.ok; ++i) {
+    if (which == 0) {
+      cb.begin(1);
+      cb.euler_job();
+    } else {
+      cb.begin(P->pi.L.nb);
+      cb.fwd_job(P->PI, P->pi, P->pi.theta, P->pi.shadow, 0, B, true);
+      cb.fwd_job(P->PI, P->pi, P->pi.theta, P->pi.shadow, B, 2 * B, false);
+    }
+    cb.launch(0, stream);
+  }
+  delete cb.L;
+  if (!cb.ok) return 1;
+  CK(cudaGetLastError());
+  return 0;
+}
 
 // leaf I/O: kind 0 kernel [nb][K_true][N_true], 1 bias [nb][N_true], 2 LayerNorm scale, 3 LayerNorm bias [nb][H];
 // which 0 theta, 1 mu, 2 nu, 3 target, 4 grad. Host buffers are unpadded fp32.

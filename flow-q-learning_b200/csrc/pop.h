@@ -158,6 +158,7 @@ int pop_total_loss_impl(Population* p, cudaStream_t stream, std::string* err);
 int pop_refresh_shadow_impl(Population* p, cudaStream_t stream, std::string* err);
 void pop_invalidate_plan(Population* p);
 int pop_launches_per_step(const Population* p);
+int pop_debug_chain_launch(Population* p, int which, int iters, cudaStream_t stream, std::string* err);
 int pop_leaf_io(Population* p, int net, int layer, int kind, int which, int member, float* host, int to_host,
                 std::string* err);
 
