@@ -125,7 +125,9 @@ struct EpiCtx {
 };
 
 // (debug) clock stamp with a site id; only the traced thread has C.tr != nullptr
+// Compiled in only with -DFQLPOP_EPI_TRACE (make TRACE=1): even the dormant branch costs registers in the epilogue.
 __device__ __forceinline__ void stamp(const EpiCtx& C, int id) {
+#ifdef FQLPOP_EPI_TRACE
   if (C.tr) {
     const long long i = C.tr[0];
     if (i < 1900) {
@@ -134,7 +136,13 @@ __device__ __forceinline__ void stamp(const EpiCtx& C, int id) {
       C.tr[0] = i + 1;
     }
   }
+#endif
 }
+
+// CL = cluster kernel. The single-CTA kernel instantiates everything with CL = false: offsets fold to 0 and the
+// publish hooks vanish at compile time.
+template <bool CL> __device__ __forceinline__ int goff(const EpiCtx& C) { return CL ? C.g_off : 0; }
+template <bool CL> __device__ __forceinline__ uint32_t tmoff(const EpiCtx& C) { return CL ? (uint32_t)C.tm_off : 0u; }
 
 // ---------------------------------------------------------------------------------------------------------------
 // Staged global traffic. A "block" is 32 rows x 64 bf16 columns = 32 x 128 bytes in shared memory, 16-byte chunk c
@@ -300,12 +308,13 @@ __device__ __forceinline__ void publish_block(const EpiCtx& C, int gblk);
 // This warp's part of accumulator tile `tile` (its 32 rows x its 128 columns = two 64-column blocks of ACT) -> global
 // rows of `dst` ([rows][H] bf16, already offset to the job's row 0 of virtual member 0), optionally with the per-column
 // sums over the warp's rows -> part[part_off + column].
+template <bool CL>
 __device__ __forceinline__ void copy_out_act(const EpiCtx& C, int tile, int n_pad, __nv_bfloat16* dst, long long wofs,
                                              float* part) {
   const int nblk = tile_chunks16(C, tile, n_pad) >> 2;
   const int col0 = tile * kTileN + C.half * 128;
   for (int b = 0; b < nblk; ++b) {
-    const int col = C.g_off + col0 + b * 64;
+    const int col = goff<CL>(C) + col0 + b * 64;
     const uint8_t* blk = C.act + (col >> 6) * kActBlockBytes + C.q * (32 * 128);
     if (part) copy_out_block_colsum(blk, dst + wofs + col, C.H, C.lane, C.rows_valid, part + C.part_off + col);
     else copy_out_block(blk, dst + wofs + col, C.H, C.lane, C.rows_valid);
@@ -318,13 +327,14 @@ __device__ __forceinline__ void copy_out_act(const EpiCtx& C, int tile, int n_pa
 // Pass 1 over this thread's chunks of one accumulator tile: bias + GELU (+ act'(z) for the backward pass, staged and
 // copied out per 64-column block); the bf16 result is parked in the drained TMEM columns or -- `direct` -- written
 // to ACT (the caller copies h out of ACT once the layer has been handed to the tensor core).
-template <bool LN, bool SAVE>
-__device__ __forceinline__ void fwd_chunk(const EpiCtx& C, const float* bias, const uint32_t (&rr)[16], int col0, int c,
-                                          bool direct, float& s1, float& s2) {
-  const int col = col0 + c * 16;
-  float4 b4[4];
+__device__ __forceinline__ void ld_bias16(const float* bias, int col, float4 (&b4)[4]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) b4[i] = __ldg(reinterpret_cast<const float4*>(bias + col) + i);
+}
+template <bool LN, bool SAVE, bool CL>
+__device__ __forceinline__ void fwd_chunk(const EpiCtx& C, const float4 (&b4)[4], const uint32_t (&rr)[16], int col0, int c,
+                                          bool direct, float& s1, float& s2) {
+  const int col = col0 + c * 16;
   uint32_t pk[8], gpk[8];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -345,20 +355,20 @@ __device__ __forceinline__ void fwd_chunk(const EpiCtx& C, const float* bias, co
     }
   }
   if (SAVE) st_stage16(C.stg, C.lane, (c & 3) * 16, gpk);
-  if (direct) st_act16(C.act, C.r, C.g_off + col, pk);
-  else tmem_st8(C.tmem_row + C.tm_off + col0 + c * 8, pk);
+  if (direct) st_act16(C.act, C.r, goff<CL>(C) + col, pk);
+  else tmem_st8(C.tmem_row + tmoff<CL>(C) + col0 + c * 8, pk);
 }
 // DB: the accumulator chunks are double-buffered in registers -- the TMEM load of chunk c + 1 is in flight while chunk c
 // is being computed (tcgen05.wait::ld waits for every outstanding load, so the next one is issued right after the
 // wait). Pays off in the cluster kernel (one pass per layer, nothing else to overlap with); the single-CTA kernel,
 // whose passes already overlap the other tile's MMAs, is faster with the plain loop (fewer live registers).
-template <bool LN, bool SAVE, bool DB>
+template <bool LN, bool SAVE, bool DB, bool CL = DB>
 __device__ __forceinline__ void fwd_pass1(const EpiCtx& C, const ChainLayer& Ly, int tile, bool direct, float& s1, float& s2) {
   const int nch = tile_chunks16(C, tile, Ly.n_pad);  // a multiple of 4
   if (nch == 0) return;
   const int col0 = tile * kTileN + C.half * 128;
-  const float* bias = C.params + Ly.off_b + C.g_off;
-  const uint32_t tbase = C.tmem_row + C.tm_off + col0;
+  const float* bias = C.params + Ly.off_b + goff<CL>(C);
+  const uint32_t tbase = C.tmem_row + tmoff<CL>(C) + col0;
   uint32_t ra[16], rb[16];
   if (DB) tmem_ld16(tbase, ra);
 #pragma unroll 1
@@ -366,33 +376,38 @@ __device__ __forceinline__ void fwd_pass1(const EpiCtx& C, const ChainLayer& Ly,
     if (DB) {
 #pragma unroll 1
       for (int c = cb; c < cb + 4; c += 2) {
+        float4 b4[4];
+        ld_bias16(bias, col0 + c * 16, b4);
         tmem_ld_wait();
         tmem_ld16(tbase + (c + 1) * 16, rb);
-        fwd_chunk<LN, SAVE>(C, bias, ra, col0, c, direct, s1, s2);
+        fwd_chunk<LN, SAVE, CL>(C, b4, ra, col0, c, direct, s1, s2);
+        ld_bias16(bias, col0 + (c + 1) * 16, b4);
         tmem_ld_wait();
         if (c + 2 < nch) tmem_ld16(tbase + (c + 2) * 16, ra);
-        fwd_chunk<LN, SAVE>(C, bias, rb, col0, c + 1, direct, s1, s2);
+        fwd_chunk<LN, SAVE, CL>(C, b4, rb, col0, c + 1, direct, s1, s2);
       }
     } else {
 #pragma unroll 1
       for (int c = cb; c < cb + 4; ++c) {
+        float4 b4[4];
+        ld_bias16(bias, col0 + c * 16, b4);
         tmem_ld16(tbase + c * 16, ra);
         tmem_ld_wait();
-        fwd_chunk<LN, SAVE>(C, bias, ra, col0, c, direct, s1, s2);
+        fwd_chunk<LN, SAVE, CL>(C, b4, ra, col0, c, direct, s1, s2);
       }
     }
     if (SAVE) {
       __syncwarp();
-      copy_out_block(C.stg, Ly.out_gp + C.wrow + C.g_off + col0 + cb * 16, C.H, C.lane, C.rows_valid);
+      copy_out_block(C.stg, Ly.out_gp + C.wrow + goff<CL>(C) + col0 + cb * 16, C.H, C.lane, C.rows_valid);
       __syncwarp();
     }
-    if (direct && C.cl) publish_block(C, (C.g_off + col0 + cb * 16) >> 6);
+    if (CL && direct) publish_block(C, (goff<CL>(C) + col0 + cb * 16) >> 6);
   }
 }
 
 // Parked tile -> ACT; LayerNorm layers normalise on the way: x = (g - mean) rstd, h = x gamma + beta (xhat staged and
 // copied out per 64-column block).
-template <bool LN, bool SAVE>
+template <bool LN, bool SAVE, bool CL>
 __device__ __forceinline__ void fwd_flush(const EpiCtx& C, const ChainLayer& Ly, int tile, float mean, float rstd) {
   const int nch = tile_chunks16(C, tile, Ly.n_pad);
   if (nch == 0) return;
@@ -406,11 +421,11 @@ __device__ __forceinline__ void fwd_flush(const EpiCtx& C, const ChainLayer& Ly,
     for (int c4 = 0; c4 < 4; ++c4) {
       const int c = cb + c4;
       const int col = col0 + c * 16;
-      tmem_ld8(C.tmem_row + C.tm_off + col0 + c * 8, pr);
+      tmem_ld8(C.tmem_row + tmoff<CL>(C) + col0 + c * 8, pr);
       tmem_ld_wait();
       if (LN) {
-        const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + C.g_off + col);
-        const float4* e4 = reinterpret_cast<const float4*>(C.params + Ly.off_beta + C.g_off + col);
+        const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + goff<CL>(C) + col);
+        const float4* e4 = reinterpret_cast<const float4*>(C.params + Ly.off_beta + goff<CL>(C) + col);
         uint32_t hk[8], xk[8];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -423,18 +438,18 @@ __device__ __forceinline__ void fwd_flush(const EpiCtx& C, const ChainLayer& Ly,
           hk[2 * i] = pack_bf16x2(fmaf(x0, ga.x, be.x), fmaf(x1, ga.y, be.y));
           hk[2 * i + 1] = pack_bf16x2(fmaf(x2, ga.z, be.z), fmaf(x3, ga.w, be.w));
         }
-        st_act16(C.act, C.r, C.g_off + col, hk);
+        st_act16(C.act, C.r, goff<CL>(C) + col, hk);
         if (save_x) st_stage16(C.stg, C.lane, c4 * 16, xk);
       } else {
-        st_act16(C.act, C.r, C.g_off + col, pr);
+        st_act16(C.act, C.r, goff<CL>(C) + col, pr);
       }
     }
     if (save_x) {
       __syncwarp();
-      copy_out_block(C.stg, Ly.out_xhat + C.wrow + C.g_off + col0 + cb * 16, C.H, C.lane, C.rows_valid);
+      copy_out_block(C.stg, Ly.out_xhat + C.wrow + goff<CL>(C) + col0 + cb * 16, C.H, C.lane, C.rows_valid);
       __syncwarp();
     }
-    if (C.cl) publish_block(C, (C.g_off + col0 + cb * 16) >> 6);
+    if (CL) publish_block(C, (goff<CL>(C) + col0 + cb * 16) >> 6);
   }
 }
 
@@ -452,6 +467,7 @@ __device__ __forceinline__ void exchange_row_sums(const EpiCtx& C, float& t1, fl
 
 template <bool LN, bool SAVE>
 __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& fullph, const ChainLayer& Ly) {
+  constexpr bool CL = false;
   const int n_tiles = (Ly.n_pad + kTileN - 1) / kTileN;
   float s1 = 0.f, s2 = 0.f;
   if (!LN) {
@@ -468,7 +484,7 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
       tmem_st_wait();
       stamp(C, 14);
       wait_tile(C, fullph, 1);  // every MMA of the layer has retired: ACT may be overwritten
-      fwd_flush<false, SAVE>(C, Ly, 0, 0.f, 1.f);
+      fwd_flush<false, SAVE, CL>(C, Ly, 0, 0.f, 1.f);
       stamp(C, 15);
       release(C.act_lo);
       stamp(C, 16);
@@ -480,7 +496,7 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
     // h -> HBM out of ACT, off the hand-off path: these rows of ACT are next written by this very warp
     if (Ly.out_h) {
       __syncwarp();
-      for (int t = 0; t < n_tiles; ++t) copy_out_act(C, t, Ly.n_pad, Ly.out_h, C.wrow, nullptr);
+      for (int t = 0; t < n_tiles; ++t) copy_out_act<CL>(C, t, Ly.n_pad, Ly.out_h, C.wrow, nullptr);
     }
   } else {
     wait_tile(C, fullph, 0);
@@ -505,15 +521,15 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
     if (C.row_ok && C.half == 0 && Ly.out_rstd) Ly.out_rstd[C.rs_off] = rstd;
     // LayerNorm layers copy h out BEFORE the hand-off: the next layer's row-sum exchange reuses the head of ACT and
     // must not overtake a slower warp's copy
-    fwd_flush<true, SAVE>(C, Ly, 0, mean, rstd);
+    fwd_flush<true, SAVE, CL>(C, Ly, 0, mean, rstd);
     stamp(C, 25);
-    if (Ly.out_h) { __syncwarp(); copy_out_act(C, 0, Ly.n_pad, Ly.out_h, C.wrow, nullptr); }
+    if (Ly.out_h) { __syncwarp(); copy_out_act<CL>(C, 0, Ly.n_pad, Ly.out_h, C.wrow, nullptr); }
     release(C.act_lo);
     stamp(C, 26);
     if (n_tiles > 1) {
-      fwd_flush<true, SAVE>(C, Ly, 1, mean, rstd);
+      fwd_flush<true, SAVE, CL>(C, Ly, 1, mean, rstd);
       stamp(C, 27);
-      if (Ly.out_h) { __syncwarp(); copy_out_act(C, 1, Ly.n_pad, Ly.out_h, C.wrow, nullptr); }
+      if (Ly.out_h) { __syncwarp(); copy_out_act<CL>(C, 1, Ly.n_pad, Ly.out_h, C.wrow, nullptr); }
     }
     release(C.act_hi);
     stamp(C, 28);
@@ -524,14 +540,16 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
 // backward hidden layer: dz = act'(z) * LNbwd?(acc), acc = dz_next W^T
 // ---------------------------------------------------------------------------------------------------------------
 // act'(z) of block `blk` (64 columns) of this warp's part of tile `tile` -> staging (asynchronous)
+template <bool CL>
 __device__ __forceinline__ void bwd_prefetch_gp(const EpiCtx& C, const ChainLayer& Ly, int tile, int blk) {
   if (!Ly.gp) return;
   if (blk * 4 >= tile_chunks16(C, tile, Ly.n_pad)) return;
-  stage_in_block(C.stg, Ly.gp + C.wrow + C.g_off + tile * kTileN + C.half * 128 + blk * 64, C.H, C.lane, C.rows_valid);
+  stage_in_block(C.stg, Ly.gp + C.wrow + goff<CL>(C) + tile * kTileN + C.half * 128 + blk * 64, C.H, C.lane, C.rows_valid);
 }
 
 // no LayerNorm: one pass, parked or direct exactly like the forward layer. The first block of act'(z) has been
 // prefetched by the caller; `next_tile` >= 0 prefetches that tile's first block on the way out.
+template <bool CL>
 __device__ __forceinline__ void bwd_pass1(const EpiCtx& C, const ChainLayer& Ly, int tile, bool direct, int next_tile) {
   const int nch = tile_chunks16(C, tile, Ly.n_pad);
   if (nch == 0) return;
@@ -554,24 +572,25 @@ __device__ __forceinline__ void bwd_pass1(const EpiCtx& C, const ChainLayer& Ly,
 #pragma unroll
         for (int i = 0; i < 8; ++i) gw[i] = C.row_ok ? 0x3F803F80u : 0u;  // bf16 (1, 1) / (0, 0)
       }
-      tmem_ld16(C.tmem_row + C.tm_off + col, rr);
+      tmem_ld16(C.tmem_row + tmoff<CL>(C) + col, rr);
       tmem_ld_wait();
       uint32_t pk[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i)
         pk[i] = pack_bf16x2(__uint_as_float(rr[2 * i]) * bf16_lo(gw[i]),
                             __uint_as_float(rr[2 * i + 1]) * bf16_hi(gw[i]));
-      if (direct) st_act16(C.act, C.r, C.g_off + col, pk);
-      else tmem_st8(C.tmem_row + C.tm_off + col0 + c * 8, pk);
+      if (direct) st_act16(C.act, C.r, goff<CL>(C) + col, pk);
+      else tmem_st8(C.tmem_row + tmoff<CL>(C) + col0 + c * 8, pk);
     }
     if (has_gp) {
       __syncwarp();
-      if (cb + 4 < nch) bwd_prefetch_gp(C, Ly, tile, (cb >> 2) + 1);
-      else if (next_tile >= 0) bwd_prefetch_gp(C, Ly, next_tile, 0);
+      if (cb + 4 < nch) bwd_prefetch_gp<CL>(C, Ly, tile, (cb >> 2) + 1);
+      else if (next_tile >= 0) bwd_prefetch_gp<CL>(C, Ly, next_tile, 0);
     }
-    if (direct && C.cl) publish_block(C, (C.g_off + col0 + cb * 16) >> 6);
+    if (CL && direct) publish_block(C, (goff<CL>(C) + col0 + cb * 16) >> 6);
   }
 }
+template <bool CL>
 __device__ __forceinline__ void bwd_flush(const EpiCtx& C, const ChainLayer& Ly, int tile) {
   const int nch = tile_chunks16(C, tile, Ly.n_pad);
   if (nch == 0) return;
@@ -580,24 +599,26 @@ __device__ __forceinline__ void bwd_flush(const EpiCtx& C, const ChainLayer& Ly,
   for (int cp = 0; cp < nch; cp += 4) {
     uint32_t pr[4][8];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) tmem_ld8(C.tmem_row + C.tm_off + col0 + (cp + j) * 8, pr[j]);
+    for (int j = 0; j < 4; ++j) tmem_ld8(C.tmem_row + tmoff<CL>(C) + col0 + (cp + j) * 8, pr[j]);
     tmem_ld_wait();
 #pragma unroll
-    for (int j = 0; j < 4; ++j) st_act16(C.act, C.r, C.g_off + col0 + (cp + j) * 16, pr[j]);
+    for (int j = 0; j < 4; ++j) st_act16(C.act, C.r, goff<CL>(C) + col0 + (cp + j) * 16, pr[j]);
   }
 }
 
 // LayerNorm backward works on half blocks (32 columns): the staging block holds two of them.
 // sub-block `sb` (0 .. 3 within the tile's 128 columns of this warp) of a saved tensor -> staging slot `slot`
+template <bool CL>
 __device__ __forceinline__ void ln_prefetch(const EpiCtx& C, const __nv_bfloat16* src, int n_pad, int tile, int sb, int slot) {
   if (sb * 2 >= tile_chunks16(C, tile, n_pad)) return;
-  stage_in_half(C.stg + slot * 2048, src + C.wrow + C.g_off + tile * kTileN + C.half * 128 + sb * 32, C.H, C.lane, C.rows_valid);
+  stage_in_half(C.stg + slot * 2048, src + C.wrow + goff<CL>(C) + tile * kTileN + C.half * 128 + sb * 32, C.H, C.lane, C.rows_valid);
 }
 
 // LayerNorm, statistics pass (overlaps the MMAs of the other tile; the accumulator stays in TMEM untouched):
 // h = xhat gamma + beta, acc = dL/dh  ->  dxhat = acc gamma; s1 = sum dxhat, s2 = sum dxhat xhat;
 // partial column sums dbeta = colsum(acc), dgamma = colsum(acc xhat). xhat is double-buffered through the two
 // staging slots; sub-block 0 has been prefetched into slot 0 by the caller.
+template <bool CL>
 __device__ __forceinline__ void bwd_ln_stats(const EpiCtx& C, const ChainLayer& Ly, int tile, int next_tile, float& s1, float& s2) {
   const int nch = tile_chunks16(C, tile, Ly.n_pad);
   if (nch == 0) return;
@@ -608,16 +629,16 @@ __device__ __forceinline__ void bwd_ln_stats(const EpiCtx& C, const ChainLayer& 
   for (int sb = 0; sb < nsb; ++sb) {
     cp_async_wait_all();
     __syncwarp();
-    if (sb + 1 < nsb) ln_prefetch(C, Ly.xhat, Ly.n_pad, tile, sb + 1, (sb + 1) & 1);
-    else if (next_tile >= 0) ln_prefetch(C, Ly.xhat, Ly.n_pad, next_tile, 0, (sb + 1) & 1);
+    if (sb + 1 < nsb) ln_prefetch<CL>(C, Ly.xhat, Ly.n_pad, tile, sb + 1, (sb + 1) & 1);
+    else if (next_tile >= 0) ln_prefetch<CL>(C, Ly.xhat, Ly.n_pad, next_tile, 0, (sb + 1) & 1);
     const uint8_t* slot = C.stg + (sb & 1) * 2048;
 #pragma unroll 1
     for (int ch = 0; ch < 2; ++ch) {
       const int col = col0 + sb * 32 + ch * 16;
       uint32_t xw[8];
       ld_half16(slot, C.lane, ch * 16, xw);
-      const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + C.g_off + col);
-      tmem_ld16(C.tmem_row + C.tm_off + col, rr);
+      const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + goff<CL>(C) + col);
+      tmem_ld16(C.tmem_row + tmoff<CL>(C) + col, rr);
       tmem_ld_wait();
       float t0[16], t1[16];
 #pragma unroll
@@ -642,8 +663,8 @@ __device__ __forceinline__ void bwd_ln_stats(const EpiCtx& C, const ChainLayer& 
         const float cb = warp_colsum16(t0, C.lane);
         const float cg = warp_colsum16(t1, C.lane);
         if (C.lane < 16) {
-          Ly.dbeta_part[C.part_off + C.g_off + col + C.lane] = cb;
-          Ly.dgamma_part[C.part_off + C.g_off + col + C.lane] = cg;
+          Ly.dbeta_part[C.part_off + goff<CL>(C) + col + C.lane] = cb;
+          Ly.dgamma_part[C.part_off + goff<CL>(C) + col + C.lane] = cg;
         }
       }
     }
@@ -651,6 +672,7 @@ __device__ __forceinline__ void bwd_ln_stats(const EpiCtx& C, const ChainLayer& 
 }
 // LayerNorm, output pass: dg = rstd (dxhat - mean(dxhat) - xhat mean(dxhat xhat)); dz = act'(z) dg -> ACT.
 // Slot 0 = xhat, slot 1 = act'(z) of the current 32-column sub-block.
+template <bool CL>
 __device__ __forceinline__ void bwd_ln_out(const EpiCtx& C, const ChainLayer& Ly, int tile, float c1, float c2, float rstd) {
   const int nch = tile_chunks16(C, tile, Ly.n_pad);
   if (nch == 0) return;
@@ -662,8 +684,8 @@ __device__ __forceinline__ void bwd_ln_out(const EpiCtx& C, const ChainLayer& Ly
 #pragma unroll 1
   for (int sb = 0; sb < nsb; ++sb) {
     __syncwarp();  // the previous sub-block has been read by every lane
-    ln_prefetch(C, Ly.xhat, Ly.n_pad, tile, sb, 0);
-    if (has_gp) ln_prefetch(C, Ly.gp, Ly.n_pad, tile, sb, 1);
+    ln_prefetch<CL>(C, Ly.xhat, Ly.n_pad, tile, sb, 0);
+    if (has_gp) ln_prefetch<CL>(C, Ly.gp, Ly.n_pad, tile, sb, 1);
     cp_async_wait_all();
     __syncwarp();
 #pragma unroll 1
@@ -676,8 +698,8 @@ __device__ __forceinline__ void bwd_ln_out(const EpiCtx& C, const ChainLayer& Ly
 #pragma unroll
         for (int i = 0; i < 8; ++i) gw[i] = C.row_ok ? 0x3F803F80u : 0u;
       }
-      const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + C.g_off + col);
-      tmem_ld16(C.tmem_row + C.tm_off + col, rr);
+      const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + goff<CL>(C) + col);
+      tmem_ld16(C.tmem_row + tmoff<CL>(C) + col, rr);
       tmem_ld_wait();
       uint32_t pk[8];
 #pragma unroll
@@ -696,54 +718,55 @@ __device__ __forceinline__ void bwd_ln_out(const EpiCtx& C, const ChainLayer& Ly
         pk[2 * i] = pack_bf16x2(dz[0], dz[1]);
         pk[2 * i + 1] = pack_bf16x2(dz[2], dz[3]);
       }
-      st_act16(C.act, C.r, C.g_off + col, pk);
+      st_act16(C.act, C.r, goff<CL>(C) + col, pk);
     }
-    if (C.cl && (sb & 1)) publish_block(C, (C.g_off + col0 + sb * 32) >> 6);
+    if (CL && (sb & 1)) publish_block(C, (goff<CL>(C) + col0 + sb * 32) >> 6);
   }
 }
 
 template <bool LN>
 __device__ __forceinline__ void bwd_hidden_layer(const EpiCtx& C, uint32_t& fullph, const ChainLayer& Ly) {
+  constexpr bool CL = false;
   const int n_tiles = (Ly.n_pad + kTileN - 1) / kTileN;
   if (!LN) {
-    bwd_prefetch_gp(C, Ly, 0, 0);
+    bwd_prefetch_gp<CL>(C, Ly, 0, 0);
     wait_tile(C, fullph, 0);
     stamp(C, 10);
     if (n_tiles == 1) {
-      bwd_pass1(C, Ly, 0, true, -1);
+      bwd_pass1<CL>(C, Ly, 0, true, -1);
       stamp(C, 11);
       release(C.act_lo);
       stamp(C, 12);
     } else {
-      bwd_pass1(C, Ly, 0, false, 1);
+      bwd_pass1<CL>(C, Ly, 0, false, 1);
       stamp(C, 13);
       tmem_st_wait();
       stamp(C, 14);
       wait_tile(C, fullph, 1);
       stamp(C, 15);
-      bwd_flush(C, Ly, 0);
+      bwd_flush<CL>(C, Ly, 0);
       stamp(C, 16);
       release(C.act_lo);
       stamp(C, 17);
-      bwd_pass1(C, Ly, 1, true, -1);
+      bwd_pass1<CL>(C, Ly, 1, true, -1);
       stamp(C, 18);
     }
     release(C.act_hi);
     stamp(C, 19);
     // dz -> HBM (+ bias-gradient partial sums) out of ACT, off the hand-off path
     __syncwarp();
-    for (int t = 0; t < n_tiles; ++t) copy_out_act(C, t, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
+    for (int t = 0; t < n_tiles; ++t) copy_out_act<CL>(C, t, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
   } else {
     float s1 = 0.f, s2 = 0.f;
-    ln_prefetch(C, Ly.xhat, Ly.n_pad, 0, 0, 0);
+    ln_prefetch<CL>(C, Ly.xhat, Ly.n_pad, 0, 0, 0);
     wait_tile(C, fullph, 0);
     stamp(C, 20);
-    bwd_ln_stats(C, Ly, 0, n_tiles > 1 ? 1 : -1, s1, s2);
+    bwd_ln_stats<CL>(C, Ly, 0, n_tiles > 1 ? 1 : -1, s1, s2);
     stamp(C, 21);
     if (n_tiles > 1) {
       wait_tile(C, fullph, 1);
       stamp(C, 22);
-      bwd_ln_stats(C, Ly, 1, -1, s1, s2);
+      bwd_ln_stats<CL>(C, Ly, 1, -1, s1, s2);
       stamp(C, 23);
     }
     float t1 = s1, t2 = s2;
@@ -752,17 +775,17 @@ __device__ __forceinline__ void bwd_hidden_layer(const EpiCtx& C, uint32_t& full
     const float inv_n = 1.0f / (float)C.H;
     const float rstd = C.row_ok ? __ldg(Ly.rstd + C.rs_off) : 0.f;
     // copies happen before the hand-off (see fwd_hidden_layer)
-    bwd_ln_out(C, Ly, 0, t1 * inv_n, t2 * inv_n, rstd);
+    bwd_ln_out<CL>(C, Ly, 0, t1 * inv_n, t2 * inv_n, rstd);
     stamp(C, 25);
     __syncwarp();
-    copy_out_act(C, 0, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
+    copy_out_act<CL>(C, 0, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
     release(C.act_lo);
     stamp(C, 26);
     if (n_tiles > 1) {
-      bwd_ln_out(C, Ly, 1, t1 * inv_n, t2 * inv_n, rstd);
+      bwd_ln_out<CL>(C, Ly, 1, t1 * inv_n, t2 * inv_n, rstd);
       stamp(C, 27);
       __syncwarp();
-      copy_out_act(C, 1, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
+      copy_out_act<CL>(C, 1, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
     }
     release(C.act_hi);
     stamp(C, 28);
@@ -851,36 +874,36 @@ __device__ __forceinline__ void fwd2_hidden_layer(EpiCtx& C, const Cl2& X, const
     const float var = fmaxf(t2 * inv_n - mean * mean, 0.f);
     const float rstd = rsqrtf(var + C.ln_eps);
     if (C.row_ok && C.half == 0 && C.g_off == 0 && Ly.out_rstd) Ly.out_rstd[C.rs_off] = rstd;
-    fwd_flush<true, SAVE>(C, Ly, 0, mean, rstd);
+    fwd_flush<true, SAVE, true>(C, Ly, 0, mean, rstd);
   }
   stamp(C, 41);
   if (Ly.out_h) {
     __syncwarp();
-    copy_out_act(C, 0, Ly.n_pad, Ly.out_h, C.wrow, nullptr);
+    copy_out_act<true>(C, 0, Ly.n_pad, Ly.out_h, C.wrow, nullptr);
   }
   stamp(C, 42);
 }
 
 template <bool LN>
 __device__ __forceinline__ void bwd2_hidden_layer(EpiCtx& C, const Cl2& X, const ChainLayer& Ly, int lc, int lnc) {
-  if (!LN) bwd_prefetch_gp(C, Ly, 0, 0);
-  else ln_prefetch(C, Ly.xhat, Ly.n_pad, 0, 0, 0);
+  if (!LN) bwd_prefetch_gp<true>(C, Ly, 0, 0);
+  else ln_prefetch<true>(C, Ly.xhat, Ly.n_pad, 0, 0, 0);
   c2_begin_layer(C, X, lc);
   stamp(C, 50);
   if (!LN) {
-    bwd_pass1(C, Ly, 0, true, -1);
+    bwd_pass1<true>(C, Ly, 0, true, -1);
   } else {
     float s1 = 0.f, s2 = 0.f;
-    bwd_ln_stats(C, Ly, 0, -1, s1, s2);
+    bwd_ln_stats<true>(C, Ly, 0, -1, s1, s2);
     float t1 = s1, t2 = s2;
     exchange_row_sums2(C, X, lnc, t1, t2);
     const float inv_n = 1.0f / (float)C.H;
     const float rstd = C.row_ok ? __ldg(Ly.rstd + C.rs_off) : 0.f;
-    bwd_ln_out(C, Ly, 0, t1 * inv_n, t2 * inv_n, rstd);
+    bwd_ln_out<true>(C, Ly, 0, t1 * inv_n, t2 * inv_n, rstd);
   }
   stamp(C, 51);
   __syncwarp();
-  copy_out_act(C, 0, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
+  copy_out_act<true>(C, 0, Ly.n_pad, Ly.out_dz, C.wdz, Ly.dbias_part);
   stamp(C, 52);
 }
 
