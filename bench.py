@@ -164,6 +164,71 @@ def chain_roofline(torch, pop, P, O, A, B, iters=50):
     return flop / (ms * 1e-3) / 1e12, ms, flop
 
 
+def rollout_bench(torch, np, dev, P, world, barrier, dist, n=4096, T=200, reps=3):
+    """BASELINE config 3 / SURVEY 8(d)-3: simulated evaluation of every member, antsoccer shape (O=42, A=8), n episodes x
+    T steps, state MLP 50->128->256->128->42 (input LayerNorm + residual), termination MLP 42->128->256->128->1, policy
+    50->512^4->8 -- ONE launch of the fused persistent rollout kernel per evaluation. The termination bias is set so that
+    no episode ends early: exactly n*T env-steps run per member (the count is read back from the kernel's own step
+    counters). `value`: init observations resident; `e2e`: init observations from pinned host memory, success rates and
+    returns read back."""
+    from fqlpop.population import Population
+    from fqlpop.envmodel import EnvModel
+    O, A, hidden = 42, 8, (128, 256, 128)
+    rng = np.random.default_rng(3)
+
+    def mlp(i, o, bias_last=0.0, scale_last=1.0):
+        dims = [i, *hidden, o]
+        t = {}
+        for l in range(len(dims) - 1):
+            k = (rng.standard_normal((dims[l], dims[l + 1])) / np.sqrt(dims[l])).astype(np.float32)   # LeCun normal
+            t[f"Dense_{l}"] = {"kernel": k, "bias": np.zeros(dims[l + 1], np.float32)}
+        t[f"Dense_{len(dims) - 2}"]["kernel"] *= scale_last
+        t[f"Dense_{len(dims) - 2}"]["bias"] += bias_last
+        return t
+
+    state = mlp(O + A, O, scale_last=0.05)
+    state["LayerNorm_0"] = {"scale": np.ones(O + A, np.float32), "bias": np.zeros(O + A, np.float32)}
+    term = mlp(O, 1, bias_last=-50.0)
+    pop = Population(dict(ob_dim=O, action_dim=A, batch_size=256, discount=0.995),
+                     np.logspace(np.log10(3), np.log10(1000), P), list(range(P)), device=dev)
+    em = EnvModel(state, term, O, A)
+    init_host = torch.randn(n, O).pin_memory()
+    init_dev = init_host.to(dev)
+    pop.rollout(em, init_dev, max_episode_steps=T, eval_seed=1)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for r in range(reps):
+        out = pop.rollout(em, init_dev, max_episode_steps=T, eval_seed=2 + r)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    steps = int(out["steps"].sum().item())          # lockstep env-steps executed, summed over members
+    e0.record()
+    for r in range(reps):
+        out = pop.rollout(em, init_host.to(dev, non_blocking=True), max_episode_steps=T, eval_seed=2 + r)
+        sr = out["success_rate"].cpu(); rm = out["return_mean"].cpu()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_e2e = e0.elapsed_time(e1) / reps
+    t = torch.tensor([ms, ms_e2e], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+    env_steps = steps * n * world
+    flop_step = 2.0 * ((O + A) * 512 + 3 * 512 * 512 + 512 * A            # policy
+                       + (O + A) * 128 + 128 * 256 + 256 * 128 + 128 * O  # state predictor
+                       + O * 128 + 128 * 256 + 256 * 128 + 128)           # termination predictor
+    pop.close()
+    return {"value": env_steps / (ms * 1e-3), "unit": "env-steps/s", "ms_per_evaluation": ms,
+            "e2e": {"value": env_steps / (ms_e2e * 1e-3), "unit": "env-steps/s", "h2d_bytes": int(init_host.numel() * 4),
+                    "d2h_bytes": int(2 * P * 4)},
+            "config": {"workload": f"simulated evaluation, antsoccer shape (O={O}, A={A}), {P} members x {n} episodes x {T} steps per GPU, "
+                                   "one fused launch per evaluation", "env_steps_per_member": steps // max(P, 1) * n},
+            "algorithmic_tflops": env_steps / world * flop_step / (ms * 1e-3) / 1e12, "flop_per_env_step": flop_step,
+            "gpu_launches": reps}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -175,6 +240,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--rows", type=int, default=1_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-rollout", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -265,6 +331,9 @@ def main():
     e2e_ms = float(t.item())
     sampler.stop_flag = True
     sampler.join(timeout=2)
+    roll = None
+    if not args.no_rollout:
+        roll = rollout_bench(torch, np, dev, P, world, barrier, dist)
 
     if rank != 0:
         if world > 1:
@@ -298,6 +367,9 @@ def main():
         "clocks": sampler.summary(),
         "last_info_member0": {k: float(v) for k, v in zip(("critic_loss", "q_mean"), info_last[0][:2])},
     }
+    if roll is not None:
+        roll["frac_of_sustained_tensor_peak"] = roll["algorithmic_tflops"] / pk["bf16_tflops_sustained"]
+        line["rollout"] = roll
     if not args.no_cpu_baseline:
         n_upd = 30
         ups, threads = cpu_oracle_updates_per_sec(O, A, B, n_upd)

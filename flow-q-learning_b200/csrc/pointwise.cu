@@ -548,49 +548,71 @@ struct AdamArgs {
 // overlap the chains. theta / mu / nu / target are touched once per step: streaming loads and stores (evict-first)
 // keep them from pushing the bf16 shadow weights -- which the next chains stream from L2 -- out of the cache.
 constexpr int kAdamThreads = 1024;
+constexpr int kAdamUnroll = 2;  // float4 quads per thread per trip: all their loads are issued before the first use
+                                // (2 x 4-5 x 16 B in flight per thread, ~160 KB per SM at 64 registers per thread)
+__device__ __forceinline__ void adam_quad(const AdamArgs& a, long long o, float ibc1, float ibc2, float4 g, float4 th,
+                                          float4 m, float4 v, float4 tg) {
+#define ADAM1(c)                                                        \
+  m.c = a.b1 * m.c + (1.f - a.b1) * g.c;                                \
+  v.c = a.b2 * v.c + (1.f - a.b2) * g.c * g.c;                          \
+  th.c = th.c - a.lr * (m.c * ibc1) / (sqrtf(v.c * ibc2) + a.eps);
+  ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
+#undef ADAM1
+  __stcs(reinterpret_cast<float4*>(a.theta + o), th);
+  __stcs(reinterpret_cast<float4*>(a.mu + o), m);
+  __stcs(reinterpret_cast<float4*>(a.nu + o), v);
+  uint2 s;
+  s.x = pack_bf16x2(th.x, th.y);
+  s.y = pack_bf16x2(th.z, th.w);
+  *reinterpret_cast<uint2*>(a.shadow + o) = s;
+  if (a.target) {
+    tg.x = a.tau * th.x + (1.f - a.tau) * tg.x;
+    tg.y = a.tau * th.y + (1.f - a.tau) * tg.y;
+    tg.z = a.tau * th.z + (1.f - a.tau) * tg.z;
+    tg.w = a.tau * th.w + (1.f - a.tau) * tg.w;
+    __stcs(reinterpret_cast<float4*>(a.target + o), tg);
+    uint2 ts;
+    ts.x = pack_bf16x2(tg.x, tg.y);
+    ts.y = pack_bf16x2(tg.z, tg.w);
+    *reinterpret_cast<uint2*>(a.tshadow + o) = ts;
+  }
+}
 __global__ void __launch_bounds__(kAdamThreads, 1) adam_kernel(const AdamArgs a) {
   long long tl_t0 = 0;
   const bool tl_on = a.timeline && threadIdx.x == 0;
   if (tl_on) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
   const int n4 = (int)(a.S >> 2);
   const long long total = (long long)a.n_virtual * n4;
-  for (long long idx = (long long)blockIdx.x * kAdamThreads + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * kAdamThreads) {
-    const int av = (int)(idx / n4);
-    const int i = (int)(idx - (long long)av * n4);
-    const int am = av / a.nb, e = av - am * a.nb;
-    const int p = a.member_list[am];
-    const long long o = ((long long)p * a.nb + e) * a.S + 4ll * i;
-    const float ibc1 = 1.f / a.adam_bc[2 * p], ibc2 = 1.f / a.adam_bc[2 * p + 1];
-    const float4 g = __ldcs(reinterpret_cast<const float4*>(a.grad + o));
-    float4 th = __ldcs(reinterpret_cast<const float4*>(a.theta + o));
-    float4 m = __ldcs(reinterpret_cast<const float4*>(a.mu + o));
-    float4 v = __ldcs(reinterpret_cast<const float4*>(a.nu + o));
-#define ADAM1(c)                                                        \
-  m.c = a.b1 * m.c + (1.f - a.b1) * g.c;                                \
-  v.c = a.b2 * v.c + (1.f - a.b2) * g.c * g.c;                          \
-  th.c = th.c - a.lr * (m.c * ibc1) / (sqrtf(v.c * ibc2) + a.eps);
-    ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
-#undef ADAM1
-    __stcs(reinterpret_cast<float4*>(a.theta + o), th);
-    __stcs(reinterpret_cast<float4*>(a.mu + o), m);
-    __stcs(reinterpret_cast<float4*>(a.nu + o), v);
-    uint2 s;
-    s.x = pack_bf16x2(th.x, th.y);
-    s.y = pack_bf16x2(th.z, th.w);
-    *reinterpret_cast<uint2*>(a.shadow + o) = s;
-    if (a.target) {
-      float4 tg = __ldcs(reinterpret_cast<const float4*>(a.target + o));
-      tg.x = a.tau * th.x + (1.f - a.tau) * tg.x;
-      tg.y = a.tau * th.y + (1.f - a.tau) * tg.y;
-      tg.z = a.tau * th.z + (1.f - a.tau) * tg.z;
-      tg.w = a.tau * th.w + (1.f - a.tau) * tg.w;
-      __stcs(reinterpret_cast<float4*>(a.target + o), tg);
-      uint2 ts;
-      ts.x = pack_bf16x2(tg.x, tg.y);
-      ts.y = pack_bf16x2(tg.z, tg.w);
-      *reinterpret_cast<uint2*>(a.tshadow + o) = ts;
+  const long long stride = (long long)gridDim.x * kAdamThreads;
+  for (long long idx0 = (long long)blockIdx.x * kAdamThreads + threadIdx.x; idx0 < total; idx0 += kAdamUnroll * stride) {
+    long long o[kAdamUnroll];
+    float ibc1[kAdamUnroll], ibc2[kAdamUnroll];
+    float4 g[kAdamUnroll], th[kAdamUnroll], m[kAdamUnroll], v[kAdamUnroll], tg[kAdamUnroll];
+    bool ok[kAdamUnroll];
+#pragma unroll
+    for (int u = 0; u < kAdamUnroll; ++u) {
+      const long long idx = idx0 + u * stride;
+      ok[u] = idx < total;
+      const long long id = ok[u] ? idx : idx0;
+      const int av = (int)(id / n4);
+      const int i = (int)(id - (long long)av * n4);
+      const int am = av / a.nb, e = av - am * a.nb;
+      const int p = a.member_list[am];
+      o[u] = ((long long)p * a.nb + e) * a.S + 4ll * i;
+      ibc1[u] = 1.f / a.adam_bc[2 * p];
+      ibc2[u] = 1.f / a.adam_bc[2 * p + 1];
     }
+#pragma unroll
+    for (int u = 0; u < kAdamUnroll; ++u) {
+      g[u] = __ldcs(reinterpret_cast<const float4*>(a.grad + o[u]));
+      th[u] = __ldcs(reinterpret_cast<const float4*>(a.theta + o[u]));
+      m[u] = __ldcs(reinterpret_cast<const float4*>(a.mu + o[u]));
+      v[u] = __ldcs(reinterpret_cast<const float4*>(a.nu + o[u]));
+      tg[u] = a.target ? __ldcs(reinterpret_cast<const float4*>(a.target + o[u])) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < kAdamUnroll; ++u)
+      if (ok[u]) adam_quad(a, o[u], ibc1[u], ibc2[u], g[u], th[u], m[u], v[u], tg[u]);
   }
   if (tl_on) tl_record(a.timeline, tl_t0, a.tag);
 }
