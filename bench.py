@@ -191,7 +191,7 @@ def rollout_bench(torch, np, dev, P, world, barrier, dist, n=4096, T=200, reps=3
     term = mlp(O, 1, bias_last=-50.0)
     pop = Population(dict(ob_dim=O, action_dim=A, batch_size=256, discount=0.995),
                      np.logspace(np.log10(3), np.log10(1000), P), list(range(P)), device=dev)
-    em = EnvModel(state, term, O, A)
+    em = EnvModel(state, term, O, A, device=dev)
     init_host = torch.randn(n, O).pin_memory()
     init_dev = init_host.to(dev)
     pop.rollout(em, init_dev, max_episode_steps=T, eval_seed=1)

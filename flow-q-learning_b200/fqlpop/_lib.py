@@ -65,3 +65,14 @@ def gemm_test(**kw):
             v = v.data_ptr()
         setattr(d, k, v)
     check(lib.fqlpop_gemm_test(ctypes.byref(d), None), "fqlpop_gemm_test")
+
+
+def default_device():
+    """The device a handle lands on when the caller names none: one process per GPU, so LOCAL_RANK (torchrun) if set,
+    else torch's current device -- never a hard-coded cuda:0."""
+    import os
+    import torch
+    lr = os.environ.get("LOCAL_RANK")
+    if lr is not None and torch.cuda.is_available() and int(lr) < torch.cuda.device_count():
+        return torch.device("cuda", int(lr))
+    return torch.device("cuda", torch.cuda.current_device() if torch.cuda.is_available() else 0)

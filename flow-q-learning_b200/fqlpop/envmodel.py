@@ -68,10 +68,10 @@ class EnvModel:
     termination: tree of TerminationPredictor (envmodel/termination_predictor.py:14-21)."""
 
     def __init__(self, state: Dict, termination: Dict, ob_dim: int, action_dim: int, ln_eps: float = 1e-6,
-                 device="cuda:0"):
+                 device=None):
         if not torch.cuda.is_available():
             raise _lib.FqlPopError("no CUDA device: the world-model rollout has no CPU fallback")
-        self.device = torch.device(device)
+        self.device = torch.device(device) if device is not None else _lib.default_device()
         torch.cuda.set_device(self.device)
         sl, tl = _dense_layers(state), _dense_layers(termination)
         if len(sl) < 2 or len(tl) < 2:

@@ -78,12 +78,12 @@ class Population:
     """P lockstep FQL agents on one GPU. `agent_config` is any mapping/object with the AgentConfig fields
     (/root/reference/trainer/config.py:6-23) plus ob_dim / action_dim."""
 
-    def __init__(self, agent_config, alphas: Sequence[float], seeds: Sequence[int], device="cuda:0"):
+    def __init__(self, agent_config, alphas: Sequence[float], seeds: Sequence[int], device=None):
         get = (lambda k, d=None: agent_config.get(k, d)) if isinstance(agent_config, dict) else (
             lambda k, d=None: getattr(agent_config, k, d))
         if not torch.cuda.is_available():
             raise _lib.FqlPopError("no CUDA device: the population hot path has no CPU fallback")
-        self.device = torch.device(device)
+        self.device = torch.device(device) if device is not None else _lib.default_device()
         torch.cuda.set_device(self.device)
         ha, nha = _uniform_width(get("actor_hidden_dims", (512,) * 4), "actor_hidden_dims")
         hv, nhv = _uniform_width(get("value_hidden_dims", (512,) * 4), "value_hidden_dims")

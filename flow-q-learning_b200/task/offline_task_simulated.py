@@ -28,8 +28,11 @@ from utils.envmodel import load_model
 class OfflineTaskWithSimulatedEvaluations(Task):
     def __init__(self, env_name: str, model: str = "baseline", data_directory: Path = None,
                  save_directory: Path = Path("exp/"), buffer_size: int = 2000000, num_evaluation_envs: int = 50,
-                 max_episode_steps: int = 1000, device="cuda:0"):
+                 max_episode_steps: int = 1000, device=None):
         self.max_episode_steps = max_episode_steps
+        if device is None:
+            from fqlpop._lib import default_device
+            device = default_device()
         self.device = device
         _, self.eval_envs, train, val = make_env_and_datasets(env_name, data_directory,
                                                               num_evaluation_envs=num_evaluation_envs)

@@ -37,7 +37,7 @@ class Experiment:
         example_batch = task.sample("train", 1)
         self.agent = FQLAgent.create(agent_config.seed, example_batch["observations"], example_batch["actions"],
                                      asdict(agent_config), population=population, slot=slot,
-                                     device=getattr(task, "device", "cuda:0"))
+                                     device=getattr(task, "device", None))
         if state_dict is None:
             name = "_".join(f"{f}_{v}" for f, v in tuned)
             self.experiment_name = f"{name}_{datetime.now().strftime('%Y%m%d_%H%M%S')}"

@@ -73,7 +73,7 @@ class Trainer:
             base["ob_dims"] = tuple(np.shape(example["observations"])[-1:])
             base["action_dim"] = int(np.shape(example["actions"])[-1])
             self.population = self._factory(base, [float(c.alpha) for c in cfgs], [int(c.seed) for c in cfgs],
-                                            getattr(task, "device", "cuda:0"))
+                                            getattr(task, "device", None))
 
         if state_dict is not None:
             for c, st in state_dict["experiments"].items():

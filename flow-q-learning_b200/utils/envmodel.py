@@ -33,9 +33,12 @@ def _zero_mlp(in_dim: int, out_dim: int, with_ln: bool) -> Dict:
 
 
 class LoadedModel:
-    def __init__(self, kind: str, params: Dict, ob_dim: int, action_dim: int, hidden_dims, device="cuda:0"):
+    def __init__(self, kind: str, params: Dict, ob_dim: int, action_dim: int, hidden_dims, device=None):
         self.kind, self.params, self.ob_dim, self.action_dim = kind, params, ob_dim, action_dim
         self.hidden_dims = tuple(hidden_dims)
+        if device is None:
+            from fqlpop._lib import default_device
+            device = default_device()
         self.device = device
         self._dev = None
 
@@ -62,7 +65,7 @@ class LoadedModel:
         return logits.cpu().numpy()
 
 
-def load_model(save_directory: Path, env_name: str, model: str, sample_batch: Dict[str, np.ndarray], device="cuda:0"):
+def load_model(save_directory: Path, env_name: str, model: str, sample_batch: Dict[str, np.ndarray], device=None):
     root = Path(save_directory) / env_name / "env_models"
     config_path = root / f"{model}_config.yaml"
     if not config_path.exists():
