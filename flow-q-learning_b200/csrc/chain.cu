@@ -121,6 +121,9 @@ struct EpiCtx {
   bool publish;          // ... unless nobody consumes this layer's output on chip
   uint64_t* blk_full;    // [8] local barriers: k-block j of ACT holds the next layer's A operand
   uint32_t peer_act, peer_blk_full;  // shared::cluster addresses of the peer's ACT / blk_full[0]
+  float* pbuf;           // smem copy of the current layer's bias [512] / LayerNorm scale [512] / LayerNorm bias [512] (the X0
+                         // block, idle after the first layer), or nullptr -> read them through L1
+  mutable bool puse;     // the current layer reads its parameters from pbuf
   long long* tr;         // (debug) stamp log of the traced epilogue thread: tr[0] = count, stamps (clock, id) from tr[2]
 };
 
@@ -143,6 +146,48 @@ __device__ __forceinline__ void stamp(const EpiCtx& C, int id) {
 // publish hooks vanish at compile time.
 template <bool CL> __device__ __forceinline__ int goff(const EpiCtx& C) { return CL ? C.g_off : 0; }
 template <bool CL> __device__ __forceinline__ uint32_t tmoff(const EpiCtx& C) { return CL ? (uint32_t)C.tm_off : 0u; }
+
+// Every bias / LayerNorm line of a layer is touched exactly once per CTA, i.e. each first use is a compulsory L1 miss
+// (measured: 600-1800 cycles under load, 8 of them per thread and LayerNorm tile pass). The epilogue threads therefore
+// pull the layer's parameter lines into L1 while they wait for the accumulator: thread t of the 256 takes line t % 16 of
+// array t / 16 (0 bias, 1 LayerNorm scale, 2 LayerNorm bias). ncols = 512 (single CTA) or this CTA's 256 columns.
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+// four consecutive parameters: from the shared-memory copy (array arr: 0 bias, 1 LayerNorm scale, 2 LayerNorm bias; absolute
+// column gcol) or through L1
+__device__ __forceinline__ float4 ldp4(const EpiCtx& C, const float* g, int arr, int gcol, int i) {
+  return C.puse ? *reinterpret_cast<const float4*>(C.pbuf + arr * 512 + gcol + 4 * i)
+                : __ldg(reinterpret_cast<const float4*>(g + gcol) + i);
+}
+// Cooperative copy of the layer's parameter vectors into pbuf (all 256 epilogue threads; barrier before -- nobody still
+// reads the previous layer's copy -- and after).
+__device__ __forceinline__ void load_layer_params(const EpiCtx& C, const ChainLayer& Ly, bool fwd, bool ln) {
+  const int t = (C.half * 4 + C.q) * 32 + C.lane;
+  epi_bar_sync();
+  float4* dst = reinterpret_cast<float4*>(C.pbuf);
+#pragma unroll 1
+  for (int i = t; i < 384; i += 256) {
+    const int arr = i >> 7, k = i & 127;
+    const long long off = arr == 0 ? Ly.off_b : (arr == 1 ? Ly.off_g : Ly.off_beta);
+    const bool need = fwd ? (arr == 0 || ln) : (ln && arr == 1);
+    if (need) dst[i] = __ldg(reinterpret_cast<const float4*>(C.params + off) + k);
+  }
+  epi_bar_sync();
+}
+template <bool CL>
+__device__ __forceinline__ void prefetch_layer_params(const EpiCtx& C, const ChainLayer& Ly, bool fwd, bool ln) {
+  const int t = (C.half * 4 + C.q) * 32 + C.lane;
+  const int line = t & 15, which = t >> 4;
+  const int ncols = CL ? 256 : Ly.n_pad;
+  if (line * 32 >= ncols) return;
+  const float* base = C.params + goff<CL>(C) + line * 32;
+  if (fwd) {
+    if (which == 0) prefetch_l1(base + Ly.off_b);
+    else if (ln && which == 1) prefetch_l1(base + Ly.off_g);
+    else if (ln && which == 2) prefetch_l1(base + Ly.off_beta);
+  } else if (ln && which == 0) {
+    prefetch_l1(base + Ly.off_g);
+  }
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // Staged global traffic. A "block" is 32 rows x 64 bf16 columns = 32 x 128 bytes in shared memory, 16-byte chunk c
@@ -327,9 +372,9 @@ __device__ __forceinline__ void copy_out_act(const EpiCtx& C, int tile, int n_pa
 // Pass 1 over this thread's chunks of one accumulator tile: bias + GELU (+ act'(z) for the backward pass, staged and
 // copied out per 64-column block); the bf16 result is parked in the drained TMEM columns or -- `direct` -- written
 // to ACT (the caller copies h out of ACT once the layer has been handed to the tensor core).
-__device__ __forceinline__ void ld_bias16(const float* bias, int col, float4 (&b4)[4]) {
+__device__ __forceinline__ void ld_bias16(const EpiCtx& C, const float* bias, int gcol, float4 (&b4)[4]) {
 #pragma unroll
-  for (int i = 0; i < 4; ++i) b4[i] = __ldg(reinterpret_cast<const float4*>(bias + col) + i);
+  for (int i = 0; i < 4; ++i) b4[i] = ldp4(C, bias, 0, gcol, i);
 }
 template <bool LN, bool SAVE, bool CL>
 __device__ __forceinline__ void fwd_chunk(const EpiCtx& C, const float4 (&b4)[4], const uint32_t (&rr)[16], int col0, int c,
@@ -367,7 +412,8 @@ __device__ __forceinline__ void fwd_pass1(const EpiCtx& C, const ChainLayer& Ly,
   const int nch = tile_chunks16(C, tile, Ly.n_pad);  // a multiple of 4
   if (nch == 0) return;
   const int col0 = tile * kTileN + C.half * 128;
-  const float* bias = C.params + Ly.off_b + goff<CL>(C);
+  const float* bias = C.params + Ly.off_b;
+  const int g0 = goff<CL>(C) + col0;  // absolute column of this thread's first chunk
   const uint32_t tbase = C.tmem_row + tmoff<CL>(C) + col0;
   uint32_t ra[16], rb[16];
   if (DB) tmem_ld16(tbase, ra);
@@ -377,11 +423,11 @@ __device__ __forceinline__ void fwd_pass1(const EpiCtx& C, const ChainLayer& Ly,
 #pragma unroll 1
       for (int c = cb; c < cb + 4; c += 2) {
         float4 b4[4];
-        ld_bias16(bias, col0 + c * 16, b4);
+        ld_bias16(C, bias, g0 + c * 16, b4);
         tmem_ld_wait();
         tmem_ld16(tbase + (c + 1) * 16, rb);
         fwd_chunk<LN, SAVE, CL>(C, b4, ra, col0, c, direct, s1, s2);
-        ld_bias16(bias, col0 + (c + 1) * 16, b4);
+        ld_bias16(C, bias, g0 + (c + 1) * 16, b4);
         tmem_ld_wait();
         if (c + 2 < nch) tmem_ld16(tbase + (c + 2) * 16, ra);
         fwd_chunk<LN, SAVE, CL>(C, b4, rb, col0, c + 1, direct, s1, s2);
@@ -390,7 +436,7 @@ __device__ __forceinline__ void fwd_pass1(const EpiCtx& C, const ChainLayer& Ly,
 #pragma unroll 1
       for (int c = cb; c < cb + 4; ++c) {
         float4 b4[4];
-        ld_bias16(bias, col0 + c * 16, b4);
+        ld_bias16(C, bias, g0 + c * 16, b4);
         tmem_ld16(tbase + c * 16, ra);
         tmem_ld_wait();
         fwd_chunk<LN, SAVE, CL>(C, b4, ra, col0, c, direct, s1, s2);
@@ -424,12 +470,11 @@ __device__ __forceinline__ void fwd_flush(const EpiCtx& C, const ChainLayer& Ly,
       tmem_ld8(C.tmem_row + tmoff<CL>(C) + col0 + c * 8, pr);
       tmem_ld_wait();
       if (LN) {
-        const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + goff<CL>(C) + col);
-        const float4* e4 = reinterpret_cast<const float4*>(C.params + Ly.off_beta + goff<CL>(C) + col);
+        const int gcol = goff<CL>(C) + col;
         uint32_t hk[8], xk[8];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const float4 ga = __ldg(g4 + i), be = __ldg(e4 + i);
+          const float4 ga = ldp4(C, C.params + Ly.off_g, 1, gcol, i), be = ldp4(C, C.params + Ly.off_beta, 2, gcol, i);
           const uint32_t w0 = pr[2 * i], w1 = pr[2 * i + 1];
           const float x0 = fmaf(bf16_lo(w0), rstd, shift), x1 = fmaf(bf16_hi(w0), rstd, shift);
           const float x2 = fmaf(bf16_lo(w1), rstd, shift), x3 = fmaf(bf16_hi(w1), rstd, shift);
@@ -470,6 +515,9 @@ __device__ __forceinline__ void fwd_hidden_layer(const EpiCtx& C, uint32_t& full
   constexpr bool CL = false;
   const int n_tiles = (Ly.n_pad + kTileN - 1) / kTileN;
   float s1 = 0.f, s2 = 0.f;
+  C.puse = C.pbuf != nullptr && !Ly.a_from_x0;
+  if (C.puse) load_layer_params(C, Ly, true, LN);
+  else prefetch_layer_params<CL>(C, Ly, true, LN);
   if (!LN) {
     wait_tile(C, fullph, 0);
     stamp(C, 10);
@@ -637,13 +685,13 @@ __device__ __forceinline__ void bwd_ln_stats(const EpiCtx& C, const ChainLayer& 
       const int col = col0 + sb * 32 + ch * 16;
       uint32_t xw[8];
       ld_half16(slot, C.lane, ch * 16, xw);
-      const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + goff<CL>(C) + col);
+      const int gcol = goff<CL>(C) + col;
       tmem_ld16(C.tmem_row + tmoff<CL>(C) + col, rr);
       tmem_ld_wait();
       float t0[16], t1[16];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const float4 ga = __ldg(g4 + i);
+        const float4 ga = ldp4(C, C.params + Ly.off_g, 1, gcol, i);
         const float gam[4] = {ga.x, ga.y, ga.z, ga.w};
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -698,13 +746,13 @@ __device__ __forceinline__ void bwd_ln_out(const EpiCtx& C, const ChainLayer& Ly
 #pragma unroll
         for (int i = 0; i < 8; ++i) gw[i] = C.row_ok ? 0x3F803F80u : 0u;
       }
-      const float4* g4 = reinterpret_cast<const float4*>(C.params + Ly.off_g + goff<CL>(C) + col);
+      const int gcol = goff<CL>(C) + col;
       tmem_ld16(C.tmem_row + tmoff<CL>(C) + col, rr);
       tmem_ld_wait();
       uint32_t pk[8];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const float4 ga = __ldg(g4 + i);
+        const float4 ga = ldp4(C, C.params + Ly.off_g, 1, gcol, i);
         const float gam[4] = {ga.x, ga.y, ga.z, ga.w};
         float dz[4];
 #pragma unroll
@@ -728,6 +776,9 @@ template <bool LN>
 __device__ __forceinline__ void bwd_hidden_layer(const EpiCtx& C, uint32_t& fullph, const ChainLayer& Ly) {
   constexpr bool CL = false;
   const int n_tiles = (Ly.n_pad + kTileN - 1) / kTileN;
+  C.puse = LN && C.pbuf != nullptr && !Ly.a_from_x0;
+  if (C.puse) load_layer_params(C, Ly, false, LN);
+  else prefetch_layer_params<CL>(C, Ly, false, LN);
   if (!LN) {
     bwd_prefetch_gp<CL>(C, Ly, 0, 0);
     wait_tile(C, fullph, 0);
@@ -859,6 +910,9 @@ __device__ __forceinline__ void exchange_row_sums2(const EpiCtx& C, const Cl2& X
 
 template <bool LN, bool SAVE>
 __device__ __forceinline__ void fwd2_hidden_layer(EpiCtx& C, const Cl2& X, const ChainLayer& Ly, int lc, int lnc) {
+  C.puse = C.pbuf != nullptr && !Ly.a_from_x0;
+  if (C.puse) load_layer_params(C, Ly, true, LN);
+  else prefetch_layer_params<true>(C, Ly, true, LN);
   c2_begin_layer(C, X, lc);
   stamp(C, 40);
   float s1 = 0.f, s2 = 0.f;
@@ -886,6 +940,9 @@ __device__ __forceinline__ void fwd2_hidden_layer(EpiCtx& C, const Cl2& X, const
 
 template <bool LN>
 __device__ __forceinline__ void bwd2_hidden_layer(EpiCtx& C, const Cl2& X, const ChainLayer& Ly, int lc, int lnc) {
+  C.puse = LN && C.pbuf != nullptr && !Ly.a_from_x0;
+  if (C.puse) load_layer_params(C, Ly, false, LN);
+  else prefetch_layer_params<true>(C, Ly, false, LN);
   if (!LN) bwd_prefetch_gp<true>(C, Ly, 0, 0);
   else ln_prefetch<true>(C, Ly.xhat, Ly.n_pad, 0, 0, 0);
   c2_begin_layer(C, X, lc);
@@ -1114,6 +1171,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1) fql_ch
     C.wrow = (long long)v * J.pass_ms + (long long)grow0 * J.H;
     C.wdz = (long long)v * J.dz_ms + (long long)grow0 * J.H;
     C.rows_valid = min(32, max(0, J.M - grow0));
+    C.pbuf = iters == 1 ? reinterpret_cast<float*>(x0s) : nullptr;  // the Euler chain re-stages X0 every iteration
+    C.puse = false;
     C.tm_off = 0; C.g_off = rank * 256; C.cl = true; C.publish = true;
     C.blk_full = blk_full;
     const uint32_t peer = (uint32_t)(rank ^ 1);
@@ -1404,6 +1463,8 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
     C.wrow = (long long)v * J.pass_ms + (long long)grow0 * J.H;
     C.wdz = (long long)v * J.dz_ms + (long long)grow0 * J.H;
     C.rows_valid = min(32, max(0, J.M - grow0));
+    C.pbuf = iters == 1 ? reinterpret_cast<float*>(x0s) : nullptr;  // the Euler chain re-stages X0 every iteration
+    C.puse = false;
     C.tm_off = 0; C.g_off = 0; C.cl = false; C.publish = false; C.blk_full = nullptr; C.peer_act = 0; C.peer_blk_full = 0;
     const bool traced = L.trace && blockIdx.x == 0 && threadIdx.x == 64;
     C.tr = traced ? L.trace + 4096 : nullptr;
