@@ -1598,13 +1598,12 @@ cudaError_t chain_init() {
 
 // The cluster kernel covers the production shape: every hidden layer 512 wide, reductions of 64 (first layer) or 512.
 static bool chain2_eligible(const ChainLaunch& L) {
-  static const int mode = [] {
-    // 0 (default): single-CTA kernel; 1: cluster kernel for every chain; 2: cluster kernel for the Euler chain only.
-    // Measured on B200 (16 members): the cluster kernel cuts a chain's latency 1.4-1.7x but costs
-    // ~20% more SM time, and the step is bound by SM time + optimizer HBM time, so the default stays 0.
-    const char* e = getenv("FQLPOP_CHAIN2");
-    return e ? atoi(e) : 0;
-  }();
+  // 0 (default): single-CTA kernel; 1: cluster kernel for every chain; 2: cluster kernel for the Euler chain only.
+  // Measured on B200 (16 members): the cluster kernel cuts a chain's latency 1.4-1.7x but costs
+  // ~20% more SM time, and the step is bound by SM time + optimizer HBM time, so the default stays 0. Read at every
+  // launch (graph capture time), so a process can build populations with either kernel.
+  const char* e = getenv("FQLPOP_CHAIN2");
+  const int mode = e ? atoi(e) : 0;
   if (!mode) return false;
   if (mode == 2 && L.job[0].iters <= 1) return false;  // 2: only the Euler chain (the step's longest serial path)
   for (int i = 0; i < L.num_jobs; ++i) {
