@@ -143,6 +143,11 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+# DRAM traffic of the roofline launch (16 members, cube-single, B=256) from one ncu --set full capture: 28.02 MB read (the
+# bf16 weights, once per member) + 3.28 MB written (most of the saved activations are still in L2 when the launch ends)
+ROOFLINE_LAUNCH_DRAM_BYTES = 28023552 + 3282688
+
+
 def chain_roofline(torch, pop, P, O, A, B, iters=50):
     """The step's dominant kernel, fql_chain_kernel<0>, in its widest launch: the one-step policy forward pass (3B rows
     of every member through the four hidden layers in one launch, activations on chip, act'(z) / h saved for the
@@ -357,7 +362,9 @@ def main():
                 "h2d_bytes_per_step": int(host.numel() * 4), "d2h_bytes_per_step": int(info_host.nbytes)},
         "gpu_launches": pop.launches_per_step * args.steps,
         "roofline": {"bound": "tensor", "achieved": tf_gemm, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
-                     "frac": tf_gemm / pk["bf16_tflops"], "traffic": None, "peak_source": pk_src + " (burst)",
+                     "frac": tf_gemm / pk["bf16_tflops"], "traffic": ROOFLINE_LAUNCH_DRAM_BYTES,
+                     "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of this launch, ncu --set full (profiles/r01d_chain_ncu_full_summary.txt)",
+                     "peak_source": pk_src + " (burst)",
                      "kernel": "fql_chain_kernel<0>: one-step policy forward pass, %d rows x 4 hidden layers x %d members in one "
                                "launch (%d CTAs of 128 rows), timed alone" % (3 * B, P, P * ((3 * B + 127) // 128)),
                      "launch_ms": gemm_ms, "flop_per_launch": gemm_flop},
