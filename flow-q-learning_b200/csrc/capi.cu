@@ -288,3 +288,82 @@ extern "C" int64_t fqlpop_rollout_launches(void* h) {
   fqlpop::Population* P = (fqlpop::Population*)h;
   return P ? P->ro.launches : 0;
 }
+
+
+// ---------------------------------------------------------------------------------------------------------
+// world-model training
+// ---------------------------------------------------------------------------------------------------------
+#include "wm.h"
+
+namespace {
+bool wm_cfg(const fqlpop_wm_config_t* c, fqlpop::WmConfig* o) {
+  if (!c || c->n_hidden < 1 || c->n_hidden >= fqlpop::kWmMaxLayers || c->term_n_hidden < 0 ||
+      c->term_n_hidden >= fqlpop::kWmMaxLayers)
+    return false;
+  memset(o, 0, sizeof(*o));
+  o->kind = c->kind; o->O = c->ob_dim; o->A = c->action_dim; o->batch = c->batch;
+  o->n_hidden = c->n_hidden; o->term_n_hidden = c->term_n_hidden;
+  for (int i = 0; i < c->n_hidden; ++i) o->hidden[i] = c->hidden[i];
+  for (int i = 0; i < c->term_n_hidden; ++i) o->term_hidden[i] = c->term_hidden[i];
+  o->decay_steps = c->decay_steps; o->lr = c->lr; o->ln_eps = c->ln_eps;
+  o->true_termination_weight = c->true_termination_weight; o->termination_weight = c->termination_weight;
+  o->reconstruction_weight = c->reconstruction_weight;
+  o->focal_alpha = c->focal_alpha; o->focal_gamma = c->focal_gamma; o->seed = c->seed;
+  return true;
+}
+}  // namespace
+#define WM(h)                                      \
+  fqlpop::WmTrainer* T = (fqlpop::WmTrainer*)(h);  \
+  if (!T) return fail("null world-model handle");  \
+  std::string err
+
+extern "C" int64_t fqlpop_wm_num_params(const fqlpop_wm_config_t* c) {
+  fqlpop::WmConfig w;
+  if (!wm_cfg(c, &w)) return -1;
+  return (w.kind == fqlpop::WM_STATE ? fqlpop::wm_layout(w.O + w.A, w.n_hidden, w.hidden, w.O, true)
+                                     : fqlpop::wm_layout(w.O, w.n_hidden, w.hidden, 1, false)).n_params;
+}
+extern "C" int fqlpop_wm_create(const fqlpop_wm_config_t* c, const float* params_host, const float* term_params_host,
+                                void** out) {
+  fqlpop::WmConfig w;
+  if (!out || !wm_cfg(c, &w)) return fail("world model: null argument or layer count outside [1, 7]");
+  fqlpop::WmTrainer* t = nullptr;
+  std::string err;
+  if (fqlpop::wm_create_impl(w, params_host, term_params_host, &t, &err)) return fail(err);
+  *out = t;
+  return 0;
+}
+extern "C" int fqlpop_wm_destroy(void* h) {
+  fqlpop::wm_destroy_impl((fqlpop::WmTrainer*)h);
+  return 0;
+}
+extern "C" int fqlpop_wm_step(void* h, int32_t train, const float* obs, const float* act, const float* next_obs,
+                              const float* rewards, const float* dropout_mask, void* stream) {
+  WM(h);
+  if (fqlpop::wm_step_impl(T, train, obs, act, next_obs, rewards, dropout_mask, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_wm_set_dataset(void* h, const float* obs, const float* act, const float* next_obs,
+                                     const float* rewards, int64_t n_rows) {
+  WM(h);
+  if (fqlpop::wm_set_dataset_impl(T, obs, act, next_obs, rewards, n_rows, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_wm_train(void* h, int32_t n_steps, const float* dropout_mask, void* stream) {
+  WM(h);
+  if (fqlpop::wm_train_impl(T, n_steps, dropout_mask, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_wm_logs(void* h, float* out_host, void* stream) {
+  WM(h);
+  if (!out_host) return fail("null argument");
+  if (fqlpop::wm_logs_impl(T, out_host, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_wm_export(void* h, int32_t which, float* out_host, int64_t n, void* stream) {
+  WM(h);
+  if (!out_host) return fail("null argument");
+  if (fqlpop::wm_export_impl(T, which, out_host, n, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int64_t fqlpop_wm_launches(void* h) { return h ? fqlpop::wm_launches((fqlpop::WmTrainer*)h) : 0; }

@@ -1,0 +1,588 @@
+// World-model training kernels (see wm.h). fp32 throughout; every reduction runs in a fixed order, so a step is
+// deterministic and reproducible across launches.
+#include "wm.h"
+
+#include <cmath>
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+#include "philox.cuh"
+
+namespace fqlpop {
+
+// ---------------------------------------------------------------------------------------------------------------------
+// C[M][N] (+)= epi(op(A) op(B)), op(A)(m,k) = TA ? A[k*lda+m] : A[m*lda+k], op(B)(k,n) = TB ? B[n*ldb+k] : B[k*ldb+n].
+// 32 x 32 x 32 tiles, 256 threads, 4 rows x 1 column per thread; the k loop runs in index order (deterministic).
+// One kernel serves the forward Dense layers (bias / relu / residual), the input-gradient products (TB, relu mask taken
+// from the saved activation) and the weight-gradient products (TA, reduction over the batch).
+// ---------------------------------------------------------------------------------------------------------------------
+enum WmEpi : int { WE_NONE = 0, WE_BIAS = 1, WE_BIAS_RELU = 2, WE_BIAS_RESID = 3, WE_MASK = 4 };
+
+constexpr int kWmTile = 32;
+
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(256) wm_gemm_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B,
+                                                      int ldb, float* __restrict__ C, int ldc, int M, int N, int K,
+                                                      int epi, const float* __restrict__ bias,
+                                                      const float* __restrict__ aux, int ldaux, int accumulate) {
+  __shared__ float As[kWmTile][kWmTile + 1];  // [k][m]
+  __shared__ float Bs[kWmTile][kWmTile + 1];  // [k][n]
+  const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
+  const int m0 = blockIdx.y * kWmTile, n0 = blockIdx.x * kWmTile;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int k0 = 0; k0 < K; k0 += kWmTile) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int e = tid + i * 256, hi = e >> 5, lo = e & 31;
+      {
+        const int m = TA ? lo : hi, k = TA ? hi : lo;
+        const int gm = m0 + m, gk = k0 + k;
+        float v = 0.f;
+        if (gm < M && gk < K) v = TA ? A[(long long)gk * lda + gm] : A[(long long)gm * lda + gk];
+        As[k][m] = v;
+      }
+      {
+        const int k = TB ? lo : hi, n = TB ? hi : lo;
+        const int gk = k0 + k, gn = n0 + n;
+        float v = 0.f;
+        if (gk < K && gn < N) v = TB ? B[(long long)gn * ldb + gk] : B[(long long)gk * ldb + gn];
+        Bs[k][n] = v;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kWmTile; ++k) {
+      const float b = Bs[k][tx];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[i] = fmaf(As[k][ty * 4 + i], b, acc[i]);
+    }
+    __syncthreads();
+  }
+  const int gn = n0 + tx;
+  if (gn >= N) return;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int gm = m0 + ty * 4 + i;
+    if (gm >= M) continue;
+    float r = acc[i];
+    if (epi == WE_BIAS || epi == WE_BIAS_RELU || epi == WE_BIAS_RESID) r += bias[gn];
+    if (epi == WE_BIAS_RELU) r = fmaxf(r, 0.f);
+    if (epi == WE_BIAS_RESID) r += aux[(long long)gm * ldaux + gn];
+    if (epi == WE_MASK) r = aux[(long long)gm * ldaux + gn] > 0.f ? r : 0.f;
+    float* c = C + (long long)gm * ldc + gn;
+    *c = accumulate ? *c + r : r;
+  }
+}
+
+// out[n] = sum_m X[m][n] (* Y[m][n]): bias gradients and the LayerNorm scale / bias gradients. One thread per column.
+__global__ void wm_colsum_kernel(const float* __restrict__ X, const float* __restrict__ Y, int ld, int M, int N,
+                                 float* __restrict__ out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float s = 0.f;
+  for (int m = 0; m < M; ++m) {
+    const float x = X[(long long)m * ld + n];
+    s += Y ? x * Y[(long long)m * ld + n] : x;
+  }
+  out[n] = s;
+}
+
+// x0 = LayerNorm(concat(obs, act)) * scale + bias (envmodel/baseline.py:31-32; flax: var = E[x^2] - E[x]^2, eps inside
+// the rsqrt). One warp per row; keeps xhat for the scale gradient.
+__global__ void wm_ln_concat_kernel(const float* __restrict__ obs, const float* __restrict__ act, int O, int A, int rows,
+                                    const float* __restrict__ scale, const float* __restrict__ bias, float eps,
+                                    float* __restrict__ x0, float* __restrict__ xhat) {
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const int D = O + A;
+  float s = 0.f, s2 = 0.f;
+  for (int j = lane; j < D; j += 32) {
+    const float v = j < O ? obs[(long long)row * O + j] : act[(long long)row * A + (j - O)];
+    s += v;
+    s2 += v * v;
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+  }
+  const float mean = s / D, var = fmaxf(s2 / D - mean * mean, 0.f), rstd = rsqrtf(var + eps);
+  for (int j = lane; j < D; j += 32) {
+    const float v = j < O ? obs[(long long)row * O + j] : act[(long long)row * A + (j - O)];
+    const float h = (v - mean) * rstd;
+    xhat[(long long)row * D + j] = h;
+    x0[(long long)row * D + j] = h * scale[j] + bias[j];
+  }
+}
+
+// termination predictor input: next_obs (* dropout multiplier)
+__global__ void wm_mask_copy_kernel(const float* __restrict__ x, const float* __restrict__ mask, long long n,
+                                    float* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = mask ? x[i] * mask[i] : x[i];
+}
+
+// StepLoader.sample on the device: uniform rows with replacement, Philox(seed, step, row, 0)
+__global__ void wm_gather_kernel(const float* __restrict__ obs, const float* __restrict__ act,
+                                 const float* __restrict__ next_obs, const float* __restrict__ rewards, long long n_rows,
+                                 int O, int A, int batch, unsigned long long seed, const int* __restrict__ step,
+                                 float* __restrict__ b_obs, float* __restrict__ b_act, float* __restrict__ b_next,
+                                 float* __restrict__ b_rew) {
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= batch) return;
+  const long long idx = philox_index(seed, (unsigned long long)*step, (uint32_t)row, 0u, (uint32_t)n_rows);
+  for (int j = lane; j < O; j += 32) {
+    b_obs[(long long)row * O + j] = obs[idx * O + j];
+    b_next[(long long)row * O + j] = next_obs[idx * O + j];
+  }
+  for (int j = lane; j < A; j += 32) b_act[(long long)row * A + j] = act[idx * A + j];
+  if (lane == 0) b_rew[row] = rewards[idx];
+}
+
+// fixed-order block reduction of up to 8 values per thread (256 threads); result valid in thread 0
+template <int NV>
+__device__ __forceinline__ void wm_block_reduce(float (&v)[NV], float (*sm)[NV]) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
+  if (lane == 0)
+#pragma unroll
+    for (int i = 0; i < NV; ++i) sm[w][i] = v[i];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      float s = 0.f;
+      for (int k = 0; k < 8; ++k) s += sm[k][i];
+      v[i] = s;
+    }
+  }
+}
+
+__device__ __forceinline__ float wm_sigmoid(float x) { return 1.f / (1.f + __expf(-x)); }
+// optax.sigmoid_binary_cross_entropy(logits, labels), stable form
+__device__ __forceinline__ float wm_bce(float x, float t) { return fmaxf(x, 0.f) - x * t + log1pf(expf(-fabsf(x))); }
+
+// state_prediction_loss (envmodel/loss.py:65-111) with weighted_binary_cross_entropy (:12-28): logs, d loss / d pred of
+// the squared-error term and d loss / d logit of the termination term. One CTA; `terminated` = rewards == 0.
+__global__ void __launch_bounds__(256) wm_state_loss_kernel(const float* __restrict__ pred,
+                                                            const float* __restrict__ next_obs,
+                                                            const float* __restrict__ logit,
+                                                            const float* __restrict__ rewards, int rows, int O,
+                                                            float ttw, float tw, float rw, float* __restrict__ dpred,
+                                                            float* __restrict__ dlogit, float* __restrict__ logs) {
+  __shared__ float sm[8][5];
+  const float denom = 1.f + tw + rw;
+  const bool term = tw > 0.f;
+  float v[5] = {0.f, 0.f, 0.f, 0.f, 0.f};  // squared error, true ce, false ce, n true, n false
+  for (int b = threadIdx.x; b < rows; b += 256) {
+    float se = 0.f;
+    for (int j = 0; j < O; ++j) {
+      const float d = pred[(long long)b * O + j] - next_obs[(long long)b * O + j];
+      se += d * d;
+      if (dpred) dpred[(long long)b * O + j] = 2.f * d / ((float)rows * O * denom);
+    }
+    v[0] += se;
+    if (term) {
+      const float x = logit[b], t = rewards[b] == 0.f ? 1.f : 0.f, ce = wm_bce(x, t);
+      if (t == 1.f) { v[1] += ce; v[3] += 1.f; } else { v[2] += ce; v[4] += 1.f; }
+      if (dlogit) dlogit[b] = (tw / denom) * (t == 1.f ? ttw : 1.f) * (wm_sigmoid(x) - t) / ((ttw + 1.f) * rows);
+    }
+  }
+  wm_block_reduce<5>(v, sm);
+  if (threadIdx.x == 0) {
+    const float mse = v[0] / ((float)rows * O);
+    const float tl = term ? (ttw * v[1] + v[2]) / ((ttw + 1.f) * rows) : 0.f;
+    logs[WL_NEXT_OBS_LOSS] = mse;
+    logs[WL_TERM_LOSS] = tl;
+    logs[WL_TRUE_LOSS] = term ? v[1] / v[3] : 0.f;   // 0 / 0 = NaN without positives, as in the reference
+    logs[WL_FALSE_LOSS] = term ? v[2] / v[4] : 0.f;
+    logs[WL_RECON_LOSS] = 0.f;
+    logs[WL_LOSS] = (mse + tw * tl) / denom;
+  }
+}
+
+// focal_loss (envmodel/loss.py:31-62) + the eval metrics of termination_predictor_trainer.py:88-126.
+__global__ void __launch_bounds__(256) wm_focal_loss_kernel(const float* __restrict__ logit,
+                                                            const float* __restrict__ rewards, int rows, float alpha,
+                                                            float gamma, float* __restrict__ dlogit,
+                                                            float* __restrict__ logs) {
+  __shared__ float sm[8][6];
+  float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // loss sum, n true, correct, true positives, predicted positives, -
+  for (int b = threadIdx.x; b < rows; b += 256) {
+    const float x = logit[b], t = rewards[b] == 0.f ? 1.f : 0.f, p = wm_sigmoid(x), ce = wm_bce(x, t);
+    float l, g;
+    if (t == 1.f) {
+      const float mod = powf(1.f - p, gamma);
+      l = alpha * mod * ce;
+      g = alpha * mod * (-gamma * p * ce - (1.f - p));
+    } else {
+      const float mod = powf(p, gamma);
+      l = (1.f - alpha) * mod * ce;
+      g = (1.f - alpha) * mod * (gamma * (1.f - p) * ce + p);
+    }
+    if (dlogit) dlogit[b] = g / rows;
+    const float pr = x > 0.f ? 1.f : 0.f;
+    v[0] += l; v[1] += t; v[2] += (pr == t) ? 1.f : 0.f; v[3] += pr * t; v[4] += pr;
+  }
+  wm_block_reduce<6>(v, sm);
+  if (threadIdx.x == 0) {
+    const float loss = v[0] / rows, nt = v[1], nf = rows - v[1];
+    logs[WL_LOSS] = loss;
+    logs[WL_TRUE_LOSS] = loss * nt / (nt + 1e-8f);   // the reference scales the MEAN loss by the class count (loss.py:57-60)
+    logs[WL_FALSE_LOSS] = loss * nf / (nf + 1e-8f);
+    const float prec = v[4] > 0.f ? v[3] / v[4] : 1.f, rec = nt > 0.f ? v[3] / nt : 1.f;
+    logs[WL_ACCURACY] = v[2] / rows;
+    logs[WL_PRECISION] = prec;
+    logs[WL_RECALL] = rec;
+    logs[WL_F1] = (prec + rec) > 0.f ? 2.f * prec * rec / (prec + rec) : 0.f;
+  }
+}
+
+// optax.adam(cosine_decay_schedule(lr0, decay_steps)): count starts at 0, the schedule is read BEFORE the increment,
+// bias correction uses count + 1; eps = 1e-8 outside the square root.
+__global__ void wm_adam_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
+                               const float* __restrict__ g, long long n, const int* __restrict__ step, float lr0,
+                               int decay_steps, float* __restrict__ logs) {
+  const int t = *step;
+  const float frac = (float)min(t, decay_steps) / (float)decay_steps;
+  const float lr = lr0 * 0.5f * (1.f + cospif(frac));
+  const float bc1 = 1.f - powf(0.9f, (float)(t + 1)), bc2 = 1.f - powf(0.999f, (float)(t + 1));
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) logs[WL_LR] = lr;
+  if (i >= n) return;
+  const float gi = g[i];
+  const float mi = 0.9f * m[i] + 0.1f * gi, vi = 0.999f * v[i] + 0.001f * gi * gi;
+  m[i] = mi;
+  v[i] = vi;
+  p[i] -= lr * (mi / bc1) / (sqrtf(vi / bc2) + 1e-8f);
+}
+
+__global__ void wm_tick_kernel(int* step, float* logs) {
+  *step += 1;
+  logs[WL_STEP] = (float)*step;
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------------------
+WmNet wm_layout(int in_dim, int n_hidden, const int* hidden, int out_dim, bool input_ln) {
+  WmNet n;
+  memset(&n, 0, sizeof(n));
+  n.n_layers = n_hidden + 1;
+  n.dims[0] = in_dim;
+  for (int i = 0; i < n_hidden; ++i) n.dims[i + 1] = hidden[i];
+  n.dims[n.n_layers] = out_dim;
+  long long off = 0;
+  n.off_ln_scale = n.off_ln_bias = -1;
+  if (input_ln) {
+    n.off_ln_scale = off; off += in_dim;
+    n.off_ln_bias = off; off += in_dim;
+  }
+  for (int l = 0; l < n.n_layers; ++l) {
+    n.offW[l] = off; off += (long long)n.dims[l] * n.dims[l + 1];
+    n.offB[l] = off; off += n.dims[l + 1];
+  }
+  n.n_params = off;
+  return n;
+}
+
+struct WmTrainer {
+  WmConfig cfg;
+  WmNet net, term;
+  int device = 0;
+  float *params = nullptr, *m = nullptr, *v = nullptr, *grads = nullptr, *term_params = nullptr;
+  float* x[kWmMaxLayers + 1] = {};    // x[0] = network input, x[l] = relu output of layer l-1, x[n_layers] = raw output
+  float* tx[kWmMaxLayers + 1] = {};   // frozen termination predictor on the prediction (tx[0] aliases the prediction)
+  float *xhat = nullptr, *pred = nullptr, *dbuf[2] = {nullptr, nullptr}, *dlogit = nullptr;
+  float *logs = nullptr;
+  int* step = nullptr;
+  // resident dataset + sampled batch
+  const float *ds_obs = nullptr, *ds_act = nullptr, *ds_next = nullptr, *ds_rew = nullptr;
+  long long ds_rows = 0;
+  float *b_obs = nullptr, *b_act = nullptr, *b_next = nullptr, *b_rew = nullptr;
+  // one captured graph per (mode, pointer set)
+  struct Key { int train; const void* p[5]; bool operator==(const Key& o) const { return train == o.train && !memcmp(p, o.p, sizeof(p)); } };
+  struct Entry { Key key; cudaGraphExec_t exec; int launches; };
+  std::vector<Entry> graphs;
+  long long launches = 0;
+  std::vector<void*> owned;
+};
+
+namespace {
+#define WM_CUDA(call)                                                                              \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      if (err) *err = std::string(#call) + ": " + cudaGetErrorString(e_);                          \
+      return 1;                                                                                    \
+    }                                                                                              \
+  } while (0)
+
+int wm_alloc(WmTrainer* t, float** p, long long n, std::string* err) {
+  WM_CUDA(cudaMalloc((void**)p, sizeof(float) * (size_t)(n > 0 ? n : 1)));
+  WM_CUDA(cudaMemset(*p, 0, sizeof(float) * (size_t)(n > 0 ? n : 1)));
+  t->owned.push_back(*p);
+  return 0;
+}
+
+struct Launcher {
+  cudaStream_t s;
+  int n = 0;
+  void gemm(bool ta, bool tb, const float* A, int lda, const float* B, int ldb, float* C, int ldc, int M, int N, int K,
+            int epi, const float* bias, const float* aux, int ldaux, int accumulate) {
+    dim3 grid((N + kWmTile - 1) / kWmTile, (M + kWmTile - 1) / kWmTile);
+    if (ta) wm_gemm_kernel<true, false><<<grid, 256, 0, s>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate);
+    else if (tb) wm_gemm_kernel<false, true><<<grid, 256, 0, s>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate);
+    else wm_gemm_kernel<false, false><<<grid, 256, 0, s>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate);
+    ++n;
+  }
+  void colsum(const float* X, const float* Y, int ld, int M, int N, float* out) {
+    wm_colsum_kernel<<<(N + 63) / 64, 64, 0, s>>>(X, Y, ld, M, N, out);
+    ++n;
+  }
+};
+
+// forward Dense stack: act[0] -> act[n_layers]; relu on hidden layers; last layer adds `resid` when given
+void wm_forward(Launcher& L, const WmNet& net, const float* params, float* const* act, int rows, const float* resid,
+                int ld_resid) {
+  for (int l = 0; l < net.n_layers; ++l) {
+    const bool last = l == net.n_layers - 1;
+    const int epi = last ? (resid ? WE_BIAS_RESID : WE_BIAS) : WE_BIAS_RELU;
+    L.gemm(false, false, act[l], net.dims[l], params + net.offW[l], net.dims[l + 1], act[l + 1], net.dims[l + 1], rows,
+           net.dims[l + 1], net.dims[l], epi, params + net.offB[l], last ? resid : nullptr, ld_resid, 0);
+  }
+}
+}  // namespace
+
+long long wm_num_params(const WmTrainer* t) { return t->net.n_params; }
+long long wm_launches(const WmTrainer* t) { return t->launches; }
+
+}  // namespace fqlpop
+
+namespace fqlpop {
+namespace {
+
+// Enqueues one step on L.s. gather != 0: the batch is first drawn from the resident dataset into the b_* buffers.
+void wm_issue(WmTrainer* t, Launcher& L, int train, int gather, const float* obs, const float* act, const float* next_obs,
+              const float* rew, const float* mask) {
+  const WmConfig& c = t->cfg;
+  const WmNet& net = t->net;
+  const int B = c.batch, O = c.O, A = c.A, nl = net.n_layers;
+  cudaStream_t s = L.s;
+  if (gather) {
+    wm_gather_kernel<<<(B * 32 + 255) / 256, 256, 0, s>>>(t->ds_obs, t->ds_act, t->ds_next, t->ds_rew, t->ds_rows, O, A, B,
+                                                         c.seed, t->step, t->b_obs, t->b_act, t->b_next, t->b_rew);
+    ++L.n;
+    obs = t->b_obs; act = t->b_act; next_obs = t->b_next; rew = t->b_rew;
+  }
+  const bool state = c.kind == WM_STATE;
+  const bool with_term = state && c.termination_weight > 0.f;
+  float* g = nullptr;  // gradient wrt the output of the layer being walked
+  if (state) {
+    wm_ln_concat_kernel<<<(B * 32 + 255) / 256, 256, 0, s>>>(obs, act, O, A, B, t->params + net.off_ln_scale,
+                                                            t->params + net.off_ln_bias, c.ln_eps, t->x[0], t->xhat);
+    ++L.n;
+    wm_forward(L, net, t->params, t->x, B, obs, O);  // x[nl] = Dense_O(x) + obs
+    if (with_term) wm_forward(L, t->term, t->term_params, t->tx, B, nullptr, 0);  // tx[0] aliases x[nl]
+    wm_state_loss_kernel<<<1, 256, 0, s>>>(t->x[nl], next_obs, with_term ? t->tx[t->term.n_layers] : nullptr, rew, B, O,
+                                           c.true_termination_weight, c.termination_weight, c.reconstruction_weight,
+                                           train ? t->pred : nullptr, train ? t->dlogit : nullptr, t->logs);
+    ++L.n;
+    if (!train) return;
+    if (with_term) {  // d loss / d prediction through the frozen termination predictor, added onto the squared-error part
+      const WmNet& tn = t->term;
+      const float* gt = t->dlogit;
+      for (int l = tn.n_layers - 1; l >= 0; --l) {
+        float* out = l == 0 ? t->pred : t->dbuf[l & 1];
+        L.gemm(false, true, gt, tn.dims[l + 1], t->term_params + tn.offW[l], tn.dims[l + 1], out, tn.dims[l], B, tn.dims[l],
+               tn.dims[l + 1], l == 0 ? WE_NONE : WE_MASK, nullptr, l == 0 ? nullptr : t->tx[l], tn.dims[l], l == 0);
+        gt = out;
+      }
+    }
+    g = t->pred;
+  } else {
+    wm_mask_copy_kernel<<<(int)(((long long)B * O + 255) / 256), 256, 0, s>>>(next_obs, train ? mask : nullptr,
+                                                                             (long long)B * O, t->x[0]);
+    ++L.n;
+    wm_forward(L, net, t->params, t->x, B, nullptr, 0);
+    wm_focal_loss_kernel<<<1, 256, 0, s>>>(t->x[nl], rew, B, c.focal_alpha, c.focal_gamma, train ? t->dlogit : nullptr,
+                                           t->logs);
+    ++L.n;
+    if (!train) return;
+    g = t->dlogit;
+  }
+  // backward through the trained network
+  for (int l = nl - 1; l >= 0; --l) {
+    const int din = net.dims[l], dout = net.dims[l + 1];
+    L.gemm(true, false, t->x[l], din, g, dout, t->grads + net.offW[l], dout, din, dout, B, WE_NONE, nullptr, nullptr, 0, 0);
+    L.colsum(g, nullptr, dout, B, dout, t->grads + net.offB[l]);
+    if (l > 0 || state) {
+      float* out = t->dbuf[l & 1];
+      L.gemm(false, true, g, dout, t->params + net.offW[l], dout, out, din, B, din, dout, l > 0 ? WE_MASK : WE_NONE, nullptr,
+             l > 0 ? t->x[l] : nullptr, din, 0);
+      g = out;
+    }
+  }
+  if (state) {  // input LayerNorm: d scale = sum_b dx0 * xhat, d bias = sum_b dx0
+    L.colsum(g, t->xhat, net.dims[0], B, net.dims[0], t->grads + net.off_ln_scale);
+    L.colsum(g, nullptr, net.dims[0], B, net.dims[0], t->grads + net.off_ln_bias);
+  }
+  wm_adam_kernel<<<(int)((net.n_params + 255) / 256), 256, 0, s>>>(t->params, t->m, t->v, t->grads, net.n_params, t->step,
+                                                                  c.lr, c.decay_steps, t->logs);
+  wm_tick_kernel<<<1, 1, 0, s>>>(t->step, t->logs);
+  L.n += 2;
+}
+
+int wm_run(WmTrainer* t, int train, int gather, int repeats, const float* obs, const float* act, const float* next_obs,
+           const float* rew, const float* mask, cudaStream_t stream, std::string* err) {
+  WM_CUDA(cudaSetDevice(t->device));
+  WmTrainer::Key key{train + 2 * gather, {obs, act, next_obs, rew, mask}};
+  WmTrainer::Entry* e = nullptr;
+  for (auto& g : t->graphs)
+    if (g.key == key) e = &g;
+  if (!e) {
+    if (t->graphs.size() >= 8) {
+      cudaGraphExecDestroy(t->graphs.front().exec);
+      t->graphs.erase(t->graphs.begin());
+    }
+    cudaStream_t cs;
+    WM_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+    WM_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+    Launcher L{cs};
+    wm_issue(t, L, train, gather, obs, act, next_obs, rew, mask);
+    cudaGraph_t graph = nullptr;
+    cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+    cudaError_t le = cudaGetLastError();
+    if (ce != cudaSuccess || le != cudaSuccess) {
+      if (err) *err = std::string("world-model step capture: ") + cudaGetErrorString(ce != cudaSuccess ? ce : le);
+      cudaStreamDestroy(cs);
+      return 1;
+    }
+    cudaGraphExec_t exec;
+    WM_CUDA(cudaGraphInstantiate(&exec, graph, 0));
+    cudaGraphDestroy(graph);
+    cudaStreamDestroy(cs);
+    t->graphs.push_back({key, exec, L.n});
+    e = &t->graphs.back();
+  }
+  for (int i = 0; i < repeats; ++i) WM_CUDA(cudaGraphLaunch(e->exec, stream));
+  t->launches += (long long)repeats * e->launches;
+  return 0;
+}
+}  // namespace
+
+int wm_create_impl(const WmConfig& cfg, const float* params_host, const float* term_params_host, WmTrainer** out,
+                   std::string* err) {
+  auto bad = [&](const char* m) { if (err) *err = m; return 1; };
+  if (cfg.kind != WM_STATE && cfg.kind != WM_TERMINATION) return bad("world model: kind must be 0 (state) or 1 (termination)");
+  if (cfg.O < 1 || cfg.A < 0 || cfg.batch < 1) return bad("world model: bad dimensions");
+  if (cfg.n_hidden < 1 || cfg.n_hidden >= kWmMaxLayers) return bad("world model: between 1 and 7 hidden layers");
+  if (cfg.decay_steps < 1) return bad("world model: decay_steps must be positive");
+  if (!params_host) return bad("world model: initial parameters are required");
+  const bool state = cfg.kind == WM_STATE;
+  const bool with_term = state && cfg.termination_weight > 0.f;
+  if (with_term && (!term_params_host || cfg.term_n_hidden < 1 || cfg.term_n_hidden >= kWmMaxLayers))
+    return bad("world model: termination_weight > 0 needs the trained termination predictor (parameters + hidden dims)");
+  WmTrainer* t = new WmTrainer();
+  t->cfg = cfg;
+  cudaGetDevice(&t->device);
+  t->net = state ? wm_layout(cfg.O + cfg.A, cfg.n_hidden, cfg.hidden, cfg.O, true)
+                 : wm_layout(cfg.O, cfg.n_hidden, cfg.hidden, 1, false);
+  const long long n = t->net.n_params;
+  const int B = cfg.batch;
+  int maxdim = 1;
+  for (int l = 0; l <= t->net.n_layers; ++l) maxdim = std::max(maxdim, t->net.dims[l]);
+  int rc = 0;
+  rc |= wm_alloc(t, &t->params, n, err) || wm_alloc(t, &t->m, n, err) || wm_alloc(t, &t->v, n, err) ||
+        wm_alloc(t, &t->grads, n, err);
+  for (int l = 0; l <= t->net.n_layers && !rc; ++l) rc |= wm_alloc(t, &t->x[l], (long long)B * t->net.dims[l], err);
+  if (!rc && state) rc |= wm_alloc(t, &t->xhat, (long long)B * t->net.dims[0], err);
+  if (!rc && with_term) {
+    t->term = wm_layout(cfg.O, cfg.term_n_hidden, cfg.term_hidden, 1, false);
+    for (int l = 0; l <= t->term.n_layers; ++l) maxdim = std::max(maxdim, t->term.dims[l]);
+    rc |= wm_alloc(t, &t->term_params, t->term.n_params, err);
+    t->tx[0] = t->x[t->net.n_layers];
+    for (int l = 1; l <= t->term.n_layers && !rc; ++l) rc |= wm_alloc(t, &t->tx[l], (long long)B * t->term.dims[l], err);
+    if (!rc && cudaMemcpy(t->term_params, term_params_host, sizeof(float) * t->term.n_params, cudaMemcpyHostToDevice) != cudaSuccess)
+      rc = bad("world model: copying the termination predictor failed");
+  }
+  if (!rc)
+    rc |= wm_alloc(t, &t->pred, (long long)B * cfg.O, err) || wm_alloc(t, &t->dbuf[0], (long long)B * maxdim, err) ||
+          wm_alloc(t, &t->dbuf[1], (long long)B * maxdim, err) || wm_alloc(t, &t->dlogit, B, err) ||
+          wm_alloc(t, &t->logs, kWmLogs, err) || wm_alloc(t, (float**)&t->step, 1, err) ||
+          wm_alloc(t, &t->b_obs, (long long)B * cfg.O, err) || wm_alloc(t, &t->b_act, (long long)B * std::max(cfg.A, 1), err) ||
+          wm_alloc(t, &t->b_next, (long long)B * cfg.O, err) || wm_alloc(t, &t->b_rew, B, err);
+  if (!rc && cudaMemcpy(t->params, params_host, sizeof(float) * n, cudaMemcpyHostToDevice) != cudaSuccess)
+    rc = bad("world model: copying the initial parameters failed");
+  if (rc) {
+    wm_destroy_impl(t);
+    return 1;
+  }
+  *out = t;
+  return 0;
+}
+
+void wm_destroy_impl(WmTrainer* t) {
+  if (!t) return;
+  cudaSetDevice(t->device);
+  cudaDeviceSynchronize();
+  for (auto& g : t->graphs) cudaGraphExecDestroy(g.exec);
+  for (void* p : t->owned) cudaFree(p);
+  delete t;
+}
+
+int wm_step_impl(WmTrainer* t, int train, const float* obs, const float* act, const float* next_obs, const float* rewards,
+                 const float* dropout_mask, cudaStream_t stream, std::string* err) {
+  if (!next_obs || !rewards || (t->cfg.kind == WM_STATE && (!obs || !act))) {
+    if (err) *err = "world-model step: null batch pointer";
+    return 1;
+  }
+  return wm_run(t, train ? 1 : 0, 0, 1, obs, act, next_obs, rewards, train ? dropout_mask : nullptr, stream, err);
+}
+
+int wm_set_dataset_impl(WmTrainer* t, const float* obs, const float* act, const float* next_obs, const float* rewards,
+                        long long n_rows, std::string* err) {
+  if (!obs || !act || !next_obs || !rewards || n_rows < 1 || n_rows > 0xffffffffLL) {
+    if (err) *err = "world-model dataset: null pointer or row count outside [1, 2^32)";
+    return 1;
+  }
+  t->ds_obs = obs; t->ds_act = act; t->ds_next = next_obs; t->ds_rew = rewards; t->ds_rows = n_rows;
+  for (auto& g : t->graphs) cudaGraphExecDestroy(g.exec);  // captured gathers hold the old pointers
+  t->graphs.clear();
+  return 0;
+}
+
+int wm_train_impl(WmTrainer* t, int n_steps, const float* dropout_mask, cudaStream_t stream, std::string* err) {
+  if (!t->ds_rows) {
+    if (err) *err = "world-model train: no resident dataset (fqlpop_wm_set_dataset)";
+    return 1;
+  }
+  if (n_steps < 0) n_steps = 0;
+  return wm_run(t, 1, 1, n_steps, t->ds_obs, t->ds_act, t->ds_next, t->ds_rew, dropout_mask, stream, err);
+}
+
+int wm_logs_impl(WmTrainer* t, float* out_host, cudaStream_t stream, std::string* err) {
+  WM_CUDA(cudaSetDevice(t->device));
+  WM_CUDA(cudaMemcpyAsync(out_host, t->logs, sizeof(float) * kWmLogs, cudaMemcpyDeviceToHost, stream));
+  WM_CUDA(cudaStreamSynchronize(stream));
+  return 0;
+}
+
+int wm_export_impl(WmTrainer* t, int which, float* out_host, long long n, cudaStream_t stream, std::string* err) {
+  if (which < 0 || which > 3 || n != t->net.n_params) {
+    if (err) *err = "world-model export: which must be 0..3 and n the parameter count";
+    return 1;
+  }
+  const float* src = which == 0 ? t->params : which == 1 ? t->m : which == 2 ? t->v : t->grads;
+  WM_CUDA(cudaSetDevice(t->device));
+  WM_CUDA(cudaMemcpyAsync(out_host, src, sizeof(float) * n, cudaMemcpyDeviceToHost, stream));
+  WM_CUDA(cudaStreamSynchronize(stream));
+  return 0;
+}
+
+}  // namespace fqlpop

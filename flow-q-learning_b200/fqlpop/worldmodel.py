@@ -1,0 +1,238 @@
+"""ctypes binding of the world-model training entry points of libfqlpop.so (include/fqlpop.h, fqlpop_wm_*).
+
+Replaces the jitted train_step / eval_step of StatePredictorTrainer
+(/root/reference/envmodel/state_predictor_trainer.py:70-125) and TerminationPredictorTrainer
+(/root/reference/envmodel/termination_predictor_trainer.py:58-126). Parameter trees use flax's auto-names
+(`LayerNorm_0`, `Dense_i` with `kernel` [in][out] / `bias`), i.e. what `flax.serialization.to_bytes(state.params)`
+stores under "params" (train_env_model.py:123-127) and what utils/envmodel.load_model reads back.
+There is no CPU fallback.
+"""
+import ctypes
+from typing import Dict, Optional, Sequence
+
+import numpy as np
+import torch
+
+from ._lib import check, default_device, lib
+
+STATE, TERMINATION = 0, 1
+LOG_SLOTS = 16
+_STATE_LOGS = {"loss": 0, "next_observation_loss": 1, "termination_loss": 2, "true_termination_loss": 3,
+               "false_termination_loss": 4}
+_TERM_LOGS = {"loss": 0, "true_loss": 3, "false_loss": 4}
+_TERM_EVAL_LOGS = {"accuracy": 6, "precision": 7, "recall": 8, "f1": 9}
+
+
+class WmConfig(ctypes.Structure):
+    _fields_ = [
+        ("kind", ctypes.c_int32), ("ob_dim", ctypes.c_int32), ("action_dim", ctypes.c_int32), ("batch", ctypes.c_int32),
+        ("n_hidden", ctypes.c_int32), ("hidden", ctypes.c_int32 * 8),
+        ("term_n_hidden", ctypes.c_int32), ("term_hidden", ctypes.c_int32 * 8),
+        ("decay_steps", ctypes.c_int32), ("lr", ctypes.c_float), ("ln_eps", ctypes.c_float),
+        ("true_termination_weight", ctypes.c_float), ("termination_weight", ctypes.c_float),
+        ("reconstruction_weight", ctypes.c_float),
+        ("focal_alpha", ctypes.c_float), ("focal_gamma", ctypes.c_float),
+        ("seed", ctypes.c_uint64),
+    ]
+
+
+_F = ctypes.POINTER(ctypes.c_float)
+lib.fqlpop_wm_num_params.argtypes = [ctypes.POINTER(WmConfig)]
+lib.fqlpop_wm_num_params.restype = ctypes.c_int64
+lib.fqlpop_wm_create.argtypes = [ctypes.POINTER(WmConfig), ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+lib.fqlpop_wm_destroy.argtypes = [ctypes.c_void_p]
+lib.fqlpop_wm_step.argtypes = [ctypes.c_void_p, ctypes.c_int32] + [ctypes.c_void_p] * 6
+lib.fqlpop_wm_set_dataset.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_int64]
+lib.fqlpop_wm_train.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]
+lib.fqlpop_wm_logs.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+lib.fqlpop_wm_export.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
+lib.fqlpop_wm_launches.argtypes = [ctypes.c_void_p]
+lib.fqlpop_wm_launches.restype = ctypes.c_int64
+
+
+def _np32(x) -> np.ndarray:
+    if hasattr(x, "detach"):
+        x = x.detach().cpu().numpy()
+    return np.ascontiguousarray(np.asarray(x, dtype=np.float32))
+
+
+def layer_dims(kind: int, ob_dim: int, action_dim: int, hidden: Sequence[int]):
+    return ([ob_dim + action_dim, *hidden, ob_dim] if kind == STATE else [ob_dim, *hidden, 1])
+
+
+def flatten_params(tree: Dict, kind: int) -> np.ndarray:
+    """flax tree -> the flat vector of include/fqlpop.h (LayerNorm scale, bias, then kernel, bias per Dense layer)."""
+    parts = []
+    if kind == STATE:
+        parts += [_np32(tree["LayerNorm_0"]["scale"]).ravel(), _np32(tree["LayerNorm_0"]["bias"]).ravel()]
+    n = sum(1 for k in tree if k.startswith("Dense_"))
+    for i in range(n):
+        parts += [_np32(tree[f"Dense_{i}"]["kernel"]).ravel(), _np32(tree[f"Dense_{i}"]["bias"]).ravel()]
+    return np.ascontiguousarray(np.concatenate(parts))
+
+
+def unflatten_params(flat: np.ndarray, kind: int, dims: Sequence[int]) -> Dict:
+    tree, off = {}, 0
+
+    def take(*shape):
+        nonlocal off
+        n = int(np.prod(shape))
+        out = flat[off:off + n].reshape(shape).copy()
+        off += n
+        return out
+
+    if kind == STATE:
+        tree["LayerNorm_0"] = {"scale": take(dims[0]), "bias": take(dims[0])}
+    for i in range(len(dims) - 1):
+        tree[f"Dense_{i}"] = {"kernel": take(dims[i], dims[i + 1]), "bias": take(dims[i + 1])}
+    assert off == flat.size
+    return tree
+
+
+def init_params(seed: int, kind: int, ob_dim: int, action_dim: int, hidden: Sequence[int]) -> Dict:
+    """flax defaults for nn.Dense / nn.LayerNorm without initialisers (envmodel/baseline.py:31-36): LeCun-normal kernels
+    (truncated at two standard deviations, variance 1/fan_in), zero biases, scale 1. The random stream is numpy's, not
+    JAX's threefry."""
+    rng = np.random.default_rng(seed)
+    dims = layer_dims(kind, ob_dim, action_dim, hidden)
+    tree = {}
+    if kind == STATE:
+        tree["LayerNorm_0"] = {"scale": np.ones(dims[0], np.float32), "bias": np.zeros(dims[0], np.float32)}
+    for i in range(len(dims) - 1):
+        n = dims[i] * dims[i + 1]
+        z = rng.standard_normal(n)
+        while True:  # truncated normal on [-2, 2] by resampling
+            bad = np.abs(z) > 2.0
+            if not bad.any():
+                break
+            z[bad] = rng.standard_normal(int(bad.sum()))
+        std = np.sqrt(1.0 / dims[i]) / 0.87962566103423978
+        tree[f"Dense_{i}"] = {"kernel": (z * std).astype(np.float32).reshape(dims[i], dims[i + 1]),
+                              "bias": np.zeros(dims[i + 1], np.float32)}
+    return tree
+
+
+class WorldModelTrainer:
+    """Device-resident trainer of one world-model network. `step` takes an explicit batch (parity mode, validation);
+    `set_dataset` + `train(n)` keep the dataset in HBM and sample on the device."""
+
+    def __init__(self, kind: int, ob_dim: int, action_dim: int, hidden_dims: Sequence[int], batch_size: int, steps: int,
+                 init_learning_rate: float = 1e-3, params: Optional[Dict] = None, seed: int = 0,
+                 termination_params: Optional[Dict] = None, termination_hidden_dims: Sequence[int] = (),
+                 true_termination_weight: float = 30.0, termination_weight: float = 1.0,
+                 reconstruction_weight: float = 0.0, focal_alpha: float = 0.25, focal_gamma: float = 2.0,
+                 ln_eps: float = 1e-6, device=None):
+        self.device = torch.device(device) if device is not None else default_device()
+        self.kind, self.ob_dim, self.action_dim = kind, ob_dim, action_dim
+        self.hidden_dims, self.batch_size = tuple(int(h) for h in hidden_dims), int(batch_size)
+        self.dims = layer_dims(kind, ob_dim, action_dim, self.hidden_dims)
+        c = WmConfig()
+        c.kind, c.ob_dim, c.action_dim, c.batch = kind, ob_dim, action_dim, batch_size
+        c.n_hidden = len(self.hidden_dims)
+        for i, h in enumerate(self.hidden_dims):
+            c.hidden[i] = h
+        with_term = kind == STATE and termination_weight > 0
+        if with_term:
+            if termination_params is None:
+                raise ValueError("termination_weight > 0 needs the trained termination predictor's parameters")
+            c.term_n_hidden = len(termination_hidden_dims)
+            for i, h in enumerate(termination_hidden_dims):
+                c.term_hidden[i] = int(h)
+        c.decay_steps, c.lr, c.ln_eps = int(steps), init_learning_rate, ln_eps
+        c.true_termination_weight, c.termination_weight = true_termination_weight, termination_weight
+        c.reconstruction_weight = reconstruction_weight
+        c.focal_alpha, c.focal_gamma, c.seed = focal_alpha, focal_gamma, seed
+        self._cfg = c
+        self.n_params = int(lib.fqlpop_wm_num_params(ctypes.byref(c)))
+        if params is None:
+            params = init_params(seed, kind, ob_dim, action_dim, self.hidden_dims)
+        flat = flatten_params(params, kind)
+        if flat.size != self.n_params:
+            raise ValueError(f"parameter tree has {flat.size} values, the network needs {self.n_params}")
+        tflat = flatten_params(termination_params, TERMINATION) if with_term else None
+        self._h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            check(lib.fqlpop_wm_create(ctypes.byref(c), flat.ctypes.data, tflat.ctypes.data if with_term else None,
+                                       ctypes.byref(self._h)), "fqlpop_wm_create")
+        self._keep = {}
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.fqlpop_wm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _dev(self, x):
+        return torch.as_tensor(np.asarray(x, dtype=np.float32) if not torch.is_tensor(x) else x,
+                               dtype=torch.float32).to(self.device).contiguous()
+
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def logs(self) -> np.ndarray:
+        out = np.zeros(LOG_SLOTS, np.float32)
+        check(lib.fqlpop_wm_logs(self._h, out.ctypes.data, self._stream()), "fqlpop_wm_logs")
+        return out
+
+    def named_logs(self, train: bool) -> Dict[str, float]:
+        raw = self.logs()
+        if self.kind == STATE:
+            keys = dict(_STATE_LOGS)
+            if not self._cfg.termination_weight > 0:
+                keys = {"loss": 0, "next_observation_loss": 1}
+        else:
+            keys = dict(_TERM_LOGS)
+            if not train:
+                keys.update(_TERM_EVAL_LOGS)
+        return {k: float(raw[i]) for k, i in keys.items()}
+
+    def step(self, batch: Dict, train: bool = True, dropout_mask=None) -> Dict[str, float]:
+        """One train_step (train=True) or eval_step on an explicit batch; returns the reference's logs dict."""
+        with torch.cuda.device(self.device):
+            t = {k: self._dev(batch[k]) for k in ("observations", "actions", "next_observations", "rewards") if k in batch}
+            n = t["next_observations"].shape[0]
+            if n != self.batch_size:
+                raise ValueError(f"batch has {n} rows, the trainer was built for {self.batch_size}")
+            m = self._dev(dropout_mask) if (dropout_mask is not None and train) else None
+            ptr = lambda k: t[k].data_ptr() if k in t else None
+            check(lib.fqlpop_wm_step(self._h, 1 if train else 0, ptr("observations"), ptr("actions"),
+                                     ptr("next_observations"), ptr("rewards"), m.data_ptr() if m is not None else None,
+                                     self._stream()), "fqlpop_wm_step")
+            return self.named_logs(train)
+
+    def set_dataset(self, dataset: Dict):
+        with torch.cuda.device(self.device):
+            self._keep = {k: self._dev(dataset[k]) for k in ("observations", "actions", "next_observations", "rewards")}
+            d = self._keep
+            check(lib.fqlpop_wm_set_dataset(self._h, d["observations"].data_ptr(), d["actions"].data_ptr(),
+                                            d["next_observations"].data_ptr(), d["rewards"].data_ptr(),
+                                            d["observations"].shape[0]), "fqlpop_wm_set_dataset")
+
+    def train(self, n_steps: int, dropout_mask=None):
+        """n_steps optimiser steps on batches sampled on the device from the resident dataset (asynchronous)."""
+        with torch.cuda.device(self.device):
+            if dropout_mask is not None:
+                self._keep["mask"] = self._dev(dropout_mask)
+            m = self._keep.get("mask")
+            check(lib.fqlpop_wm_train(self._h, int(n_steps), m.data_ptr() if m is not None else None, self._stream()),
+                  "fqlpop_wm_train")
+
+    def export(self, which: int = 0) -> np.ndarray:
+        out = np.zeros(self.n_params, np.float32)
+        check(lib.fqlpop_wm_export(self._h, which, out.ctypes.data, self.n_params, self._stream()), "fqlpop_wm_export")
+        return out
+
+    def params(self) -> Dict:
+        return unflatten_params(self.export(0), self.kind, self.dims)
+
+    def grads(self) -> Dict:
+        return unflatten_params(self.export(3), self.kind, self.dims)
+
+    @property
+    def launches(self) -> int:
+        return int(lib.fqlpop_wm_launches(self._h))

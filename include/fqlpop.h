@@ -160,6 +160,47 @@ int fqlpop_env_step(void* envmodel, const float* obs, const float* actions, int3
 /* Kernels launched so far by fqlpop_rollout / fqlpop_sample_actions on this handle (bench.py's gpu_launches). */
 int64_t fqlpop_rollout_launches(void* handle);
 
+/* ---- world-model training ----------------------------------------------------------------
+ * Replaces StatePredictorTrainer.train_step / eval_step (envmodel/state_predictor_trainer.py:70-125) for the
+ * BaselineStatePredictor (envmodel/baseline.py:25-37) and TerminationPredictorTrainer.train_step / eval_step
+ * (envmodel/termination_predictor_trainer.py:58-126) for the TerminationPredictor, with the losses of
+ * envmodel/loss.py:7-111 and optax.adam over optax.cosine_decay_schedule(init_learning_rate, steps).
+ * Parameters travel as ONE flat fp32 vector: [LayerNorm scale, LayerNorm bias (state predictor only, ob_dim+action_dim
+ * each)], then per Dense layer (hidden..., output) kernel [in][out] (flax layout) followed by bias [out].             */
+typedef struct {
+  int32_t kind;                       /* 0 state predictor, 1 termination predictor                               */
+  int32_t ob_dim, action_dim, batch;
+  int32_t n_hidden, hidden[8];
+  int32_t term_n_hidden, term_hidden[8]; /* kind 0, termination_weight > 0: the frozen termination predictor      */
+  int32_t decay_steps;                /* TrainerConfig.steps (envmodel/config.py:8)                               */
+  float lr, ln_eps;                   /* init_learning_rate (config.py:15); flax LayerNorm eps 1e-6               */
+  float true_termination_weight, termination_weight, reconstruction_weight;   /* config.py:11-13                 */
+  float focal_alpha, focal_gamma;     /* kind 1: focal_loss defaults 0.25 / 2.0 (loss.py:34-35)                  */
+  uint64_t seed;                      /* Philox stream of fqlpop_wm_train's sampler                               */
+} fqlpop_wm_config_t;
+/* Number of floats of the flat parameter vector of a network with this config (same for m, v, gradients).  */
+int64_t fqlpop_wm_num_params(const fqlpop_wm_config_t* cfg);
+int fqlpop_wm_create(const fqlpop_wm_config_t* cfg, const float* params_host, const float* term_params_host,
+                     void** out_handle);
+int fqlpop_wm_destroy(void* wm);
+/* One optimiser step (train != 0) or one forward-only evaluation on an explicit batch (all dev, fp32):
+ * obs[batch][ob_dim], act[batch][action_dim] (kind 0 only), next_obs[batch][ob_dim], rewards[batch]
+ * (terminated = rewards == 0), dropout_mask[batch][ob_dim] (kind 1 training, optional): the multiplier
+ * keep / (1 - 0.1) of nn.Dropout(0.1) -- the reference passes the SAME rng every step, i.e. one fixed mask.       */
+int fqlpop_wm_step(void* wm, int32_t train, const float* obs, const float* act, const float* next_obs,
+                   const float* rewards, const float* dropout_mask, void* stream);
+/* StepLoader.sample on the device (utils/data_loader.py:42-47): borrow a resident dataset of n_rows transitions,
+ * then run n_steps optimiser steps, each on `batch` rows drawn uniformly with replacement (Philox(seed, step)).  */
+int fqlpop_wm_set_dataset(void* wm, const float* obs, const float* act, const float* next_obs, const float* rewards,
+                          int64_t n_rows);
+int fqlpop_wm_train(void* wm, int32_t n_steps, const float* dropout_mask, void* stream);
+/* out_host[16]: 0 loss, 1 next_observation_loss, 2 termination_loss, 3 true_(termination_)loss, 4 false_(termination_)loss,
+ * 5 reconstruction_loss, 6 accuracy, 7 precision, 8 recall, 9 f1, 10 learning rate of the last step, 11 steps taken. */
+int fqlpop_wm_logs(void* wm, float* out_host, void* stream);
+/* which: 0 parameters, 1 Adam m, 2 Adam v, 3 gradients of the last training step; n = fqlpop_wm_num_params.     */
+int fqlpop_wm_export(void* wm, int32_t which, float* out_host, int64_t n, void* stream);
+int64_t fqlpop_wm_launches(void* wm);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,185 @@
+"""Parity of world-model training (fqlpop_wm_* through the C-ABI) with the CPU oracle oracle/wm_oracle.py (GPU only).
+
+The kernels compute in fp32 like the reference; the oracle runs in float64 with autograd. Tolerances:
+  * logs (losses, metrics): rtol 2e-5 / atol 1e-6;
+  * gradients of one step: max-abs error <= 2e-5 * max|g| per leaf (fp32 accumulation order);
+  * parameters after a few Adam steps: atol 2e-4 at lr 1e-3 -- the first Adam steps move every weight by ~lr * sign(g),
+    so a gradient whose sign is decided by rounding moves by up to lr in either direction; the FRACTION of such entries
+    is bounded (< 0.1 %) and everything else must agree to 2e-5.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import fql_oracle as orc  # noqa: E402  (checker only)
+from oracle import philox_oracle as phx  # noqa: E402
+from oracle import wm_oracle as wmo  # noqa: E402
+
+O, A, B = 28, 5, 256
+HID = (128, 256, 128)
+THID = (128, 256, 128)
+
+
+def _t64(tree):
+    return {k: (_t64(v) if isinstance(v, dict) else torch.as_tensor(np.asarray(v), dtype=torch.float64)) for k, v in tree.items()}
+
+
+def _np(tree):
+    return {k: (_np(v) if isinstance(v, dict) else v.detach().cpu().numpy().astype(np.float32)) for k, v in tree.items()}
+
+
+def _batch(seed, rows=B, p_term=0.1):
+    g = torch.Generator().manual_seed(seed)
+    obs = torch.randn(rows, O, generator=g, dtype=torch.float64)
+    act = torch.rand(rows, A, generator=g, dtype=torch.float64) * 2 - 1
+    nxt = obs + 0.05 * torch.randn(rows, O, generator=g, dtype=torch.float64)
+    rew = -(torch.rand(rows, generator=g) >= p_term).to(torch.float64)  # 0 with probability p_term, else -1
+    return {"observations": obs, "actions": act, "next_observations": nxt, "rewards": rew}
+
+
+def _f32(batch):
+    return {k: v.to(torch.float32).numpy() for k, v in batch.items()}
+
+
+def _envmodel(seed=5):
+    em = orc.init_envmodel(seed, O, A, HID, dtype=torch.float64)
+    g = torch.Generator().manual_seed(seed + 1)
+    for net in ("state", "termination"):
+        for name, leaf in orc.tree_leaves(em[net]):
+            if name.endswith("bias") or name.endswith("scale"):
+                leaf.add_(0.05 * torch.randn(leaf.shape, generator=g, dtype=torch.float64))
+    return em
+
+
+def _check_tree(got, want, rel, what):
+    for (name, w) in wmo.tree_leaves(want):
+        gv = got
+        for k in name.split("/"):
+            gv = gv[k]
+        w = w.detach().numpy()
+        err = np.abs(gv.astype(np.float64) - w).max()
+        assert err <= rel * max(np.abs(w).max(), 1e-12), f"{what} {name}: max err {err:.3e} vs scale {np.abs(w).max():.3e}"
+
+
+def _check_params(got, want, lr):
+    tot = bad = 0
+    for (name, w) in wmo.tree_leaves(want):
+        gv = got
+        for k in name.split("/"):
+            gv = gv[k]
+        d = np.abs(gv.astype(np.float64) - w.detach().numpy())
+        assert d.max() <= 4 * lr, f"{name}: {d.max():.3e}"
+        tot += d.size
+        bad += int((d > 2e-5).sum())
+    assert bad <= 1e-3 * tot, f"{bad} of {tot} parameters differ by more than 2e-5"
+
+
+def _logs_close(got, want, keys):
+    for k in keys:
+        assert got[k] == pytest.approx(want[k], rel=2e-5, abs=1e-6), (k, got[k], want[k])
+
+
+@pytest.mark.parametrize("termination_weight", [1.0, 0.0], ids=["with_termination", "mse_only"])
+def test_state_predictor_steps_match_oracle(termination_weight):
+    from fqlpop.worldmodel import STATE, WorldModelTrainer
+    em = _envmodel()
+    params, term = em["state"], em["termination"]
+    tr = WorldModelTrainer(STATE, O, A, HID, B, steps=100, init_learning_rate=1e-3, params=_np(params),
+                           termination_params=_np(term) if termination_weight > 0 else None,
+                           termination_hidden_dims=THID, true_termination_weight=30.0,
+                           termination_weight=termination_weight)
+    opt = wmo.new_opt_state(params)
+    keys = ["loss", "next_observation_loss"] + (["termination_loss", "true_termination_loss", "false_termination_loss"]
+                                                if termination_weight > 0 else [])
+    for step in range(3):
+        batch = _batch(10 + step)
+        params, want, g = wmo.state_step(params, opt, batch, term, lr0=1e-3, decay_steps=100,
+                                         true_termination_weight=30.0, termination_weight=termination_weight)
+        got = tr.step(_f32(batch), train=True)
+        _logs_close(got, want, keys)
+        if step == 0:
+            _check_tree(tr.grads(), g, 2e-5, "grad")
+        assert tr.logs()[10] == pytest.approx(want["learning_rate"], rel=1e-5)
+    _check_params(tr.params(), params, 1e-3)
+    # eval_step: forward only, parameters untouched
+    before = tr.export(0)
+    batch = _batch(77)
+    _, want, _ = wmo.state_step(_t64(tr.params()), None, batch, term, lr0=1e-3, decay_steps=100,
+                                true_termination_weight=30.0, termination_weight=termination_weight, train=False)
+    _logs_close(tr.step(_f32(batch), train=False), want, keys)
+    assert np.array_equal(before, tr.export(0))
+    assert tr.logs()[11] == 3.0
+
+
+def test_termination_predictor_steps_match_oracle():
+    from fqlpop.worldmodel import TERMINATION, WorldModelTrainer
+    params = _envmodel(9)["termination"]
+    tr = WorldModelTrainer(TERMINATION, O, A, THID, B, steps=50, init_learning_rate=1e-3, params=_np(params))
+    opt = wmo.new_opt_state(params)
+    g = torch.Generator().manual_seed(3)
+    mask = (torch.rand(B, O, generator=g) >= 0.1).to(torch.float64) / 0.9  # nn.Dropout(0.1) multiplier, fixed
+    for step in range(3):
+        batch = _batch(20 + step)
+        params, want, gr = wmo.termination_step(params, opt, batch, mask, lr0=1e-3, decay_steps=50)
+        got = tr.step(_f32(batch), train=True, dropout_mask=mask.to(torch.float32).numpy())
+        _logs_close(got, want, ["loss", "true_loss", "false_loss"])
+        if step == 0:
+            _check_tree(tr.grads(), gr, 2e-5, "grad")
+    _check_params(tr.params(), params, 1e-3)
+    batch = _batch(88, p_term=0.5)
+    _, want, _ = wmo.termination_step(_t64(tr.params()), None, batch, lr0=1e-3, decay_steps=50, train=False)
+    got = tr.step(_f32(batch), train=False)
+    _logs_close(got, want, ["loss", "true_loss", "false_loss", "accuracy", "precision", "recall", "f1"])
+
+
+def test_cosine_schedule_reaches_zero_and_stays():
+    from fqlpop.worldmodel import TERMINATION, WorldModelTrainer
+    tr = WorldModelTrainer(TERMINATION, O, A, (32,), B, steps=4, init_learning_rate=1e-2, seed=1)
+    batch = _f32(_batch(1))
+    lrs = []
+    for _ in range(6):
+        tr.step(batch, train=True)
+        lrs.append(float(tr.logs()[10]))
+    want = [wmo.cosine_lr(c, 1e-2, 4) for c in range(6)]
+    assert lrs == pytest.approx(want, rel=1e-5, abs=1e-9)
+    assert lrs[4] == pytest.approx(0.0, abs=1e-9) and lrs[5] == pytest.approx(0.0, abs=1e-9)
+
+
+def test_resident_dataset_sampling_matches_explicit_batches():
+    """fqlpop_wm_train draws row Philox(seed, step, b, 0) % N for batch row b of optimiser step `step`; feeding the same
+    rows through fqlpop_wm_step must give bit-identical parameters."""
+    from fqlpop.worldmodel import STATE, WorldModelTrainer
+    em = _envmodel(11)
+    data = _f32(_batch(5, rows=5000))
+    kw = dict(steps=20, params=_np(em["state"]), termination_params=_np(em["termination"]), termination_hidden_dims=THID, seed=1234)
+    a = WorldModelTrainer(STATE, O, A, HID, B, **kw)
+    b = WorldModelTrainer(STATE, O, A, HID, B, **kw)
+    a.set_dataset(data)
+    a.train(4)
+    for step in range(4):
+        idx = np.array([phx.index(1234, step, r, 0, 5000) for r in range(B)])
+        b.step({k: v[idx] for k, v in data.items()}, train=True)
+    assert np.array_equal(a.export(0), b.export(0))
+    assert a.logs()[11] == 4.0
+
+
+def test_training_learns_a_synthetic_transition_function():
+    """Sanity at scale: 300 device-sampled steps on next = obs + 0.1 * tanh(obs @ W) reduce the validation loss >5x."""
+    from fqlpop.worldmodel import STATE, WorldModelTrainer
+    g = torch.Generator().manual_seed(0)
+    N = 20000
+    obs = torch.randn(N, O, generator=g)
+    act = torch.rand(N, A, generator=g) * 2 - 1
+    W = torch.randn(O + A, O, generator=g) / 6
+    nxt = obs + 0.1 * torch.tanh(torch.cat([obs, act], 1) @ W)
+    data = {"observations": obs.numpy(), "actions": act.numpy(), "next_observations": nxt.numpy(),
+            "rewards": -np.ones(N, np.float32)}
+    tr = WorldModelTrainer(STATE, O, A, HID, B, steps=300, termination_weight=0.0, seed=3)
+    val = {k: v[:B] for k, v in data.items()}
+    first = tr.step(val, train=False)["next_observation_loss"]
+    tr.set_dataset(data)
+    tr.train(300)
+    last = tr.step(val, train=False)["next_observation_loss"]
+    assert np.isfinite(last) and last < first / 5, (first, last)
