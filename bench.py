@@ -234,6 +234,75 @@ def rollout_bench(torch, np, dev, P, world, barrier, dist, n=4096, T=200, reps=3
             "gpu_launches": reps}
 
 
+def worldmodel_bench(torch, np, dev, steps=2000, cpu_steps=100, with_cpu=True):
+    """world-model training. State predictor 50->128->256->128->42 (antsoccer shape, input LayerNorm +
+    residual) against a frozen termination predictor 42->128->256->128->1, batch 256, squared error + weighted BCE, Adam
+    with cosine decay -- the reference's `train_env_model.py --model baseline`. `value`: optimiser steps/s with the
+    1M-row training set resident in HBM and batches drawn on the device (one CUDA graph replay per step); `e2e`: every
+    batch comes from pinned host memory (host-side sampling, H2D inside the timed region) and the logs are read back
+    every step. cpu_baseline: the torch-CPU fp32 oracle of the same step (oracle/wm_oracle.py)."""
+    from fqlpop.worldmodel import STATE, TERMINATION, WorldModelTrainer, init_params
+    O, A, B, hid, N = 42, 8, 256, (128, 256, 128), 1_000_000
+    g = torch.Generator().manual_seed(0)
+    obs = torch.randn(N, O, generator=g)
+    data = {"observations": obs, "actions": torch.rand(N, A, generator=g) * 2 - 1,
+            "next_observations": obs + 0.05 * torch.randn(N, O, generator=g),
+            "rewards": -(torch.rand(N, generator=g) >= 0.005).float()}
+    term = init_params(1, TERMINATION, O, A, hid)
+    tr = WorldModelTrainer(STATE, O, A, hid, B, steps=steps, params=init_params(0, STATE, O, A, hid), termination_params=term,
+                           termination_hidden_dims=hid, device=dev)
+    tr.set_dataset(data)
+    tr.train(50)
+    torch.cuda.synchronize()
+    l0 = tr.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    tr.train(steps)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    launches = tr.launches - l0
+    n_e2e = 200
+    pinned = {k: torch.empty((B,) + tuple(v.shape[1:])).pin_memory() for k, v in data.items()}
+    idx = torch.randint(0, N, (n_e2e, B), generator=g)
+    e0.record()
+    for i in range(n_e2e):
+        for k, v in data.items():
+            torch.index_select(v, 0, idx[i], out=pinned[k])         # StepLoader.sample on the host
+        logs = tr.step({k: v.to(dev, non_blocking=True) for k, v in pinned.items()}, train=True)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_e2e = e0.elapsed_time(e1)
+    dims_s, dims_t = [O + A, *hid, O], [O, *hid, 1]
+    mac = lambda d: sum(a * b for a, b in zip(d[:-1], d[1:]))
+    flop = 2.0 * B * (3 * mac(dims_s) + 2 * mac(dims_t))   # fwd + dgrad + wgrad of the trained net, fwd + dgrad of the frozen one
+    out = {"value": steps / (ms * 1e-3), "unit": "optimiser steps/s", "ms_per_step": ms / steps,
+           "e2e": {"value": n_e2e / (ms_e2e * 1e-3), "unit": "optimiser steps/s",
+                   "h2d_bytes_per_step": int(B * (2 * O + A + 1) * 4), "d2h_bytes_per_step": 64},
+           "config": {"workload": f"state predictor {dims_s} vs frozen termination predictor {dims_t}, batch {B}, "
+                                  f"{N} resident rows, fp32"},
+           "dtype": "f32", "gpu_launches": int(launches), "launches_per_step": int(launches // steps),
+           "algorithmic_gflops": flop * steps / (ms * 1e-3) / 1e9, "flop_per_step": flop,
+           "bound": "launch latency (0.37 GFLOP per step over ~30 dependent kernels of <=64 CTAs)",
+           "last_loss": float(logs["loss"])}
+    tr.close()
+    if with_cpu:
+        from oracle import wm_oracle as wmo   # checker / CPU baseline only
+        t32 = lambda t: {k: (t32(v) if isinstance(v, dict) else torch.as_tensor(v, dtype=torch.float32)) for k, v in t.items()}
+        params, tp = t32(init_params(0, STATE, O, A, hid)), t32(term)
+        opt = wmo.new_opt_state(params)
+        t0 = None
+        for i in range(cpu_steps + 5):
+            if i == 5:
+                t0 = time.perf_counter()
+            batch = {k: v[idx[i % n_e2e]] for k, v in data.items()}
+            params, _, _ = wmo.state_step(params, opt, batch, tp, lr0=1e-3, decay_steps=steps)
+        out["cpu_baseline"] = {"value": cpu_steps / (time.perf_counter() - t0), "unit": "optimiser steps/s",
+                               "cores": torch.get_num_threads(), "kind": "port",
+                               "sample": f"{cpu_steps} steps of the same configuration, torch CPU fp32 oracle"}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -246,6 +315,7 @@ def main():
     ap.add_argument("--rows", type=int, default=1_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-rollout", action="store_true")
+    ap.add_argument("--no-worldmodel", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -374,6 +444,8 @@ def main():
         "clocks": sampler.summary(),
         "last_info_member0": {k: float(v) for k, v in zip(("critic_loss", "q_mean"), info_last[0][:2])},
     }
+    if not args.no_worldmodel:
+        line["worldmodel_training"] = worldmodel_bench(torch, np, dev, with_cpu=not args.no_cpu_baseline)
     if roll is not None:
         roll["frac_of_sustained_tensor_peak"] = roll["algorithmic_tflops"] / pk["bf16_tflops_sustained"]
         line["rollout"] = roll

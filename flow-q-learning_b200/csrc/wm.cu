@@ -13,46 +13,47 @@ namespace fqlpop {
 
 // ---------------------------------------------------------------------------------------------------------------------
 // C[M][N] (+)= epi(op(A) op(B)), op(A)(m,k) = TA ? A[k*lda+m] : A[m*lda+k], op(B)(k,n) = TB ? B[n*ldb+k] : B[k*ldb+n].
-// 32 x 32 x 32 tiles, 256 threads, 4 rows x 1 column per thread; the k loop runs in index order (deterministic).
+// 32 x 32 output tiles, 128-deep k tiles (K <= 256 here: at most two rounds of global loads, all of a round's loads in
+// flight together), 256 threads, 4 rows x 1 column per thread; the k loop runs in index order (deterministic).
 // One kernel serves the forward Dense layers (bias / relu / residual), the input-gradient products (TB, relu mask taken
 // from the saved activation) and the weight-gradient products (TA, reduction over the batch).
 // ---------------------------------------------------------------------------------------------------------------------
 enum WmEpi : int { WE_NONE = 0, WE_BIAS = 1, WE_BIAS_RELU = 2, WE_BIAS_RESID = 3, WE_MASK = 4 };
 
 constexpr int kWmTile = 32;
+constexpr int kWmBK = 128;
 
 template <bool TA, bool TB>
 __global__ void __launch_bounds__(256) wm_gemm_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B,
                                                       int ldb, float* __restrict__ C, int ldc, int M, int N, int K,
                                                       int epi, const float* __restrict__ bias,
                                                       const float* __restrict__ aux, int ldaux, int accumulate) {
-  __shared__ float As[kWmTile][kWmTile + 1];  // [k][m]
-  __shared__ float Bs[kWmTile][kWmTile + 1];  // [k][n]
+  __shared__ float As[kWmBK][kWmTile + 1];  // [k][m]
+  __shared__ float Bs[kWmBK][kWmTile + 1];  // [k][n]
   const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
   const int m0 = blockIdx.y * kWmTile, n0 = blockIdx.x * kWmTile;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int k0 = 0; k0 < K; k0 += kWmTile) {
+  for (int k0 = 0; k0 < K; k0 += kWmBK) {
+    const int kt = min(kWmBK, K - k0);
+    float ra[16], rb[16];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int e = tid + i * 256, hi = e >> 5, lo = e & 31;
-      {
-        const int m = TA ? lo : hi, k = TA ? hi : lo;
-        const int gm = m0 + m, gk = k0 + k;
-        float v = 0.f;
-        if (gm < M && gk < K) v = TA ? A[(long long)gk * lda + gm] : A[(long long)gm * lda + gk];
-        As[k][m] = v;
-      }
-      {
-        const int k = TB ? lo : hi, n = TB ? hi : lo;
-        const int gk = k0 + k, gn = n0 + n;
-        float v = 0.f;
-        if (gk < K && gn < N) v = TB ? B[(long long)gn * ldb + gk] : B[(long long)gk * ldb + gn];
-        Bs[k][n] = v;
-      }
+    for (int i = 0; i < 16; ++i) {  // issue every global load of the round before the first shared store
+      const int e = tid + i * 256;
+      const int am = TA ? (e & 31) : (e >> 7), ak = TA ? (e >> 5) : (e & 127);
+      const int bk = TB ? (e & 127) : (e >> 5), bn = TB ? (e >> 7) : (e & 31);
+      const int gm = m0 + am, gka = k0 + ak, gkb = k0 + bk, gn = n0 + bn;
+      ra[i] = (gm < M && gka < K) ? (TA ? A[(long long)gka * lda + gm] : A[(long long)gm * lda + gka]) : 0.f;
+      rb[i] = (gkb < K && gn < N) ? (TB ? B[(long long)gn * ldb + gkb] : B[(long long)gkb * ldb + gn]) : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int e = tid + i * 256;
+      As[TA ? (e >> 5) : (e & 127)][TA ? (e & 31) : (e >> 7)] = ra[i];
+      Bs[TB ? (e & 127) : (e >> 5)][TB ? (e >> 7) : (e & 31)] = rb[i];
     }
     __syncthreads();
-#pragma unroll
-    for (int k = 0; k < kWmTile; ++k) {
+#pragma unroll 8
+    for (int k = 0; k < kt; ++k) {
       const float b = Bs[k][tx];
 #pragma unroll
       for (int i = 0; i < 4; ++i) acc[i] = fmaf(As[k][ty * 4 + i], b, acc[i]);
@@ -76,16 +77,20 @@ __global__ void __launch_bounds__(256) wm_gemm_kernel(const float* __restrict__ 
 }
 
 // out[n] = sum_m X[m][n] (* Y[m][n]): bias gradients and the LayerNorm scale / bias gradients. One thread per column.
+// (both at once for the LayerNorm: out = sum X, out_xy = sum X * Y)
 __global__ void wm_colsum_kernel(const float* __restrict__ X, const float* __restrict__ Y, int ld, int M, int N,
-                                 float* __restrict__ out) {
+                                 float* __restrict__ out, float* __restrict__ out_xy) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
-  float s = 0.f;
+  float s = 0.f, sxy = 0.f;
+#pragma unroll 8
   for (int m = 0; m < M; ++m) {
     const float x = X[(long long)m * ld + n];
-    s += Y ? x * Y[(long long)m * ld + n] : x;
+    s += x;
+    if (Y) sxy += x * Y[(long long)m * ld + n];
   }
   out[n] = s;
+  if (Y) out_xy[n] = sxy;
 }
 
 // x0 = LayerNorm(concat(obs, act)) * scale + bias (envmodel/baseline.py:31-32; flax: var = E[x^2] - E[x]^2, eps inside
@@ -162,6 +167,16 @@ __device__ __forceinline__ void wm_block_reduce(float (&v)[NV], float (*sm)[NV])
   }
 }
 
+// Training steps only (step != nullptr): hand the optimiser its count (step[1]) and advance the counter the sampler of
+// the NEXT step reads (step[0]). Runs in the single-CTA loss kernel: after this step's gather, before its Adam launch.
+__device__ __forceinline__ void wm_tick(int* step, float* logs) {
+  if (!step) return;
+  const int t = step[0];
+  step[1] = t;
+  step[0] = t + 1;
+  logs[WL_STEP] = (float)(t + 1);
+}
+
 __device__ __forceinline__ float wm_sigmoid(float x) { return 1.f / (1.f + __expf(-x)); }
 // optax.sigmoid_binary_cross_entropy(logits, labels), stable form
 __device__ __forceinline__ float wm_bce(float x, float t) { return fmaxf(x, 0.f) - x * t + log1pf(expf(-fabsf(x))); }
@@ -173,7 +188,8 @@ __global__ void __launch_bounds__(256) wm_state_loss_kernel(const float* __restr
                                                             const float* __restrict__ logit,
                                                             const float* __restrict__ rewards, int rows, int O,
                                                             float ttw, float tw, float rw, float* __restrict__ dpred,
-                                                            float* __restrict__ dlogit, float* __restrict__ logs) {
+                                                            float* __restrict__ dlogit, float* __restrict__ logs,
+                                                            int* __restrict__ step) {
   __shared__ float sm[8][5];
   const float denom = 1.f + tw + rw;
   const bool term = tw > 0.f;
@@ -202,6 +218,7 @@ __global__ void __launch_bounds__(256) wm_state_loss_kernel(const float* __restr
     logs[WL_FALSE_LOSS] = term ? v[2] / v[4] : 0.f;
     logs[WL_RECON_LOSS] = 0.f;
     logs[WL_LOSS] = (mse + tw * tl) / denom;
+    wm_tick(step, logs);
   }
 }
 
@@ -209,7 +226,7 @@ __global__ void __launch_bounds__(256) wm_state_loss_kernel(const float* __restr
 __global__ void __launch_bounds__(256) wm_focal_loss_kernel(const float* __restrict__ logit,
                                                             const float* __restrict__ rewards, int rows, float alpha,
                                                             float gamma, float* __restrict__ dlogit,
-                                                            float* __restrict__ logs) {
+                                                            float* __restrict__ logs, int* __restrict__ step) {
   __shared__ float sm[8][6];
   float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // loss sum, n true, correct, true positives, predicted positives, -
   for (int b = threadIdx.x; b < rows; b += 256) {
@@ -239,6 +256,7 @@ __global__ void __launch_bounds__(256) wm_focal_loss_kernel(const float* __restr
     logs[WL_PRECISION] = prec;
     logs[WL_RECALL] = rec;
     logs[WL_F1] = (prec + rec) > 0.f ? 2.f * prec * rec / (prec + rec) : 0.f;
+    wm_tick(step, logs);
   }
 }
 
@@ -247,7 +265,7 @@ __global__ void __launch_bounds__(256) wm_focal_loss_kernel(const float* __restr
 __global__ void wm_adam_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
                                const float* __restrict__ g, long long n, const int* __restrict__ step, float lr0,
                                int decay_steps, float* __restrict__ logs) {
-  const int t = *step;
+  const int t = step[1];
   const float frac = (float)min(t, decay_steps) / (float)decay_steps;
   const float lr = lr0 * 0.5f * (1.f + cospif(frac));
   const float bc1 = 1.f - powf(0.9f, (float)(t + 1)), bc2 = 1.f - powf(0.999f, (float)(t + 1));
@@ -261,10 +279,6 @@ __global__ void wm_adam_kernel(float* __restrict__ p, float* __restrict__ m, flo
   p[i] -= lr * (mi / bc1) / (sqrtf(vi / bc2) + 1e-8f);
 }
 
-__global__ void wm_tick_kernel(int* step, float* logs) {
-  *step += 1;
-  logs[WL_STEP] = (float)*step;
-}
 
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -299,6 +313,7 @@ struct WmTrainer {
   float* x[kWmMaxLayers + 1] = {};    // x[0] = network input, x[l] = relu output of layer l-1, x[n_layers] = raw output
   float* tx[kWmMaxLayers + 1] = {};   // frozen termination predictor on the prediction (tx[0] aliases the prediction)
   float *xhat = nullptr, *pred = nullptr, *dbuf[2] = {nullptr, nullptr}, *dlogit = nullptr;
+  float* gx[kWmMaxLayers + 1] = {};   // gx[l] = d loss / d x[l], one buffer per layer (side streams read them late)
   float *logs = nullptr;
   int* step = nullptr;
   // resident dataset + sampled batch
@@ -330,19 +345,42 @@ int wm_alloc(WmTrainer* t, float** p, long long n, std::string* err) {
   return 0;
 }
 
+// Kernels go to `cur`. fork(): the side streams (weight gradients / column sums) pick up after what `s` holds so far;
+// join(): `s` waits for both. Under stream capture the events become graph edges, so the weight-gradient products and
+// the bias sums leave the critical path (only the input-gradient chain is sequential).
 struct Launcher {
-  cudaStream_t s;
+  cudaStream_t s, w, c, cur;
   int n = 0;
+  std::vector<cudaEvent_t> evs;
+  cudaEvent_t ev() {
+    cudaEvent_t e;
+    cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+    evs.push_back(e);
+    return e;
+  }
+  void fork() {
+    cudaEvent_t e = ev();
+    cudaEventRecord(e, s);
+    cudaStreamWaitEvent(w, e, 0);
+    cudaStreamWaitEvent(c, e, 0);
+  }
+  void join() {
+    cudaEvent_t a = ev(), b = ev();
+    cudaEventRecord(a, w);
+    cudaEventRecord(b, c);
+    cudaStreamWaitEvent(s, a, 0);
+    cudaStreamWaitEvent(s, b, 0);
+  }
   void gemm(bool ta, bool tb, const float* A, int lda, const float* B, int ldb, float* C, int ldc, int M, int N, int K,
             int epi, const float* bias, const float* aux, int ldaux, int accumulate) {
     dim3 grid((N + kWmTile - 1) / kWmTile, (M + kWmTile - 1) / kWmTile);
-    if (ta) wm_gemm_kernel<true, false><<<grid, 256, 0, s>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate);
-    else if (tb) wm_gemm_kernel<false, true><<<grid, 256, 0, s>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate);
-    else wm_gemm_kernel<false, false><<<grid, 256, 0, s>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate);
+    if (ta) wm_gemm_kernel<true, false><<<grid, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate);
+    else if (tb) wm_gemm_kernel<false, true><<<grid, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate);
+    else wm_gemm_kernel<false, false><<<grid, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate);
     ++n;
   }
-  void colsum(const float* X, const float* Y, int ld, int M, int N, float* out) {
-    wm_colsum_kernel<<<(N + 63) / 64, 64, 0, s>>>(X, Y, ld, M, N, out);
+  void colsum(const float* X, const float* Y, int ld, int M, int N, float* out, float* out_xy) {
+    wm_colsum_kernel<<<(N + 31) / 32, 32, 0, cur>>>(X, Y, ld, M, N, out, out_xy);
     ++n;
   }
 };
@@ -391,7 +429,8 @@ void wm_issue(WmTrainer* t, Launcher& L, int train, int gather, const float* obs
     if (with_term) wm_forward(L, t->term, t->term_params, t->tx, B, nullptr, 0);  // tx[0] aliases x[nl]
     wm_state_loss_kernel<<<1, 256, 0, s>>>(t->x[nl], next_obs, with_term ? t->tx[t->term.n_layers] : nullptr, rew, B, O,
                                            c.true_termination_weight, c.termination_weight, c.reconstruction_weight,
-                                           train ? t->pred : nullptr, train ? t->dlogit : nullptr, t->logs);
+                                           train ? t->pred : nullptr, train ? t->dlogit : nullptr, t->logs,
+                                           train ? t->step : nullptr);
     ++L.n;
     if (!train) return;
     if (with_term) {  // d loss / d prediction through the frozen termination predictor, added onto the squared-error part
@@ -411,31 +450,34 @@ void wm_issue(WmTrainer* t, Launcher& L, int train, int gather, const float* obs
     ++L.n;
     wm_forward(L, net, t->params, t->x, B, nullptr, 0);
     wm_focal_loss_kernel<<<1, 256, 0, s>>>(t->x[nl], rew, B, c.focal_alpha, c.focal_gamma, train ? t->dlogit : nullptr,
-                                           t->logs);
+                                           t->logs, train ? t->step : nullptr);
     ++L.n;
     if (!train) return;
     g = t->dlogit;
   }
-  // backward through the trained network
+  // backward through the trained network: the input-gradient chain stays on the main stream, weight gradients and
+  // bias sums of every layer branch off as soon as that layer's output gradient exists
   for (int l = nl - 1; l >= 0; --l) {
     const int din = net.dims[l], dout = net.dims[l + 1];
+    L.fork();
+    L.cur = L.w;
     L.gemm(true, false, t->x[l], din, g, dout, t->grads + net.offW[l], dout, din, dout, B, WE_NONE, nullptr, nullptr, 0, 0);
-    L.colsum(g, nullptr, dout, B, dout, t->grads + net.offB[l]);
+    L.cur = L.c;
+    L.colsum(g, nullptr, dout, B, dout, t->grads + net.offB[l], nullptr);
+    L.cur = L.s;
     if (l > 0 || state) {
-      float* out = t->dbuf[l & 1];
+      float* out = t->gx[l];
       L.gemm(false, true, g, dout, t->params + net.offW[l], dout, out, din, B, din, dout, l > 0 ? WE_MASK : WE_NONE, nullptr,
              l > 0 ? t->x[l] : nullptr, din, 0);
       g = out;
     }
   }
-  if (state) {  // input LayerNorm: d scale = sum_b dx0 * xhat, d bias = sum_b dx0
-    L.colsum(g, t->xhat, net.dims[0], B, net.dims[0], t->grads + net.off_ln_scale);
-    L.colsum(g, nullptr, net.dims[0], B, net.dims[0], t->grads + net.off_ln_bias);
-  }
+  if (state)  // input LayerNorm: d scale = sum_b dx0 * xhat, d bias = sum_b dx0
+    L.colsum(g, t->xhat, net.dims[0], B, net.dims[0], t->grads + net.off_ln_bias, t->grads + net.off_ln_scale);
+  L.join();
   wm_adam_kernel<<<(int)((net.n_params + 255) / 256), 256, 0, s>>>(t->params, t->m, t->v, t->grads, net.n_params, t->step,
                                                                   c.lr, c.decay_steps, t->logs);
-  wm_tick_kernel<<<1, 1, 0, s>>>(t->step, t->logs);
-  L.n += 2;
+  ++L.n;
 }
 
 int wm_run(WmTrainer* t, int train, int gather, int repeats, const float* obs, const float* act, const float* next_obs,
@@ -453,11 +495,17 @@ int wm_run(WmTrainer* t, int train, int gather, int repeats, const float* obs, c
     cudaStream_t cs;
     WM_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
     WM_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
-    Launcher L{cs};
+    cudaStream_t sw, sc;
+    WM_CUDA(cudaStreamCreateWithFlags(&sw, cudaStreamNonBlocking));
+    WM_CUDA(cudaStreamCreateWithFlags(&sc, cudaStreamNonBlocking));
+    Launcher L{cs, sw, sc, cs};
     wm_issue(t, L, train, gather, obs, act, next_obs, rew, mask);
     cudaGraph_t graph = nullptr;
     cudaError_t ce = cudaStreamEndCapture(cs, &graph);
     cudaError_t le = cudaGetLastError();
+    for (cudaEvent_t e : L.evs) cudaEventDestroy(e);
+    cudaStreamDestroy(sw);
+    cudaStreamDestroy(sc);
     if (ce != cudaSuccess || le != cudaSuccess) {
       if (err) *err = std::string("world-model step capture: ") + cudaGetErrorString(ce != cudaSuccess ? ce : le);
       cudaStreamDestroy(cs);
@@ -500,7 +548,8 @@ int wm_create_impl(const WmConfig& cfg, const float* params_host, const float* t
   int rc = 0;
   rc |= wm_alloc(t, &t->params, n, err) || wm_alloc(t, &t->m, n, err) || wm_alloc(t, &t->v, n, err) ||
         wm_alloc(t, &t->grads, n, err);
-  for (int l = 0; l <= t->net.n_layers && !rc; ++l) rc |= wm_alloc(t, &t->x[l], (long long)B * t->net.dims[l], err);
+  for (int l = 0; l <= t->net.n_layers && !rc; ++l)
+    rc |= wm_alloc(t, &t->x[l], (long long)B * t->net.dims[l], err) || wm_alloc(t, &t->gx[l], (long long)B * t->net.dims[l], err);
   if (!rc && state) rc |= wm_alloc(t, &t->xhat, (long long)B * t->net.dims[0], err);
   if (!rc && with_term) {
     t->term = wm_layout(cfg.O, cfg.term_n_hidden, cfg.term_hidden, 1, false);
@@ -514,7 +563,7 @@ int wm_create_impl(const WmConfig& cfg, const float* params_host, const float* t
   if (!rc)
     rc |= wm_alloc(t, &t->pred, (long long)B * cfg.O, err) || wm_alloc(t, &t->dbuf[0], (long long)B * maxdim, err) ||
           wm_alloc(t, &t->dbuf[1], (long long)B * maxdim, err) || wm_alloc(t, &t->dlogit, B, err) ||
-          wm_alloc(t, &t->logs, kWmLogs, err) || wm_alloc(t, (float**)&t->step, 1, err) ||
+          wm_alloc(t, &t->logs, kWmLogs, err) || wm_alloc(t, (float**)&t->step, 2, err) ||
           wm_alloc(t, &t->b_obs, (long long)B * cfg.O, err) || wm_alloc(t, &t->b_act, (long long)B * std::max(cfg.A, 1), err) ||
           wm_alloc(t, &t->b_next, (long long)B * cfg.O, err) || wm_alloc(t, &t->b_rew, B, err);
   if (!rc && cudaMemcpy(t->params, params_host, sizeof(float) * n, cudaMemcpyHostToDevice) != cudaSuccess)

@@ -185,6 +185,8 @@ class WorldModelTrainer:
             keys = dict(_STATE_LOGS)
             if not self._cfg.termination_weight > 0:
                 keys = {"loss": 0, "next_observation_loss": 1}
+            if self._cfg.reconstruction_weight > 0:
+                keys["reconstruction_loss"] = 5
         else:
             keys = dict(_TERM_LOGS)
             if not train:

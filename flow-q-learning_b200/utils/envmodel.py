@@ -19,7 +19,7 @@ from typing import Dict
 import numpy as np
 import yaml
 
-from utils.flax_msgpack import from_bytes
+from utils.flax_msgpack import from_bytes, to_bytes
 
 _STATE_MODELS = ("baseline", "multistep")
 
@@ -82,3 +82,17 @@ def load_model(save_directory: Path, env_name: str, model: str, sample_batch: Di
     params = tree["params"]["ScanCell_0"]["cell"] if model == "multistep" else tree["params"]
     return LoadedModel(model, params, int(np.shape(sample_batch["observations"])[-1]),
                        int(np.shape(sample_batch["actions"])[-1]), model_config["hidden_dims"], device=device)
+
+
+def save_model(params: Dict, save_directory: Path, env_name: str, model: str, model_config: Dict) -> Path:
+    """Writes what train_env_model.py leaves behind (/root/reference/train_env_model.py:118-127):
+    `<save>/<env>/env_models/<model>_config.yaml` (yaml of model_config) and `<model>.pt` = flax msgpack bytes of
+    `trainer.state.params` ({"params": {...}}). Returns the .pt path."""
+    root = Path(save_directory) / env_name / "env_models"
+    root.mkdir(parents=True, exist_ok=True)
+    with open(root / f"{model}_config.yaml", "w") as f:
+        yaml.dump(dict(model_config), f)
+    tree = params if "params" in params else {"params": params}
+    path = root / f"{model}.pt"
+    path.write_bytes(to_bytes(tree))
+    return path

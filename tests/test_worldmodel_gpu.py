@@ -183,3 +183,64 @@ def test_training_learns_a_synthetic_transition_function():
     tr.train(300)
     last = tr.step(val, train=False)["next_observation_loss"]
     assert np.isfinite(last) and last < first / 5, (first, last)
+
+
+def test_trainers_train_save_and_reload(tmp_path):
+    """The reference's two-stage recipe end to end on synthetic data: train the termination predictor, save it in the
+    reference's file layout, train the state predictor against it (termination_weight > 0 loads it through load_model),
+    save, and read both back with load_model for the simulated task."""
+    from functools import partial
+    from envmodel.baseline import BaselineStatePredictor, TerminationPredictor
+    from envmodel.config import TrainerConfig
+    from envmodel.loss import focal_loss, state_prediction_loss
+    from envmodel.state_predictor_trainer import StatePredictorTrainer
+    from envmodel.termination_predictor_trainer import TerminationPredictorTrainer
+    from utils.data_loader import StepLoader
+    from utils.envmodel import load_model, save_model
+
+    g = torch.Generator().manual_seed(0)
+    N = 8000
+    obs = torch.randn(N, O, generator=g)
+    act = torch.rand(N, A, generator=g) * 2 - 1
+    nxt = obs + 0.1 * torch.tanh(torch.cat([obs, act], 1) @ (torch.randn(O + A, O, generator=g) / 6))
+    rew = -(nxt[:, 0] < 1.0).float()  # "terminated" (reward 0) where the first coordinate is large: learnable, ~16 % positives
+    data = {"observations": obs.numpy(), "actions": act.numpy(), "next_observations": nxt.numpy(), "rewards": rew.numpy(),
+            "masks": (rew != 0).float().numpy(), "terminals": np.zeros(N, np.float32)}
+    np.random.seed(0)
+    logged = []
+
+    class Log:
+        def log(self, d, step):
+            logged.append((step, d))
+
+    cfg = TrainerConfig(steps=400, env_name="synthetic-env", model="termination_predictor", val_batches=2,
+                        model_config={"hidden_dims": (64, 64)}, save_directory=tmp_path)
+    tt = TerminationPredictorTrainer(TerminationPredictor(O, (64, 64)), StepLoader(data), StepLoader(data), focal_loss, cfg,
+                                     logger=Log(), device_sampling=True)
+    tt.train()
+    first_val = [d["val/loss"] for st_, d in logged if st_ == 0 and "val/loss" in d][0]
+    assert tt.last_validation["loss"] < first_val / 2 and tt.last_validation["accuracy"] > 0.84 and tt.state.step == 400
+    assert any("val/f1" in d for _, d in logged) and any("train/learning_rate" in d for _, d in logged)
+    save_model(tt.state.params, tmp_path, cfg.env_name, "termination_predictor", cfg.model_config)
+
+    cfg2 = TrainerConfig(steps=150, env_name="synthetic-env", model="baseline", val_batches=2,
+                         model_config={"hidden_dims": (64, 64)}, save_directory=tmp_path)
+    loss = partial(state_prediction_loss, true_termination_weight=cfg2.true_termination_weight,
+                   termination_weight=cfg2.termination_weight, reconstruction_weight=0.0)
+    st = StatePredictorTrainer(BaselineStatePredictor(O, A, (64, 64)), StepLoader(data), StepLoader(data), loss, cfg2)
+    first = st._validate(0)
+    st.train()  # host-sampled batches: one np.random draw per step, as the reference
+    assert st.last_validation["next_observation_loss"] < first["next_observation_loss"] / 2
+    assert set(st.last_validation) == {"loss", "next_observation_loss", "termination_loss", "true_termination_loss",
+                                      "false_termination_loss"}
+    save_model(st.state.params, tmp_path, cfg2.env_name, "baseline", cfg2.model_config)
+
+    sample = {k: v[:4] for k, v in data.items()}
+    sp = load_model(tmp_path, "synthetic-env", "baseline", sample)
+    tp = load_model(tmp_path, "synthetic-env", "termination_predictor", sample)
+    pred, same = sp(sample["observations"], sample["actions"])
+    assert pred.shape == (4, O) and np.array_equal(same, sample["observations"])
+    want = orc.state_predictor_apply(_t64(st.state.params["params"]), torch.as_tensor(sample["observations"], dtype=torch.float64),
+                                     torch.as_tensor(sample["actions"], dtype=torch.float64)).numpy()
+    assert np.abs(pred - want).max() < 3e-2  # the rollout kernels multiply in bf16
+    assert tp(sample["next_observations"]).shape == (4,)
