@@ -367,3 +367,27 @@ extern "C" int fqlpop_wm_export(void* h, int32_t which, float* out_host, int64_t
   return 0;
 }
 extern "C" int64_t fqlpop_wm_launches(void* h) { return h ? fqlpop::wm_launches((fqlpop::WmTrainer*)h) : 0; }
+
+// initial-observation generator (VAE decoder)
+extern "C" int fqlpop_decoder_create(int32_t latent_dim, int32_t n_hidden, const int32_t* hidden, int32_t out_dim,
+                                     const float* params_host, void** out) {
+  if (!out || !hidden) return fail("null argument");
+  int h[fqlpop::kWmMaxLayers] = {};
+  if (n_hidden < 1 || n_hidden >= fqlpop::kWmMaxLayers) return fail("decoder: between 1 and 7 hidden layers");
+  for (int i = 0; i < n_hidden; ++i) h[i] = hidden[i];
+  fqlpop::WmDecoder* d = nullptr;
+  std::string err;
+  if (fqlpop::wm_decoder_create_impl(latent_dim, n_hidden, h, out_dim, params_host, &d, &err)) return fail(err);
+  *out = d;
+  return 0;
+}
+extern "C" int fqlpop_decoder_destroy(void* h) {
+  fqlpop::wm_decoder_destroy_impl((fqlpop::WmDecoder*)h);
+  return 0;
+}
+extern "C" int fqlpop_decoder_sample(void* h, int32_t n, const float* noise, uint64_t seed, float* out, void* stream) {
+  if (!h) return fail("null decoder handle");
+  std::string err;
+  if (fqlpop::wm_decoder_sample_impl((fqlpop::WmDecoder*)h, n, noise, seed, out, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}

@@ -635,3 +635,82 @@ int wm_export_impl(WmTrainer* t, int which, float* out_host, long long n, cudaSt
 }
 
 }  // namespace fqlpop
+
+// ---------------------------------------------------------------------------------------------------------------------
+// initial-observation generator (VAE decoder)
+// ---------------------------------------------------------------------------------------------------------------------
+namespace fqlpop {
+
+__global__ void wm_normal_kernel(unsigned long long seed, int rows, int cols, float* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < (long long)rows * cols) out[i] = philox_normal(seed, 0ull, (uint32_t)(i / cols), (uint32_t)(i % cols));
+}
+
+struct WmDecoder {
+  WmNet net;
+  int device = 0, cap = 0;
+  float* params = nullptr;
+  float* act[kWmMaxLayers + 1] = {};  // act[0] = z ... act[n_layers - 1]; the last layer writes straight into `out`
+};
+
+int wm_decoder_create_impl(int latent_dim, int n_hidden, const int* hidden, int out_dim, const float* params_host,
+                           WmDecoder** out, std::string* err) {
+  if (latent_dim < 1 || out_dim < 1 || n_hidden < 1 || n_hidden >= kWmMaxLayers || !params_host) {
+    if (err) *err = "decoder: bad dimensions, layer count outside [1, 7] or null parameters";
+    return 1;
+  }
+  WmDecoder* d = new WmDecoder();
+  d->net = wm_layout(latent_dim, n_hidden, hidden, out_dim, false);
+  cudaGetDevice(&d->device);
+  if (cudaMalloc((void**)&d->params, sizeof(float) * d->net.n_params) != cudaSuccess ||
+      cudaMemcpy(d->params, params_host, sizeof(float) * d->net.n_params, cudaMemcpyHostToDevice) != cudaSuccess) {
+    if (err) *err = "decoder: allocating / copying the parameters failed";
+    wm_decoder_destroy_impl(d);
+    return 1;
+  }
+  *out = d;
+  return 0;
+}
+
+void wm_decoder_destroy_impl(WmDecoder* d) {
+  if (!d) return;
+  cudaSetDevice(d->device);
+  cudaDeviceSynchronize();
+  cudaFree(d->params);
+  for (float* a : d->act) cudaFree(a);
+  delete d;
+}
+
+int wm_decoder_sample_impl(WmDecoder* d, int n, const float* noise, unsigned long long seed, float* out,
+                           cudaStream_t stream, std::string* err) {
+  if (n < 1 || !out) {
+    if (err) *err = "decoder sample: n must be positive and out non-null";
+    return 1;
+  }
+  WM_CUDA(cudaSetDevice(d->device));
+  const WmNet& net = d->net;
+  if (n > d->cap) {  // grow the activation buffers (stream-ordered with respect to earlier samples: sync first)
+    WM_CUDA(cudaDeviceSynchronize());
+    for (int l = 0; l < net.n_layers; ++l) {
+      cudaFree(d->act[l]);
+      d->act[l] = nullptr;
+      WM_CUDA(cudaMalloc((void**)&d->act[l], sizeof(float) * (size_t)n * net.dims[l]));
+    }
+    d->cap = n;
+  }
+  float* act[kWmMaxLayers + 1];
+  for (int l = 0; l < net.n_layers; ++l) act[l] = d->act[l];
+  act[net.n_layers] = out;
+  if (noise) {
+    WM_CUDA(cudaMemcpyAsync(act[0], noise, sizeof(float) * (size_t)n * net.dims[0], cudaMemcpyDeviceToDevice, stream));
+  } else {
+    const long long tot = (long long)n * net.dims[0];
+    wm_normal_kernel<<<(int)((tot + 255) / 256), 256, 0, stream>>>(seed, n, net.dims[0], act[0]);
+  }
+  Launcher L{stream, stream, stream, stream};
+  wm_forward(L, net, d->params, act, n, nullptr, 0);
+  WM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace fqlpop

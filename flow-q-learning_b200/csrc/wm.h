@@ -80,6 +80,16 @@ int wm_logs_impl(WmTrainer* t, float* out_host, cudaStream_t stream, std::string
 // which: 0 params, 1 Adam m, 2 Adam v, 3 gradients of the last train step
 int wm_export_impl(WmTrainer* t, int which, float* out_host, long long n, cudaStream_t stream, std::string* err);
 long long wm_num_params(const WmTrainer* t);
+
+// Initial-observation generator: the VAE decoder z -> [Dense, relu]* -> Dense(O)
+// (/root/reference/envmodel/initial_observation.py:21-30, sampled as at /root/reference/distribution_visualizer.py:96-99).
+struct WmDecoder;
+int wm_decoder_create_impl(int latent_dim, int n_hidden, const int* hidden, int out_dim, const float* params_host,
+                           WmDecoder** out, std::string* err);
+void wm_decoder_destroy_impl(WmDecoder* d);
+// out[n][out_dim] = decoder(z); z = noise[n][latent_dim] (dev) or N(0, I) from Philox(seed) when noise == nullptr
+int wm_decoder_sample_impl(WmDecoder* d, int n, const float* noise, unsigned long long seed, float* out,
+                           cudaStream_t stream, std::string* err);
 long long wm_launches(const WmTrainer* t);
 
 }  // namespace fqlpop

@@ -168,7 +168,7 @@ class WorldModelTrainer:
             pass
 
     def _dev(self, x):
-        return torch.as_tensor(np.asarray(x, dtype=np.float32) if not torch.is_tensor(x) else x,
+        return torch.as_tensor(np.array(x, dtype=np.float32) if not torch.is_tensor(x) else x,
                                dtype=torch.float32).to(self.device).contiguous()
 
     def _stream(self):
@@ -238,3 +238,55 @@ class WorldModelTrainer:
     @property
     def launches(self) -> int:
         return int(lib.fqlpop_wm_launches(self._h))
+
+
+lib.fqlpop_decoder_create.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(ctypes.c_int32), ctypes.c_int32,
+                                      ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+lib.fqlpop_decoder_destroy.argtypes = [ctypes.c_void_p]
+lib.fqlpop_decoder_sample.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p,
+                                      ctypes.c_void_p]
+
+
+class Decoder:
+    """Device copy of the VAE decoder that generates initial observations (envmodel/initial_observation.py:21-30):
+    `sample(n, seed)` = decoder(z), z ~ N(0, I) -- the sampling of distribution_visualizer.py:96-99, on the GPU, so that a
+    simulated evaluation never touches a real environment. `params` is the flax subtree ["params"]["decoder"]."""
+
+    def __init__(self, params: Dict, latent_dim: int, hidden_dims: Sequence[int], output_dimension: int, device=None):
+        self.device = torch.device(device) if device is not None else default_device()
+        self.latent_dim, self.output_dimension = int(latent_dim), int(output_dimension)
+        self.hidden_dims = tuple(int(h) for h in hidden_dims)
+        flat = flatten_params(params, TERMINATION)  # plain Dense stack: kernel, bias per layer
+        dims = [self.latent_dim, *self.hidden_dims, self.output_dimension]
+        want = sum(a * b + b for a, b in zip(dims[:-1], dims[1:]))
+        if flat.size != want:
+            raise ValueError(f"decoder parameters hold {flat.size} values, dims {dims} need {want}")
+        hid = (ctypes.c_int32 * len(self.hidden_dims))(*self.hidden_dims)
+        self._h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            check(lib.fqlpop_decoder_create(self.latent_dim, len(self.hidden_dims), hid, self.output_dimension,
+                                            flat.ctypes.data, ctypes.byref(self._h)), "fqlpop_decoder_create")
+
+    def sample(self, n: int, seed: int = 0, noise=None):
+        """-> torch.float32 [n, output_dimension] on the device."""
+        with torch.cuda.device(self.device):
+            out = torch.empty(n, self.output_dimension, dtype=torch.float32, device=self.device)
+            z = None
+            if noise is not None:
+                z = torch.as_tensor(noise, dtype=torch.float32).to(self.device).contiguous()
+                if tuple(z.shape) != (n, self.latent_dim):
+                    raise ValueError(f"noise must be [{n}, {self.latent_dim}]")
+            check(lib.fqlpop_decoder_sample(self._h, n, z.data_ptr() if z is not None else None, int(seed), out.data_ptr(),
+                                            torch.cuda.current_stream(self.device).cuda_stream), "fqlpop_decoder_sample")
+            return out
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.fqlpop_decoder_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

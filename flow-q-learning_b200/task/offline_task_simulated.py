@@ -28,8 +28,9 @@ from utils.envmodel import load_model
 class OfflineTaskWithSimulatedEvaluations(Task):
     def __init__(self, env_name: str, model: str = "baseline", data_directory: Path = None,
                  save_directory: Path = Path("exp/"), buffer_size: int = 2000000, num_evaluation_envs: int = 50,
-                 max_episode_steps: int = 1000, device=None):
+                 max_episode_steps: int = 1000, device=None, generated_initial_observations: bool = False):
         self.max_episode_steps = max_episode_steps
+        self.num_evaluation_envs = num_evaluation_envs
         if device is None:
             from fqlpop._lib import default_device
             device = default_device()
@@ -45,6 +46,12 @@ class OfflineTaskWithSimulatedEvaluations(Task):
         example = self.train_dataset.sample(1)
         self.state_predictor = load_model(save_directory, env_name, model, example, device=device)
         self.termination_predictor = load_model(save_directory, env_name, "termination_predictor", example, device=device)
+        # optional: initial observations from the trained VAE decoder on the device instead of environment resets
+        self.initial_observation_decoder = None
+        if generated_initial_observations:
+            from envmodel.initial_observation import load_initial_observation_decoder
+            self.initial_observation_decoder = load_initial_observation_decoder(
+                save_directory, env_name, self.state_predictor.ob_dim, device=device)
         self.current_observations = None
         self.episode_steps = 0
         self.invalidate = []
@@ -107,8 +114,11 @@ class OfflineTaskWithSimulatedEvaluations(Task):
     def rollout_population(self, population, seed: Optional[int] = None, trajectory: bool = False):
         """Simulated evaluation of every active member at once -> dict of device tensors indexed by member id
         (`success_rate[P]` is evaluate_actor_fn's stats["success"])."""
-        observations, _ = self.reset(seed=seed)
         eval_seed = int(np.random.randint(0, 2 ** 31)) if seed is None else int(seed)
+        if self.initial_observation_decoder is not None:
+            observations = self.initial_observation_decoder.sample(self.num_evaluation_envs, seed=eval_seed)
+        else:
+            observations, _ = self.reset(seed=seed)
         return population.rollout(self.envmodel(), observations, self.max_episode_steps, eval_seed=eval_seed,
                                   trajectory=trajectory)
 

@@ -201,6 +201,17 @@ int fqlpop_wm_logs(void* wm, float* out_host, void* stream);
 int fqlpop_wm_export(void* wm, int32_t which, float* out_host, int64_t n, void* stream);
 int64_t fqlpop_wm_launches(void* wm);
 
+/* ---- initial-observation generator -------------------------------------------------------
+ * The decoder half of InitialObservationEnvModel (envmodel/initial_observation.py:21-30): z -> [Dense, relu]* ->
+ * Dense(ob_dim), sampled with z ~ N(0, I) as at distribution_visualizer.py:96-99; replaces real-environment resets
+ * (task/offline_task_simulated.py:60-83) as the source of the rollout's initial observations.
+ * params_host: per Dense layer (hidden..., output) kernel [in][out] then bias [out], fp32.                          */
+int fqlpop_decoder_create(int32_t latent_dim, int32_t n_hidden, const int32_t* hidden, int32_t out_dim,
+                          const float* params_host, void** out_handle);
+int fqlpop_decoder_destroy(void* decoder);
+/* out[n][out_dim] (dev) = decoder(z); z = noise[n][latent_dim] (dev) or Philox normal(seed, 0, row, col) when NULL. */
+int fqlpop_decoder_sample(void* decoder, int32_t n, const float* noise, uint64_t seed, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

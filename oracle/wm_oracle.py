@@ -142,7 +142,7 @@ def state_step(params, opt, batch: Dict[str, torch.Tensor], term_params: Optiona
     loss, logs = state_prediction_loss(pred, batch["next_observations"], logit, batch["rewards"] == 0,
                                        batch["observations"], batch["observations"], true_termination_weight,
                                        termination_weight, reconstruction_weight)
-    logs = {k: float(v) for k, v in logs.items()}
+    logs = {k: float(v.detach()) if torch.is_tensor(v) else float(v) for k, v in logs.items()}
     if not train:
         return params, logs, None
     loss.backward()
@@ -162,8 +162,8 @@ def termination_step(params, opt, batch, dropout_mask=None, *, lr0, decay_steps,
     logit = termination_predictor_apply(p, x)
     targets = batch["rewards"] == 0
     loss, logs = focal_loss(logit, targets, alpha, gamma)
-    logs = {k: float(v) for k, v in logs.items()}
-    logs["loss"] = float(loss)
+    logs = {k: float(v.detach()) if torch.is_tensor(v) else float(v) for k, v in logs.items()}
+    logs["loss"] = float(loss.detach())
     if not train:
         pred = logit > 0
         tp, pp, ap = float((pred & targets).sum()), float(pred.sum()), float(targets.sum())

@@ -76,3 +76,10 @@ def test_flat_layout_round_trip_and_count():
     assert k.shape == (128, 256) and abs(float(k.std()) - math.sqrt(1 / 128)) < 0.05 * math.sqrt(1 / 128)
     assert float(np.abs(k).max()) <= 2 * math.sqrt(1 / 128) / 0.87962566103423978 + 1e-6
     assert not tree["Dense_0"]["bias"].any() and (tree["LayerNorm_0"]["scale"] == 1).all()
+
+
+def test_initial_observation_loader_errors_like_the_reference(tmp_path):
+    """Missing files raise FileNotFoundError with the reference's messages (distribution_visualizer.py:68-75,84-91)."""
+    from envmodel.initial_observation import load_initial_observation_decoder
+    with pytest.raises(FileNotFoundError, match="Configuration file not found"):
+        load_initial_observation_decoder(tmp_path, "some-env", 28)

@@ -244,3 +244,45 @@ def test_trainers_train_save_and_reload(tmp_path):
                                      torch.as_tensor(sample["actions"], dtype=torch.float64)).numpy()
     assert np.abs(pred - want).max() < 3e-2  # the rollout kernels multiply in bf16
     assert tp(sample["next_observations"]).shape == (4,)
+
+
+def test_initial_observation_decoder_matches_oracle_and_loads_from_reference_files(tmp_path):
+    """Decoder z -> [Dense, relu]* -> Dense(O) (envmodel/initial_observation.py:21-30): explicit noise against a float64
+    restatement (fp32 kernels: rtol 1e-5), device Philox noise against oracle/philox_oracle.py, ragged sample counts, and
+    the reference's file layout (initial_observation.pt holds encoder AND decoder; hidden_dims is stored encoder-order)."""
+    import yaml
+    from envmodel.initial_observation import load_initial_observation_decoder
+    from utils.flax_msgpack import to_bytes
+    latent, enc_hidden = 8, (128, 64)
+    dims = [latent, *enc_hidden[::-1], O]
+    g = torch.Generator().manual_seed(4)
+    dec = {f"Dense_{i}": {"kernel": torch.randn(dims[i], dims[i + 1], generator=g, dtype=torch.float64) / np.sqrt(dims[i]),
+                          "bias": 0.1 * torch.randn(dims[i + 1], generator=g, dtype=torch.float64)} for i in range(3)}
+    root = tmp_path / "synthetic-env" / "env_models"
+    root.mkdir(parents=True)
+    with open(root / "initial_observation_config.yaml", "w") as f:
+        yaml.dump({"hidden_dims": enc_hidden, "latent_dim": latent}, f)
+    with pytest.raises(FileNotFoundError, match="Model file not found"):
+        load_initial_observation_decoder(tmp_path, "synthetic-env", O)
+    (root / "initial_observation.pt").write_bytes(to_bytes({"params": {"decoder": _np(dec), "encoder": {"Dense_0": {
+        "kernel": np.zeros((O, 4), np.float32), "bias": np.zeros(4, np.float32)}}}}))
+    d = load_initial_observation_decoder(tmp_path, "synthetic-env", O)
+    assert d.hidden_dims == enc_hidden[::-1]
+
+    def ref(z):
+        x = z
+        for i in range(3):
+            x = x @ dec[f"Dense_{i}"]["kernel"] + dec[f"Dense_{i}"]["bias"]
+            if i < 2:
+                x = torch.relu(x)
+        return x.numpy()
+
+    for n in (1, 33, 1100):   # 1100 = the sample count of distribution_visualizer.py:97
+        z = torch.randn(n, latent, generator=g, dtype=torch.float64)
+        got = d.sample(n, noise=z.to(torch.float32)).cpu().numpy()
+        np.testing.assert_allclose(got, ref(z), rtol=1e-5, atol=1e-5)
+    n = 64
+    z = torch.tensor([[phx.normal(77, 0, r, c) for c in range(latent)] for r in range(n)], dtype=torch.float64)
+    np.testing.assert_allclose(d.sample(n, seed=77).cpu().numpy(), ref(z), rtol=1e-4, atol=1e-4)
+    a, b = d.sample(n, seed=78), d.sample(n, seed=78)
+    assert torch.equal(a, b) and not torch.equal(a, d.sample(n, seed=79))
