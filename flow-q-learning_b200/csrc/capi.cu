@@ -309,6 +309,7 @@ bool wm_cfg(const fqlpop_wm_config_t* c, fqlpop::WmConfig* o) {
   o->true_termination_weight = c->true_termination_weight; o->termination_weight = c->termination_weight;
   o->reconstruction_weight = c->reconstruction_weight;
   o->focal_alpha = c->focal_alpha; o->focal_gamma = c->focal_gamma; o->seed = c->seed;
+  o->seq_len = c->seq_len;
   return true;
 }
 }  // namespace
@@ -320,7 +321,7 @@ bool wm_cfg(const fqlpop_wm_config_t* c, fqlpop::WmConfig* o) {
 extern "C" int64_t fqlpop_wm_num_params(const fqlpop_wm_config_t* c) {
   fqlpop::WmConfig w;
   if (!wm_cfg(c, &w)) return -1;
-  return (w.kind == fqlpop::WM_STATE ? fqlpop::wm_layout(w.O + w.A, w.n_hidden, w.hidden, w.O, true)
+  return (w.kind != fqlpop::WM_TERMINATION ? fqlpop::wm_layout(w.O + w.A, w.n_hidden, w.hidden, w.O, true)
                                      : fqlpop::wm_layout(w.O, w.n_hidden, w.hidden, 1, false)).n_params;
 }
 extern "C" int fqlpop_wm_create(const fqlpop_wm_config_t* c, const float* params_host, const float* term_params_host,

@@ -27,13 +27,19 @@ template <bool TA, bool TB>
 __global__ void __launch_bounds__(256) wm_gemm_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B,
                                                       int ldb, float* __restrict__ C, int ldc, int M, int N, int K,
                                                       int epi, const float* __restrict__ bias,
-                                                      const float* __restrict__ aux, int ldaux, int accumulate) {
+                                                      const float* __restrict__ aux, int ldaux, int accumulate,
+                                                      int k_chunk, long long c_split_stride) {
   __shared__ float As[kWmBK][kWmTile + 1];  // [k][m]
   __shared__ float Bs[kWmBK][kWmTile + 1];  // [k][n]
   const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
   const int m0 = blockIdx.y * kWmTile, n0 = blockIdx.x * kWmTile;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int k0 = 0; k0 < K; k0 += kWmBK) {
+  // split-K (weight gradients over a long batch axis): slice blockIdx.z reduces k in [z * k_chunk, ...) into its own
+  // partial C; wm_reduce_kernel adds the slices in index order
+  const int kbeg = blockIdx.z * k_chunk;
+  K = min(K, kbeg + k_chunk);
+  C += blockIdx.z * c_split_stride;
+  for (int k0 = kbeg; k0 < K; k0 += kWmBK) {
     const int kt = min(kWmBK, K - k0);
     float ra[16], rb[16];
 #pragma unroll
@@ -77,33 +83,46 @@ __global__ void __launch_bounds__(256) wm_gemm_kernel(const float* __restrict__ 
 }
 
 // out[n] = sum_m X[m][n] (* Y[m][n]): bias gradients and the LayerNorm scale / bias gradients. One thread per column.
-// (both at once for the LayerNorm: out = sum X, out_xy = sum X * Y)
+// (both at once for the LayerNorm: out = sum X, out_xy = sum X * Y). blockIdx.y = row slice (rows_per_slice rows each,
+// its sums go to out + y * N: partials for wm_reduce_kernel when gridDim.y > 1).
 __global__ void wm_colsum_kernel(const float* __restrict__ X, const float* __restrict__ Y, int ld, int M, int N,
-                                 float* __restrict__ out, float* __restrict__ out_xy) {
+                                 float* __restrict__ out, float* __restrict__ out_xy, int rows_per_slice) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
+  const int m0 = blockIdx.y * rows_per_slice, m1 = min(M, m0 + rows_per_slice);
   float s = 0.f, sxy = 0.f;
 #pragma unroll 8
-  for (int m = 0; m < M; ++m) {
+  for (int m = m0; m < m1; ++m) {
     const float x = X[(long long)m * ld + n];
     s += x;
     if (Y) sxy += x * Y[(long long)m * ld + n];
   }
-  out[n] = s;
-  if (Y) out_xy[n] = sxy;
+  out[(long long)blockIdx.y * N + n] = s;
+  if (Y) out_xy[(long long)blockIdx.y * N + n] = sxy;
+}
+
+// out[i] = sum_s part[s][i], slices added in index order
+__global__ void wm_reduce_kernel(const float* __restrict__ part, int S, long long n, float* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float s = 0.f;
+  for (int k = 0; k < S; ++k) s += part[(long long)k * n + i];
+  out[i] = s;
 }
 
 // x0 = LayerNorm(concat(obs, act)) * scale + bias (envmodel/baseline.py:31-32; flax: var = E[x^2] - E[x]^2, eps inside
 // the rsqrt). One warp per row; keeps xhat for the scale gradient.
-__global__ void wm_ln_concat_kernel(const float* __restrict__ obs, const float* __restrict__ act, int O, int A, int rows,
-                                    const float* __restrict__ scale, const float* __restrict__ bias, float eps,
-                                    float* __restrict__ x0, float* __restrict__ xhat) {
+// act_stride: elements between the action rows of consecutive batch entries (A, or T * A inside a [B][T][A] window).
+__global__ void wm_ln_concat_kernel(const float* __restrict__ obs, const float* __restrict__ act, int act_stride, int O,
+                                    int A, int rows, const float* __restrict__ scale, const float* __restrict__ bias,
+                                    float eps, float* __restrict__ x0, float* __restrict__ xhat,
+                                    float* __restrict__ rstd_out) {
   const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (row >= rows) return;
   const int D = O + A;
   float s = 0.f, s2 = 0.f;
   for (int j = lane; j < D; j += 32) {
-    const float v = j < O ? obs[(long long)row * O + j] : act[(long long)row * A + (j - O)];
+    const float v = j < O ? obs[(long long)row * O + j] : act[(long long)row * act_stride + (j - O)];
     s += v;
     s2 += v * v;
   }
@@ -114,11 +133,45 @@ __global__ void wm_ln_concat_kernel(const float* __restrict__ obs, const float* 
   }
   const float mean = s / D, var = fmaxf(s2 / D - mean * mean, 0.f), rstd = rsqrtf(var + eps);
   for (int j = lane; j < D; j += 32) {
-    const float v = j < O ? obs[(long long)row * O + j] : act[(long long)row * A + (j - O)];
+    const float v = j < O ? obs[(long long)row * O + j] : act[(long long)row * act_stride + (j - O)];
     const float h = (v - mean) * rstd;
     xhat[(long long)row * D + j] = h;
     x0[(long long)row * D + j] = h * scale[j] + bias[j];
   }
+  if (rstd_out && lane == 0) rstd_out[row] = rstd;
+}
+
+// Back-propagation through time, one step: dx = LayerNorm backward of dx0 (d loss / d LN output) to concat(obs, act);
+// the observation part plus this step's output gradient (residual connection o' = f(o, a) + o) is what the PREVIOUS
+// step's prediction receives: g_prev[b][j] += g_cur[b][j] + dx[b][j], j < O. One warp per row.
+__global__ void wm_ln_bwd_kernel(const float* __restrict__ dx0, const float* __restrict__ xhat,
+                                 const float* __restrict__ rstd, const float* __restrict__ scale, int O, int D, int rows,
+                                 const float* __restrict__ g_cur, float* __restrict__ g_prev) {
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  float s1 = 0.f, s2 = 0.f;
+  for (int j = lane; j < D; j += 32) {
+    const float d = dx0[(long long)row * D + j] * scale[j];
+    s1 += d;
+    s2 += d * xhat[(long long)row * D + j];
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+  }
+  const float m1 = s1 / D, m2 = s2 / D, r = rstd[row];
+  for (int j = lane; j < O; j += 32) {
+    const float d = dx0[(long long)row * D + j] * scale[j];
+    const float dx = r * (d - m1 - xhat[(long long)row * D + j] * m2);
+    g_prev[(long long)row * O + j] += g_cur[(long long)row * O + j] + dx;
+  }
+}
+
+// o_0 = observations[:, 0, :] of a [B][T][O] window (envmodel/multistep.py:50)
+__global__ void wm_take_first_kernel(const float* __restrict__ obs, int B, int T, int O, float* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B * O) out[i] = obs[(long long)(i / O) * T * O + (i % O)];
 }
 
 // termination predictor input: next_obs (* dropout multiplier)
@@ -182,43 +235,59 @@ __device__ __forceinline__ float wm_sigmoid(float x) { return 1.f / (1.f + __exp
 __device__ __forceinline__ float wm_bce(float x, float t) { return fmaxf(x, 0.f) - x * t + log1pf(expf(-fabsf(x))); }
 
 // state_prediction_loss (envmodel/loss.py:65-111) with weighted_binary_cross_entropy (:12-28): logs, d loss / d pred of
-// the squared-error term and d loss / d logit of the termination term. One CTA; `terminated` = rewards == 0.
+// the squared-error term and d loss / d logit of the termination term; `terminated` = rewards == 0.
+// Rows of pred / logit / dpred / dlogit are TIME-major (row = t * B + b) while next_obs / rewards arrive batch-major
+// ([B][T][...]); T == 1 makes the two the same. Any grid: every CTA leaves its partial sums in `part`, the LAST CTA to
+// finish (ticket counter) adds them in CTA order and writes the logs, so the result does not depend on scheduling.
 __global__ void __launch_bounds__(256) wm_state_loss_kernel(const float* __restrict__ pred,
                                                             const float* __restrict__ next_obs,
                                                             const float* __restrict__ logit,
-                                                            const float* __restrict__ rewards, int rows, int O,
-                                                            float ttw, float tw, float rw, float* __restrict__ dpred,
-                                                            float* __restrict__ dlogit, float* __restrict__ logs,
-                                                            int* __restrict__ step) {
+                                                            const float* __restrict__ rewards, int rows, int B, int T,
+                                                            int O, float ttw, float tw, float rw,
+                                                            float* __restrict__ dpred, float* __restrict__ dlogit,
+                                                            float* __restrict__ logs, int* __restrict__ step,
+                                                            float* __restrict__ part, unsigned int* __restrict__ ticket) {
   __shared__ float sm[8][5];
+  __shared__ bool last;
   const float denom = 1.f + tw + rw;
   const bool term = tw > 0.f;
   float v[5] = {0.f, 0.f, 0.f, 0.f, 0.f};  // squared error, true ce, false ce, n true, n false
-  for (int b = threadIdx.x; b < rows; b += 256) {
+  for (int r = blockIdx.x * 256 + threadIdx.x; r < rows; r += gridDim.x * 256) {
+    const long long src = T > 1 ? (long long)(r % B) * T + r / B : r;
     float se = 0.f;
     for (int j = 0; j < O; ++j) {
-      const float d = pred[(long long)b * O + j] - next_obs[(long long)b * O + j];
+      const float d = pred[(long long)r * O + j] - next_obs[src * O + j];
       se += d * d;
-      if (dpred) dpred[(long long)b * O + j] = 2.f * d / ((float)rows * O * denom);
+      if (dpred) dpred[(long long)r * O + j] = 2.f * d / ((float)rows * O * denom);
     }
     v[0] += se;
     if (term) {
-      const float x = logit[b], t = rewards[b] == 0.f ? 1.f : 0.f, ce = wm_bce(x, t);
+      const float x = logit[r], t = rewards[src] == 0.f ? 1.f : 0.f, ce = wm_bce(x, t);
       if (t == 1.f) { v[1] += ce; v[3] += 1.f; } else { v[2] += ce; v[4] += 1.f; }
-      if (dlogit) dlogit[b] = (tw / denom) * (t == 1.f ? ttw : 1.f) * (wm_sigmoid(x) - t) / ((ttw + 1.f) * rows);
+      if (dlogit) dlogit[r] = (tw / denom) * (t == 1.f ? ttw : 1.f) * (wm_sigmoid(x) - t) / ((ttw + 1.f) * rows);
     }
   }
   wm_block_reduce<5>(v, sm);
   if (threadIdx.x == 0) {
-    const float mse = v[0] / ((float)rows * O);
-    const float tl = term ? (ttw * v[1] + v[2]) / ((ttw + 1.f) * rows) : 0.f;
-    logs[WL_NEXT_OBS_LOSS] = mse;
-    logs[WL_TERM_LOSS] = tl;
-    logs[WL_TRUE_LOSS] = term ? v[1] / v[3] : 0.f;   // 0 / 0 = NaN without positives, as in the reference
-    logs[WL_FALSE_LOSS] = term ? v[2] / v[4] : 0.f;
-    logs[WL_RECON_LOSS] = 0.f;
-    logs[WL_LOSS] = (mse + tw * tl) / denom;
-    wm_tick(step, logs);
+    for (int i = 0; i < 5; ++i) part[blockIdx.x * 5 + i] = v[i];
+    __threadfence();
+    last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    if (last) {
+      __threadfence();
+      *ticket = 0u;
+      for (int i = 0; i < 5; ++i) v[i] = 0.f;
+      for (unsigned int c = 0; c < gridDim.x; ++c)
+        for (int i = 0; i < 5; ++i) v[i] += ((volatile float*)part)[c * 5 + i];
+      const float mse = v[0] / ((float)rows * O);
+      const float tl = term ? (ttw * v[1] + v[2]) / ((ttw + 1.f) * rows) : 0.f;
+      logs[WL_NEXT_OBS_LOSS] = mse;
+      logs[WL_TERM_LOSS] = tl;
+      logs[WL_TRUE_LOSS] = term ? v[1] / v[3] : 0.f;   // 0 / 0 = NaN without positives, as in the reference
+      logs[WL_FALSE_LOSS] = term ? v[2] / v[4] : 0.f;
+      logs[WL_RECON_LOSS] = 0.f;
+      logs[WL_LOSS] = (mse + tw * tl) / denom;
+      wm_tick(step, logs);
+    }
   }
 }
 
@@ -314,8 +383,10 @@ struct WmTrainer {
   float* tx[kWmMaxLayers + 1] = {};   // frozen termination predictor on the prediction (tx[0] aliases the prediction)
   float *xhat = nullptr, *pred = nullptr, *dbuf[2] = {nullptr, nullptr}, *dlogit = nullptr;
   float* gx[kWmMaxLayers + 1] = {};   // gx[l] = d loss / d x[l], one buffer per layer (side streams read them late)
-  float *logs = nullptr;
+  float *logs = nullptr, *loss_part = nullptr, *rstd = nullptr, *ocur = nullptr, *wpart = nullptr, *cpart = nullptr;
+  unsigned int* ticket = nullptr;
   int* step = nullptr;
+  int rows = 0;  // batch * sequence length
   // resident dataset + sampled batch
   const float *ds_obs = nullptr, *ds_act = nullptr, *ds_next = nullptr, *ds_rew = nullptr;
   long long ds_rows = 0;
@@ -371,16 +442,25 @@ struct Launcher {
     cudaStreamWaitEvent(s, a, 0);
     cudaStreamWaitEvent(s, b, 0);
   }
+  // splits > 1: slice z of the k range goes to C + z * M * N (ldc must be N); wm_reduce adds the slices
   void gemm(bool ta, bool tb, const float* A, int lda, const float* B, int ldb, float* C, int ldc, int M, int N, int K,
-            int epi, const float* bias, const float* aux, int ldaux, int accumulate) {
-    dim3 grid((N + kWmTile - 1) / kWmTile, (M + kWmTile - 1) / kWmTile);
-    if (ta) wm_gemm_kernel<true, false><<<grid, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate);
-    else if (tb) wm_gemm_kernel<false, true><<<grid, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate);
-    else wm_gemm_kernel<false, false><<<grid, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate);
+            int epi, const float* bias, const float* aux, int ldaux, int accumulate, int splits = 1) {
+    dim3 grid((N + kWmTile - 1) / kWmTile, (M + kWmTile - 1) / kWmTile, splits);
+    const int kc = splits > 1 ? ((K + splits - 1) / splits + kWmBK - 1) / kWmBK * kWmBK : K;
+    const long long cs = splits > 1 ? (long long)M * N : 0;
+    if (ta) wm_gemm_kernel<true, false><<<grid, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate, kc, cs);
+    else if (tb) wm_gemm_kernel<false, true><<<grid, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate, kc, cs);
+    else wm_gemm_kernel<false, false><<<grid, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate, kc, cs);
     ++n;
   }
-  void colsum(const float* X, const float* Y, int ld, int M, int N, float* out, float* out_xy) {
-    wm_colsum_kernel<<<(N + 31) / 32, 32, 0, cur>>>(X, Y, ld, M, N, out, out_xy);
+  // slices > 1: out / out_xy receive [slices][N] partials
+  void colsum(const float* X, const float* Y, int ld, int M, int N, float* out, float* out_xy, int slices = 1) {
+    dim3 grid((N + 31) / 32, slices);
+    wm_colsum_kernel<<<grid, 32, 0, cur>>>(X, Y, ld, M, N, out, out_xy, (M + slices - 1) / slices);
+    ++n;
+  }
+  void reduce(const float* part, int S, long long cnt, float* out) {
+    wm_reduce_kernel<<<(int)((cnt + 255) / 256), 256, 0, cur>>>(part, S, cnt, out);
     ++n;
   }
 };
@@ -422,15 +502,16 @@ void wm_issue(WmTrainer* t, Launcher& L, int train, int gather, const float* obs
   const bool with_term = state && c.termination_weight > 0.f;
   float* g = nullptr;  // gradient wrt the output of the layer being walked
   if (state) {
-    wm_ln_concat_kernel<<<(B * 32 + 255) / 256, 256, 0, s>>>(obs, act, O, A, B, t->params + net.off_ln_scale,
-                                                            t->params + net.off_ln_bias, c.ln_eps, t->x[0], t->xhat);
+    wm_ln_concat_kernel<<<(B * 32 + 255) / 256, 256, 0, s>>>(obs, act, A, O, A, B, t->params + net.off_ln_scale,
+                                                            t->params + net.off_ln_bias, c.ln_eps, t->x[0], t->xhat,
+                                                            nullptr);
     ++L.n;
     wm_forward(L, net, t->params, t->x, B, obs, O);  // x[nl] = Dense_O(x) + obs
     if (with_term) wm_forward(L, t->term, t->term_params, t->tx, B, nullptr, 0);  // tx[0] aliases x[nl]
-    wm_state_loss_kernel<<<1, 256, 0, s>>>(t->x[nl], next_obs, with_term ? t->tx[t->term.n_layers] : nullptr, rew, B, O,
-                                           c.true_termination_weight, c.termination_weight, c.reconstruction_weight,
+    wm_state_loss_kernel<<<1, 256, 0, s>>>(t->x[nl], next_obs, with_term ? t->tx[t->term.n_layers] : nullptr, rew, B, B, 1,
+                                           O, c.true_termination_weight, c.termination_weight, c.reconstruction_weight,
                                            train ? t->pred : nullptr, train ? t->dlogit : nullptr, t->logs,
-                                           train ? t->step : nullptr);
+                                           train ? t->step : nullptr, t->loss_part, t->ticket);
     ++L.n;
     if (!train) return;
     if (with_term) {  // d loss / d prediction through the frozen termination predictor, added onto the squared-error part
@@ -480,6 +561,88 @@ void wm_issue(WmTrainer* t, Launcher& L, int train, int gather, const float* obs
   ++L.n;
 }
 
+
+constexpr int kWmLossCtas = 128, kWmSplits = 64;
+
+// One step of the multistep predictor (envmodel/multistep.py:34-54: nn.scan of the baseline cell over the window, each
+// prediction fed back as the next observation; loss over all T predictions, state_predictor_trainer.py:79-97).
+// Activations are kept TIME-major ([T][B][width] slabs) so that every time step is a plain [B][width] matrix, the frozen
+// termination predictor and the loss run ONCE over all T*B rows, and after back-propagation through time each weight
+// gradient is ONE product over the T*B rows (split-K, slices added in order) instead of T small ones.
+void wm_issue_multistep(WmTrainer* t, Launcher& L, int train, const float* obs, const float* act, const float* next_obs,
+                        const float* rew) {
+  const WmConfig& c = t->cfg;
+  const WmNet& net = t->net;
+  const int B = c.batch, T = c.seq_len, O = c.O, A = c.A, nl = net.n_layers, D0 = net.dims[0], R = t->rows;
+  cudaStream_t s = L.s;
+  const bool with_term = c.termination_weight > 0.f;
+  const float* scale = t->params + net.off_ln_scale;
+  wm_take_first_kernel<<<(B * O + 255) / 256, 256, 0, s>>>(obs, B, T, O, t->ocur);
+  ++L.n;
+  for (int ti = 0; ti < T; ++ti) {
+    float* act_l[kWmMaxLayers + 1];
+    for (int l = 0; l < nl; ++l) act_l[l] = t->x[l] + (long long)ti * B * net.dims[l];
+    float* o_t = t->ocur + (long long)ti * B * O;
+    act_l[nl] = o_t + (long long)B * O;  // o_{t+1}: prediction of this step, input of the next
+    wm_ln_concat_kernel<<<(B * 32 + 255) / 256, 256, 0, s>>>(o_t, act + (long long)ti * A, T * A, O, A, B, scale,
+                                                            t->params + net.off_ln_bias, c.ln_eps, act_l[0],
+                                                            t->xhat + (long long)ti * B * D0, t->rstd + ti * B);
+    ++L.n;
+    wm_forward(L, net, t->params, act_l, B, o_t, O);
+  }
+  float* pred = t->ocur + (long long)B * O;  // [T][B][O]
+  if (with_term) wm_forward(L, t->term, t->term_params, t->tx, R, nullptr, 0);  // tx[0] aliases pred
+  wm_state_loss_kernel<<<kWmLossCtas, 256, 0, s>>>(pred, next_obs, with_term ? t->tx[t->term.n_layers] : nullptr, rew, R, B,
+                                                  T, O, c.true_termination_weight, c.termination_weight,
+                                                  c.reconstruction_weight, train ? t->gx[nl] : nullptr,
+                                                  train ? t->dlogit : nullptr, t->logs, train ? t->step : nullptr,
+                                                  t->loss_part, t->ticket);
+  ++L.n;
+  if (!train) return;
+  if (with_term) {
+    const WmNet& tn = t->term;
+    const float* gt = t->dlogit;
+    for (int l = tn.n_layers - 1; l >= 0; --l) {
+      float* out = l == 0 ? t->gx[nl] : t->dbuf[l & 1];
+      L.gemm(false, true, gt, tn.dims[l + 1], t->term_params + tn.offW[l], tn.dims[l + 1], out, tn.dims[l], R, tn.dims[l],
+             tn.dims[l + 1], l == 0 ? WE_NONE : WE_MASK, nullptr, l == 0 ? nullptr : t->tx[l], tn.dims[l], l == 0);
+      gt = out;
+    }
+  }
+  // back-propagation through time: input-gradient chain of step ti, then LayerNorm backward + residual into step ti-1
+  for (int ti = T - 1; ti >= 0; --ti) {
+    const float* g = t->gx[nl] + (long long)ti * B * O;
+    for (int l = nl - 1; l >= 0; --l) {
+      const int din = net.dims[l], dout = net.dims[l + 1];
+      float* out = t->gx[l] + (long long)ti * B * din;
+      L.gemm(false, true, g, dout, t->params + net.offW[l], dout, out, din, B, din, dout, l > 0 ? WE_MASK : WE_NONE, nullptr,
+             l > 0 ? t->x[l] + (long long)ti * B * din : nullptr, din, 0);
+      g = out;
+    }
+    if (ti > 0) {
+      wm_ln_bwd_kernel<<<(B * 32 + 255) / 256, 256, 0, s>>>(g, t->xhat + (long long)ti * B * D0, t->rstd + ti * B, scale, O,
+                                                           D0, B, t->gx[nl] + (long long)ti * B * O,
+                                                           t->gx[nl] + (long long)(ti - 1) * B * O);
+      ++L.n;
+    }
+  }
+  // parameter gradients over all T*B rows at once
+  for (int l = nl - 1; l >= 0; --l) {
+    const int din = net.dims[l], dout = net.dims[l + 1];
+    L.gemm(true, false, t->x[l], din, t->gx[l + 1], dout, t->wpart, dout, din, dout, R, WE_NONE, nullptr, nullptr, 0, 0,
+           kWmSplits);
+    L.reduce(t->wpart, kWmSplits, (long long)din * dout, t->grads + net.offW[l]);
+    L.colsum(t->gx[l + 1], nullptr, dout, R, dout, t->cpart, nullptr, kWmSplits);
+    L.reduce(t->cpart, kWmSplits, dout, t->grads + net.offB[l]);
+  }
+  L.colsum(t->gx[0], t->xhat, D0, R, D0, t->cpart, t->cpart + (long long)kWmSplits * D0, kWmSplits);
+  L.reduce(t->cpart, kWmSplits, D0, t->grads + net.off_ln_bias);
+  L.reduce(t->cpart + (long long)kWmSplits * D0, kWmSplits, D0, t->grads + net.off_ln_scale);
+  wm_adam_kernel<<<(int)((net.n_params + 255) / 256), 256, 0, s>>>(t->params, t->m, t->v, t->grads, net.n_params, t->step,
+                                                                  c.lr, c.decay_steps, t->logs);
+  ++L.n;
+}
+
 int wm_run(WmTrainer* t, int train, int gather, int repeats, const float* obs, const float* act, const float* next_obs,
            const float* rew, const float* mask, cudaStream_t stream, std::string* err) {
   WM_CUDA(cudaSetDevice(t->device));
@@ -499,7 +662,8 @@ int wm_run(WmTrainer* t, int train, int gather, int repeats, const float* obs, c
     WM_CUDA(cudaStreamCreateWithFlags(&sw, cudaStreamNonBlocking));
     WM_CUDA(cudaStreamCreateWithFlags(&sc, cudaStreamNonBlocking));
     Launcher L{cs, sw, sc, cs};
-    wm_issue(t, L, train, gather, obs, act, next_obs, rew, mask);
+    if (t->cfg.kind == WM_MULTISTEP) wm_issue_multistep(t, L, train, obs, act, next_obs, rew);
+    else wm_issue(t, L, train, gather, obs, act, next_obs, rew, mask);
     cudaGraph_t graph = nullptr;
     cudaError_t ce = cudaStreamEndCapture(cs, &graph);
     cudaError_t le = cudaGetLastError();
@@ -527,43 +691,60 @@ int wm_run(WmTrainer* t, int train, int gather, int repeats, const float* obs, c
 int wm_create_impl(const WmConfig& cfg, const float* params_host, const float* term_params_host, WmTrainer** out,
                    std::string* err) {
   auto bad = [&](const char* m) { if (err) *err = m; return 1; };
-  if (cfg.kind != WM_STATE && cfg.kind != WM_TERMINATION) return bad("world model: kind must be 0 (state) or 1 (termination)");
+  if (cfg.kind != WM_STATE && cfg.kind != WM_TERMINATION && cfg.kind != WM_MULTISTEP)
+    return bad("world model: kind must be 0 (state), 1 (termination) or 2 (multistep)");
   if (cfg.O < 1 || cfg.A < 0 || cfg.batch < 1) return bad("world model: bad dimensions");
   if (cfg.n_hidden < 1 || cfg.n_hidden >= kWmMaxLayers) return bad("world model: between 1 and 7 hidden layers");
   if (cfg.decay_steps < 1) return bad("world model: decay_steps must be positive");
   if (!params_host) return bad("world model: initial parameters are required");
-  const bool state = cfg.kind == WM_STATE;
+  const bool multi = cfg.kind == WM_MULTISTEP;
+  if (multi && (cfg.seq_len < 1 || (long long)cfg.seq_len * cfg.batch > (1 << 24)))
+    return bad("world model: multistep needs 1 <= seq_len and batch * seq_len <= 2^24");
+  const bool state = cfg.kind != WM_TERMINATION;
   const bool with_term = state && cfg.termination_weight > 0.f;
   if (with_term && (!term_params_host || cfg.term_n_hidden < 1 || cfg.term_n_hidden >= kWmMaxLayers))
     return bad("world model: termination_weight > 0 needs the trained termination predictor (parameters + hidden dims)");
   WmTrainer* t = new WmTrainer();
   t->cfg = cfg;
+  if (!multi) t->cfg.seq_len = 1;
   cudaGetDevice(&t->device);
   t->net = state ? wm_layout(cfg.O + cfg.A, cfg.n_hidden, cfg.hidden, cfg.O, true)
                  : wm_layout(cfg.O, cfg.n_hidden, cfg.hidden, 1, false);
   const long long n = t->net.n_params;
-  const int B = cfg.batch;
+  const int B = cfg.batch, nl = t->net.n_layers;
+  const long long R = (long long)B * t->cfg.seq_len;  // rows every per-row buffer holds (time-major slabs for multistep)
+  t->rows = (int)R;
   int maxdim = 1;
-  for (int l = 0; l <= t->net.n_layers; ++l) maxdim = std::max(maxdim, t->net.dims[l]);
+  long long maxw = 1;
+  for (int l = 0; l <= nl; ++l) maxdim = std::max(maxdim, t->net.dims[l]);
+  for (int l = 0; l < nl; ++l) maxw = std::max(maxw, (long long)t->net.dims[l] * t->net.dims[l + 1]);
   int rc = 0;
   rc |= wm_alloc(t, &t->params, n, err) || wm_alloc(t, &t->m, n, err) || wm_alloc(t, &t->v, n, err) ||
         wm_alloc(t, &t->grads, n, err);
-  for (int l = 0; l <= t->net.n_layers && !rc; ++l)
-    rc |= wm_alloc(t, &t->x[l], (long long)B * t->net.dims[l], err) || wm_alloc(t, &t->gx[l], (long long)B * t->net.dims[l], err);
-  if (!rc && state) rc |= wm_alloc(t, &t->xhat, (long long)B * t->net.dims[0], err);
+  for (int l = 0; l <= nl && !rc; ++l) {
+    if (!(multi && l == nl)) rc |= wm_alloc(t, &t->x[l], R * t->net.dims[l], err);  // multistep: predictions live in ocur
+    rc |= wm_alloc(t, &t->gx[l], R * t->net.dims[l], err);
+  }
+  if (!rc && state) rc |= wm_alloc(t, &t->xhat, R * t->net.dims[0], err) || wm_alloc(t, &t->rstd, R, err);
+  if (!rc && multi) {
+    rc |= wm_alloc(t, &t->ocur, (R + B) * cfg.O, err) || wm_alloc(t, &t->wpart, kWmSplits * maxw, err) ||
+          wm_alloc(t, &t->cpart, 2LL * kWmSplits * maxdim, err);
+    t->x[nl] = t->ocur ? t->ocur + (long long)B * cfg.O : nullptr;
+  }
   if (!rc && with_term) {
     t->term = wm_layout(cfg.O, cfg.term_n_hidden, cfg.term_hidden, 1, false);
     for (int l = 0; l <= t->term.n_layers; ++l) maxdim = std::max(maxdim, t->term.dims[l]);
     rc |= wm_alloc(t, &t->term_params, t->term.n_params, err);
-    t->tx[0] = t->x[t->net.n_layers];
-    for (int l = 1; l <= t->term.n_layers && !rc; ++l) rc |= wm_alloc(t, &t->tx[l], (long long)B * t->term.dims[l], err);
+    t->tx[0] = t->x[nl];
+    for (int l = 1; l <= t->term.n_layers && !rc; ++l) rc |= wm_alloc(t, &t->tx[l], R * t->term.dims[l], err);
     if (!rc && cudaMemcpy(t->term_params, term_params_host, sizeof(float) * t->term.n_params, cudaMemcpyHostToDevice) != cudaSuccess)
       rc = bad("world model: copying the termination predictor failed");
   }
   if (!rc)
-    rc |= wm_alloc(t, &t->pred, (long long)B * cfg.O, err) || wm_alloc(t, &t->dbuf[0], (long long)B * maxdim, err) ||
-          wm_alloc(t, &t->dbuf[1], (long long)B * maxdim, err) || wm_alloc(t, &t->dlogit, B, err) ||
+    rc |= wm_alloc(t, &t->pred, (long long)B * cfg.O, err) || wm_alloc(t, &t->dbuf[0], R * maxdim, err) ||
+          wm_alloc(t, &t->dbuf[1], R * maxdim, err) || wm_alloc(t, &t->dlogit, R, err) ||
           wm_alloc(t, &t->logs, kWmLogs, err) || wm_alloc(t, (float**)&t->step, 2, err) ||
+          wm_alloc(t, &t->loss_part, kWmLossCtas * 5, err) || wm_alloc(t, (float**)&t->ticket, 1, err) ||
           wm_alloc(t, &t->b_obs, (long long)B * cfg.O, err) || wm_alloc(t, &t->b_act, (long long)B * std::max(cfg.A, 1), err) ||
           wm_alloc(t, &t->b_next, (long long)B * cfg.O, err) || wm_alloc(t, &t->b_rew, B, err);
   if (!rc && cudaMemcpy(t->params, params_host, sizeof(float) * n, cudaMemcpyHostToDevice) != cudaSuccess)
@@ -587,7 +768,7 @@ void wm_destroy_impl(WmTrainer* t) {
 
 int wm_step_impl(WmTrainer* t, int train, const float* obs, const float* act, const float* next_obs, const float* rewards,
                  const float* dropout_mask, cudaStream_t stream, std::string* err) {
-  if (!next_obs || !rewards || (t->cfg.kind == WM_STATE && (!obs || !act))) {
+  if (!next_obs || !rewards || (t->cfg.kind != WM_TERMINATION && (!obs || !act))) {
     if (err) *err = "world-model step: null batch pointer";
     return 1;
   }
@@ -607,6 +788,10 @@ int wm_set_dataset_impl(WmTrainer* t, const float* obs, const float* act, const 
 }
 
 int wm_train_impl(WmTrainer* t, int n_steps, const float* dropout_mask, cudaStream_t stream, std::string* err) {
+  if (t->cfg.kind == WM_MULTISTEP) {
+    if (err) *err = "world-model train: the multistep predictor takes explicit windows (fqlpop_wm_step)";
+    return 1;
+  }
   if (!t->ds_rows) {
     if (err) *err = "world-model train: no resident dataset (fqlpop_wm_set_dataset)";
     return 1;

@@ -22,7 +22,7 @@ namespace fqlpop {
 constexpr int kWmMaxLayers = 8;  // Dense layers of one network, output layer included
 constexpr int kWmLogs = 16;
 
-enum WmKind : int { WM_STATE = 0, WM_TERMINATION = 1 };
+enum WmKind : int { WM_STATE = 0, WM_TERMINATION = 1, WM_MULTISTEP = 2 };
 
 // logs[] slots (float). State predictor: the keys of state_prediction_loss's logs (envmodel/loss.py:98-109).
 // Termination predictor: focal_loss's logs + the eval_step metrics (termination_predictor_trainer.py:88-126).
@@ -51,6 +51,7 @@ struct WmNet {
 
 struct WmConfig {
   int kind, O, A, batch;
+  int seq_len;  // WM_MULTISTEP: window length T (batch arrays are [batch][T][...]); 1 otherwise
   int n_hidden, hidden[kWmMaxLayers];
   int term_n_hidden, term_hidden[kWmMaxLayers];  // frozen termination predictor inside the state loss (0 = none)
   int decay_steps;

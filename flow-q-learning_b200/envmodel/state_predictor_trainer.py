@@ -26,7 +26,10 @@ class _State:
 
     @property
     def params(self) -> Dict:
-        return {"params": self._t.device_trainer.params()}
+        tree = self._t.device_trainer.params()
+        if getattr(self._t, "multistep", False):  # nn.scan(Cell) with the baseline predictor as `cell` (multistep.py:17-21,41-53)
+            tree = {"ScanCell_0": {"cell": tree}}
+        return {"params": tree}
 
     @property
     def step(self) -> int:
@@ -46,7 +49,11 @@ def _loss_weights(loss_fn, config: TrainerConfig):
 class StatePredictorTrainer:
     def __init__(self, model, train_loader: DataLoader, val_loader: DataLoader, loss_fn, config: TrainerConfig,
                  logger=None, device=None, device_sampling: bool = False, params: Optional[Dict] = None):
-        from fqlpop.worldmodel import STATE, WorldModelTrainer  # needs libfqlpop.so; no CPU fallback
+        from fqlpop.worldmodel import MULTISTEP, STATE, WorldModelTrainer  # needs libfqlpop.so; no CPU fallback
+        from envmodel.multistep import MultistepStatePredictor
+        self.multistep = isinstance(model, MultistepStatePredictor)
+        if self.multistep and device_sampling:
+            raise ValueError("the multistep predictor trains on host-sampled windows (MultistepLoader)")
         self.model, self.train_loader, self.val_loader = model, train_loader, val_loader
         self.loss_fn, self.config, self.logger = loss_fn, config, logger
         self.device_sampling = device_sampling
@@ -54,13 +61,17 @@ class StatePredictorTrainer:
         ttw, tw, rw = _loss_weights(loss_fn, config)
         term_params, term_hidden = None, ()
         if tw > 0:  # frozen, already trained (state_predictor_trainer.py:47-56)
-            tp = load_model(config.save_directory, config.env_name, "termination_predictor", sample_batch, device=device)
+            tp = load_model(config.save_directory, config.env_name, "termination_predictor",
+                            {k: np.reshape(v, (-1,) + np.shape(v)[2:]) if self.multistep else v for k, v in sample_batch.items()},
+                            device=device)
             term_params, term_hidden = tp.params, tp.hidden_dims
         self.device_trainer = WorldModelTrainer(
-            STATE, int(np.shape(sample_batch["observations"])[-1]), int(np.shape(sample_batch["actions"])[-1]),
+            MULTISTEP if self.multistep else STATE, int(np.shape(sample_batch["observations"])[-1]),
+            int(np.shape(sample_batch["actions"])[-1]),
             tuple(model.hidden_dims), config.batch_size, config.steps, config.init_learning_rate, params=params,
             seed=config.seed, termination_params=term_params, termination_hidden_dims=term_hidden,
-            true_termination_weight=ttw, termination_weight=tw, reconstruction_weight=rw, device=device)
+            true_termination_weight=ttw, termination_weight=tw, reconstruction_weight=rw,
+            sequence_length=int(np.shape(sample_batch["actions"])[1]) if self.multistep else 1, device=device)
         self.state = _State(self)
 
     def schedule(self, step: int) -> float:

@@ -15,7 +15,7 @@ import torch
 
 from ._lib import check, default_device, lib
 
-STATE, TERMINATION = 0, 1
+STATE, TERMINATION, MULTISTEP = 0, 1, 2
 LOG_SLOTS = 16
 _STATE_LOGS = {"loss": 0, "next_observation_loss": 1, "termination_loss": 2, "true_termination_loss": 3,
                "false_termination_loss": 4}
@@ -32,7 +32,7 @@ class WmConfig(ctypes.Structure):
         ("true_termination_weight", ctypes.c_float), ("termination_weight", ctypes.c_float),
         ("reconstruction_weight", ctypes.c_float),
         ("focal_alpha", ctypes.c_float), ("focal_gamma", ctypes.c_float),
-        ("seed", ctypes.c_uint64),
+        ("seed", ctypes.c_uint64), ("seq_len", ctypes.c_int32), ("reserved", ctypes.c_int32),
     ]
 
 
@@ -57,13 +57,13 @@ def _np32(x) -> np.ndarray:
 
 
 def layer_dims(kind: int, ob_dim: int, action_dim: int, hidden: Sequence[int]):
-    return ([ob_dim + action_dim, *hidden, ob_dim] if kind == STATE else [ob_dim, *hidden, 1])
+    return ([ob_dim + action_dim, *hidden, ob_dim] if kind != TERMINATION else [ob_dim, *hidden, 1])
 
 
 def flatten_params(tree: Dict, kind: int) -> np.ndarray:
     """flax tree -> the flat vector of include/fqlpop.h (LayerNorm scale, bias, then kernel, bias per Dense layer)."""
     parts = []
-    if kind == STATE:
+    if kind != TERMINATION:
         parts += [_np32(tree["LayerNorm_0"]["scale"]).ravel(), _np32(tree["LayerNorm_0"]["bias"]).ravel()]
     n = sum(1 for k in tree if k.startswith("Dense_"))
     for i in range(n):
@@ -81,7 +81,7 @@ def unflatten_params(flat: np.ndarray, kind: int, dims: Sequence[int]) -> Dict:
         off += n
         return out
 
-    if kind == STATE:
+    if kind != TERMINATION:
         tree["LayerNorm_0"] = {"scale": take(dims[0]), "bias": take(dims[0])}
     for i in range(len(dims) - 1):
         tree[f"Dense_{i}"] = {"kernel": take(dims[i], dims[i + 1]), "bias": take(dims[i + 1])}
@@ -96,7 +96,7 @@ def init_params(seed: int, kind: int, ob_dim: int, action_dim: int, hidden: Sequ
     rng = np.random.default_rng(seed)
     dims = layer_dims(kind, ob_dim, action_dim, hidden)
     tree = {}
-    if kind == STATE:
+    if kind != TERMINATION:
         tree["LayerNorm_0"] = {"scale": np.ones(dims[0], np.float32), "bias": np.zeros(dims[0], np.float32)}
     for i in range(len(dims) - 1):
         n = dims[i] * dims[i + 1]
@@ -121,9 +121,10 @@ class WorldModelTrainer:
                  termination_params: Optional[Dict] = None, termination_hidden_dims: Sequence[int] = (),
                  true_termination_weight: float = 30.0, termination_weight: float = 1.0,
                  reconstruction_weight: float = 0.0, focal_alpha: float = 0.25, focal_gamma: float = 2.0,
-                 ln_eps: float = 1e-6, device=None):
+                 ln_eps: float = 1e-6, sequence_length: int = 1, device=None):
         self.device = torch.device(device) if device is not None else default_device()
         self.kind, self.ob_dim, self.action_dim = kind, ob_dim, action_dim
+        self.sequence_length = int(sequence_length) if kind == MULTISTEP else 1
         self.hidden_dims, self.batch_size = tuple(int(h) for h in hidden_dims), int(batch_size)
         self.dims = layer_dims(kind, ob_dim, action_dim, self.hidden_dims)
         c = WmConfig()
@@ -131,7 +132,7 @@ class WorldModelTrainer:
         c.n_hidden = len(self.hidden_dims)
         for i, h in enumerate(self.hidden_dims):
             c.hidden[i] = h
-        with_term = kind == STATE and termination_weight > 0
+        with_term = kind != TERMINATION and termination_weight > 0
         if with_term:
             if termination_params is None:
                 raise ValueError("termination_weight > 0 needs the trained termination predictor's parameters")
@@ -142,6 +143,7 @@ class WorldModelTrainer:
         c.true_termination_weight, c.termination_weight = true_termination_weight, termination_weight
         c.reconstruction_weight = reconstruction_weight
         c.focal_alpha, c.focal_gamma, c.seed = focal_alpha, focal_gamma, seed
+        c.seq_len = self.sequence_length
         self._cfg = c
         self.n_params = int(lib.fqlpop_wm_num_params(ctypes.byref(c)))
         if params is None:
@@ -181,7 +183,7 @@ class WorldModelTrainer:
 
     def named_logs(self, train: bool) -> Dict[str, float]:
         raw = self.logs()
-        if self.kind == STATE:
+        if self.kind != TERMINATION:
             keys = dict(_STATE_LOGS)
             if not self._cfg.termination_weight > 0:
                 keys = {"loss": 0, "next_observation_loss": 1}
@@ -200,6 +202,8 @@ class WorldModelTrainer:
             n = t["next_observations"].shape[0]
             if n != self.batch_size:
                 raise ValueError(f"batch has {n} rows, the trainer was built for {self.batch_size}")
+            if self.kind == MULTISTEP and tuple(t["actions"].shape[:2]) != (n, self.sequence_length):
+                raise ValueError(f"multistep windows must be [batch, {self.sequence_length}, ...]")
             m = self._dev(dropout_mask) if (dropout_mask is not None and train) else None
             ptr = lambda k: t[k].data_ptr() if k in t else None
             check(lib.fqlpop_wm_step(self._h, 1 if train else 0, ptr("observations"), ptr("actions"),

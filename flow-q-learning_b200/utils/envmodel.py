@@ -56,9 +56,9 @@ class LoadedModel:
         import torch
         if train:
             raise NotImplementedError("world-model training (Dropout active) is outside the rollout hot path")
-        obs = torch.as_tensor(np.asarray(observations, dtype=np.float32))
+        obs = torch.as_tensor(np.array(observations, dtype=np.float32))
         if self.kind in _STATE_MODELS:
-            nxt, _ = self._device_model().step(obs, torch.as_tensor(np.asarray(actions, dtype=np.float32)))
+            nxt, _ = self._device_model().step(obs, torch.as_tensor(np.array(actions, dtype=np.float32)))
             return nxt.cpu().numpy(), np.asarray(observations)
         zeros = torch.zeros(obs.shape[0], self.action_dim)
         _, logits = self._device_model().step(obs, zeros)

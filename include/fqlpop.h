@@ -168,7 +168,11 @@ int64_t fqlpop_rollout_launches(void* handle);
  * Parameters travel as ONE flat fp32 vector: [LayerNorm scale, LayerNorm bias (state predictor only, ob_dim+action_dim
  * each)], then per Dense layer (hidden..., output) kernel [in][out] (flax layout) followed by bias [out].             */
 typedef struct {
-  int32_t kind;                       /* 0 state predictor, 1 termination predictor                               */
+  int32_t kind;                       /* 0 state predictor, 1 termination predictor, 2 multistep state predictor  *
+                                       * (envmodel/multistep.py:34-54: the kind-0 cell scanned over a window; batch   *
+                                       * arrays are then obs[batch][T][ob_dim] (only t = 0 is read), act[batch][T]    *
+                                       * [action_dim], next_obs[batch][T][ob_dim], rewards[batch][T]; same flat       *
+                                       * parameter vector as kind 0; explicit windows only, no fqlpop_wm_train)       */
   int32_t ob_dim, action_dim, batch;
   int32_t n_hidden, hidden[8];
   int32_t term_n_hidden, term_hidden[8]; /* kind 0, termination_weight > 0: the frozen termination predictor      */
@@ -177,6 +181,8 @@ typedef struct {
   float true_termination_weight, termination_weight, reconstruction_weight;   /* config.py:11-13                 */
   float focal_alpha, focal_gamma;     /* kind 1: focal_loss defaults 0.25 / 2.0 (loss.py:34-35)                  */
   uint64_t seed;                      /* Philox stream of fqlpop_wm_train's sampler                               */
+  int32_t seq_len;                    /* kind 2: window length T (TrainerConfig.sequence_length, config.py:17)    */
+  int32_t reserved;
 } fqlpop_wm_config_t;
 /* Number of floats of the flat parameter vector of a network with this config (same for m, v, gradients).  */
 int64_t fqlpop_wm_num_params(const fqlpop_wm_config_t* cfg);

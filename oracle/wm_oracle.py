@@ -177,3 +177,31 @@ def termination_step(params, opt, batch, dropout_mask=None, *, lr0, decay_steps,
     new = _detach(p)
     logs["learning_rate"] = _adam(new, g, opt, lr0, decay_steps)
     return new, logs, g
+
+
+def multistep_step(params, opt, batch, term_params, *, lr0, decay_steps, true_termination_weight=30.0,
+                   termination_weight=1.0, reconstruction_weight=0.0, train=True):
+    """StatePredictorTrainer.train_step with the MultistepStatePredictor (envmodel/multistep.py:34-54): the baseline cell
+    scanned along axis 1 of actions from observations[:, 0, :], each prediction fed back as the next observation; the loss
+    sees all T predictions [B, T, O] (and the termination predictor's logits on them) against next_observations / rewards
+    [B, T]. `params` is the cell's tree (params["ScanCell_0"]["cell"] in the reference's checkpoint)."""
+    p = _with_grad(params) if train else params
+    o = batch["observations"][:, 0, :]
+    preds, recon = [], []
+    for t in range(batch["actions"].shape[1]):
+        recon.append(o)
+        o = state_predictor_apply(p, o, batch["actions"][:, t, :])
+        preds.append(o)
+    pred, recon = torch.stack(preds, 1), torch.stack(recon, 1)
+    logit = termination_predictor_apply(term_params, pred) if termination_weight > 0 else None
+    loss, logs = state_prediction_loss(pred, batch["next_observations"], logit, batch["rewards"] == 0, recon,
+                                       batch["observations"], true_termination_weight, termination_weight,
+                                       reconstruction_weight)
+    logs = {k: float(v.detach()) if torch.is_tensor(v) else float(v) for k, v in logs.items()}
+    if not train:
+        return params, logs, None
+    loss.backward()
+    g = _grads(p)
+    new = _detach(p)
+    logs["learning_rate"] = _adam(new, g, opt, lr0, decay_steps)
+    return new, logs, g

@@ -286,3 +286,81 @@ def test_initial_observation_decoder_matches_oracle_and_loads_from_reference_fil
     np.testing.assert_allclose(d.sample(n, seed=77).cpu().numpy(), ref(z), rtol=1e-4, atol=1e-4)
     a, b = d.sample(n, seed=78), d.sample(n, seed=78)
     assert torch.equal(a, b) and not torch.equal(a, d.sample(n, seed=79))
+
+
+@pytest.mark.parametrize("T,rows", [(6, 64), (40, 256)], ids=["T6_B64", "T40_B256"])
+def test_multistep_predictor_steps_match_oracle(T, rows):
+    """Back-propagation through time of the scanned cell (envmodel/multistep.py) against torch autograd in float64:
+    logs, every gradient leaf of the first step, parameters after three Adam steps, and a forward-only evaluation."""
+    from fqlpop.worldmodel import MULTISTEP, WorldModelTrainer
+    em = _envmodel(21)
+    # a trained cell predicts small residuals; keep the synthetic one contractive so T steps stay O(1)
+    em["state"][f"Dense_{len(HID)}"]["kernel"].mul_(0.1)
+    params, term = em["state"], em["termination"]
+    tr = WorldModelTrainer(MULTISTEP, O, A, HID, rows, steps=100, params=_np(params), termination_params=_np(term),
+                           termination_hidden_dims=THID, sequence_length=T)
+    opt = wmo.new_opt_state(params)
+    keys = ["loss", "next_observation_loss", "termination_loss", "true_termination_loss", "false_termination_loss"]
+
+    def window(seed):
+        g = torch.Generator().manual_seed(seed)
+        obs = torch.randn(rows, T, O, generator=g, dtype=torch.float64)
+        return {"observations": obs, "actions": torch.rand(rows, T, A, generator=g, dtype=torch.float64) * 2 - 1,
+                "next_observations": obs + 0.05 * torch.randn(rows, T, O, generator=g, dtype=torch.float64),
+                "rewards": -(torch.rand(rows, T, generator=g) >= 0.1).to(torch.float64)}
+
+    for step in range(3):
+        batch = window(30 + step)
+        params, want, g = wmo.multistep_step(params, opt, batch, term, lr0=1e-3, decay_steps=100)
+        got = tr.step(_f32(batch), train=True)
+        _logs_close(got, want, keys)
+        if step == 0:  # fp32 sums over T*B rows through T chained steps: 5e-5 of the leaf's scale at T=6, 3e-4 at T=40
+            _check_tree(tr.grads(), g, 5e-5 if T <= 8 else 3e-4, "grad")
+    _check_params(tr.params(), params, 1e-3)
+    batch = window(99)
+    _, want, _ = wmo.multistep_step(_t64(tr.params()), None, batch, term, lr0=1e-3, decay_steps=100, train=False)
+    _logs_close(tr.step(_f32(batch), train=False), want, keys)
+
+
+def test_multistep_trainer_checkpoint_loads_as_rollout_model(tmp_path):
+    """StatePredictorTrainer with the MultistepStatePredictor on MultistepLoader windows (1000-step episodes): the loss
+    falls, and the checkpoint (params/ScanCell_0/cell, the reference's nesting) loads through load_model("multistep")."""
+    from functools import partial
+    from envmodel.config import TrainerConfig
+    from envmodel.loss import state_prediction_loss
+    from envmodel.multistep import MultistepStatePredictor
+    from envmodel.state_predictor_trainer import StatePredictorTrainer
+    from utils.data_loader import MultistepLoader
+    from utils.envmodel import load_model, save_model
+    g = torch.Generator().manual_seed(1)
+    N = 4000  # four episodes
+    act = torch.rand(N, A, generator=g) * 2 - 1
+    W = torch.randn(O + A, O, generator=g) / 8
+    obs = torch.zeros(N, O)
+    nxt = torch.zeros(N, O)
+    for ep in range(4):
+        o = 0.5 * torch.randn(O, generator=g)
+        for i in range(ep * 1000, (ep + 1) * 1000):
+            obs[i] = o
+            o = 0.9 * o + 0.1 * torch.tanh(torch.cat([o, act[i]]) @ W)
+            nxt[i] = o
+    data = {"observations": obs.numpy(), "actions": act.numpy(), "next_observations": nxt.numpy(),
+            "rewards": -np.ones(N, np.float32)}
+    np.random.seed(2)
+    cfg = TrainerConfig(steps=120, env_name="synthetic-env", model="multistep", val_batches=1, batch_size=32,
+                        sequence_length=8, model_config={"hidden_dims": (64, 64)}, save_directory=tmp_path)
+    loss = partial(state_prediction_loss, true_termination_weight=30.0, termination_weight=0.0, reconstruction_weight=0.0)
+    st = StatePredictorTrainer(MultistepStatePredictor(O, A, (64, 64)), MultistepLoader(data, sequence_length=8),
+                               MultistepLoader(data, sequence_length=8), loss, cfg)
+    first = st._validate(0)["next_observation_loss"]
+    st.train()
+    assert st.last_validation["next_observation_loss"] < first / 3
+    tree = st.state.params
+    assert set(tree["params"]) == {"ScanCell_0"} and "Dense_0" in tree["params"]["ScanCell_0"]["cell"]
+    save_model(tree, tmp_path, "synthetic-env", "multistep", cfg.model_config)
+    sp = load_model(tmp_path, "synthetic-env", "multistep", {k: v[:4] for k, v in data.items()})
+    pred, _ = sp(data["observations"][:4], data["actions"][:4])
+    want = orc.state_predictor_apply(_t64(tree["params"]["ScanCell_0"]["cell"]),
+                                     torch.as_tensor(data["observations"][:4], dtype=torch.float64),
+                                     torch.as_tensor(data["actions"][:4], dtype=torch.float64)).numpy()
+    assert np.abs(pred - want).max() < 3e-2  # the rollout kernels multiply in bf16
