@@ -39,11 +39,10 @@ __global__ void __launch_bounds__(256) wm_gemm_kernel(const float* __restrict__ 
   const int kbeg = blockIdx.z * k_chunk;
   K = min(K, kbeg + k_chunk);
   C += blockIdx.z * c_split_stride;
-  for (int k0 = kbeg; k0 < K; k0 += kWmBK) {
-    const int kt = min(kWmBK, K - k0);
-    float ra[16], rb[16];
+  float ra[16], rb[16];
+  auto load_round = [&](int k0) {  // every global load of a round is issued before anything consumes one
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {  // issue every global load of the round before the first shared store
+    for (int i = 0; i < 16; ++i) {
       const int e = tid + i * 256;
       const int am = TA ? (e & 31) : (e >> 7), ak = TA ? (e >> 5) : (e & 127);
       const int bk = TB ? (e & 127) : (e >> 5), bn = TB ? (e >> 7) : (e & 31);
@@ -51,6 +50,10 @@ __global__ void __launch_bounds__(256) wm_gemm_kernel(const float* __restrict__ 
       ra[i] = (gm < M && gka < K) ? (TA ? A[(long long)gka * lda + gm] : A[(long long)gm * lda + gka]) : 0.f;
       rb[i] = (gkb < K && gn < N) ? (TB ? B[(long long)gn * ldb + gkb] : B[(long long)gkb * ldb + gn]) : 0.f;
     }
+  };
+  if (kbeg < K) load_round(kbeg);
+  for (int k0 = kbeg; k0 < K; k0 += kWmBK) {
+    const int kt = min(kWmBK, K - k0);
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
       const int e = tid + i * 256;
@@ -58,6 +61,7 @@ __global__ void __launch_bounds__(256) wm_gemm_kernel(const float* __restrict__ 
       Bs[TB ? (e & 127) : (e >> 5)][TB ? (e >> 7) : (e & 31)] = rb[i];
     }
     __syncthreads();
+    if (k0 + kWmBK < K) load_round(k0 + kWmBK);  // next round's loads fly while this round is multiplied
 #pragma unroll 8
     for (int k = 0; k < kt; ++k) {
       const float b = Bs[k][tx];
@@ -85,20 +89,45 @@ __global__ void __launch_bounds__(256) wm_gemm_kernel(const float* __restrict__ 
 // out[n] = sum_m X[m][n] (* Y[m][n]): bias gradients and the LayerNorm scale / bias gradients. One thread per column.
 // (both at once for the LayerNorm: out = sum X, out_xy = sum X * Y). blockIdx.y = row slice (rows_per_slice rows each,
 // its sums go to out + y * N: partials for wm_reduce_kernel when gridDim.y > 1).
-__global__ void wm_colsum_kernel(const float* __restrict__ X, const float* __restrict__ Y, int ld, int M, int N,
-                                 float* __restrict__ out, float* __restrict__ out_xy, int rows_per_slice) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= N) return;
+__global__ void __launch_bounds__(256) wm_colsum_kernel(const float* __restrict__ X, const float* __restrict__ Y, int ld,
+                                                        int M, int N, float* __restrict__ out,
+                                                        float* __restrict__ out_xy, int rows_per_slice) {
+  // 32 columns x 8 row lanes per CTA: row lane ty sums rows m0 + ty, m0 + ty + 8, ... (loads of a warp are 128 contiguous
+  // bytes, 8 independent accumulation chains per column), then the 8 partials are added in lane order.
+  __shared__ float sm[2][8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int n = blockIdx.x * 32 + tx;
   const int m0 = blockIdx.y * rows_per_slice, m1 = min(M, m0 + rows_per_slice);
   float s = 0.f, sxy = 0.f;
-#pragma unroll 8
-  for (int m = m0; m < m1; ++m) {
-    const float x = X[(long long)m * ld + n];
-    s += x;
-    if (Y) sxy += x * Y[(long long)m * ld + n];
+  if (n < N) {
+    for (int mb = m0 + ty; mb < m1; mb += 256) {  // 32 rows per round, all loads of a round independent
+      float x[32], y[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const int m = mb + 8 * i;
+        x[i] = m < m1 ? X[(long long)m * ld + n] : 0.f;
+        y[i] = (Y && m < m1) ? Y[(long long)m * ld + n] : 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        s += x[i];
+        sxy += x[i] * y[i];
+      }
+    }
   }
-  out[(long long)blockIdx.y * N + n] = s;
-  if (Y) out_xy[(long long)blockIdx.y * N + n] = sxy;
+  sm[0][ty][tx] = s;
+  sm[1][ty][tx] = sxy;
+  __syncthreads();
+  if (ty == 0 && n < N) {
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      a += sm[0][k][tx];
+      b += sm[1][k][tx];
+    }
+    out[(long long)blockIdx.y * N + n] = a;
+    if (Y) out_xy[(long long)blockIdx.y * N + n] = b;
+  }
 }
 
 // out[i] = sum_s part[s][i], slices added in index order
@@ -255,6 +284,7 @@ __global__ void __launch_bounds__(256) wm_state_loss_kernel(const float* __restr
   for (int r = blockIdx.x * 256 + threadIdx.x; r < rows; r += gridDim.x * 256) {
     const long long src = T > 1 ? (long long)(r % B) * T + r / B : r;
     float se = 0.f;
+#pragma unroll 7
     for (int j = 0; j < O; ++j) {
       const float d = pred[(long long)r * O + j] - next_obs[src * O + j];
       se += d * d;
@@ -456,7 +486,7 @@ struct Launcher {
   // slices > 1: out / out_xy receive [slices][N] partials
   void colsum(const float* X, const float* Y, int ld, int M, int N, float* out, float* out_xy, int slices = 1) {
     dim3 grid((N + 31) / 32, slices);
-    wm_colsum_kernel<<<grid, 32, 0, cur>>>(X, Y, ld, M, N, out, out_xy, (M + slices - 1) / slices);
+    wm_colsum_kernel<<<grid, 256, 0, cur>>>(X, Y, ld, M, N, out, out_xy, (M + slices - 1) / slices);
     ++n;
   }
   void reduce(const float* part, int S, long long cnt, float* out) {
