@@ -213,3 +213,65 @@ def test_cluster_and_single_cta_kernels_agree_over_steps(monkeypatch):
     for t0, t1 in zip(c0 + a0, c1 + a1):
         for name, x, y in _leaf_pairs(t0, {k: {kk: torch.as_tensor(vv) for kk, vv in v.items()} for k, v in t1.items()}):
             assert np.abs(x - y).max() <= 5 * 2.2 * cfg.lr, name
+
+
+@pytest.mark.parametrize("B,P,active", [(192, 2, None), (1024, 2, None), (64, 3, None), (256, 6, [0, 2, 5]), (256, 5, None)],
+                         ids=["ragged_B192", "cube_double_B1024", "small_B64", "active_subset", "ragged_group_P5"])
+def test_update_edge_shapes_match_oracle(B, P, active):
+    """Batch sizes that do not fill a 128-row tile (192, 64), the B=1024 configuration of BASELINE config 5, a population
+    that does not fill the last member group (5 with groups of 4), and a pruned population (successive halving leaves
+    members inactive): losses / info of every ACTIVE member against the oracle, parameters inside the Adam bound, and
+    every bit of an INACTIVE member's state untouched."""
+    from fqlpop.population import INFO_KEYS, Population
+    O, A = (37, 5) if B == 1024 else (28, 5)
+    cfg = orc.FQLConfig(ob_dim=O, action_dim=A, batch_size=B)
+    alphas = list(np.logspace(np.log10(3), np.log10(1000), P))
+    seeds = list(range(40, 40 + P))
+    states = [orc.init_state(s, cfg) for s in seeds]
+    g = torch.Generator().manual_seed(6)
+    for st in states:
+        for net in st["params"]:
+            for name, leaf in orc.tree_leaves(st["params"][net]):
+                if name.endswith("bias"):
+                    leaf.add_(0.05 * torch.randn(leaf.shape, generator=g))
+    batches, noises = _make_case(P, cfg, seed=3)
+    pop = Population(_cfg_dict(cfg), alphas, seeds)
+    _load_population(pop, states)
+    _bind(pop, batches, noises)
+    members = list(range(P)) if active is None else active
+    if active is not None:
+        pop.set_active(active)
+    before = {p: {net: pop.get_tree(p, net, "params") for net in ("critic", "actor_bc_flow", "actor_onestep_flow")}
+              for p in range(P) if p not in members}
+    pop.step(1)
+    info = pop.info(with_grad_stats=False)
+    for p in members:
+        new_e, info_e, _ = orc.update(states[p], batches[p], noises[p], cfg, alphas[p], emulate_bf16=True, return_grads=True)
+        for i, k in enumerate(INFO_KEYS):
+            if k.startswith("grad/"):
+                continue
+            got, want = float(info[p, i]), info_e[k]
+            assert abs(got - want) <= 5e-3 * max(1.0, abs(want)), f"B={B} member {p} {k}: cuda {got} oracle {want}"
+        for net in ("critic", "actor_bc_flow", "actor_onestep_flow"):
+            for name, a, b in _leaf_pairs(pop.get_tree(p, net, "params"), new_e["params"][net], net):
+                assert np.abs(a - b).max() <= 2.2 * cfg.lr, f"B={B} member {p} params {name}"
+                assert float((np.abs(a - b) < 0.2 * cfg.lr).mean()) > 0.97, f"B={B} member {p} params {name}"
+    for p, trees in before.items():
+        for net, tree in trees.items():
+            after = pop.get_tree(p, net, "params")
+            for layer in tree:
+                for leaf in tree[layer]:
+                    assert np.array_equal(tree[layer][leaf], after[layer][leaf]), f"inactive member {p} {net}/{layer}/{leaf} changed"
+    steps, _ = pop.get_counters()
+    assert list(steps) == [1 if p in members else 0 for p in range(P)]
+    pop.close()
+
+
+def test_batch_size_must_be_a_multiple_of_64():
+    """Documented limit of the weight-gradient kernels; the reference's batch sizes (256, 1024) satisfy it. It must fail
+    loudly at create time, not silently pad."""
+    from fqlpop._lib import FqlPopError
+    from fqlpop.population import Population
+    cfg = orc.FQLConfig(ob_dim=28, action_dim=5, batch_size=200)
+    with pytest.raises(FqlPopError, match="multiple of 64"):
+        Population(_cfg_dict(cfg), [3.0], [0])
