@@ -376,28 +376,65 @@ def main():
     host[:, 2 * O:2 * O + A].clamp_(-1, 1)
     host[:, -2] = -1.0
     host[:, -1] = 1.0
-    stage = torch.empty(P * B, row, device=dev)
+    # Two-slot pipeline, as a training loop over host data would run it: step i's H2D is issued on a copy stream while
+    # step i-1 computes, step i's info block comes back by an async D2H into pinned memory and is READ (after its
+    # event) while step i+1 runs. Every step still moves its own inputs H2D and its own result D2H inside the timed region.
+    stage = [torch.empty(P * B, row, device=dev) for _ in range(2)]
     d_obs, d_nxt = torch.empty(P * B, O, device=dev), torch.empty(P * B, O, device=dev)
     d_act, d_rew, d_mask = torch.empty(P * B, A, device=dev), torch.empty(P * B, device=dev), torch.empty(P * B, device=dev)
     pop.set_dataset(d_obs, d_act, d_nxt, d_rew, d_mask)
     pop.set_noise(indices=torch.arange(P * B).view(P, B))
-    info_host = np.zeros((P, 16), np.float32)
+    info_pinned = [torch.zeros(P, 16).pin_memory() for _ in range(2)]
+    copy_stream = torch.cuda.Stream(device=dev)
+    main_stream = torch.cuda.current_stream(dev)
+    ev_h2d = [torch.cuda.Event() for _ in range(2)]
+    ev_free = [torch.cuda.Event() for _ in range(2)]
+    ev_info = [torch.cuda.Event() for _ in range(2)]
+    state = {"i": 0, "read": 0.0}
+
+    def issue_h2d(slot):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(ev_free[slot])
+            stage[slot].copy_(host, non_blocking=True)
+            ev_h2d[slot].record(copy_stream)
+
+    for slot in range(2):
+        ev_free[slot].record(main_stream)
+    issue_h2d(0)
 
     def e2e_step():
-        stage.copy_(host, non_blocking=True)
-        d_obs.copy_(stage[:, :O]); d_nxt.copy_(stage[:, O:2 * O]); d_act.copy_(stage[:, 2 * O:2 * O + A])
-        d_rew.copy_(stage[:, -2]); d_mask.copy_(stage[:, -1])
+        i = state["i"]
+        slot = i & 1
+        main_stream.wait_event(ev_h2d[slot])
+        st = stage[slot]
+        d_obs.copy_(st[:, :O]); d_nxt.copy_(st[:, O:2 * O]); d_act.copy_(st[:, 2 * O:2 * O + A])
+        d_rew.copy_(st[:, -2]); d_mask.copy_(st[:, -1])
+        ev_free[slot].record(main_stream)
         pop.step(1)
-        return pop.info()  # D2H + sync
+        pop.info_async(info_pinned[slot])
+        ev_info[slot].record(main_stream)
+        issue_h2d(slot ^ 1)                       # next step's inputs travel while this step computes
+        if i > 0:                                 # read the previous step's result while this one runs
+            ev_info[slot ^ 1].synchronize()
+            state["read"] += float(info_pinned[slot ^ 1][0, 0])
+        state["i"] = i + 1
+
+    def e2e_drain():
+        last = (state["i"] - 1) & 1
+        ev_info[last].synchronize()
+        state["read"] += float(info_pinned[last][0, 0])
+        return info_pinned[last].numpy()
 
     for _ in range(args.warmup):
         e2e_step()
+    e2e_drain()
     barrier()
     e2e_steps = max(10, args.steps // 2)
     t0 = time.perf_counter()
     e0.record()
     for _ in range(e2e_steps):
-        info_host = e2e_step()
+        e2e_step()
+    info_host = e2e_drain()
     e1.record()
     torch.cuda.synchronize()
     t = torch.tensor([e0.elapsed_time(e1)], device=dev)

@@ -147,6 +147,14 @@ extern "C" int fqlpop_info(void* h, float* out_host, int32_t with_grad_stats, vo
   if (e != cudaSuccess) return fail(std::string("fqlpop_info: ") + cudaGetErrorString(e));
   return 0;
 }
+extern "C" int fqlpop_info_async(void* h, float* out_pinned, void* stream) {
+  POP(h);
+  if (!out_pinned) return fail("null output");
+  cudaError_t e = cudaMemcpyAsync(out_pinned, P->info, sizeof(float) * P->c.P * fqlpop::kInfoSlots,
+                                  cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(std::string("fqlpop_info_async: ") + cudaGetErrorString(e));
+  return 0;
+}
 extern "C" int fqlpop_leaf(void* h, int32_t net, int32_t layer, int32_t kind, int32_t which, int32_t member,
                            float* host, int32_t to_host) {
   POP(h);

@@ -49,6 +49,7 @@ lib.fqlpop_set_active.argtypes = [_vp, _vp, ctypes.c_int32]
 lib.fqlpop_step.argtypes = [_vp, ctypes.c_int32, _vp]
 lib.fqlpop_total_loss.argtypes = [_vp, _vp]
 lib.fqlpop_info.argtypes = [_vp, _vp, ctypes.c_int32, _vp]
+lib.fqlpop_info_async.argtypes = [_vp, _vp, _vp]
 lib.fqlpop_leaf.argtypes = [_vp] + [ctypes.c_int32] * 5 + [_vp, ctypes.c_int32]
 lib.fqlpop_refresh_shadow.argtypes = [_vp, _vp]
 lib.fqlpop_counters.argtypes = [_vp, _vp, _vp, ctypes.c_int32]
@@ -169,6 +170,13 @@ class Population:
         s = torch.cuda.current_stream(self.device).cuda_stream
         check(lib.fqlpop_info(self._h, out.ctypes.data, int(with_grad_stats), s), "fqlpop_info")
         return out
+
+    def info_async(self, out_pinned: torch.Tensor, stream: Optional[torch.cuda.Stream] = None):
+        """Enqueue the copy of the info block into `out_pinned` ([P, INFO_SLOTS] float32, pinned) without waiting; record
+        an event on the stream afterwards and synchronise on it before reading."""
+        assert out_pinned.is_pinned() and out_pinned.dtype == torch.float32 and out_pinned.numel() == self.P * INFO_SLOTS
+        s = (stream or torch.cuda.current_stream(self.device)).cuda_stream
+        check(lib.fqlpop_info_async(self._h, out_pinned.data_ptr(), s), "fqlpop_info_async")
 
     def info_dict(self, member: int, with_grad_stats: bool = False) -> Dict[str, float]:
         row = self.info(with_grad_stats)[member]

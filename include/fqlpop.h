@@ -77,6 +77,9 @@ int fqlpop_total_loss(void* handle, void* stream);
 /* Info dict of the last step / loss evaluation: host float [population][16], slots as oracle.INFO_KEYS
  * (13 used). with_grad_stats != 0 also reduces grad/max, grad/min, grad/norm. Synchronises.               */
 int fqlpop_info(void* handle, float* out_host, int32_t with_grad_stats, void* stream);
+/* Same block without the synchronisation: the copy is enqueued on `stream` into PINNED host memory and the caller
+ * waits on its own event -- lets a training loop read step i's info while step i+1 runs.                  */
+int fqlpop_info_async(void* handle, float* out_pinned, void* stream);
 
 /* Parameter / optimizer-state I/O for one member (utils/agent.py:9-41 load_agent, experiment.py:128-141
  * save_agent). net: 0 critic, 1 actor_bc_flow, 2 actor_onestep_flow; kind: 0 kernel [E][in][out], 1 bias,
