@@ -1,12 +1,14 @@
 """Command-line surface of tune_alpha.py / reproduce.py: the same flags, dotted `--agent.*` namespace, defaults and
 store_true behaviour as the reference (/root/reference/argparser.py:9-169). Note `--agent.layer_norm` is a store_true
 flag, so from the CLI it is False unless passed even though AgentConfig defaults to True -- the reference's launch
-scripts always pass it. The world-model training parser of the reference (lines 172-292) is out of scope."""
+scripts always pass it. `get_env_model_argparser` / `build_env_model_config_from_args` mirror the world-model training
+parser (lines 172-292): `--model.*` flags land in TrainerConfig.model_config."""
 import argparse
 from ast import literal_eval
 from dataclasses import fields
 from pathlib import Path
 
+from envmodel.config import TrainerConfig as EnvModelTrainerConfig
 from trainer.config import AgentConfig, TrainerConfig
 
 _TRAINER_FLAGS = [
@@ -74,3 +76,42 @@ def build_config_from_args(args: argparse.Namespace) -> TrainerConfig:
     if isinstance(agent_kwargs.get("value_hidden_dims"), str):
         agent_kwargs["value_hidden_dims"] = literal_eval(agent_kwargs["value_hidden_dims"])
     return TrainerConfig(**trainer_kwargs, agent=AgentConfig(**agent_kwargs))
+
+
+_ENV_MODEL_FLAGS = [
+    ("model", str, "baseline", "The environment model to be used."),
+    ("model.hidden_dims", literal_eval, (128, 256, 128), "The dimension of hidden layers."),
+    ("model.latent_dim", int, 4, "The dimension of latent representation."),
+    ("true_termination_weight", float, 30.0, "Weight for the true class in the termination loss in the env model."),
+    ("termination_weight", float, 1.0, "Weight for the termination loss in the env model."),
+    ("reconstruction_weight", float, 1.0, "Weight for the reconstruction loss in the env model."),
+    ("sequence_length", int, 256, "The length of sequences for the multistep model."),
+    ("steps", int, 20000, "The number of training steps."),
+    ("env_name", str, "cube-single-play-singletask-task2-v0", "The environment task."),
+    ("init_learning_rate", float, 1e-3, "Initial learning rate."),
+    ("seed", int, 0, "Random seed for training."),
+    ("batch_size", int, 256, "Batch size."),
+    ("val_batches", int, 50, "Number of validation batches."),
+    ("data_directory", str, "data/", "Path to a directory where training data is stored."),
+    ("save_directory", str, "exp/", "Path to a directory where model parameters will be saved."),
+]
+
+
+def get_env_model_argparser() -> argparse.ArgumentParser:
+    parser = argparse.ArgumentParser(description="The configurations of the environment model.")
+    for name, typ, default, text in _ENV_MODEL_FLAGS:
+        parser.add_argument(f"--{name}", type=typ, default=default, help=text)
+    return parser
+
+
+def build_env_model_config_from_args(args: argparse.Namespace) -> EnvModelTrainerConfig:
+    model_config, trainer_kwargs = {}, {}
+    for key, value in vars(args).items():
+        if key.startswith("model."):
+            model_config[key[len("model."):]] = value
+        else:
+            trainer_kwargs[key] = value
+    for key in ("save_directory", "data_directory"):
+        trainer_kwargs[key] = Path(trainer_kwargs[key])
+    names = {f.name for f in fields(EnvModelTrainerConfig)}
+    return EnvModelTrainerConfig(**{k: v for k, v in trainer_kwargs.items() if k in names}, model_config=model_config)

@@ -128,3 +128,31 @@ def test_single_experiment_save_and_load_agent(workdir):
     exp.stop()
     exp.agent.close()
     agent2.close()
+
+
+def test_scripts_train_env_models_then_tune_alpha(tmp_path, monkeypatch):
+    """The reference's workflow with its own command lines: train_env_model.py (termination predictor, then the state
+    predictor against it) leaves the env-model files, tune_alpha.py sweeps alpha with evaluations in that world model and
+    leaves checkpoint.pkl + per-experiment logs."""
+    import fql.envs.env_utils as eu
+    monkeypatch.setattr(eu, "SYNTHETIC_ROWS", 8000)
+    import train_env_model
+    import tune_alpha
+    common = ["--env_name", ENV, "--save_directory", str(tmp_path), "--data_directory", str(tmp_path / "nodata")]
+    wm = ["--steps", "60", "--val_batches", "2", "--model.hidden_dims", "(64, 64)"] + common
+    t = train_env_model.main(["--model", "termination_predictor", "--device_sampling"] + wm)
+    assert t.state.step == 60
+    s = train_env_model.main(["--model", "baseline"] + wm)
+    assert set(s.last_validation) >= {"loss", "next_observation_loss", "termination_loss"}
+    root = tmp_path / ENV / "env_models"
+    assert sorted(p.name for p in root.iterdir()) == ["baseline.pt", "baseline_config.yaml", "termination_predictor.pt",
+                                                      "termination_predictor_config.yaml"]
+    trainer = tune_alpha.main(["--number_of_alphas", "3", "--number_of_seeds", "1", "--max_evaluations", "6",
+                               "--steps", "40", "--eval_interval", "20", "--log_interval", "20", "--eval_episodes", "32",
+                               "--agent.layer_norm", "--simulated_evaluations", "--max_episode_steps", "20",
+                               "--strategy", "successive_halving", "--total_evaluations", "6", "--history_length", "1"]
+                              + common)
+    with open(tmp_path / ENV / "checkpoint.pkl", "rb") as f:
+        ck = pickle.load(f)
+    assert set(ck) == {"trainer", "strategy"}
+    assert trainer.strategy.performed_evaluations == 2  # steps 40 / eval_interval 20
