@@ -41,3 +41,37 @@ def test_no_silent_cpu_fallback_without_a_gpu():
     import pytest
     with pytest.raises(_lib.FqlPopError):
         Population(dict(ob_dim=28, action_dim=5), [10.0], [0])
+
+
+def test_argument_errors_come_back_as_status_and_message():
+    """Error behaviour of the boundary: a non-zero status and a message from fqlpop_last_error, never an exception or
+    a crash; checked on the host-only argument validation (no device work)."""
+    lib = ctypes.CDLL(LIB)
+    lib.fqlpop_last_error.restype = ctypes.c_char_p
+    vp = ctypes.c_void_p
+    lib.fqlpop_step.argtypes = [vp, ctypes.c_int32, vp]
+    assert lib.fqlpop_step(None, 1, None) != 0 and lib.fqlpop_last_error()
+    lib.fqlpop_wm_step.argtypes = [vp, ctypes.c_int32] + [vp] * 6
+    assert lib.fqlpop_wm_step(None, 1, None, None, None, None, None, None) != 0
+    assert b"handle" in lib.fqlpop_last_error()
+    lib.fqlpop_decoder_sample.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_uint64, vp, vp]
+    assert lib.fqlpop_decoder_sample(None, 4, None, 0, None, None) != 0
+    hid = (ctypes.c_int32 * 1)(64)
+    out = vp()
+    lib.fqlpop_decoder_create.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(ctypes.c_int32), ctypes.c_int32,
+                                          vp, ctypes.POINTER(vp)]
+    assert lib.fqlpop_decoder_create(8, 0, hid, 28, None, ctypes.byref(out)) != 0   # no hidden layer
+    assert b"hidden" in lib.fqlpop_last_error()
+    from fqlpop.worldmodel import WmConfig
+    lib.fqlpop_wm_num_params.argtypes = [ctypes.POINTER(WmConfig)]
+    lib.fqlpop_wm_num_params.restype = ctypes.c_int64
+    c = WmConfig()
+    c.n_hidden = 0
+    assert lib.fqlpop_wm_num_params(ctypes.byref(c)) == -1
+    c.kind, c.ob_dim, c.action_dim, c.n_hidden = 2, 42, 8, 3
+    for i, h in enumerate((128, 256, 128)):
+        c.hidden[i] = h
+    # multistep shares the state predictor's layout: LayerNorm (2 * 50) + 50*128+128 + 128*256+256 + 256*128+128 + 128*42+42
+    assert lib.fqlpop_wm_num_params(ctypes.byref(c)) == 100 + 6528 + 33024 + 32896 + 5418
+    lib.fqlpop_wm_create.argtypes = [ctypes.POINTER(WmConfig), vp, vp, ctypes.POINTER(vp)]
+    assert lib.fqlpop_wm_create(ctypes.byref(c), None, None, ctypes.byref(out)) != 0   # decay_steps 0 / no parameters
