@@ -303,6 +303,7 @@ struct ChainBuilder {
     finalize_chain(L);
     L->timeline = P->timeline;
     L->tag = (long long)count | ((long long)P->g_off << 8);
+    if (const char* e = getenv("FQLPOP_CHAIN_DEBUG")) L->debug_flags = atoi(e);  // (debug) bit 0: no weight stream
     {  // (debug) FQLPOP_CHAIN_TRACE=1: clock stamps of CTA 0 of chain launch FQLPOP_TRACE_LAUNCH (default 0 = Euler)
       const char* tl = getenv("FQLPOP_TRACE_LAUNCH");
       L->trace = (P->chain_trace && count == (tl ? atoi(tl) : 0) && P->g_off == 0) ? P->chain_trace : nullptr;
@@ -504,7 +505,6 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   if (chain) {
     cb.begin(1);
     cb.euler_job();
-    if (const char* e = getenv("FQLPOP_CHAIN_DEBUG")) cb.L->debug_flags = atoi(e);
     cb.launch(0, s0);
   } else {
     for (int i = 0; i < c.F; ++i) {

@@ -29,8 +29,8 @@ constexpr int kThreads = 192;
 constexpr int kStages = 5;
 constexpr int kActBlockBytes = 128 * 64 * 2;  // one 64-wide k-block of the A operand = 16 KB
 constexpr int kActBytes = 8 * kActBlockBytes;  // 128 KB
-constexpr int kStageBytes = 64 * 128 * 2;      // (64 k) x (128 n) bf16 = 16 KB = two TMA boxes
-constexpr int kBoxBytes = 64 * 64 * 2;
+constexpr int kStageBytes = 32 * 256 * 2;      // (32 k) x (256 n) bf16 = 16 KB = four TMA boxes
+constexpr int kBoxBytes = 64 * 32 * 2;         // 64 n x 32 k
 constexpr int kBarBytes = 256;
 constexpr int kSmemBytes = kActBytes + kActBlockBytes + kStages * kStageBytes + kBarBytes + 1024;
 
@@ -131,14 +131,14 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
         for (int li = 0; li < n_layers; ++li) {
           const RoLayer& Ly = P.layer[li];
           const int batch = Ly.per_member ? member : 0;
-          for (int n0 = 0; n0 < Ly.n_pad; n0 += 128) {
-            const int ncols = min(128, Ly.n_pad - n0);
-            for (int kb = 0; kb < Ly.k_blocks; ++kb) {
+          for (int n0 = 0; n0 < Ly.n_pad; n0 += 256) {
+            const int ncols = min(256, Ly.n_pad - n0);
+            for (int ks = 0; ks < Ly.k_blocks * 2; ++ks) {  // one stage = 32 k x ncols n
               mbar_wait(&empty_bar[stage], phase ^ 1);
               uint8_t* sb = stage_base + stage * kStageBytes;
               mbar_arrive_expect_tx(&full_bar[stage], (ncols / 64) * kBoxBytes);
-              tma_load_3d(sb, &P.maps[li], &full_bar[stage], n0, kb * 64, batch);
-              if (ncols > 64) tma_load_3d(sb + kBoxBytes, &P.maps[li], &full_bar[stage], n0 + 64, kb * 64, batch);
+              for (int b = 0; b < ncols / 64; ++b)
+                tma_load_3d(sb + b * kBoxBytes, &P.maps[li], &full_bar[stage], n0 + 64 * b, ks * 32, batch);
               if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
           }
@@ -159,19 +159,21 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
           mbar_wait(act_ready, it & 1);
           tc_fence_after();
           const uint32_t a_base = Ly.a_from_x0 ? x0_addr : act_addr;
-          for (int n0 = 0; n0 < Ly.n_pad; n0 += 128) {
-            const int ncols = min(128, Ly.n_pad - n0);
+          // 128 x 256 x 16 MMAs (96 % of the tensor pipe's rate against 57 % for 128 x 128, profiles/ubench): a stage holds
+          // 32 k x up to 256 n as 64n x 32k boxes
+          for (int n0 = 0; n0 < Ly.n_pad; n0 += 256) {
+            const int ncols = min(256, Ly.n_pad - n0);
             const uint32_t idesc = make_idesc_bf16(128, (uint32_t)ncols, 0, 1);
-            for (int kb = 0; kb < Ly.k_blocks; ++kb) {
+            for (int ks = 0; ks < Ly.k_blocks * 2; ++ks) {
               mbar_wait(&full_bar[stage], phase);
               tc_fence_after();
-              const uint32_t sa = a_base + kb * kActBlockBytes;
+              const uint32_t sa = a_base + (ks >> 1) * kActBlockBytes + (ks & 1) * 64;
               const uint32_t sb = smem_u32(stage_base + stage * kStageBytes);
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {
+              for (int k = 0; k < 2; ++k) {
                 const uint64_t adesc = make_smem_desc_sw128(sa + k * 32, 16, 1024);
                 const uint64_t bdesc = make_smem_desc_sw128(sb + k * 2048, kBoxBytes, 1024);
-                umma_bf16(tmem_base + n0, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                umma_bf16(tmem_base + n0, adesc, bdesc, idesc, (ks | k) != 0 ? 1u : 0u);
               }
               umma_commit(&empty_bar[stage]);
               if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -576,7 +578,7 @@ struct Program {
       return -1;
     }
     const int i = R->n_layers++;
-    if (encode_tmap_bf16(&R->maps[i], w, N_pad, K_pad, batch, N_pad, ms, 64) != 0) {
+    if (encode_tmap_bf16(&R->maps[i], w, N_pad, K_pad, batch, N_pad, ms, 32) != 0) {
       ok = false;
       if (err) *err = "rollout: cuTensorMapEncodeTiled failed";
     }
