@@ -25,7 +25,7 @@ namespace fqlpop {
 
 namespace {
 
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;  // TMA, MMA, 4 episode warps (own the rows' state), 4 helper warps (share the wide hidden epilogues)
 constexpr int kStages = 5;
 constexpr int kActBlockBytes = 128 * 64 * 2;  // one 64-wide k-block of the A operand = 16 KB
 constexpr int kActBytes = 8 * kActBlockBytes;  // 128 KB
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    mbar_init(act_ready, 128);
+    mbar_init(act_ready, 256);
     mbar_init(layer_done, 1);
     *first_done = INT_MAX;
     *steps_done = 0;
@@ -181,6 +181,47 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
           }
           umma_commit(layer_done);
         }
+      }
+    }
+  } else if (warp >= 6) {
+    // ======================================= helper epilogue =====================================
+    // Same TMEM lane quarter as episode warp (warp - 4); takes the odd 32-column chunks of the bias + activation
+    // epilogue of the plain hidden layers, so a row's 512 columns are split over two threads. Holds no episode state.
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    uint32_t it = 0;
+    mbar_arrive(act_ready);
+    for (int step = 0; step < n_steps; ++step) {
+      if (step >= 2 && ld_volatile_s32(first_done) <= step - 2) break;
+      for (int li = 0; li < n_layers; ++li, ++it) {
+        const RoLayer& Ly = P.layer[li];
+        mbar_wait(layer_done, it & 1);
+        tc_fence_after();
+        if (Ly.kind == RO_HIDDEN && !Ly.ln) {
+          const float* bias = Ly.bias + (Ly.per_member ? (long long)member * Ly.bias_ms : 0);
+          const int nchunks = Ly.n_pad / 32;
+          for (int c = 1; c < nchunks; c += 2) {
+            uint32_t rr[32];
+            tmem_ld32(tmem_row + c * 32, rr);
+            tmem_ld_wait();
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float z = __uint_as_float(rr[j]) + __ldg(bias + c * 32 + j);
+              if (Ly.act == ACT_GELU) {
+                float gp;
+                gelu_fwd(z, v[j], gp);
+              } else {
+                v[j] = fmaxf(z, 0.f);
+              }
+            }
+            st_act32(act, r, c * 32, v);
+          }
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        mbar_arrive(act_ready);
       }
     }
   } else {
@@ -269,7 +310,7 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
         if (Ly.kind == RO_HIDDEN) {
           const int nchunks = Ly.n_pad / 32;
           if (!Ly.ln) {
-            for (int c = 0; c < nchunks; ++c) {
+            for (int c = 0; c < nchunks; c += 2) {  // odd chunks: helper warps
               uint32_t rr[32];
               tmem_ld32(tmem_row + c * 32, rr);
               tmem_ld_wait();
