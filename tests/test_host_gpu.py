@@ -156,3 +156,9 @@ def test_scripts_train_env_models_then_tune_alpha(tmp_path, monkeypatch):
         ck = pickle.load(f)
     assert set(ck) == {"trainer", "strategy"}
     assert trainer.strategy.performed_evaluations == 2  # steps 40 / eval_interval 20
+    # reproduce.py: seed sweep at the default alpha, single-experiment mode (train -> evaluate -> save_agent)
+    import reproduce
+    exp = reproduce.main(["--number_of_seeds", "2", "--single_experiment", "--job_id", "1", "--steps", "20",
+                          "--eval_interval", "10", "--log_interval", "10", "--eval_episodes", "16", "--agent.layer_norm",
+                          "--simulated_evaluations", "--max_episode_steps", "10"] + common)
+    assert exp.current_step == 20
