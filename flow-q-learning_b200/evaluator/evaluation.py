@@ -26,19 +26,22 @@ def supply_rng(f, rng=0):
 
 
 def flatten(d, parent_key="", sep="."):
-    out = {}
-    for k, v in d.items():
-        key = f"{parent_key}{sep}{k}" if parent_key else k
-        if hasattr(v, "items"):
-            out.update(flatten(v, key, sep=sep))
-        else:
-            out[key] = v
-    return out
+    """{"a": {"b": 1}} -> {"a.b": 1} (nested info dicts of an environment step)."""
+    flat, stack = {}, [(parent_key, d)]
+    while stack:
+        prefix, node = stack.pop()
+        for name, value in node.items():
+            path = name if not prefix else f"{prefix}{sep}{name}"
+            if hasattr(value, "items"):
+                stack.append((path, value))
+            else:
+                flat[path] = value
+    return flat
 
 
 def add_to(dict_of_lists, single_dict):
-    for k, v in single_dict.items():
-        dict_of_lists[k].append(v)
+    for name in single_dict:
+        dict_of_lists[name].append(single_dict[name])
 
 
 def evaluate_agent(agent, env, seed: Optional[int] = None, eval_temperature: float = 0):
@@ -53,21 +56,22 @@ def evaluate_agent(agent, env, seed: Optional[int] = None, eval_temperature: flo
 
 
 def evaluate_actor_fn(actor_fn: Callable, env, seed: Optional[int] = None, eval_temperature: float = 0):
+    """Host loop over any Task: all environments step together until every one of them has been done once; an
+    environment contributes its info dict exactly once, at its first done step (later steps carry info["invalid"])."""
     if seed is not None:
         random.seed(seed)
         np.random.seed(seed)
-    stats = defaultdict(list)
-    observations, infos = env.reset(seed=seed)
-    done = np.zeros(len(observations), dtype=bool)
-    transitions = []
-    while not np.all(done):
-        actions = np.clip(np.array(actor_fn(observations=observations, temperature=eval_temperature)), -1, 1)
-        next_observations, _, terminated, truncated, infos = env.step(actions)
-        mask = np.array([info.get("invalid", False) for info in infos], dtype=bool)
-        done = np.logical_or(np.logical_or(terminated, truncated), mask)
-        for i, info in enumerate(infos):
-            if done[i] and not mask[i]:      # the environment's first done step
-                add_to(stats, flatten(info))
-        transitions.append((observations, actions, mask))
-        observations = next_observations
-    return {k: np.mean(v) for k, v in stats.items()}, transitions
+    obs, _ = env.reset(seed=seed)
+    n_envs = len(obs)
+    finished = np.zeros(n_envs, dtype=bool)
+    collected, transitions = defaultdict(list), []
+    while not finished.all():
+        act = np.clip(np.array(actor_fn(observations=obs, temperature=eval_temperature)), -1, 1)
+        nxt, _, terminated, truncated, infos = env.step(act)
+        stale = np.fromiter((bool(i.get("invalid", False)) for i in infos), dtype=bool, count=n_envs)
+        finished = np.asarray(terminated, dtype=bool) | np.asarray(truncated, dtype=bool) | stale
+        for idx in np.flatnonzero(finished & ~stale):
+            add_to(collected, flatten(infos[idx]))
+        transitions.append((obs, act, stale))
+        obs = nxt
+    return {name: np.mean(values) for name, values in collected.items()}, transitions

@@ -22,28 +22,29 @@ class StrategyEvaluator:
             self.experiments[c] = ExperimentFromFile(experiment_config=c, save_directory=self.config.save_directory,
                                                      env_name=self.config.env_name)
 
+    def _round(self, step: int, best: float):
+        """One strategy round at `step`: advance every live candidate's log cursor, score it, feed the strategy.
+        Returns the best score after the round."""
+        interval, episodes = self.config.eval_interval, self.config.eval_episodes
+        self.finished_candidates.update(c for c in self.candidates if self.experiments[c].train(interval))
+        for c in self.candidates:  # strategy.update order = candidate order, as in Trainer.train
+            score = self.experiments[c].evaluate(episodes)
+            best = max(best, score)
+            self.strategy.update(c, score)
+        return best
+
     def evaluate(self) -> dict:
-        best_score = 0.0
-        score_curve = {}
-        current_step = 0
-        while True:
-            for c in self.candidates:
-                if self.experiments[c].train(self.config.eval_interval):
-                    self.finished_candidates.add(c)
-            current_step += self.config.eval_interval
-            score_updated = False
-            for c in self.candidates:
-                score = self.experiments[c].evaluate(self.config.eval_episodes)
-                if score > best_score:
-                    best_score = score
-                    score_updated = True
-                self.strategy.update(c, score)
-            if score_updated or current_step == self.config.steps:
-                score_curve[current_step] = best_score
+        curve, best, step = {}, 0.0, 0
+        live = True
+        while live:
+            step += self.config.eval_interval
+            new_best = self._round(step, best)
+            if new_best > best or step == self.config.steps:  # a point where the incumbent improved, and the last step
+                curve[step] = new_best
+            best = new_best
             self.candidates = self.strategy.sample()
-            if all(c in self.finished_candidates for c in self.candidates):
-                break
-        return score_curve
+            live = not self.finished_candidates.issuperset(self.candidates)
+        return curve
 
     def plot(self):
         import matplotlib.pyplot as plt  # noqa: F401  (optional; absent in this image)
