@@ -162,3 +162,40 @@ def test_scripts_train_env_models_then_tune_alpha(tmp_path, monkeypatch):
                           "--eval_interval", "10", "--log_interval", "10", "--eval_episodes", "16", "--agent.layer_norm",
                           "--simulated_evaluations", "--max_episode_steps", "10"] + common)
     assert exp.current_step == 20
+
+
+def test_checkpoint_sweep_scores_many_agents_in_one_rollout(workdir):
+    """evaluate_checkpoints (the measurement loop of evaluate_success_rate_correlation.py): three saved checkpoints of two
+    experiments scored in one batched rollout equal the one-at-a-time evaluate_agent results with the same seed."""
+    from evaluator.checkpoint_sweep import evaluate_checkpoints, find_experiment, success_rate_correlation
+    from evaluator.evaluation import evaluate_agent
+    from trainer.config import AgentConfig, ExperimentConfig, TrainerConfig
+    from trainer.experiment import Experiment
+    from utils.agent import load_agent
+    save_dir, _ = workdir
+    task = _task(save_dir, n_envs=64, max_steps=12)
+    cfg = TrainerConfig(steps=6, eval_interval=3, log_interval=3, save_directory=save_dir / "ckpt", env_name=ENV,
+                        agent=AgentConfig(batch_size=64))
+    names = []
+    for seed, alpha in ((1, 3.0), (2, 300.0)):
+        exp = Experiment(task, cfg, ExperimentConfig(seed=seed, alpha=alpha))
+        while not exp.train(cfg.eval_interval):
+            exp.save_agent(checkpoint=True)
+        exp.save_agent(checkpoint=True)
+        names.append(exp.experiment_name)
+        exp.stop()
+    root = save_dir / "ckpt"
+    found = find_experiment(root, ENV, 1, "3.0")
+    assert found is not None and found.name == names[0]
+    assert find_experiment(root, ENV, 9, "3.0") is None
+    ckpts = [(root / ENV / names[0], "checkpoint_3"), (root / ENV / names[0], "checkpoint_6"),
+             (root / ENV / names[1], "checkpoint_6")]
+    batched = evaluate_checkpoints(task, ckpts, batch=2, seed=5)     # 2 slots -> two fused launches
+    single = []
+    for directory, filename in ckpts:
+        agent = load_agent(directory, task.sample("train", 1), agent_filename=filename)
+        single.append(evaluate_agent(agent, task, seed=5)[0]["success"])
+    assert batched == pytest.approx(single, abs=1e-6)
+    stats = success_rate_correlation([0.1, 0.4, 0.35, 0.8], [0.2, 0.3, 0.5, 0.9])
+    assert stats["spearman_rho"] == pytest.approx(0.8) and stats["kendall_tau"] == pytest.approx(2 / 3)
+    assert 0.9 < stats["pearson_r"] <= 1.0
