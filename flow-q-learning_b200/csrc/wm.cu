@@ -227,6 +227,30 @@ __global__ void wm_gather_kernel(const float* __restrict__ obs, const float* __r
   if (lane == 0) b_rew[row] = rewards[idx];
 }
 
+// MultistepLoader.sample on the device (utils/data_loader.py:25-47): batch row b draws an episode (Philox slot 0) and a
+// window start inside it (slot 1, uniform in [0, episode_len - T)), then copies the T transitions of the window.
+// One warp per (b, t).
+__global__ void wm_gather_windows_kernel(const float* __restrict__ obs, const float* __restrict__ act,
+                                         const float* __restrict__ next_obs, const float* __restrict__ rewards,
+                                         long long n_rows, int episode_len, int O, int A, int batch, int T,
+                                         unsigned long long seed, const int* __restrict__ step, float* __restrict__ b_obs,
+                                         float* __restrict__ b_act, float* __restrict__ b_next, float* __restrict__ b_rew) {
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= (long long)batch * T) return;
+  const int b = (int)(w / T), t = (int)(w % T);
+  const unsigned long long st = (unsigned long long)*step;
+  const long long episode = philox_index(seed, st, (uint32_t)b, 0u, (uint32_t)(n_rows / episode_len));
+  const long long start = philox_index(seed, st, (uint32_t)b, 1u, (uint32_t)(episode_len - T));
+  const long long src = episode * episode_len + start + t;
+  for (int j = lane; j < O; j += 32) {
+    b_obs[w * O + j] = obs[src * O + j];
+    b_next[w * O + j] = next_obs[src * O + j];
+  }
+  for (int j = lane; j < A; j += 32) b_act[w * A + j] = act[src * A + j];
+  if (lane == 0) b_rew[w] = rewards[src];
+}
+
 // fixed-order block reduction of up to 8 values per thread (256 threads); result valid in thread 0
 template <int NV>
 __device__ __forceinline__ void wm_block_reduce(float (&v)[NV], float (*sm)[NV]) {
@@ -593,20 +617,28 @@ void wm_issue(WmTrainer* t, Launcher& L, int train, int gather, const float* obs
 
 
 constexpr int kWmLossCtas = 128, kWmSplits = 64;
+constexpr int kWmEpisodeLen = 1000;  // OGBench episodes (stride 1000 at utils/data_loader.py:16,30)
 
 // One step of the multistep predictor (envmodel/multistep.py:34-54: nn.scan of the baseline cell over the window, each
 // prediction fed back as the next observation; loss over all T predictions, state_predictor_trainer.py:79-97).
 // Activations are kept TIME-major ([T][B][width] slabs) so that every time step is a plain [B][width] matrix, the frozen
 // termination predictor and the loss run ONCE over all T*B rows, and after back-propagation through time each weight
 // gradient is ONE product over the T*B rows (split-K, slices added in order) instead of T small ones.
-void wm_issue_multistep(WmTrainer* t, Launcher& L, int train, const float* obs, const float* act, const float* next_obs,
-                        const float* rew) {
+void wm_issue_multistep(WmTrainer* t, Launcher& L, int train, int gather, const float* obs, const float* act,
+                        const float* next_obs, const float* rew) {
   const WmConfig& c = t->cfg;
   const WmNet& net = t->net;
   const int B = c.batch, T = c.seq_len, O = c.O, A = c.A, nl = net.n_layers, D0 = net.dims[0], R = t->rows;
   cudaStream_t s = L.s;
   const bool with_term = c.termination_weight > 0.f;
   const float* scale = t->params + net.off_ln_scale;
+  if (gather) {
+    wm_gather_windows_kernel<<<(int)(((long long)R * 32 + 255) / 256), 256, 0, s>>>(
+        t->ds_obs, t->ds_act, t->ds_next, t->ds_rew, t->ds_rows, kWmEpisodeLen, O, A, B, T, c.seed, t->step, t->b_obs,
+        t->b_act, t->b_next, t->b_rew);
+    ++L.n;
+    obs = t->b_obs; act = t->b_act; next_obs = t->b_next; rew = t->b_rew;
+  }
   wm_take_first_kernel<<<(B * O + 255) / 256, 256, 0, s>>>(obs, B, T, O, t->ocur);
   ++L.n;
   for (int ti = 0; ti < T; ++ti) {
@@ -692,7 +724,7 @@ int wm_run(WmTrainer* t, int train, int gather, int repeats, const float* obs, c
     WM_CUDA(cudaStreamCreateWithFlags(&sw, cudaStreamNonBlocking));
     WM_CUDA(cudaStreamCreateWithFlags(&sc, cudaStreamNonBlocking));
     Launcher L{cs, sw, sc, cs};
-    if (t->cfg.kind == WM_MULTISTEP) wm_issue_multistep(t, L, train, obs, act, next_obs, rew);
+    if (t->cfg.kind == WM_MULTISTEP) wm_issue_multistep(t, L, train, gather, obs, act, next_obs, rew);
     else wm_issue(t, L, train, gather, obs, act, next_obs, rew, mask);
     cudaGraph_t graph = nullptr;
     cudaError_t ce = cudaStreamEndCapture(cs, &graph);
@@ -775,8 +807,8 @@ int wm_create_impl(const WmConfig& cfg, const float* params_host, const float* t
           wm_alloc(t, &t->dbuf[1], R * maxdim, err) || wm_alloc(t, &t->dlogit, R, err) ||
           wm_alloc(t, &t->logs, kWmLogs, err) || wm_alloc(t, (float**)&t->step, 2, err) ||
           wm_alloc(t, &t->loss_part, kWmLossCtas * 5, err) || wm_alloc(t, (float**)&t->ticket, 1, err) ||
-          wm_alloc(t, &t->b_obs, (long long)B * cfg.O, err) || wm_alloc(t, &t->b_act, (long long)B * std::max(cfg.A, 1), err) ||
-          wm_alloc(t, &t->b_next, (long long)B * cfg.O, err) || wm_alloc(t, &t->b_rew, B, err);
+          wm_alloc(t, &t->b_obs, R * cfg.O, err) || wm_alloc(t, &t->b_act, R * std::max(cfg.A, 1), err) ||
+          wm_alloc(t, &t->b_next, R * cfg.O, err) || wm_alloc(t, &t->b_rew, R, err);
   if (!rc && cudaMemcpy(t->params, params_host, sizeof(float) * n, cudaMemcpyHostToDevice) != cudaSuccess)
     rc = bad("world model: copying the initial parameters failed");
   if (rc) {
@@ -818,8 +850,9 @@ int wm_set_dataset_impl(WmTrainer* t, const float* obs, const float* act, const 
 }
 
 int wm_train_impl(WmTrainer* t, int n_steps, const float* dropout_mask, cudaStream_t stream, std::string* err) {
-  if (t->cfg.kind == WM_MULTISTEP) {
-    if (err) *err = "world-model train: the multistep predictor takes explicit windows (fqlpop_wm_step)";
+  if (t->cfg.kind == WM_MULTISTEP && t->ds_rows &&
+      (t->ds_rows % kWmEpisodeLen != 0 || t->cfg.seq_len >= kWmEpisodeLen)) {
+    if (err) *err = "world-model train: multistep windows need a dataset of whole 1000-step episodes and seq_len < 1000";
     return 1;
   }
   if (!t->ds_rows) {

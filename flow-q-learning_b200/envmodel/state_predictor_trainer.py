@@ -52,8 +52,6 @@ class StatePredictorTrainer:
         from fqlpop.worldmodel import MULTISTEP, STATE, WorldModelTrainer  # needs libfqlpop.so; no CPU fallback
         from envmodel.multistep import MultistepStatePredictor
         self.multistep = isinstance(model, MultistepStatePredictor)
-        if self.multistep and device_sampling:
-            raise ValueError("the multistep predictor trains on host-sampled windows (MultistepLoader)")
         self.model, self.train_loader, self.val_loader = model, train_loader, val_loader
         self.loss_fn, self.config, self.logger = loss_fn, config, logger
         self.device_sampling = device_sampling
@@ -94,7 +92,10 @@ class StatePredictorTrainer:
     def train(self) -> None:
         step = 0
         if self.device_sampling:
-            self.device_trainer.set_dataset(self.train_loader.dataset)
+            data = self.train_loader.dataset
+            if self.multistep:  # MultistepLoader keeps [episodes, 1000, ...]; the device sampler wants the flat rows back
+                data = {k: np.reshape(v, (-1,) + tuple(np.shape(v)[2:])) for k, v in data.items()}
+            self.device_trainer.set_dataset(data)
         while step < self.config.steps:
             if step % 100 == 0:
                 self._validate(step)

@@ -21,7 +21,7 @@ def main(argv=None):
     parser = get_env_model_argparser()
     parser.add_argument("--use_wandb", action="store_true", help="Log to Weights & Biases (if installed).")
     parser.add_argument("--device_sampling", action="store_true",
-                        help="Keep the training set in HBM and draw batches on the device (baseline / termination_predictor).")
+                        help="Keep the training set in HBM and draw batches (or multistep windows) on the device.")
     args = parser.parse_args(argv)
     use_wandb, device_sampling = args.use_wandb, args.device_sampling
     del args.use_wandb, args.device_sampling
@@ -56,7 +56,7 @@ def main(argv=None):
         logger = wandb.init(name=f"{config.env_name}_{config.model}", project="fql_env_model", config=asdict(config), dir="exp/")
     cls = TerminationPredictorTrainer if config.model == "termination_predictor" else StatePredictorTrainer
     trainer = cls(model=model, train_loader=train_loader, val_loader=val_loader, loss_fn=loss_fn, config=config,
-                  logger=logger, device_sampling=device_sampling and config.model != "multistep")
+                  logger=logger, device_sampling=device_sampling)
     trainer.train()
     path = save_model(trainer.state.params, config.save_directory, config.env_name, config.model, config.model_config)
     print(f"saved {path}; validation: {trainer.last_validation}")

@@ -175,7 +175,8 @@ typedef struct {
                                        * (envmodel/multistep.py:34-54: the kind-0 cell scanned over a window; batch   *
                                        * arrays are then obs[batch][T][ob_dim] (only t = 0 is read), act[batch][T]    *
                                        * [action_dim], next_obs[batch][T][ob_dim], rewards[batch][T]; same flat       *
-                                       * parameter vector as kind 0; explicit windows only, no fqlpop_wm_train)       */
+                                       * parameter vector as kind 0; fqlpop_wm_train draws an episode and a window start   *
+                                       * per batch row from a resident dataset of whole 1000-step episodes)            */
   int32_t ob_dim, action_dim, batch;
   int32_t n_hidden, hidden[8];
   int32_t term_n_hidden, term_hidden[8]; /* kind 0, termination_weight > 0: the frozen termination predictor      */

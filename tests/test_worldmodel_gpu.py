@@ -364,3 +364,25 @@ def test_multistep_trainer_checkpoint_loads_as_rollout_model(tmp_path):
                                      torch.as_tensor(data["observations"][:4], dtype=torch.float64),
                                      torch.as_tensor(data["actions"][:4], dtype=torch.float64)).numpy()
     assert np.abs(pred - want).max() < 3e-2  # the rollout kernels multiply in bf16
+
+
+def test_resident_window_sampling_matches_explicit_windows():
+    """fqlpop_wm_train for the multistep predictor: batch row b of optimiser step s takes episode Philox(seed, s, b, 0) %
+    n_episodes and window start Philox(seed, s, b, 1) % (1000 - T); the same windows fed explicitly give identical bits."""
+    from fqlpop.worldmodel import MULTISTEP, WorldModelTrainer
+    T, rows, n_ep = 12, 32, 3
+    em = _envmodel(31)
+    em["state"][f"Dense_{len(HID)}"]["kernel"].mul_(0.1)
+    data = _f32(_batch(8, rows=n_ep * 1000))
+    kw = dict(steps=20, params=_np(em["state"]), termination_params=_np(em["termination"]), termination_hidden_dims=THID,
+              seed=77, sequence_length=T)
+    a = WorldModelTrainer(MULTISTEP, O, A, HID, rows, **kw)
+    b = WorldModelTrainer(MULTISTEP, O, A, HID, rows, **kw)
+    a.set_dataset(data)
+    a.train(3)
+    for step in range(3):
+        idx = np.stack([phx.index(77, step, r, 0, n_ep) * 1000 + phx.index(77, step, r, 1, 1000 - T) + np.arange(T)
+                        for r in range(rows)])                       # [rows, T]
+        b.step({k: v[idx] for k, v in data.items()}, train=True)
+    assert np.array_equal(a.export(0), b.export(0))
+    assert a.logs()[11] == 3.0
