@@ -1598,14 +1598,17 @@ cudaError_t chain_init() {
   return cudaFuncSetAttribute(fql_chain2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
 }
 
+constexpr int kClusterMaxMembers = 10;
+
 // The cluster kernel covers the production shape: every hidden layer 512 wide, reductions of 64 (first layer) or 512.
 static bool chain2_eligible(const ChainLaunch& L) {
-  // 0 (default): single-CTA kernel; 1: cluster kernel for every chain; 2: cluster kernel for the Euler chain only.
-  // Measured on B200 (16 members): the cluster kernel cuts a chain's latency 1.4-1.7x but costs
-  // ~20% more SM time, and the step is bound by SM time + optimizer HBM time, so the default stays 0. Read at every
-  // launch (graph capture time), so a process can build populations with either kernel.
+  // FQLPOP_CHAIN2 = 0: single-CTA kernel; 1: cluster kernel for every chain; 2: cluster kernel for the Euler chain only;
+  // unset: by population size. The cluster kernel cuts a chain's latency 1.4-1.7x but costs ~20 % more SM time: with few
+  // active members the step is latency-bound and it wins (4 members 6.5k -> 9.8k updates/s, 8 members 11.8k -> 15.3k), from
+  // ~12 members on the GPU is saturated and SM time decides (16 members 17.2k vs 16.2k). Successive halving walks through
+  // exactly these sizes. Read at every launch (graph capture time; pruning the population re-captures the graphs).
   const char* e = getenv("FQLPOP_CHAIN2");
-  const int mode = e ? atoi(e) : 0;
+  const int mode = e ? atoi(e) : ((L.population_active > 0 && L.population_active <= kClusterMaxMembers) ? 1 : 0);
   if (!mode) return false;
   if (mode == 2 && L.job[0].iters <= 1) return false;  // 2: only the Euler chain (the step's longest serial path)
   for (int i = 0; i < L.num_jobs; ++i) {

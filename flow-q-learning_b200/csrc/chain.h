@@ -77,6 +77,7 @@ struct ChainLaunch {
   int n_virtual;            // active virtual members (grid = sum_jobs m_tiles * n_virtual)
   const int* member_list;   // (dev) [n_virtual] virtual member ids
   int debug_flags;          // (debug) bit 0: no weight TMA / no stage waits (timing of the bare MMA stream; results are garbage)
+  int population_active;    // active members of the whole population on this GPU (picks the kernel: see chain2_eligible)
   int stages;               // weight stages (set by launch_chain: 5, or 3 when the epilogue stages tensors through smem)
   long long* trace;         // (dev, debug) clock64 stamps of CTA 0: [0,4096) MMA thread, [4096,8192) epilogue thread 0
   long long* timeline;      // (dev, debug) [0] = record counter; records of 4 words from [8]: start ns, end ns, smid, tag

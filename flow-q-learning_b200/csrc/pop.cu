@@ -304,6 +304,7 @@ struct ChainBuilder {
     L->timeline = P->timeline;
     L->tag = (long long)count | ((long long)P->g_off << 8);
     if (const char* e = getenv("FQLPOP_CHAIN_DEBUG")) L->debug_flags = atoi(e);  // (debug) bit 0: no weight stream
+    L->population_active = (int)P->h_members.size();
     {  // (debug) FQLPOP_CHAIN_TRACE=1: clock stamps of CTA 0 of chain launch FQLPOP_TRACE_LAUNCH (default 0 = Euler)
       const char* tl = getenv("FQLPOP_TRACE_LAUNCH");
       L->trace = (P->chain_trace && count == (tl ? atoi(tl) : 0) && P->g_off == 0) ? P->chain_trace : nullptr;
