@@ -627,12 +627,14 @@ void destroy_groups(Plan* pl) {
   pl->groups.clear();
 }
 
-// Splits the active list into member groups of FQLPOP_GROUP_SIZE members (default 4; 0 = one lockstep group).
+// Splits the active list into member groups of FQLPOP_GROUP_SIZE members (0 = one lockstep group). Default: 4, or 2 while
+// at most 10 members are active (small populations are latency-bound: more, smaller graphs in flight; measured 4 members
+// 9.8k -> 10.5k updates/s, 8 members 15.3k -> 15.6k; from 12 members on the group size is within +-3 %).
 int make_groups(Population* P, std::string* err) {
   Plan* pl = P->plan;
   destroy_groups(pl);
   const int n = (int)P->h_members.size();
-  int gs = 4;
+  int gs = n <= 10 ? 2 : 4;
   if (const char* e = getenv("FQLPOP_GROUP_SIZE")) gs = atoi(e);
   if (gs <= 0 || gs > n) gs = n;
   const int G = (n + gs - 1) / gs;
