@@ -1598,7 +1598,7 @@ cudaError_t chain_init() {
   return cudaFuncSetAttribute(fql_chain2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
 }
 
-constexpr int kClusterMaxMembers = 10;
+constexpr int kClusterMaxMembers = 11;
 
 // The cluster kernel covers the production shape: every hidden layer 512 wide, reductions of 64 (first layer) or 512.
 static bool chain2_eligible(const ChainLaunch& L) {
