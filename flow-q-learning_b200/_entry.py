@@ -62,16 +62,56 @@ def run_one(task, config, experiment_config: ExperimentConfig, after_round: Call
     return experiment
 
 
+def init_distributed():
+    """One process per GPU under torchrun: torchrun only sets RANK / WORLD_SIZE / LOCAL_RANK, so the process group the
+    Trainer shards over is created here (NCCL on GPUs, gloo without). Returns True when this call created the group."""
+    import os
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world <= 1:
+        return False
+    import torch
+    import torch.distributed as dist
+    if dist.is_initialized():
+        return False
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if torch.cuda.is_available():
+        local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        dist.init_process_group("gloo")
+    return True
+
+
+def checkpoint_path(config, rank: int):
+    """Rank 0 keeps the reference's file name; the other ranks write their shard (their members' weights and optimiser
+    state) beside it."""
+    name = "checkpoint.pkl" if rank == 0 else f"checkpoint.rank{rank}.pkl"
+    return config.save_directory / config.env_name / name
+
+
 def run_population(args, task, config, population: List[ExperimentConfig]):
-    """Population mode: resume from <save>/<env>/checkpoint.pkl if present, train, write the checkpoint back (rank 0)."""
-    path = config.save_directory / config.env_name / "checkpoint.pkl"
+    """Population mode: resume from <save>/<env>/checkpoint[.rankR].pkl if present, train, write this rank's shard back."""
+    created = init_distributed()
+    try:
+        return _run_population(args, task, config, population)
+    finally:
+        if created:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+def _run_population(args, task, config, population: List[ExperimentConfig]):
+    import os
+    rank = int(os.environ.get("RANK", "0")) if int(os.environ.get("WORLD_SIZE", "1")) > 1 else 0
+    path = checkpoint_path(config, rank)
     saved = pickle.loads(path.read_bytes()) if path.exists() else {}
     kw = dict(population=population, total_evaluations=args.total_evaluations, state_dict=saved.get("strategy"))
     strategy = (SuccessiveHalving(fraction=args.fraction, history_length=args.history_length, **kw)
                 if args.strategy == "successive_halving" else Identity(**kw))
     trainer = Trainer(task, strategy, config, state_dict=saved.get("trainer"))
     trainer.train(max_evaluations=args.max_evaluations)
-    if trainer.rank == 0:
-        path.parent.mkdir(parents=True, exist_ok=True)
-        path.write_bytes(pickle.dumps({"trainer": trainer.state_dict(), "strategy": trainer.strategy.state_dict()}))
+    path = checkpoint_path(config, trainer.rank)
+    path.parent.mkdir(parents=True, exist_ok=True)
+    path.write_bytes(pickle.dumps({"trainer": trainer.state_dict(), "strategy": trainer.strategy.state_dict()}))
     return trainer

@@ -1367,9 +1367,12 @@ __global__ void __launch_bounds__(kThreads, 1) fql_chain_kernel(const __grid_con
             for (int ks = 0; ks < k_steps; ++ks) {
               mbar_wait(&empty_bar[stage], phase ^ 1);
               uint8_t* sb = stage_base + stage * kStageBytes;
-              if (L.debug_flags & 1) {  // (debug) no weight stream: the MMAs run on whatever the stage holds
+#ifdef FQLPOP_DEBUG_SWITCHES
+              if (L.debug_flags & 1) {  // (make TRACE=1 only) no weight stream: the MMAs run on whatever the stage holds
                 mbar_arrive(&full_bar[stage]);
-              } else if (MODE == 0) {
+              } else
+#endif
+              if (MODE == 0) {
                 // W[k][n], n contiguous: boxes of 64 n x 32 k
                 mbar_arrive_expect_tx(&full_bar[stage], ncols * kStageK * 2);
                 for (int b = 0; b < ncols / 64; ++b)
@@ -1595,7 +1598,9 @@ cudaError_t chain_init() {
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(fql_chain2_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(fql_chain2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  e = cudaFuncSetAttribute(fql_chain2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  if (e != cudaSuccess) return e;
+  return chain16_init();
 }
 
 constexpr int kClusterMaxMembers = 11;
@@ -1634,6 +1639,10 @@ cudaError_t launch_chain(ChainLaunch& L, int mode, cudaStream_t stream) {
     for (int l = 0; l < L.job[i].n_layers; ++l)
       if (L.job[i].layer[l].out_gp || L.job[i].layer[l].out_xhat) staged = true;
   L.stages = staged ? kStagesStaged : kStages;
+  // kernel generation: FQLPOP_CHAIN_GEN=1 forces the first-generation kernels (A/B measurements, parity cross-checks)
+  static const int gen = [] { const char* e = getenv("FQLPOP_CHAIN_GEN"); return e ? atoi(e) : 2; }();
+  if (gen >= 2 && chain16_eligible(L) && !(getenv("FQLPOP_CHAIN2") && chain2_eligible(L)))
+    return launch_chain16(L, mode, grid, stream);
   if (chain2_eligible(L)) {
     if (mode == 0) fql_chain2_kernel<0><<<2 * grid, kThreads2, kSmemBytes, stream>>>(L);
     else fql_chain2_kernel<1><<<2 * grid, kThreads2, kSmemBytes, stream>>>(L);

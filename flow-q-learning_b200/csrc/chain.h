@@ -91,4 +91,10 @@ cudaError_t chain_init();
 // Fills tile_begin of every job; returns the grid size.
 int finalize_chain(ChainLaunch* L);
 
+// Second-generation kernel (chain16.cu): 16 epilogue warps, per-k-block hand-off. launch_chain picks it whenever the
+// launch has the production shape (chain16_eligible).
+cudaError_t chain16_init();
+bool chain16_eligible(const ChainLaunch& L);
+cudaError_t launch_chain16(ChainLaunch& L, int mode, int grid, cudaStream_t stream);
+
 }  // namespace fqlpop

@@ -303,7 +303,9 @@ struct ChainBuilder {
     finalize_chain(L);
     L->timeline = P->timeline;
     L->tag = (long long)count | ((long long)P->g_off << 8);
-    if (const char* e = getenv("FQLPOP_CHAIN_DEBUG")) L->debug_flags = atoi(e);  // (debug) bit 0: no weight stream
+#ifdef FQLPOP_DEBUG_SWITCHES
+    if (const char* e = getenv("FQLPOP_CHAIN_DEBUG")) L->debug_flags = atoi(e);  // (make TRACE=1 only) bit 0: no weight stream
+#endif
     L->population_active = (int)P->h_members.size();
     {  // (debug) FQLPOP_CHAIN_TRACE=1: clock stamps of CTA 0 of chain launch FQLPOP_TRACE_LAUNCH (default 0 = Euler)
       const char* tl = getenv("FQLPOP_TRACE_LAUNCH");
@@ -440,7 +442,13 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   // schedule knobs (measured on B200): FQLPOP_SCHED bit 0 = critic forward / actor-critic pass
   // on their own streams (s3, s4) instead of queued behind s1 / s2; bit 1 = optimizer kernels on separate streams;
   // FQLPOP_ADAM_PRIO = priority of those streams (0 low, 1 same as compute)
-  static const int dbg_skip = [] { const char* e = getenv("FQLPOP_DEBUG_SKIP"); return e ? atoi(e) : 0; }();  // timing experiments only
+  // Switches that change RESULTS (skip Adam, run without the weight stream, ...) exist only in the trace build
+  // (make TRACE=1 -> lib/libfqlpop_trace.so); the product library cannot be talked into skipping work by an env var.
+#ifdef FQLPOP_DEBUG_SWITCHES
+  static const int dbg_skip = [] { const char* e = getenv("FQLPOP_DEBUG_SKIP"); return e ? atoi(e) : 0; }();
+#else
+  constexpr int dbg_skip = 0;
+#endif
   static const int sched = [] { const char* e = getenv("FQLPOP_SCHED"); return e ? atoi(e) : 7; }();
   cudaStream_t s0 = gp.s[0], s1 = gp.s[1], s2 = gp.s[2];
   cudaStream_t s3 = (sched & 1) ? gp.s[3] : s1, s4 = (sched & 1) ? gp.s[4] : s2;
@@ -754,7 +762,10 @@ int pop_create_impl(const PopParams& c, const float* alphas, const unsigned long
   // The layer-chain kernels need every network input to fit one 64-wide block (true for all OGBench shapes the
   // reference uses) and at most kChainMaxLayers GEMMs per chain; otherwise the per-layer kernels are used.
   P->use_chain = Lq.in_pad == 64 && Lb.in_pad == 64 && Lp.in_pad == 64 && c.n_hidden_actor + 1 <= kChainMaxLayers &&
-                 c.n_hidden_value + 1 <= kChainMaxLayers && getenv("FQLPOP_NO_CHAIN") == nullptr;
+                 c.n_hidden_value + 1 <= kChainMaxLayers;
+#ifdef FQLPOP_DEBUG_SWITCHES
+  if (getenv("FQLPOP_NO_CHAIN")) P->use_chain = false;
+#endif
   if (getenv("FQLPOP_CHAIN_TRACE")) rc = rc || dev_alloc(P, &P->chain_trace, 8192, err);
   if (getenv("FQLPOP_TIMELINE")) rc = rc || dev_alloc(P, &P->timeline, 8 + 4 * 65536, err);
   for (BwdBuf* bw : {&P->bQC, &P->bQA, &P->bBC, &P->bPI}) bw->part_rows = bw->m_tiles * (P->use_chain ? 4 : 1);
@@ -847,7 +858,11 @@ static int run_plan(Population* P, bool train, int n_steps, cudaStream_t stream,
     if (err) *err = "no dataset / batch bound (call fqlpop_set_dataset first)";
     return 1;
   }
+#ifdef FQLPOP_DEBUG_SWITCHES
   const bool eager = getenv("FQLPOP_EAGER") != nullptr;
+#else
+  constexpr bool eager = false;
+#endif
   cudaEvent_t e_in;
   CK(cudaEventCreateWithFlags(&e_in, cudaEventDisableTiming));
   CK(cudaEventRecord(e_in, stream));
@@ -898,7 +913,8 @@ int pop_refresh_shadow_impl(Population* P, cudaStream_t stream, std::string* err
 int pop_launches_per_step(const Population* P) { return P->plan ? P->plan->launches_per_step : 0; }
 
 // (measurement) `iters` back-to-back launches, on `stream`, of one layer-chain launch of the step covering every
-// active member: which = 0 the Euler flow chain, 1 the one-step policy forward pass (3B rows, first B saved).
+// active member: which = 0 the Euler flow chain, 1 the one-step policy forward pass (3B rows, first B saved), 2 the critic
+// forward pass (LayerNorm + saves), 3 the critic input-gradient chain, 4 the target-critic forward pass.
 // The pass buffers must hold a step's inputs (call after fqlpop_step). Leaves the population state untouched except
 // for those scratch buffers.
 int pop_debug_chain_launch(Population* P, int which, int iters, cudaStream_t stream, std::string* err) {
@@ -910,15 +926,26 @@ int pop_debug_chain_launch(Population* P, int which, int iters, cudaStream_t str
   cb.L = new ChainLaunch;
   const int B = P->c.B;
   for (int i = 0; i < iters && cb.ok; ++i) {
+    int mode = 0;
     if (which == 0) {
       cb.begin(1);
       cb.euler_job();
-    } else {
+    } else if (which == 1) {
       cb.begin(P->pi.L.nb);
       cb.fwd_job(P->PI, P->pi, P->pi.theta, P->pi.shadow, 0, B, true);
       cb.fwd_job(P->PI, P->pi, P->pi.theta, P->pi.shadow, B, 2 * B, false);
+    } else if (which == 2) {  // critic forward pass (LayerNorm, tensors saved for the backward pass)
+      cb.begin(P->critic.L.nb);
+      cb.fwd_job(P->QC, P->critic, P->critic.theta, P->critic.shadow, 0, B, true);
+    } else if (which == 3) {  // critic input-gradient chain (LayerNorm backward, bias / LayerNorm gradient partials)
+      cb.begin(P->critic.L.nb);
+      cb.bwd_job(P->QC, P->bQC, P->critic, 0, true, nullptr);
+      mode = 1;
+    } else {                  // target-critic forward pass (LayerNorm, nothing saved)
+      cb.begin(P->critic.L.nb);
+      cb.fwd_job(P->TQ, P->critic, P->critic.target, P->critic.tshadow, 0, B, false);
     }
-    cb.launch(0, stream);
+    cb.launch(mode, stream);
   }
   delete cb.L;
   if (!cb.ok) return 1;

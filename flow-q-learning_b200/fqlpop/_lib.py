@@ -6,7 +6,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libfqlpop.so")
+# FQLPOP_LIB: another build of the same library (profiling tools load lib/libfqlpop_trace.so, `make TRACE=1`)
+LIB_PATH = os.environ.get("FQLPOP_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libfqlpop.so")
 
 
 class FqlPopError(RuntimeError):

@@ -57,7 +57,13 @@ class Trainer:
 
         if state_dict is not None:
             self.candidates = state_dict["candidates"]
-            initial = list(state_dict["experiments"].keys())
+            # "order" = the full initial population in slot order (every rank saves it); checkpoints written before it
+            # existed are single-rank ones, where the experiment keys are that list
+            initial = list(state_dict.get("order") or state_dict["experiments"].keys())
+            saved_world = state_dict.get("world", 1)
+            if saved_world != self.world:
+                raise ValueError(f"checkpoint was written by {saved_world} rank(s), this job has {self.world}: member "
+                                 "placement (candidate i on rank i mod world) would not match the saved shards")
         else:
             self.candidates = self.strategy.sample()
             initial = list(self.candidates)
@@ -80,6 +86,7 @@ class Trainer:
                 self.create_experiment(c, state_dict=st)
             self.untrained_candidates = state_dict["untrained_candidates"]
             self.finished_candidates = state_dict["finished_candidates"]
+            self._remote_steps = dict(state_dict.get("remote_steps", {}))
             random.setstate(state_dict["random_rng_state"])
             np.random.set_state(state_dict["np_rng_state"])
         else:
@@ -96,9 +103,14 @@ class Trainer:
         return sorted(candidates, key=lambda c: self._order[c])
 
     def state_dict(self) -> dict:
+        """This rank's shard: its own experiments plus the replicated bookkeeping every rank needs to resume (the
+        reference's keys, /root/reference/trainer/trainer.py:50-59, + order / world / remote_steps)."""
         return {
             "experiments": {c: e.state_dict() for c, e in self.experiments.items()},
             "candidates": self.candidates,
+            "order": self._ordered(self._order),
+            "world": self.world,
+            "remote_steps": dict(getattr(self, "_remote_steps", {})),
             "random_rng_state": random.getstate(),
             "np_rng_state": np.random.get_state(),
             "untrained_candidates": self.untrained_candidates,

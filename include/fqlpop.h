@@ -107,7 +107,8 @@ int fqlpop_debug_chain_trace(void* handle, long long* host_out, int32_t n);
  * << 8 | blockIdx << 32). *n_out = number of records copied; the log is reset.                                    */
 int fqlpop_debug_timeline(void* handle, long long* host_out, int32_t max_records, int32_t* n_out);
 /* Measurement: `iters` back-to-back launches on `stream` of one layer-chain launch of the step over every active
- * member (which = 0: Euler flow chain, 1: one-step policy forward pass). Call after fqlpop_step.                */
+ * member (which = 0: Euler flow chain, 1: one-step policy forward pass, 2: critic forward pass with LayerNorm and
+ * saved tensors, 3: critic input-gradient chain, 4: target-critic forward pass). Call after fqlpop_step.        */
 int fqlpop_debug_chain_launch(void* handle, int32_t which, int32_t iters, void* stream);
 /* Number of kernels one replay of the captured step launches (bench.py's gpu_launches).                   */
 int fqlpop_launches_per_step(void* handle);

@@ -12,6 +12,7 @@ pop.set_dataset(*synth_dataset(1000000, 28, 5, "cuda"))
 pop.step(3)
 torch.cuda.synchronize()
 lib.fqlpop_debug_chain_launch.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
-check(lib.fqlpop_debug_chain_launch(pop._h, 1, 3, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+which = int(sys.argv[1]) if len(sys.argv) > 1 else 1   # 0 euler, 1 policy fwd, 2 critic fwd (LN+save), 3 critic bwd, 4 target critic
+check(lib.fqlpop_debug_chain_launch(pop._h, which, 3, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
 torch.cuda.synchronize()
 print("done")

@@ -10,7 +10,7 @@ for p in (os.path.join(ROOT, "flow-q-learning_b200"), ROOT, HERE):
         sys.path.insert(0, p)
 
 
-def main(rank, world, port, out_dir):
+def main(rank, world, port, out_dir, mode="plain"):
     import numpy as np
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
@@ -26,6 +26,13 @@ def main(rank, world, port, out_dir):
     pop = [ExperimentConfig(seed=i, alpha=a) for i, a in enumerate(np.logspace(np.log10(3), 3, 8).tolist())]
     sh = SuccessiveHalving(set(pop), total_evaluations=4, fraction=0.5, history_length=1)
     tr = Trainer(FakeTask(), sh, cfg, population_factory=FakePopulation)
+    if mode == "resume":
+        # stop after the first sweep + half of the second, write this rank's shard, rebuild everything from it
+        import pickle
+        tr.train(max_evaluations=10)
+        shard = pickle.loads(pickle.dumps({"trainer": tr.state_dict(), "strategy": tr.strategy.state_dict()}))
+        sh = SuccessiveHalving(set(pop), total_evaluations=4, fraction=0.5, history_length=1, state_dict=shard["strategy"])
+        tr = Trainer(FakeTask(), sh, cfg, state_dict=shard["trainer"], population_factory=FakePopulation)
     tr.train(max_evaluations=100)
     out = {"rank": rank, "local_members": len(tr.experiments), "candidates": sorted(c.alpha for c in tr.candidates),
            "scores": {str(c.alpha): v for c, v in sh.candidate_scores.items()},
@@ -36,4 +43,4 @@ def main(rank, world, port, out_dir):
 
 
 if __name__ == "__main__":
-    main(int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3]), sys.argv[4])
+    main(int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3]), sys.argv[4], *(sys.argv[5:6]))

@@ -13,13 +13,29 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def test_two_rank_trainer_agrees_on_pruning(tmp_path):
+def _run_two_ranks(tmp_path, mode="plain"):
     port = _free_port()
     worker = os.path.join(os.path.dirname(__file__), "dist_worker.py")
-    procs = [subprocess.Popen([sys.executable, worker, str(r), "2", str(port), str(tmp_path)]) for r in range(2)]
+    procs = [subprocess.Popen([sys.executable, worker, str(r), "2", str(port), str(tmp_path), mode]) for r in range(2)]
     for p in procs:
         assert p.wait(timeout=240) == 0
-    r0, r1 = (json.load(open(tmp_path / f"rank{r}.json")) for r in range(2))
+    return tuple(json.load(open(tmp_path / f"rank{r}.json")) for r in range(2))
+
+
+def test_two_rank_save_then_resume_matches_uninterrupted_run(tmp_path):
+    """Every rank writes its own shard (its members' state + the replicated bookkeeping: slot order, remote step
+    counts) and a job resumed from the shards ends exactly where the uninterrupted one does."""
+    (tmp_path / "a").mkdir(); (tmp_path / "b").mkdir()
+    plain = _run_two_ranks(tmp_path / "a")
+    resumed = _run_two_ranks(tmp_path / "b", "resume")
+    for p, r in zip(plain, resumed):
+        assert p["candidates"] == r["candidates"]
+        assert p["steps"] == r["steps"]
+        assert p["scores"] == r["scores"]
+
+
+def test_two_rank_trainer_agrees_on_pruning(tmp_path):
+    r0, r1 = _run_two_ranks(tmp_path)
     assert r0["local_members"] == 4 and r1["local_members"] == 4          # member i -> rank i mod 2
     assert r0["candidates"] == r1["candidates"] and len(r0["candidates"]) == 2
     assert r0["scores"] == r1["scores"] and len(r0["scores"]) == 8        # every rank saw every score
