@@ -177,15 +177,11 @@ extern "C" int fqlpop_counters(void* h, int32_t* adam_steps, uint64_t* step_coun
   const cudaMemcpyKind k = set ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
   if (adam_steps) e = set ? cudaMemcpy(P->adam_step, adam_steps, sizeof(int) * P->c.P, k)
                           : cudaMemcpy(adam_steps, P->adam_step, sizeof(int) * P->c.P, k);
-  if (e == cudaSuccess && step_counter) {
-    // the counter is kept per member (member groups step independently); active members always agree
-    if (set) {
-      std::vector<uint64_t> all((size_t)P->c.P, *step_counter);
-      e = cudaMemcpy(P->step_counter, all.data(), sizeof(uint64_t) * all.size(), k);
-    } else {
-      e = cudaMemcpy(step_counter, P->step_counter + P->h_members[0], sizeof(uint64_t), k);
-    }
-  }
+  // the Philox stream position is kept per member (member groups step independently; a resumed member continues its
+  // own stream): [population] in both directions
+  if (e == cudaSuccess && step_counter)
+    e = set ? cudaMemcpy(P->step_counter, step_counter, sizeof(uint64_t) * P->c.P, k)
+            : cudaMemcpy(step_counter, P->step_counter, sizeof(uint64_t) * P->c.P, k);
   if (e != cudaSuccess) return fail(std::string("fqlpop_counters: ") + cudaGetErrorString(e));
   return 0;
 }

@@ -872,25 +872,32 @@ static int run_plan(Population* P, bool train, int n_steps, cudaStream_t stream,
     for (GroupPlan& gp : pl->groups)
       if (!rc) rc = build_graph(P, train, gp, err);
   }
-  // every group runs its n_steps back to back on its own streams; the groups only meet again on `stream`
-  for (GroupPlan& gp : pl->groups) {
-    if (rc) break;
-    cudaStreamWaitEvent(gp.s[0], e_in, 0);
-    if (eager) {
+  // every group runs its n_steps back to back on its own streams; the groups only meet again on `stream`. The launches
+  // are submitted ROUND-ROBIN over the groups: the stream launch queue is finite (~1k pending launches), so submitting
+  // all n_steps of group 0 first would block the host inside group 0's loop and serialise the groups for large n_steps
+  // (the Trainer steps in chunks of log_interval = 5000).
+  for (GroupPlan& gp : pl->groups) cudaStreamWaitEvent(gp.s[0], e_in, 0);
+  if (eager) {
+    for (GroupPlan& gp : pl->groups) {
+      if (rc) break;
       Window w(P, gp);
       if (train) pl->launches_per_step = 0;
       for (int i = 0; i < n_steps && !rc; ++i) rc = issue_step(P, train, gp, err);
-    } else {
-      cudaGraphExec_t x = train ? gp.x_step : gp.x_loss;
-      for (int i = 0; i < n_steps && !rc; ++i) {
-        cudaError_t e = cudaGraphLaunch(x, gp.s[0]);
+    }
+  } else {
+    for (int i = 0; i < n_steps && !rc; ++i) {
+      for (GroupPlan& gp : pl->groups) {
+        cudaError_t e = cudaGraphLaunch(train ? gp.x_step : gp.x_loss, gp.s[0]);
         if (e != cudaSuccess) {
           if (err) *err = std::string("cudaGraphLaunch: ") + cudaGetErrorString(e);
           rc = 1;
+          break;
         }
       }
     }
-    if (!rc) {
+  }
+  if (!rc) {
+    for (GroupPlan& gp : pl->groups) {
       cudaEventRecord(gp.done, gp.s[0]);
       cudaStreamWaitEvent(stream, gp.done, 0);
     }

@@ -112,7 +112,7 @@ class FQLAgent:
         return {"rng": self.rng.copy(),
                 "network": {"step": int(adam_steps[m]) + 1, "params": params,
                             "opt_state": {"0": {"count": int(adam_steps[m]), "mu": mu, "nu": nu}, "1": {}}},
-                "fqlpop": {"philox_step": int(counter)}}
+                "fqlpop": {"philox_step": int(counter[m])}}
 
     def load_state_dict(self, state: dict) -> "FQLAgent":
         pop, m = self.population, self.slot
@@ -127,7 +127,10 @@ class FQLAgent:
         pop.refresh_shadow()
         steps, counter = pop.get_counters()
         steps[m] = int(opt.get("count", 0))
-        pop.set_counters(adam_steps=steps)
+        # continue this member's batch-index / noise stream where the saved run stopped (the reference restores the
+        # agent rng and the numpy RNG state on resume, /root/reference/trainer/trainer.py:55-56)
+        counter[m] = int(state.get("fqlpop", {}).get("philox_step", counter[m]))
+        pop.set_counters(adam_steps=steps, step_counter=counter)
         if "rng" in state:
             self.rng = np.asarray(state["rng"], dtype=np.uint32).copy()
         return self

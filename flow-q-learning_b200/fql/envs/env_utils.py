@@ -4,9 +4,10 @@
 
 ogbench / MuJoCo are not installed here ("unavailable on this box"), so:
   * datasets come from `<data_directory>/<env_name>.npz` and `<env_name>-val.npz` when those files exist (OGBench's
-    on-disk layout: observations, actions, terminals [, next_observations, rewards, masks]); otherwise a synthetic
-    dataset with the OGBench shape of that environment family is generated (N rows,
-    obs ~ N(0,1), next = obs + 0.05 N(0,1), actions ~ U(-1,1), rewards in {-1,0} with P(0)=0.005, 1000-step episodes);
+    on-disk layout: observations, actions, terminals [, next_observations, rewards, masks]); a missing file raises
+    FileNotFoundError. ONLY with the explicit opt-in FQLPOP_SYNTHETIC=1 (tests, benchmarks) a synthetic dataset with the
+    OGBench shape of that environment family is generated instead (N rows, obs ~ N(0,1),
+    next = obs + 0.05 N(0,1), actions ~ U(-1,1), rewards in {-1,0} with P(0)=0.005, 1000-step episodes);
   * evaluation "environments" only know how to reset: they return dataset episode-start observations (the same rows
     InitialObservationLoader keeps, /root/reference/utils/data_loader.py:14-22). Their dynamics are the learned world
     model on the GPU (task/offline_task_simulated.py); calling step() on them raises.
@@ -51,6 +52,7 @@ def _load_npz(path: Path) -> dict:
     terminals = d["terminals"].astype(np.float32)
     if "next_observations" not in d:  # OGBench compact layout: next row of the same episode
         keep = np.nonzero(terminals == 0)[0]
+        keep = keep[keep + 1 < len(obs)]  # a trailing row without terminals == 1 has no successor
         d = {"observations": obs[keep], "actions": d["actions"][keep].astype(np.float32),
              "next_observations": obs[keep + 1], "terminals": terminals[keep + 1],
              **({"rewards": d["rewards"][keep].astype(np.float32)} if "rewards" in d else {})}
@@ -79,15 +81,29 @@ class ResetOnlyEnv:
         pass
 
 
+def synthetic_allowed() -> bool:
+    return os.environ.get("FQLPOP_SYNTHETIC", "0") not in ("", "0")
+
+
 def make_env_and_datasets(env_name: str, data_directory=None, num_evaluation_envs: int = 1, **_):
+    """Returns (env, eval_envs, train_dataset, val_dataset). A missing dataset file raises; generated data is used only
+    under FQLPOP_SYNTHETIC=1 and announced on stdout."""
     train = val = None
-    if data_directory is not None:
-        p = Path(data_directory) / f"{env_name}.npz"
-        if p.exists():
-            train = _load_npz(p)
-            pv = Path(data_directory) / f"{env_name}-val.npz"
-            val = _load_npz(pv) if pv.exists() else None
+    p = Path(data_directory) / f"{env_name}.npz" if data_directory is not None else None
+    if p is not None and p.exists():
+        train = _load_npz(p)
+        pv = Path(data_directory) / f"{env_name}-val.npz"
+        if pv.exists():
+            val = _load_npz(pv)
+        elif not synthetic_allowed():
+            raise FileNotFoundError(f"validation dataset {pv} not found (set FQLPOP_SYNTHETIC=1 to train on generated data)")
+    elif not synthetic_allowed():
+        raise FileNotFoundError(
+            f"dataset {p if p is not None else '<data_directory>/' + env_name + '.npz'} not found: pass --data_directory "
+            "with the OGBench .npz files. Agents and world models are NOT trained on generated data unless "
+            "FQLPOP_SYNTHETIC=1 is set explicitly (tests and benchmarks do).")
     if train is None:
+        print(f"[fqlpop] data: synthetic ({SYNTHETIC_ROWS} generated rows of {env_name} shape; FQLPOP_SYNTHETIC=1)")
         train = synthetic_dataset(env_name, SYNTHETIC_ROWS, seed=0)
     if val is None:
         val = synthetic_dataset(env_name, max(EPISODE_LENGTH, len(train["observations"]) // 10), seed=1)

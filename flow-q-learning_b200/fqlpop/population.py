@@ -261,14 +261,16 @@ class Population:
         torch.cuda.synchronize(self.device)
 
     def get_counters(self):
+        """(adam_steps [P] int32, step_counter [P] uint64): optimiser step counts and each member's Philox stream position."""
         steps = np.zeros(self.P, np.int32)
-        ctr = np.zeros(1, np.uint64)
+        ctr = np.zeros(self.P, np.uint64)
         check(lib.fqlpop_counters(self._h, steps.ctypes.data, ctr.ctypes.data, 0), "fqlpop_counters")
-        return steps, int(ctr[0])
+        return steps, ctr
 
     def set_counters(self, adam_steps=None, step_counter=None):
         steps = None if adam_steps is None else np.ascontiguousarray(np.asarray(adam_steps, np.int32))
-        ctr = None if step_counter is None else np.asarray([step_counter], np.uint64)
+        ctr = None if step_counter is None else np.ascontiguousarray(
+            np.broadcast_to(np.asarray(step_counter, np.uint64), (self.P,)))
         check(lib.fqlpop_counters(self._h, None if steps is None else steps.ctypes.data,
                                   None if ctr is None else ctr.ctypes.data, 1), "fqlpop_counters")
 

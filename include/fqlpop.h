@@ -89,7 +89,8 @@ int fqlpop_leaf(void* handle, int32_t net, int32_t layer, int32_t kind, int32_t 
                 float* host, int32_t to_host);
 /* Re-derives the bf16 GEMM copies after parameters were written with fqlpop_leaf.                         */
 int fqlpop_refresh_shadow(void* handle, void* stream);
-/* Adam step counts [population] and the lockstep step counter (Philox stream position); set != 0 writes.  */
+/* Adam step counts [population] and the per-member step counters [population] (position of each member's Philox
+ * stream: batch indices and noise of its next update); set != 0 writes. NULL skips an array.                   */
 int fqlpop_counters(void* handle, int32_t* adam_steps, uint64_t* step_counter, int32_t set);
 /* Rewards / masks [population][batch] (host) of the batch the last step gathered: lets a test recover the row
  * indices the on-device uniform gather drew (Dataset.sample, task/offline_task_simulated.py:53-58).         */

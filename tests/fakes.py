@@ -57,7 +57,7 @@ class FakePopulation:
         pass
 
     def get_counters(self):
-        return self.steps_done.astype(np.int32).copy(), int(self.steps_done.max())
+        return self.steps_done.astype(np.int32).copy(), self.steps_done.astype(np.uint64)
 
     def set_counters(self, adam_steps=None, step_counter=None):
         pass

@@ -121,3 +121,29 @@ def test_strategy_is_updated_by_config_not_by_experiment(tmp_path):
     tr, pop, _ = _trainer(tmp_path, n=4)
     tr.train(max_evaluations=4)
     assert set(tr.strategy.candidate_scores) == set(pop)
+
+
+def test_missing_dataset_raises_unless_synthetic_is_opted_in(tmp_path, monkeypatch):
+    """A wrong --data_directory must not silently train on noise (only FQLPOP_SYNTHETIC=1 generates data); the compact
+    OGBench layout with a trailing non-terminal row loads without indexing past the end."""
+    import numpy as np
+    import pytest
+    from fql.envs import env_utils
+    monkeypatch.setenv("FQLPOP_SYNTHETIC", "0")
+    with pytest.raises(FileNotFoundError):
+        env_utils.make_env_and_datasets("cube-single-play-singletask-task2-v0", tmp_path)
+    with pytest.raises(FileNotFoundError):
+        env_utils.make_env_and_datasets("cube-single-play-singletask-task2-v0", None)
+    rng = np.random.default_rng(0)
+    n = 50
+    term = np.zeros(n, np.float32); term[24] = 1.0                      # last row: terminals == 0
+    np.savez(tmp_path / "cube-single-x.npz", observations=rng.standard_normal((n, 28)).astype(np.float32),
+             actions=rng.uniform(-1, 1, (n, 5)).astype(np.float32), terminals=term)
+    with pytest.raises(FileNotFoundError):                              # validation file missing, no opt-in
+        env_utils.make_env_and_datasets("cube-single-x", tmp_path)
+    monkeypatch.setenv("FQLPOP_SYNTHETIC", "1")
+    monkeypatch.setattr(env_utils, "SYNTHETIC_ROWS", 2000)
+    _, _, train, val = env_utils.make_env_and_datasets("cube-single-x", tmp_path)
+    assert len(train["observations"]) == n - 2 and train["next_observations"].shape == train["observations"].shape
+    _, _, train, _ = env_utils.make_env_and_datasets("cube-single-y", None)
+    assert len(train["observations"]) == 2000

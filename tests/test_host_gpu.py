@@ -130,6 +130,35 @@ def test_single_experiment_save_and_load_agent(workdir):
     agent2.close()
 
 
+def test_resumed_experiment_continues_its_batch_and_noise_stream(workdir):
+    """A member restored from its state dict draws, at its next update, exactly the dataset rows (and noise) the
+    uninterrupted run draws: the per-member Philox step counter travels with the checkpoint."""
+    from trainer.config import AgentConfig, ExperimentConfig, TrainerConfig
+    from trainer.experiment import Experiment
+    save_dir, _ = workdir
+    task = _task(save_dir, n_envs=8, max_steps=4)
+    cfg = TrainerConfig(steps=20, eval_interval=5, log_interval=100, save_directory=save_dir / "resume", env_name=ENV,
+                        agent=AgentConfig(batch_size=64))
+    a = Experiment(task, cfg, ExperimentConfig(seed=11, alpha=30.0))
+    a.train(3)
+    state = pickle.loads(pickle.dumps(a.state_dict()))
+    assert state["agent"]["fqlpop"]["philox_step"] == 3
+    b = Experiment(task, cfg, ExperimentConfig(seed=11, alpha=30.0), state_dict=state)
+    assert int(b.agent.population.get_counters()[1][0]) == 3
+    a.train(1)
+    rew_a, mask_a = a.agent.population.last_batch()
+    b._bound = None
+    b.train(1)
+    rew_b, mask_b = b.agent.population.last_batch()
+    np.testing.assert_array_equal(rew_a, rew_b)
+    np.testing.assert_array_equal(mask_a, mask_b)
+    ia, ib = a.agent.population.info(), b.agent.population.info()
+    np.testing.assert_allclose(ia[0, :10], ib[0, :10], rtol=1e-4, atol=1e-5)   # same rows, same noise, same parameters
+    for e in (a, b):
+        e.stop()
+        e.agent.close()
+
+
 def test_scripts_train_env_models_then_tune_alpha(tmp_path, monkeypatch):
     """The reference's workflow with its own command lines: train_env_model.py (termination predictor, then the state
     predictor against it) leaves the env-model files, tune_alpha.py sweeps alpha with evaluations in that world model and

@@ -154,7 +154,7 @@ def test_one_update_matches_oracle(shape, variant, chain_kernel):
         for name, a, b in _leaf_pairs(t_c, new_e["params"]["target_critic"], "target"):
             assert np.abs(a - b).max() <= 2.2 * cfg.lr * cfg.tau + 1e-7, f"member {p} target {name}"
     steps, ctr = pop.get_counters()
-    assert list(steps) == [1] * P and ctr == 1
+    assert list(steps) == [1] * P and list(ctr) == [1] * P
     pop.close()
 
 
@@ -183,7 +183,7 @@ def test_total_loss_matches_update_info_and_leaves_state_untouched():
             want = float(info_e[k])
             assert abs(float(info[p, i]) - want) <= 5e-3 * max(1.0, abs(want)), (p, k, float(info[p, i]), want)
     steps, ctr = pop.get_counters()
-    assert list(steps) == [0, 0] and ctr == 0
+    assert list(steps) == [0, 0] and list(ctr) == [0, 0]
     pop.close()
 
 
