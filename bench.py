@@ -101,6 +101,9 @@ def cpu_oracle_updates_per_sec(O, A, B, n_updates, warm=2):
     """Times the CPU oracle (oracle/fql_oracle.py, fp32, all host threads) on a bounded sample."""
     import torch
     from oracle import fql_oracle as orc
+    # all host cores, whatever the launcher exported (torchrun sets OMP_NUM_THREADS=1 for its workers): the CPU figure
+    # must not depend on how many GPU ranks were started beside it
+    torch.set_num_threads(os.cpu_count() or 1)
     cfg = orc.FQLConfig(ob_dim=O, action_dim=A, batch_size=B)
     st = orc.init_state(0, cfg)
     g = torch.Generator().manual_seed(0)
@@ -120,6 +123,14 @@ def cpu_oracle_updates_per_sec(O, A, B, n_updates, warm=2):
     return n_updates / dt, torch.get_num_threads()
 
 
+def update_config(args, O, A):
+    """`config` of the headline workload -- the same dict in both arms."""
+    return {"workload": f"lockstep population of {args.population} alpha-agents per GPU, {args.shape} shape (O={O}, A={A}), "
+                        f"batch {args.batch}, 4x512 MLPs, E=2 critics, 10 flow steps; dataset {args.rows} rows in HBM",
+            "population_per_gpu": args.population, "batch": args.batch,
+            "l2": "working set (params+Adam state+dataset, >1 GB) exceeds L2"}
+
+
 def run_reference(args, rank, world):
     """Reference arm: the reference's own CPU path is not installable (missing fql submodule, no jax); the CPU
     oracle restating it is timed on the host cores instead. Rank 0 only."""
@@ -132,60 +143,67 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": "fql_member_updates_per_sec", "value": ups, "unit": "updates/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * per_step / ups,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"population of {args.population} alpha-agents, {args.shape} shape, batch {args.batch}, "
-                               "4x512 MLPs, 10 flow steps", "population": args.population, "batch": args.batch},
+        "config": update_config(args, O, A),
         "cpu_baseline": {"value": ups, "unit": "updates/s", "cores": threads, "kind": "port",
                          "sample": f"{per_step} sequential member-updates per step (of {args.population}), "
-                                   f"{args.steps} steps, torch CPU fp32 oracle"},
+                                   f"{args.steps} steps, torch CPU fp32 oracle; ONE process on all host cores whatever N is "
+                                   "(the GPU arm's value is whole-job over N GPUs)"},
         "e2e": {"value": ups, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
 
 
-# DRAM traffic of the roofline launch (16 members, cube-single, B=256) from one ncu --set full capture: 28.02 MB read (the
-# bf16 weights, once per member) + 3.28 MB written (most of the saved activations are still in L2 when the launch ends)
-ROOFLINE_LAUNCH_DRAM_BYTES = 28023552 + 3282688
+# DRAM traffic of the roofline launch by (shape, members, batch), from the committed ncu --set full capture of that launch
+ROOFLINE_TRAFFIC = {("cube-single", 16, 256): 28023552 + 3282688}
+ROOFLINE_TRAFFIC_SOURCE = "profiles/r01d_chain_ncu_full_summary.txt"
 
 
-def chain_roofline(torch, pop, P, O, A, B, iters=50):
-    """The step's dominant kernel, fql_chain_kernel<0>, in its widest launch: the one-step policy forward pass (3B rows
-    of every member through the four hidden layers in one launch, activations on chip, act'(z) / h saved for the
-    backward pass). Launched alone, back to back, on the current stream and bracketed by CUDA events on that stream ->
-    the burst tensor peak is the denominator. FLOP = algorithmic (true input width, not the padded 64)."""
+def chain_launch_roofline(torch, pop, P, O, A, B, which, iters=50):
+    """One layer-chain launch of the step covering every member, launched alone, back to back, on the current stream and
+    bracketed by CUDA events on that stream -> the burst tensor peak is the denominator. FLOP = algorithmic (true input
+    width, not the padded 64). which: 0 Euler flow chain (10 steps x (4 hidden layers + head), B rows), 1 one-step policy
+    forward pass (3B rows, saves for the backward pass), 2 critic forward pass (LayerNorm, E=2, saves), 3 critic
+    input-gradient chain (LayerNorm backward, 3 hidden-layer products), 4 target-critic forward pass."""
     import ctypes
     from fqlpop._lib import lib, check
     lib.fqlpop_debug_chain_launch.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
     st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-    check(lib.fqlpop_debug_chain_launch(pop._h, 1, 5, st))
+    check(lib.fqlpop_debug_chain_launch(pop._h, which, 5, st))
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    check(lib.fqlpop_debug_chain_launch(pop._h, 1, iters, st))
+    check(lib.fqlpop_debug_chain_launch(pop._h, which, iters, st))
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / iters
-    flop = 2.0 * P * 3 * B * ((O + A) * HID + 3 * HID * HID)   # policy input = (obs, noise): O + A wide
-    return flop / (ms * 1e-3) / 1e12, ms, flop
+    E, F = 2, 10
+    hid3 = 3 * HID * HID
+    if which == 0:
+        flop, what, rows, V = 2.0 * P * B * F * ((O + A + 1) * HID + hid3 + HID * A), "Euler flow chain, 10 steps x 5 layers", B, P
+    elif which == 1:
+        flop, what, rows, V = 2.0 * P * 3 * B * ((O + A) * HID + hid3), "one-step policy forward pass, 4 hidden layers (saved for backward)", 3 * B, P
+    elif which == 2:
+        flop, what, rows, V = 2.0 * P * E * B * ((O + A) * HID + hid3), "critic forward pass, 4 hidden layers, LayerNorm, saved for backward", B, P * E
+    elif which == 3:
+        flop, what, rows, V = 2.0 * P * E * B * (HID * 1 + hid3), "critic input-gradient chain, LayerNorm backward", B, P * E
+    else:
+        flop, what, rows, V = 2.0 * P * E * B * ((O + A) * HID + hid3), "target-critic forward pass, 4 hidden layers, LayerNorm", B, P * E
+    return {"achieved": flop / (ms * 1e-3) / 1e12, "launch_ms": ms, "flop_per_launch": flop,
+            "kernel": f"layer-chain kernel: {what}; {rows} rows x {V} virtual members in one launch "
+                      f"({V * ((rows + 127) // 128)} CTAs of 128 rows), timed alone"}
 
 
-def rollout_bench(torch, np, dev, P, world, barrier, dist, n=4096, T=200, reps=3):
-    """BASELINE config 3 / SURVEY 8(d)-3: simulated evaluation of every member, antsoccer shape (O=42, A=8), n episodes x
-    T steps, state MLP 50->128->256->128->42 (input LayerNorm + residual), termination MLP 42->128->256->128->1, policy
-    50->512^4->8 -- ONE launch of the fused persistent rollout kernel per evaluation. The termination bias is set so that
-    no episode ends early: exactly n*T env-steps run per member (the count is read back from the kernel's own step
-    counters). `value`: init observations resident; `e2e`: init observations from pinned host memory, success rates and
-    returns read back."""
-    from fqlpop.population import Population
-    from fqlpop.envmodel import EnvModel
-    O, A, hidden = 42, 8, (128, 256, 128)
-    rng = np.random.default_rng(3)
+def synthetic_envmodel_trees(np, O, A, hidden=(128, 256, 128), term_bias=0.0, seed=3):
+    """Random world model of the reference's architecture (envmodel/baseline.py:25-37, termination_predictor.py:14-21):
+    LeCun-normal kernels, zero biases, small output layer of the state predictor (residual steps stay O(1))."""
+    rng = np.random.default_rng(seed)
 
     def mlp(i, o, bias_last=0.0, scale_last=1.0):
         dims = [i, *hidden, o]
         t = {}
         for l in range(len(dims) - 1):
-            k = (rng.standard_normal((dims[l], dims[l + 1])) / np.sqrt(dims[l])).astype(np.float32)   # LeCun normal
+            k = (rng.standard_normal((dims[l], dims[l + 1])) / np.sqrt(dims[l])).astype(np.float32)
             t[f"Dense_{l}"] = {"kernel": k, "bias": np.zeros(dims[l + 1], np.float32)}
         t[f"Dense_{len(dims) - 2}"]["kernel"] *= scale_last
         t[f"Dense_{len(dims) - 2}"]["bias"] += bias_last
@@ -193,45 +211,128 @@ def rollout_bench(torch, np, dev, P, world, barrier, dist, n=4096, T=200, reps=3
 
     state = mlp(O + A, O, scale_last=0.05)
     state["LayerNorm_0"] = {"scale": np.ones(O + A, np.float32), "bias": np.zeros(O + A, np.float32)}
-    term = mlp(O, 1, bias_last=-50.0)
+    term = mlp(O, 1, bias_last=term_bias)
+    return state, term
+
+
+def calibrated_envmodel(torch, np, dev, pop, O, A, T, target=0.5, n=1024):
+    """'termination threshold bias tuned so ~50 % of episodes terminate before T'. Bisection on the bias of
+    the termination predictor's output layer against member 0's rollout (a handful of 1024-episode rollouts, untimed)."""
+    from fqlpop.envmodel import EnvModel
+    init = torch.randn(n, O, generator=torch.Generator().manual_seed(7)).to(dev)
+    lo, hi = -30.0, 30.0
+    active = list(pop.active)
+    pop.set_active(active[:1])
+    em, rate = None, None
+    for _ in range(12):
+        mid = 0.5 * (lo + hi)
+        st, tm = synthetic_envmodel_trees(np, O, A, term_bias=mid)
+        em = EnvModel(st, tm, O, A, device=dev)
+        rate = float(pop.rollout(em, init, max_episode_steps=T, eval_seed=1)["success_rate"][active[0]])
+        if abs(rate - target) < 0.03:
+            break
+        if rate > target:
+            hi = mid
+        else:
+            lo = mid
+    pop.set_active(active)
+    return em, mid, rate
+
+
+def cpu_rollout_env_steps_per_sec(O, A, n, T, term_bias):
+    """CPU baseline of the second metric: the oracle's restatement of evaluate_actor_fn + Task.step
+    (/root/reference/evaluator/evaluation.py:84-114, task/offline_task_simulated.py:85-107) for ONE member on a
+    bounded sample of n episodes x T steps, all host threads."""
+    import numpy as np
+    import torch
+    from oracle import fql_oracle as orc
+    torch.set_num_threads(os.cpu_count() or 1)
+    cfg = orc.FQLConfig(ob_dim=O, action_dim=A, batch_size=256)
+    st = orc.init_state(0, cfg)
+    state, term = synthetic_envmodel_trees(np, O, A, term_bias=term_bias)
+    t = lambda tree: {k: (t(v) if isinstance(v, dict) else torch.as_tensor(v)) for k, v in tree.items()}
+    env = {"state": t(state), "termination": t(term)}
+    g = torch.Generator().manual_seed(0)
+    init = torch.randn(n, O, generator=g)
+    noise = torch.randn(T, n, A, generator=g)
+    t0 = time.perf_counter()
+    out = orc.rollout(st["params"]["actor_onestep_flow"], env, init, noise, cfg, T)
+    dt = time.perf_counter() - t0
+    steps = int(out["steps"])
+    return steps * n / dt, torch.get_num_threads(), steps
+
+
+def rollout_bench(torch, np, dev, P, world, barrier, dist, n=4096, T=200, reps=3, with_cpu=True):
+    """BASELINE config 3 / SURVEY 8(d)-3: simulated evaluation of every member, antsoccer shape (O=42, A=8), n episodes x
+    T steps, state MLP 50->128->256->128->42 (input LayerNorm + residual), termination MLP 42->128->256->128->1, policy
+    50->512^4->8 -- ONE launch of the fused persistent rollout kernel per evaluation. Headline: the termination
+    predictor's output bias is calibrated so that ~50 % of the episodes terminate before T (the done /
+    invalid bookkeeping and the per-CTA early exit are inside the timed region); `no_termination` repeats the run with a
+    bias of -50 (nothing ends early: exactly n*T env-steps per member). Env-steps are the lockstep steps the kernel
+    reports it executed x n (the reference keeps stepping finished episodes until all are done, evaluation.py:93).
+    `value`: init observations resident; `e2e`: init observations from pinned host memory, success rates and returns
+    read back."""
+    from fqlpop.population import Population
+    from fqlpop.envmodel import EnvModel
+    O, A = 42, 8
     pop = Population(dict(ob_dim=O, action_dim=A, batch_size=256, discount=0.995),
                      np.logspace(np.log10(3), np.log10(1000), P), list(range(P)), device=dev)
-    em = EnvModel(state, term, O, A, device=dev)
+    em_half, bias, rate0 = calibrated_envmodel(torch, np, dev, pop, O, A, T)
+    st, tm = synthetic_envmodel_trees(np, O, A, term_bias=-50.0)
+    em_none = EnvModel(st, tm, O, A, device=dev)
     init_host = torch.randn(n, O).pin_memory()
     init_dev = init_host.to(dev)
-    pop.rollout(em, init_dev, max_episode_steps=T, eval_seed=1)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for r in range(reps):
-        out = pop.rollout(em, init_dev, max_episode_steps=T, eval_seed=2 + r)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / reps
-    steps = int(out["steps"].sum().item())          # lockstep env-steps executed, summed over members
-    e0.record()
-    for r in range(reps):
-        out = pop.rollout(em, init_host.to(dev, non_blocking=True), max_episode_steps=T, eval_seed=2 + r)
-        sr = out["success_rate"].cpu(); rm = out["return_mean"].cpu()
-    e1.record()
-    torch.cuda.synchronize()
-    ms_e2e = e0.elapsed_time(e1) / reps
-    t = torch.tensor([ms, ms_e2e], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, ms_e2e = float(t[0]), float(t[1])
-    env_steps = steps * n * world
     flop_step = 2.0 * ((O + A) * 512 + 3 * 512 * 512 + 512 * A            # policy
                        + (O + A) * 128 + 128 * 256 + 256 * 128 + 128 * O  # state predictor
                        + O * 128 + 128 * 256 + 256 * 128 + 128)           # termination predictor
+
+    def run(em):
+        pop.rollout(em, init_dev, max_episode_steps=T, eval_seed=1)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for r in range(reps):
+            out = pop.rollout(em, init_dev, max_episode_steps=T, eval_seed=2 + r)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        steps = int(out["steps"].sum().item())          # lockstep env-steps executed, summed over members
+        sr = float(out["success_rate"].mean().item())
+        e0.record()
+        for r in range(reps):
+            out = pop.rollout(em, init_host.to(dev, non_blocking=True), max_episode_steps=T, eval_seed=2 + r)
+            out["success_rate"].cpu(); out["return_mean"].cpu()
+        e1.record()
+        torch.cuda.synchronize()
+        ms_e2e = e0.elapsed_time(e1) / reps
+        t = torch.tensor([ms, ms_e2e], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(t[0]), float(t[1])
+        env_steps = steps * n * world
+        return {"value": env_steps / (ms * 1e-3), "unit": "env-steps/s", "ms_per_evaluation": ms,
+                "e2e": {"value": env_steps / (ms_e2e * 1e-3), "unit": "env-steps/s", "h2d_bytes": int(init_host.numel() * 4),
+                        "d2h_bytes": int(2 * P * 4)},
+                "mean_success_rate": sr, "lockstep_steps_per_member": steps / max(P, 1),
+                "algorithmic_tflops": env_steps / world * flop_step / (ms * 1e-3) / 1e12}
+
+    half = run(em_half)
+    none = run(em_none)
     pop.close()
-    return {"value": env_steps / (ms * 1e-3), "unit": "env-steps/s", "ms_per_evaluation": ms,
-            "e2e": {"value": env_steps / (ms_e2e * 1e-3), "unit": "env-steps/s", "h2d_bytes": int(init_host.numel() * 4),
-                    "d2h_bytes": int(2 * P * 4)},
-            "config": {"workload": f"simulated evaluation, antsoccer shape (O={O}, A={A}), {P} members x {n} episodes x {T} steps per GPU, "
-                                   "one fused launch per evaluation", "env_steps_per_member": steps // max(P, 1) * n},
-            "algorithmic_tflops": env_steps / world * flop_step / (ms * 1e-3) / 1e12, "flop_per_env_step": flop_step,
-            "gpu_launches": reps}
+    out = dict(half)
+    out["config"] = {"workload": f"simulated evaluation, antsoccer shape (O={O}, A={A}), {P} members x {n} episodes x {T} steps per GPU, "
+                                 f"one fused launch per evaluation; termination bias {bias:+.3f} calibrated to ~50 % of the "
+                                 f"episodes terminating before T (member 0: {rate0:.2f})"}
+    out["no_termination"] = none
+    out["flop_per_env_step"] = flop_step
+    out["gpu_launches"] = 2 * (2 * reps + 1)
+    if with_cpu:
+        n_cpu = 512
+        v, threads, steps = cpu_rollout_env_steps_per_sec(O, A, n_cpu, T, bias)
+        out["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": threads, "kind": "port",
+                               "sample": f"one member, {n_cpu} episodes x {steps} lockstep steps (same calibrated world model), "
+                                         "torch CPU fp32 oracle of evaluate_actor_fn + Task.step"}
+    return out
 
 
 def worldmodel_bench(torch, np, dev, steps=2000, cpu_steps=100, with_cpu=True):
@@ -303,6 +404,137 @@ def worldmodel_bench(torch, np, dev, steps=2000, cpu_steps=100, with_cpu=True):
     return out
 
 
+def sh64_bench(torch, np, dev, rank, world, dist, barrier, n_alphas=64, shape="antsoccer", batch=256, eval_interval=20,
+               total_evaluations=50, episodes=256, T=200):
+    """BASELINE config 4: successive halving (f=0.5, h=2, total_evaluations=50) over 64 alpha values of a LIVE population
+    sharded over the ranks (member i -> rank i mod world), antsoccer shape, batch 256 -- the real Trainer +
+    SuccessiveHalving + fused simulated evaluation, evaluation scores all-gathered (NCCL) after every evaluation so that
+    every rank prunes identically. eval_interval is shortened (the reference trains 20 000 steps between evaluations);
+    the schedule of population sizes is the reference's (64 -> 32 -> 16 -> 8 -> 4 -> 2 -> 1 at
+    evaluations 2, 3, 5, 8, 14, 26). STRONG scaling: the job is fixed, ranks only split it.
+    Reports whole-job member-updates/s, per-evaluation wall time by population size, all-gather latency and the idle-GPU
+    fraction per rung (1 - mean / max of the ranks' busy time)."""
+    import contextlib
+    import random
+    import tempfile
+    from pathlib import Path
+    from fqlpop.envmodel import EnvModel
+    from hpo.successive_halving import SuccessiveHalving
+    from task.task import Task
+    from trainer.config import AgentConfig, ExperimentConfig, TrainerConfig
+    from trainer.trainer import Trainer
+    O, A = SHAPES[shape]
+    ds = synth_dataset(200_000, O, A, dev, seed=0)
+
+    class SimTask(Task):
+        """Device-resident synthetic dataset + calibrated random world model (no files)."""
+        device = dev
+
+        def __init__(self):
+            # the same world model on every rank: calibrated against a fixed one-member population (alpha 10, seed 0)
+            from fqlpop.population import Population
+            cal = Population(dict(ob_dim=O, action_dim=A, batch_size=batch), [10.0], [0], device=dev)
+            self.em, self.bias, self.rate0 = calibrated_envmodel(torch, np, dev, cal, O, A, T)
+            cal.close()
+            self.init = torch.randn(episodes, O, generator=torch.Generator().manual_seed(5)).to(dev)
+            self.eval_no = 0
+
+        def sample(self, dataset, batch_size):
+            idx = torch.randint(0, ds[0].shape[0], (batch_size,), device=dev)
+            keys = ("observations", "actions", "next_observations", "rewards", "masks")
+            return {k: v[idx].cpu().numpy() for k, v in zip(keys, ds)}
+
+        def device_dataset(self, split="train"):
+            return ds
+
+        def rollout_population(self, population, seed=None, trajectory=False):
+            self.eval_no += 1
+            return population.rollout(self.em, self.init, T, eval_seed=1000 + self.eval_no)
+
+        def reset(self, seed=0): raise NotImplementedError
+        def step(self, action): raise NotImplementedError
+        def close(self): pass
+
+    rec = []   # one record per evaluation sweep
+
+    class TimedTrainer(Trainer):
+        def _train_lockstep(self, mine, num_steps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            super()._train_lockstep(mine, num_steps)
+            torch.cuda.synchronize()
+            self._t_train = time.perf_counter() - t0
+
+        def _evaluate(self, mine):
+            t0 = time.perf_counter()
+            out = super()._evaluate(mine)
+            torch.cuda.synchronize()
+            self._t_eval = time.perf_counter() - t0
+            return out
+
+        def _gather_scores(self, now, local):
+            t0 = time.perf_counter()
+            out = super()._gather_scores(now, local)
+            t_gather = time.perf_counter() - t0
+            busy = getattr(self, "_t_train", 0.0) + getattr(self, "_t_eval", 0.0)
+            self._t_train = self._t_eval = 0.0
+            busy_all = [busy]
+            if world > 1:
+                t = torch.tensor([busy], device=dev, dtype=torch.float64)
+                g = [torch.empty_like(t) for _ in range(world)]
+                dist.all_gather(g, t)                      # measurement only (not part of the product path)
+                busy_all = [float(x) for x in g]
+            mine = sum(1 for c in now if self.owns(c))
+            rec.append({"population": len(now), "local_members": mine, "busy_s": busy_all, "gather_s": t_gather})
+            return out
+
+    random.seed(0); np.random.seed(0)
+    alphas = np.logspace(np.log10(3), np.log10(1000), n_alphas).tolist()           # tune_alpha.py:43-45
+    seeds = random.Random(0).sample(range(10000), n_alphas)
+    pop_cfgs = [ExperimentConfig(seed=s, alpha=a) for a, s in zip(alphas, seeds)]
+    tmp = tempfile.mkdtemp(prefix=f"sh64_r{rank}_")
+    cfg = TrainerConfig(steps=eval_interval * total_evaluations, eval_interval=eval_interval,
+                        log_interval=eval_interval * total_evaluations, save_directory=Path(tmp), env_name=shape,
+                        agent=AgentConfig(batch_size=batch, discount=0.995 if shape == "antsoccer" else 0.99))
+    sh = SuccessiveHalving(set(pop_cfgs), total_evaluations=total_evaluations, fraction=0.5, history_length=2)
+    with contextlib.redirect_stdout(sys.stderr):
+        tr = TimedTrainer(SimTask(), sh, cfg)
+        barrier()
+        t0 = time.perf_counter()
+        tr.train(max_evaluations=10 ** 9)
+        barrier()
+        total_s = time.perf_counter() - t0
+    t = torch.tensor([total_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_s = float(t)
+    updates = sum(r["population"] for r in rec) * eval_interval
+    rungs = {}
+    for r in rec:
+        g = rungs.setdefault(r["population"], {"evaluations": 0, "wall_s": 0.0, "busy_max_s": 0.0, "busy_mean_s": 0.0,
+                                                "gather_ms": []})
+        g["evaluations"] += 1
+        g["wall_s"] += max(r["busy_s"]) + r["gather_s"]
+        g["busy_max_s"] += max(r["busy_s"])
+        g["busy_mean_s"] += sum(r["busy_s"]) / len(r["busy_s"])
+        g["gather_ms"].append(1e3 * r["gather_s"])
+    per_rung = [{"population": n, "evaluations": g["evaluations"], "wall_s": round(g["wall_s"], 4),
+                 "member_updates_per_s": n * eval_interval * g["evaluations"] / max(g["wall_s"], 1e-9),
+                 "idle_gpu_fraction": 1.0 - g["busy_mean_s"] / max(g["busy_max_s"], 1e-12),
+                 "allgather_ms_median": sorted(g["gather_ms"])[len(g["gather_ms"]) // 2]}
+                for n, g in sorted(rungs.items(), reverse=True)]
+    survivors = sorted(c.alpha for c in tr.candidates)
+    if tr.population is not None:
+        tr.population.close()
+    return {"value": updates / total_s, "unit": "updates/s", "scaling": "strong", "total_s": total_s,
+            "member_updates": updates, "evaluations": len(rec), "n_gpus": world,
+            "config": {"workload": f"successive halving f=0.5 h=2 over {n_alphas} alpha values, {shape} shape (O={O}, A={A}), "
+                                   f"batch {batch}, {total_evaluations} evaluations of {episodes} episodes x {T} steps, "
+                                   f"eval_interval {eval_interval} steps (shortened), members placed i mod {world}, "
+                                   "scores all-gathered over NCCL after every evaluation"},
+            "population_sizes": [r["population"] for r in rec], "per_rung": per_rung, "survivor_alphas": survivors}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -316,6 +548,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-rollout", action="store_true")
     ap.add_argument("--no-worldmodel", action="store_true")
+    ap.add_argument("--workload", default="update", choices=["update", "sh64"],
+                    help="update: BASELINE configs[1] (lockstep population update; the headline). sh64: BASELINE configs[3], "
+                         "successive halving over 64 alpha values sharded over the ranks (strong scaling).")
+    ap.add_argument("--sh-eval-interval", type=int, default=20)
+    ap.add_argument("--no-sh64", action="store_true", help="N > 1: skip the successive-halving job appended to the line")
+    ap.add_argument("--blocks", type=int, default=5, help="timed blocks of --steps steps; the median block is reported")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -336,6 +574,26 @@ def main():
     P, B = args.population, args.batch
     dev = torch.device("cuda", local)
     import random
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    env_switches = {k: v for k, v in os.environ.items() if k.startswith("FQLPOP_")}
+    if args.workload == "sh64":
+        out = sh64_bench(torch, np, dev, rank, world, dist, barrier, eval_interval=args.sh_eval_interval)
+        if rank == 0:
+            line = {"metric": "fql_member_updates_per_sec", "value": out["value"], "unit": "updates/s", "n_gpus": world,
+                    "steps": out["evaluations"] * args.sh_eval_interval, "warmup": 0,
+                    "ms_per_step": 1e3 * out["total_s"] / (out["evaluations"] * args.sh_eval_interval),
+                    "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                    "config": out["config"], "sh64": out, "env_switches": env_switches}
+            print(json.dumps(line), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     alphas_all = np.logspace(np.log10(3), np.log10(1000), P * world)   # tune_alpha.py:43-45
     seeds_all = random.Random(0).sample(range(10000), P * world)       # tune_alpha.py:40,46
     alphas = alphas_all[rank::world]                                    # member i -> GPU i mod G
@@ -345,27 +603,27 @@ def main():
     ds = synth_dataset(args.rows, O, A, dev, seed=0)
     pop.set_dataset(*ds)
 
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
     # ---- device-resident throughput -------------------------------------------------------------------
+    # `blocks` timed blocks of exactly `steps` steps each (barrier + synchronize on both sides of every block, CUDA events,
+    # max over ranks per block); the MEDIAN block is reported. Several blocks keep the GPU under load long enough (>= 1 s
+    # at the default K) for the clock sampler to see it.
     pop.step(args.warmup)
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    pop.step(args.steps)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1)
-    t = torch.tensor([ms], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total = float(t.item())
+    block_ms = []
+    for _ in range(max(1, args.blocks)):
+        barrier()
+        e0.record()
+        pop.step(args.steps)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        block_ms.append(float(t.item()))
+    ms_total = sorted(block_ms)[len(block_ms) // 2]
     info_last = pop.info()
 
     # ---- end to end: host batches (pinned) -> H2D -> step -> info D2H, every step ---------------------------
@@ -443,9 +701,18 @@ def main():
     e2e_ms = float(t.item())
     sampler.stop_flag = True
     sampler.join(timeout=2)
+    # N > 1: BASELINE configs[3] (successive halving over 64 alpha values sharded over the ranks, NCCL score all-gather)
+    # rides along as an extra key: a strong-scaling number with the product collective inside the timed region
+    sh64 = None
+    if world > 1 and not args.no_sh64:
+        pop.close()
+        sh64 = sh64_bench(torch, np, dev, rank, world, dist, barrier, eval_interval=args.sh_eval_interval)
+        pop = Population(cfg, alphas, seeds, device=dev)
+        pop.set_dataset(*ds)
+        pop.step(3)
     roll = None
     if not args.no_rollout:
-        roll = rollout_bench(torch, np, dev, P, world, barrier, dist)
+        roll = rollout_bench(torch, np, dev, P, world, barrier, dist, with_cpu=(rank == 0 and not args.no_cpu_baseline))
 
     if rank != 0:
         if world > 1:
@@ -455,30 +722,33 @@ def main():
     value = P * world * args.steps / (ms_total * 1e-3)
     ms_step = ms_total / args.steps
     flop_upd = flop_per_update(O, A, B)
-    tf_gemm, gemm_ms, gemm_flop = chain_roofline(torch, pop, P, O, A, B)
+    roofs = {w: chain_launch_roofline(torch, pop, P, O, A, B, w) for w in (0, 1, 2, 3, 4)}
+    for r in roofs.values():
+        r.update(bound="tensor", peak=pk["bf16_tflops"], unit="TFLOP/s", frac=r["achieved"] / pk["bf16_tflops"],
+                 peak_source=pk_src + " (burst)")
     step_tflops = flop_upd * P / (ms_step * 1e-3) / 1e12
     adam_b = adam_bytes_per_update(O, A)
     line = {
         "metric": "fql_member_updates_per_sec", "value": value, "unit": "updates/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": f"lockstep population of {P} alpha-agents per GPU, {args.shape} shape (O={O}, A={A}), "
-                               f"batch {B}, 4x512 MLPs, E=2 critics, 10 flow steps; dataset {args.rows} rows in HBM",
-                   "population_per_gpu": P, "batch": B, "l2": "working set (params+Adam state+dataset, >1 GB) exceeds L2"},
+        "config": update_config(args, O, A),
         "e2e": {"value": P * world * e2e_steps / (e2e_ms * 1e-3), "unit": "updates/s",
                 "h2d_bytes_per_step": int(host.numel() * 4), "d2h_bytes_per_step": int(info_host.nbytes)},
         "gpu_launches": pop.launches_per_step * args.steps,
-        "roofline": {"bound": "tensor", "achieved": tf_gemm, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
-                     "frac": tf_gemm / pk["bf16_tflops"], "traffic": ROOFLINE_LAUNCH_DRAM_BYTES,
-                     "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of this launch, ncu --set full (profiles/r01d_chain_ncu_full_summary.txt)",
-                     "peak_source": pk_src + " (burst)",
-                     "kernel": "fql_chain_kernel<0>: one-step policy forward pass, %d rows x 4 hidden layers x %d members in one "
-                               "launch (%d CTAs of 128 rows), timed alone" % (3 * B, P, P * ((3 * B + 127) // 128)),
-                     "launch_ms": gemm_ms, "flop_per_launch": gemm_flop},
+        # the dominant kernel (layer-chain kernel, forward instantiation) in its widest launch; `traffic` comes from the ncu
+        # capture of this very launch committed under profiles/ (null when the shape is not the profiled one)
+        "roofline": dict(roofs[1], traffic=ROOFLINE_TRAFFIC.get((args.shape, P, B)),
+                         traffic_source="dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, " + ROOFLINE_TRAFFIC_SOURCE),
+        # the other chain launches of the step, same method: the critic's LayerNorm passes are the slowest per FLOP
+        "roofline_other_launches": {"euler_chain": roofs[0], "critic_forward_layernorm_saved": roofs[2],
+                                    "critic_backward_layernorm": roofs[3], "target_critic_forward_layernorm": roofs[4]},
         "step_roofline": {"algorithmic_tflops": step_tflops, "frac_of_sustained_tensor_peak": step_tflops / pk["bf16_tflops_sustained"],
                           "flop_per_member_update": flop_upd, "adam_bytes_per_member_update": adam_b,
                           "adam_hbm_floor_ms_per_step": adam_b * P / (pk["hbm_gbs"] * 1e9) * 1e3},
         "clocks": sampler.summary(),
+        "timed_blocks_ms": block_ms,
+        "env_switches": env_switches,
         "last_info_member0": {k: float(v) for k, v in zip(("critic_loss", "q_mean"), info_last[0][:2])},
     }
     if not args.no_worldmodel:
@@ -487,10 +757,12 @@ def main():
         roll["frac_of_sustained_tensor_peak"] = roll["algorithmic_tflops"] / pk["bf16_tflops_sustained"]
         line["rollout"] = roll
     if not args.no_cpu_baseline:
-        n_upd = 30
+        n_upd = 200   # BASELINE configs[0] asks for 1000 CPU updates; bounded to ~10 s here, rate is per update
         ups, threads = cpu_oracle_updates_per_sec(O, A, B, n_upd)
         line["cpu_baseline"] = {"value": ups, "unit": "updates/s", "cores": threads, "kind": "port",
                                 "sample": f"{n_upd} single-agent updates (alpha=10, batch {B}, {args.shape} shape), torch CPU fp32 oracle"}
+    if sh64 is not None:
+        line["sh64"] = sh64
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
