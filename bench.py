@@ -404,7 +404,7 @@ def worldmodel_bench(torch, np, dev, steps=2000, cpu_steps=100, with_cpu=True):
     return out
 
 
-def sh64_bench(torch, np, dev, rank, world, dist, barrier, n_alphas=64, shape="antsoccer", batch=256, eval_interval=20,
+def sh64_bench(torch, np, dev, rank, world, dist, barrier, n_alphas=64, shape="antsoccer", batch=256, eval_interval=100,
                total_evaluations=50, episodes=256, T=200):
     """BASELINE config 4: successive halving (f=0.5, h=2, total_evaluations=50) over 64 alpha values of a LIVE population
     sharded over the ranks (member i -> rank i mod world), antsoccer shape, batch 256 -- the real Trainer +
@@ -551,7 +551,7 @@ def main():
     ap.add_argument("--workload", default="update", choices=["update", "sh64"],
                     help="update: BASELINE configs[1] (lockstep population update; the headline). sh64: BASELINE configs[3], "
                          "successive halving over 64 alpha values sharded over the ranks (strong scaling).")
-    ap.add_argument("--sh-eval-interval", type=int, default=20)
+    ap.add_argument("--sh-eval-interval", type=int, default=100)
     ap.add_argument("--no-sh64", action="store_true", help="N > 1: skip the successive-halving job appended to the line")
     ap.add_argument("--blocks", type=int, default=5, help="timed blocks of --steps steps; the median block is reported")
     args = ap.parse_args()

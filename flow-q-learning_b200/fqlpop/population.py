@@ -153,6 +153,8 @@ class Population:
 
     def set_active(self, members: Sequence[int]):
         m = np.asarray(list(members), dtype=np.int32)
+        if [int(x) for x in m] == list(self.active):
+            return  # unchanged: keep the captured step graphs (set_active invalidates and re-captures them)
         check(lib.fqlpop_set_active(self._h, m.ctypes.data, len(m)), "fqlpop_set_active")
         self.active = [int(x) for x in m]
 

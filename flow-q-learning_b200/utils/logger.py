@@ -16,9 +16,14 @@ class CsvLogger:
         if resume and path.exists() and path.stat().st_size > 0:
             with open(path, "r") as f:
                 self.header = f.readline().strip().split(",")
+        self.path = path
         self.file = open(path, "a" if resume else "w")
 
     def log(self, row: dict, step=None):
+        if self.file is None:
+            # a stopped experiment that trains again: SuccessiveHalving ranks every candidate ever scored, so a pruned
+            # candidate can re-enter the population after Trainer has called stop() on it
+            self.file = open(self.path, "a")
         row = dict(row)
         if step is not None:
             row["step"] = step
