@@ -1629,6 +1629,18 @@ static bool chain2_eligible(const ChainLaunch& L) {
   return true;
 }
 
+// Which kernel generation runs a chain of this shape: the second-generation kernel (chain16.cu) unless
+// FQLPOP_CHAIN_GEN=1 (first-generation kernels: A/B measurements, parity cross-checks) or FQLPOP_CHAIN2=1/2 forces the
+// N-split cluster kernel. The builders in pop.cu ask the same question: the weight boxes of a backward chain are sized
+// for the kernel that will read them.
+bool chain16_selected_shape(int H, int in_pad, bool ln, int iters) {
+  static const int gen = [] { const char* e = getenv("FQLPOP_CHAIN_GEN"); return e ? atoi(e) : 2; }();
+  if (gen < 2 || H != 512 || in_pad != 64 || (ln && iters > 1)) return false;
+  const char* e = getenv("FQLPOP_CHAIN2");
+  const int m = e ? atoi(e) : 0;
+  return !(m == 1 || (m == 2 && iters > 1));
+}
+
 cudaError_t launch_chain(ChainLaunch& L, int mode, cudaStream_t stream) {
   int grid = 0;
   for (int i = 0; i < L.num_jobs; ++i) grid += L.job[i].m_tiles * L.n_virtual;
@@ -1639,9 +1651,7 @@ cudaError_t launch_chain(ChainLaunch& L, int mode, cudaStream_t stream) {
     for (int l = 0; l < L.job[i].n_layers; ++l)
       if (L.job[i].layer[l].out_gp || L.job[i].layer[l].out_xhat) staged = true;
   L.stages = staged ? kStagesStaged : kStages;
-  // kernel generation: FQLPOP_CHAIN_GEN=1 forces the first-generation kernels (A/B measurements, parity cross-checks)
-  static const int gen = [] { const char* e = getenv("FQLPOP_CHAIN_GEN"); return e ? atoi(e) : 2; }();
-  if (gen >= 2 && chain16_eligible(L) && !(getenv("FQLPOP_CHAIN2") && chain2_eligible(L)))
+  if (chain16_eligible(L) && chain16_selected_shape(L.job[0].H, 64, L.job[0].ln != 0, L.job[0].iters))
     return launch_chain16(L, mode, grid, stream);
   if (chain2_eligible(L)) {
     if (mode == 0) fql_chain2_kernel<0><<<2 * grid, kThreads2, kSmemBytes, stream>>>(L);

@@ -79,6 +79,8 @@ struct ChainLaunch {
   int debug_flags;          // (debug) bit 0: no weight TMA / no stage waits (timing of the bare MMA stream; results are garbage)
   int population_active;    // active members of the whole population on this GPU (picks the kernel: see chain2_eligible)
   int stages;               // weight stages (set by launch_chain: 5, or 3 when the epilogue stages tensors through smem)
+  int staged;               // (chain16) the epilogue stages tensors through shared memory
+  int _pad1;
   long long* trace;         // (dev, debug) clock64 stamps of CTA 0: [0,4096) MMA thread, [4096,8192) epilogue thread 0
   long long* timeline;      // (dev, debug) [0] = record counter; records of 4 words from [8]: start ns, end ns, smid, tag
   long long tag;            // (debug) launch index within the step | first member of the group << 8 | blockIdx << 32
@@ -95,6 +97,9 @@ int finalize_chain(ChainLaunch* L);
 // launch has the production shape (chain16_eligible).
 cudaError_t chain16_init();
 bool chain16_eligible(const ChainLaunch& L);
+bool chain16_selected_shape(int H, int in_pad, bool ln, int iters);
+bool chain16_pair_mode();
+bool chain16_pairs_rows(int M);  // ... and only for jobs with an even number of 128-row tiles  // clusters of two CTAs, tcgen05.mma.cta_group::2 (default; FQLPOP_CHAIN_PAIR=0 disables)
 cudaError_t launch_chain16(ChainLaunch& L, int mode, int grid, cudaStream_t stream);
 
 }  // namespace fqlpop

@@ -49,6 +49,7 @@ constexpr int kStageK = 32;
 constexpr int kTileN = 256;
 constexpr int kFwdBoxBytes = 64 * kStageK * 2;
 constexpr int kBarBytes = 512;
+constexpr int kMaxSlots = 2 * kStages;         // pair mode: 8 KB weight slots
 constexpr int kSmemBytes16 = kActBytes + kActBlockBytes + kStages * kStageBytes + kBarBytes + 1024;
 
 __device__ __forceinline__ float clip1(float x) { return fminf(fmaxf(x, -1.f), 1.f); }
@@ -163,7 +164,11 @@ __device__ __forceinline__ void copy_out_block_colsum(const uint8_t* blk, __nv_b
 // Per-thread view of the epilogue.
 struct Epi {
   uint32_t tmem_row;       // TMEM address of this thread's lane, column 0
-  uint64_t *tmem_full, *blk_full, *drained;
+  uint64_t* tmem_full;     // this CTA's accumulator-ready barriers (the MMA commit is multicast to both CTAs of a pair)
+  // shared::cluster addresses of the barriers the MMA issuer waits on: blk_full[0], drained[0], x0_ready of the pair's
+  // LEADER CTA (of this CTA itself when CTAs are not paired). One arrival per WARP.
+  uint32_t blk_full_a, drained_a, x0_ready_a;
+  bool remote;             // those barriers live in the other CTA of the pair
   uint8_t* act;
   const float* params;     // this virtual member's fp32 parameter block
   float2* ex;              // LayerNorm row-sum exchange [4 column groups][128 rows] (the X0 block, idle by then)
@@ -184,15 +189,26 @@ __device__ __forceinline__ void stamp(const Epi& C, int slot) {
 #endif
 }
 
-// this thread's row of ACT block `blk` is written and its accumulator columns are read: let the tensor core have it
+// this warp's rows of ACT block `blk` are written and its accumulator columns are read: let the tensor core have them.
+// Every lane orders its own generic-proxy writes before the async proxy (the fence also waits for them to be performed),
+// the warp converges, one lane arrives. The barrier may live in the other CTA of the pair; the arrive is deliberately NOT
+// .release.cluster (measured: that form costs ~5000 cycles per layer -- a cluster-scope fence per warp that also drops
+// the L1 lines the bias loads hit): what it publishes is this CTA's own shared memory, read by this CTA's own tensor
+// core, already fenced for the async proxy above.
+__device__ __forceinline__ void arrive_on(const Epi& C, uint32_t addr) {
+  if (C.remote) mbar_arrive_cluster(addr);
+  else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(addr) : "memory");
+}
 __device__ __forceinline__ void publish(const Epi& C, int blk) {
   tc_fence_before();
   fence_proxy_async_smem();
-  mbar_arrive(&C.blk_full[blk]);
+  __syncwarp();
+  if (C.lane == 0) arrive_on(C, C.blk_full_a + 8u * (uint32_t)blk);
 }
 __device__ __forceinline__ void arrive_drained(const Epi& C, int t) {
   tc_fence_before();
-  mbar_arrive(&C.drained[t]);
+  __syncwarp();
+  if (C.lane == 0) arrive_on(C, C.drained_a + 8u * (uint32_t)t);
 }
 __device__ __forceinline__ void wait_full(const Epi& C, int t, uint32_t parity) {
   mbar_wait(&C.tmem_full[t], parity);
@@ -618,7 +634,13 @@ __device__ __forceinline__ void bwd_hidden_layer(const Epi& C, const ChainLayer&
 }
 
 // ===============================================================================================================
-template <int MODE, bool LN>  // MODE 0 = forward / Euler flow, 1 = backward (input-gradient chain)
+// PAIR: CTAs run as clusters of two (the two CTAs carry adjacent 128-row tiles of the same virtual member) and every
+// product is ONE tcgen05.mma.cta_group::2 of M = 256 issued by the leader (cluster rank 0): each CTA stages only HALF of
+// the N columns of every weight stage (8 KB instead of 16 KB per 32-deep k step), so the bytes a CTA has to pull through
+// its shared memory per layer halve -- the weight stream (stage round trip ~3000 cycles, measured) is what bounds the
+// single-CTA kernel. Everything the leader's MMA issuer waits on (ACT blocks, drained accumulators, X0, weight stages)
+// collects arrivals from both CTAs; its commits are multicast to both.
+template <int MODE, bool LN, bool PAIR>  // MODE 0 = forward / Euler flow, 1 = backward (input-gradient chain)
 __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid_constant__ ChainLaunch L) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -626,69 +648,88 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
   uint8_t* x0s = smem + kActBytes;
   uint8_t* stage_base = x0s + kActBlockBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(stage_base + kStages * kStageBytes);
-  uint64_t* full_bar = bars;                    // [kStages]
-  uint64_t* empty_bar = bars + kStages;         // [kStages]
-  uint64_t* tmem_full = bars + 2 * kStages;     // [2] one per 256-column accumulator tile
+  uint64_t* full_bar = bars;                    // [kMaxSlots]
+  uint64_t* empty_bar = bars + kMaxSlots;       // [kMaxSlots]
+  uint64_t* tmem_full = bars + 2 * kMaxSlots;   // [2] one per 256-column accumulator tile
   uint64_t* blk_full = tmem_full + 2;           // [8] ACT k-block j holds the next layer's A operand
-  uint64_t* drained = blk_full + 8;             // [2] every epilogue thread has read its part of accumulator tile t
+  uint64_t* drained = blk_full + 8;             // [2] every epilogue warp has read its part of accumulator tile t
   uint64_t* a0_full = drained + 2;
   uint64_t* x0_ready = a0_full + 1;             // Euler: the X0 block holds the next step's input
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(x0_ready + 1);
+  constexpr int kSlotBytes = PAIR ? kStageBytes / 2 : kStageBytes;
+  constexpr uint32_t kCtas = PAIR ? 2 : 1;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+  const bool leader = rank == 0;
   long long tl_t0 = 0;
   if (L.timeline && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
 
   // ---- tile decode ---------------------------------------------------------------------------------
-  int ji = 0;
+  // work unit = one CTA (a 128-row tile) or one PAIR of CTAs (two adjacent row tiles; the second one may lie beyond
+  // the job's rows: it then computes on zero / foreign rows and stores nothing)
+  const int unit = PAIR ? (int)blockIdx.x >> 1 : (int)blockIdx.x;
+  int ji = 0, ub = 0;
 #pragma unroll 1
-  for (int i = 1; i < L.num_jobs; ++i)
-    if ((int)blockIdx.x >= L.job[i].tile_begin) ji = i;
+  for (int i = 0; i < L.num_jobs; ++i) {
+    const int per = PAIR ? (L.job[i].m_tiles + 1) >> 1 : L.job[i].m_tiles;
+    const int n_units = per * L.n_virtual;
+    if (unit < ub + n_units || i == L.num_jobs - 1) { ji = i; break; }
+    ub += n_units;
+  }
   const ChainJob& J = L.job[ji];
-  const int rel = (int)blockIdx.x - J.tile_begin;
-  const int bidx = rel / J.m_tiles;
-  const int mt = rel - bidx * J.m_tiles;
+  const int per_member = PAIR ? (J.m_tiles + 1) >> 1 : J.m_tiles;
+  const int rel = unit - ub;
+  const int bidx = rel / per_member;
+  const int mt = PAIR ? 2 * (rel - bidx * per_member) + (int)rank : rel - bidx * per_member;
   const int v = L.member_list ? __ldg(L.member_list + bidx) : bidx;
   const int n_layers = J.n_layers;
   const int iters = J.iters;
-  const int n_stages = L.stages;
+  const int n_stages = L.stages;  // weight slots in use
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&J.mapA0);
     for (int i = 0; i < n_layers; ++i) tma_prefetch_desc(&J.mapW[i]);
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < kMaxSlots; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(&tmem_full[0], 1);
     mbar_init(&tmem_full[1], 1);
-    for (int i = 0; i < 8; ++i) mbar_init(&blk_full[i], 128);
-    mbar_init(&drained[0], kEpiWarps * 32);
-    mbar_init(&drained[1], kEpiWarps * 32);
+    for (int i = 0; i < 8; ++i) mbar_init(&blk_full[i], 4 * kCtas);      // one arrival per producing warp
+    mbar_init(&drained[0], kEpiWarps * kCtas);
+    mbar_init(&drained[1], kEpiWarps * kCtas);
     mbar_init(a0_full, 1);
-    mbar_init(x0_ready, 128);
+    mbar_init(x0_ready, 4 * kCtas);
     fence_barrier_init();
     fence_proxy_async_smem();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, 512);
-    tmem_relinquish();
+    if (PAIR) { tmem_alloc_2sm(tmem_slot, 512); tmem_relinquish_2sm(); }
+    else { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
   }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // the peer's barriers are initialised before anything is signalled to them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   if (kRebalanceRegs) {
     if (warp < kFirstEpiWarp) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsLight));
     else asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsEpi));
   }
+  // shared::cluster addresses of the leader's copies of the barriers both CTAs signal
+  const uint32_t full_bar_l = PAIR ? mapa_u32(smem_u32(full_bar), 0) : smem_u32(full_bar);
+  const uint32_t a0_full_l = PAIR ? mapa_u32(smem_u32(a0_full), 0) : smem_u32(a0_full);
 
   if (warp == 0) {
     // ========================================= TMA producer =========================================
+    // (both CTAs of a pair: each streams its own half of every weight stage and its own X0 block; the bytes are counted on
+    // the leader's barriers, which the leader arms with the total)
     if (lane == 0) {
-      mbar_arrive_expect_tx(a0_full, kActBlockBytes);
-      tma_load_3d(x0s, &J.mapA0, a0_full, 0, J.row0 + mt * 128, v);
+      if (leader) mbar_arrive_expect_tx(a0_full, kActBlockBytes * kCtas);
+      if (PAIR) tma_load_3d_2sm(x0s, &J.mapA0, a0_full_l, 0, J.row0 + mt * 128, v);
+      else tma_load_3d(x0s, &J.mapA0, a0_full, 0, J.row0 + mt * 128, v);
       int stage = 0;
       uint32_t phase = 0;
       for (int it = 0; it < iters; ++it) {
@@ -697,23 +738,34 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
           const int k_steps = Ly.k_blocks * 2;
           for (int n0 = 0; n0 < Ly.n_pad; n0 += kTileN) {
             const int ncols = min(kTileN, Ly.n_pad - n0);
+            // columns of this MMA tile staged by THIS CTA: [c0, c0 + mycols). A narrow layer (64 columns) is issued as an
+            // N = 128 product in pair mode: the second CTA's half lies outside the weight tensor and is zero-filled.
+            const int mycols = PAIR ? max(ncols / 2, 64) : ncols;
+            const int c0 = n0 + (int)rank * mycols;
+            const uint32_t my_bytes = MODE == 0 ? (uint32_t)mycols * kStageK * 2
+                                                : (uint32_t)(PAIR ? mycols : Ly.b_box_rows) * kStageK * 2;
             for (int ks = 0; ks < k_steps; ++ks) {
               mbar_wait(&empty_bar[stage], phase ^ 1);
-              uint8_t* sb = stage_base + stage * kStageBytes;
+              uint8_t* sb = stage_base + stage * kSlotBytes;
+              const uint32_t fb = full_bar_l + 8u * (uint32_t)stage;
 #ifdef FQLPOP_DEBUG_SWITCHES
               if (L.debug_flags & 1) {  // (make TRACE=1 only) no weight stream: the MMAs run on whatever the stage holds
-                mbar_arrive(&full_bar[stage]);
+                if (leader) mbar_arrive(&full_bar[stage]);
               } else
 #endif
-              if (MODE == 0) {
-                // W[k][n], n contiguous: boxes of 64 n x 32 k
-                mbar_arrive_expect_tx(&full_bar[stage], ncols * kStageK * 2);
-                for (int b = 0; b < ncols / 64; ++b)
-                  tma_load_3d(sb + b * kFwdBoxBytes, &J.mapW[li], &full_bar[stage], n0 + 64 * b, ks * kStageK, v);
-              } else {
-                // the same array read as B^T: rows = output columns of this GEMM, 32 reduction elements per 64-byte row
-                mbar_arrive_expect_tx(&full_bar[stage], Ly.b_box_rows * kStageK * 2);
-                tma_load_3d(sb, &J.mapW[li], &full_bar[stage], ks * kStageK, n0, v);
+              {
+                if (leader) mbar_arrive_expect_tx(&full_bar[stage], my_bytes * kCtas);
+                if (MODE == 0) {
+                  // W[k][n], n contiguous: boxes of 64 n x 32 k
+                  for (int b = 0; b < mycols / 64; ++b) {
+                    if (PAIR) tma_load_3d_2sm(sb + b * kFwdBoxBytes, &J.mapW[li], fb, c0 + 64 * b, ks * kStageK, v);
+                    else tma_load_3d(sb + b * kFwdBoxBytes, &J.mapW[li], &full_bar[stage], c0 + 64 * b, ks * kStageK, v);
+                  }
+                } else {
+                  // the same array read as B^T: rows = output columns of this GEMM, 32 reduction elements per 64-byte row
+                  if (PAIR) tma_load_3d_2sm(sb, &J.mapW[li], fb, ks * kStageK, c0, v);
+                  else tma_load_3d(sb, &J.mapW[li], &full_bar[stage], ks * kStageK, c0, v);
+                }
               }
               if (++stage == n_stages) { stage = 0; phase ^= 1; }
             }
@@ -723,7 +775,9 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
     }
   } else if (warp == 1) {
     // ========================================= MMA issuer ===========================================
-    // The whole warp walks the loop (waits are warp-uniform); one elected lane issues the MMAs and commits.
+    // The whole warp walks the loop (waits are warp-uniform); one elected lane issues the MMAs and commits. In a pair only
+    // the leader CTA issues.
+    if (leader) {
     int stage = 0;
     uint32_t phase = 0;
     int lc = 0;  // layers issued so far (every layer uses accumulator tile 0)
@@ -764,9 +818,10 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
         int tile = 0;
         for (int n0 = 0; n0 < Ly.n_pad; n0 += kTileN, ++tile) {
           const int ncols = min(kTileN, Ly.n_pad - n0);
-          const uint32_t idesc = make_idesc_bf16(128, (uint32_t)ncols, 0, MODE == 0 ? 1 : 0);
+          const uint32_t n_inst = PAIR ? (uint32_t)max(ncols, 128) : (uint32_t)ncols;
+          const uint32_t idesc = make_idesc_bf16(PAIR ? 256 : 128, n_inst, 0, MODE == 0 ? 1 : 0);
           const uint32_t tmem_d = tmem_base + n0;
-          // the accumulator tile must have been read by every epilogue thread
+          // the accumulator tile must have been read by every epilogue warp (of both CTAs)
           {
             TR_T0();
             if (tile == 0) {
@@ -793,11 +848,20 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
               tc_fence_after();
               if (elect_one()) {
                 const uint64_t ad = adesc0 + (uint64_t)(kb * (kActBlockBytes >> 4) + h * 4);
-                const uint64_t bd = bdesc0 + (uint64_t)(stage * (kStageBytes >> 4));
-                umma_bf16(tmem_d, ad, bd, idesc, (kb != 0 || h != 0) ? 1u : 0u);
-                umma_bf16(tmem_d, ad + 2, bd + kBStep, idesc, 1u);
-                umma_commit(&empty_bar[stage]);
-                if (kb == nkb - 1 && h == 1) umma_commit(&tmem_full[tile]);
+                const uint64_t bd = bdesc0 + (uint64_t)(stage * (kSlotBytes >> 4));
+                const uint32_t acc = (kb != 0 || h != 0) ? 1u : 0u;
+                const bool last = kb == nkb - 1 && h == 1;
+                if (PAIR) {
+                  umma_bf16_2sm(tmem_d, ad, bd, idesc, acc);
+                  umma_bf16_2sm(tmem_d, ad + 2, bd + kBStep, idesc, 1u);
+                  umma_commit_2sm(&empty_bar[stage], 3);
+                  if (last) umma_commit_2sm(&tmem_full[tile], 3);
+                } else {
+                  umma_bf16(tmem_d, ad, bd, idesc, acc);
+                  umma_bf16(tmem_d, ad + 2, bd + kBStep, idesc, 1u);
+                  umma_commit(&empty_bar[stage]);
+                  if (last) umma_commit(&tmem_full[tile]);
+                }
               }
               __syncwarp();
               if (++stage == n_stages) { stage = 0; phase ^= 1; }
@@ -814,6 +878,7 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
 #endif
       }
     }
+    }
   } else if (warp >= kFirstEpiWarp) {
     // ========================================= epilogue =============================================
     const int q = warp & 3;              // TMEM lane quarter this warp may access
@@ -823,7 +888,11 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
     const bool row_ok = grow < J.M;
     Epi C;
     C.tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-    C.tmem_full = tmem_full; C.blk_full = blk_full; C.drained = drained;
+    C.tmem_full = tmem_full;
+    C.remote = PAIR && !leader;
+    C.blk_full_a = C.remote ? mapa_u32(smem_u32(blk_full), 0) : smem_u32(blk_full);
+    C.drained_a = C.remote ? mapa_u32(smem_u32(drained), 0) : smem_u32(drained);
+    C.x0_ready_a = C.remote ? mapa_u32(smem_u32(x0_ready), 0) : smem_u32(x0_ready);
     C.act = act;
     C.params = J.params + (long long)v * J.S;
     C.ex = reinterpret_cast<float2*>(x0s);
@@ -832,7 +901,7 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
     C.rs_off = (long long)v * J.pass_rs + grow;
     C.part_off = (long long)v * J.part_ms + (long long)(mt * 4 + q) * J.H;
     C.ln_eps = J.ln_eps;
-    C.stg = n_stages == kStages ? nullptr : stage_base + kStagesStaged * kStageBytes + (warp - kFirstEpiWarp) * kStgBytes;
+    C.stg = L.staged ? stage_base + kStagesStaged * kStageBytes + (warp - kFirstEpiWarp) * kStgBytes : nullptr;
     const int grow0 = mt * 128 + q * 32;
     C.wrow = (long long)v * J.pass_ms + (long long)grow0 * J.H;
     C.wdz = (long long)v * J.dz_ms + (long long)grow0 * J.H;
@@ -897,7 +966,8 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
             }
             tc_fence_before();
             fence_proxy_async_smem();
-            mbar_arrive(x0_ready);
+            __syncwarp();
+            if (lane == 0) arrive_on(C, C.x0_ready_a);
           }
           arrive_drained(C, 0);
         } else {  // CL_DINPUT: gradient with respect to the (padded, <= 64 wide) network input, fp32
@@ -928,9 +998,11 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
 
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // no CTA leaves (or frees TMEM) while its peer may still signal it or run MMAs into it
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    if (PAIR) tmem_dealloc_2sm(tmem_base, 512);
+    else tmem_dealloc(tmem_base, 512);
   }
   if (L.timeline && threadIdx.x == 0) {
     long long t1;
@@ -947,15 +1019,30 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
 
 }  // namespace
 
-cudaError_t chain16_init() {
-  cudaError_t e = cudaFuncSetAttribute(fql_chain16_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes16);
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(fql_chain16_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes16);
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(fql_chain16_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes16);
-  if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(fql_chain16_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes16);
+template <int MODE, bool LN, bool PAIR>
+static cudaError_t set_smem() {
+  return cudaFuncSetAttribute(fql_chain16_kernel<MODE, LN, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes16);
 }
+cudaError_t chain16_init() {
+  cudaError_t e;
+  if ((e = set_smem<0, false, false>()) != cudaSuccess) return e;
+  if ((e = set_smem<0, true, false>()) != cudaSuccess) return e;
+  if ((e = set_smem<1, false, false>()) != cudaSuccess) return e;
+  if ((e = set_smem<1, true, false>()) != cudaSuccess) return e;
+  if ((e = set_smem<0, false, true>()) != cudaSuccess) return e;
+  if ((e = set_smem<0, true, true>()) != cudaSuccess) return e;
+  if ((e = set_smem<1, false, true>()) != cudaSuccess) return e;
+  return set_smem<1, true, true>();
+}
+
+// Pair mode (cta_group::2) is the default; FQLPOP_CHAIN_PAIR=0 runs the same kernel one CTA per row tile. Read once: the
+// weight tensor maps of a backward chain are encoded for one mode or the other (pop.cu asks chain16_pair_mode()).
+bool chain16_pair_mode() {
+  static const bool on = [] { const char* e = getenv("FQLPOP_CHAIN_PAIR"); return e ? atoi(e) != 0 : true; }();
+  return on;
+}
+// a job's row tiles are paired only when there is an even number of them (no half-empty pairs)
+bool chain16_pairs_rows(int M) { return (((M + 127) / 128) & 1) == 0; }
 
 // The 16-warp kernel covers the production shape: every hidden layer 512 wide, reductions of 64 (first layer) or 512,
 // narrow layers (Euler head, input gradient) of one 64-column block.
@@ -968,7 +1055,7 @@ bool chain16_eligible(const ChainLaunch& L) {
     for (int l = 0; l < j.n_layers; ++l) {
       const ChainLayer& y = j.layer[l];
       if (y.kind == CL_HIDDEN && y.n_pad != 512) return false;
-      if (y.kind != CL_HIDDEN && y.n_pad > kTileN) return false;
+      if (y.kind != CL_HIDDEN && y.n_pad != 64) return false;
       if (y.a_from_x0 ? y.k_blocks != 1 : y.k_blocks != 8) return false;
       if (y.a_from_x0 && l != 0) return false;
     }
@@ -976,16 +1063,38 @@ bool chain16_eligible(const ChainLaunch& L) {
   return true;
 }
 
-cudaError_t launch_chain16(ChainLaunch& L, int mode, int grid, cudaStream_t stream) {
-  const bool ln = L.job[0].ln != 0;
-  if (mode == 0) {
-    if (ln) fql_chain16_kernel<0, true><<<grid, kThreads16, kSmemBytes16, stream>>>(L);
-    else fql_chain16_kernel<0, false><<<grid, kThreads16, kSmemBytes16, stream>>>(L);
-  } else {
-    if (ln) fql_chain16_kernel<1, true><<<grid, kThreads16, kSmemBytes16, stream>>>(L);
-    else fql_chain16_kernel<1, false><<<grid, kThreads16, kSmemBytes16, stream>>>(L);
+template <int MODE, bool LN>
+static cudaError_t launch_variant(ChainLaunch& L, bool pair, int units, cudaStream_t stream) {
+  if (!pair) {
+    fql_chain16_kernel<MODE, LN, false><<<units, kThreads16, kSmemBytes16, stream>>>(L);
+    return cudaGetLastError();
   }
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * units);
+  cfg.blockDim = dim3(kThreads16);
+  cfg.dynamicSmemBytes = kSmemBytes16;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, fql_chain16_kernel<MODE, LN, true>, L);
+}
+
+cudaError_t launch_chain16(ChainLaunch& L, int mode, int grid, cudaStream_t stream) {
+  (void)grid;
+  const bool ln = L.job[0].ln != 0;
+  bool pair = chain16_pair_mode();
+  for (int i = 0; i < L.num_jobs; ++i) pair = pair && chain16_pairs_rows(L.job[i].M);
+  int units = 0;
+  for (int i = 0; i < L.num_jobs; ++i)
+    units += (pair ? (L.job[i].m_tiles + 1) / 2 : L.job[i].m_tiles) * L.n_virtual;
+  // weight slots: 16 KB each (8 KB in pair mode); launches that stage tensors through shared memory give up the last 32 KB
+  L.staged = L.stages != kStages;
+  L.stages = (L.staged ? kStagesStaged : kStages) * (pair ? 2 : 1);
+  if (mode == 0) return ln ? launch_variant<0, true>(L, pair, units, stream) : launch_variant<0, false>(L, pair, units, stream);
+  return ln ? launch_variant<1, true>(L, pair, units, stream) : launch_variant<1, false>(L, pair, units, stream);
 }
 
 }  // namespace fqlpop

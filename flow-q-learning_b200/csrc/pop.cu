@@ -268,6 +268,16 @@ struct Builder {
 // ---------------------------------------------------------------------------------------------------
 void record(Plan* pl, cudaEvent_t* out, cudaStream_t s);
 
+// Holds a stream for `ns` nanoseconds (one thread, sleeping): staggers the member groups of a multi-step call.
+__global__ void delay_kernel(long long ns) {
+  long long t0, t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  do {
+    __nanosleep(2000);
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  } while (t - t0 < ns);
+}
+
 struct ChainBuilder {
   Population* P;
   std::string* err;
@@ -392,11 +402,13 @@ struct ChainBuilder {
     j.part_ms = (long long)bw.part_rows * N.H;
     tmap(&j.mapA0, bw.dout, kHeadPad, bw.M, bw.V, kHeadPad, (long long)bw.M * kHeadPad, 128);
     const long long roff = (long long)row0 * N.H;
+    // rows of a weight box = output columns one CTA stages per k step: 256, or 128 when CTAs run as cta_group::2 pairs
+    const int cap = (chain16_selected_shape(N.H, N.in_pad, N.ln != 0, 1) && chain16_pair_mode() && chain16_pairs_rows(bw.M)) ? 128 : 256;
     int s = 0;
     for (int l = N.n_hidden; l >= 1; --l, ++s) {
       const int Kd = N.N(l);
       ChainLayer& y = j.layer[s];
-      y.b_box_rows = N.K(l) < 256 ? N.K(l) : 256;
+      y.b_box_rows = N.K(l) < cap ? N.K(l) : cap;
       tmap64(&j.mapW[s], ar.shadow + N.offW[l], Kd, N.K(l), ar.V, Kd, N.S, y.b_box_rows);
       y.kind = CL_HIDDEN; y.k_blocks = Kd / 64; y.n_pad = N.H; y.a_from_x0 = s == 0;
       y.off_g = N.offg[l - 1];
@@ -416,7 +428,7 @@ struct ChainBuilder {
     }
     if (dinput_out) {
       ChainLayer& y = j.layer[s];
-      y.b_box_rows = N.in_pad < 256 ? N.in_pad : 256;
+      y.b_box_rows = N.in_pad < cap ? N.in_pad : cap;
       tmap64(&j.mapW[s], ar.shadow + N.offW[0], N.H, N.in_pad, ar.V, N.H, N.S, y.b_box_rows);
       y.kind = CL_DINPUT; y.k_blocks = N.H / 64; y.n_pad = N.in_pad; y.a_from_x0 = 0;
       y.out_f32 = dinput_out; y.out_ld = N.in_pad;
@@ -877,6 +889,15 @@ static int run_plan(Population* P, bool train, int n_steps, cudaStream_t stream,
   // all n_steps of group 0 first would block the host inside group 0's loop and serialise the groups for large n_steps
   // (the Trainer steps in chunks of log_interval = 5000).
   for (GroupPlan& gp : pl->groups) cudaStreamWaitEvent(gp.s[0], e_in, 0);
+  // Multi-step calls start the groups STAGGERED: groups that start together stay in phase, and then every group reaches
+  // its optimizer kernels (HBM-bound, no tensor work) at the same time while nobody runs layer chains (tensor-bound, no
+  // HBM traffic) -- measured as alternating ~450 us chain / ~400 us optimizer phases. Out of phase, one group's optimizer
+  // traffic overlaps the other groups' chains. FQLPOP_STAGGER_US = offset between consecutive groups (0 disables).
+  static const int stagger_us = [] { const char* e = getenv("FQLPOP_STAGGER_US"); return e ? atoi(e) : 200; }();
+  if (train && !eager && stagger_us > 0 && n_steps >= 8 && pl->groups.size() > 1) {
+    for (size_t g = 1; g < pl->groups.size(); ++g)
+      delay_kernel<<<1, 1, 0, pl->groups[g].s[0]>>>((long long)g * stagger_us * 1000ll);
+  }
   if (eager) {
     for (GroupPlan& gp : pl->groups) {
       if (rc) break;

@@ -49,3 +49,24 @@ for g in sorted(set(grp)):
 r = r[tag < 10]
 busy = (r[:, 1] - r[:, 0]).sum() / 1e3
 print(f"chain CTA-us total {busy:.0f}; / 148 SMs = {busy / 148:.1f} us; SMs used {len(set(r[:, 2]))}")
+
+# ---- occupancy profile (TL_PROFILE=bin_us): chain / adam / head CTAs resident per time bin over the recorded window
+if os.environ.get("TL_PROFILE"):
+    binus = float(os.environ["TL_PROFILE"])
+    r = buf[:cnt.value]
+    t0 = r[:, 0].min(); span = (r[:, 1].max() - t0) / 1e3
+    nb = int(span / binus) + 1
+    tag = r[:, 3] & 0xFF
+    kinds = {"chain": tag < 10, "head": (tag >= 20) & (tag < 30), "adam": tag >= 30}
+    prof = {k: np.zeros(nb) for k in kinds}
+    for k, m in kinds.items():
+        for s, e in zip((r[m, 0] - t0) / 1e3, (r[m, 1] - t0) / 1e3):
+            b0, b1 = int(s / binus), int(e / binus)
+            for b in range(b0, b1 + 1):
+                lo, hi = max(s, b * binus), min(e, (b + 1) * binus)
+                if hi > lo:
+                    prof[k][b] += (hi - lo) / binus
+    print(f"occupancy profile, {binus} us bins, mean resident CTAs (chain CTAs fill an SM; adam CTAs fill an SM; heads do not)")
+    for b in range(nb):
+        print(f"{b * binus:8.0f} us  chain {prof['chain'][b]:6.1f}  adam {prof['adam'][b]:6.1f}  head {prof['head'][b]:6.1f}")
+    print("totals CTA-us:", {k: float(v.sum() * binus) for k, v in prof.items()}, "span", span)
