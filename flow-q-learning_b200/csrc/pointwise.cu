@@ -617,103 +617,6 @@ __global__ void __launch_bounds__(kAdamThreads, 1) adam_kernel(const AdamArgs a)
   if (tl_on) tl_record(a.timeline, tl_t0, a.tag);
 }
 
-// ------------------------------------------------------------------------------------------------------
-// The same update as a STREAMING kernel: the five input arrays travel global -> shared by 1-D bulk copies (cp.async.bulk,
-// the TMA engine) through a ring of mbarrier-guarded stages (~190 KB per SM in flight, no registers or L1 miss slots tied
-// up while the bytes travel); eight update warps each own a fixed slice of every tile, read it from shared memory, hand the
-// stage back (one arrival per warp, no CTA-wide barrier) and write the results straight to global memory with coalesced
-// 16-byte stores (stores need no slot to wait in). CTA = 1 producer warp + 8 update warps.
-// ------------------------------------------------------------------------------------------------------
-constexpr int kAdamTile = 2048;                       // parameters per tile: 2 float4 per lane and array
-constexpr int kAdamArrayBytes = kAdamTile * 4;        // 8 KB
-constexpr int kAdamStageBytes = 5 * kAdamArrayBytes;  // g | theta | mu | nu | target
-constexpr int kAdamStages = 5;                        // 200 KB
-constexpr int kAdamTmaThreads = 32 + 256;
-constexpr int kAdamTmaSmem = kAdamStages * kAdamStageBytes + 256 + 128;
-
-__global__ void __launch_bounds__(kAdamTmaThreads, 1) adam_stream_kernel(const AdamArgs a) {
-  extern __shared__ uint8_t adam_smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(adam_smem_raw) + 127) & ~uintptr_t(127));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kAdamStages * kAdamStageBytes);
-  uint64_t* empty = full + kAdamStages;
-  long long tl_t0 = 0;
-  const bool tl_on = a.timeline && threadIdx.x == 0;
-  if (tl_on) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < kAdamStages; ++s) {
-      mbar_init(&full[s], 1);
-      mbar_init(&empty[s], 8);   // one arrival per update warp
-    }
-    fence_barrier_init();
-    fence_proxy_async_smem();
-  }
-  __syncthreads();
-  const int tiles_per = (int)((a.S + kAdamTile - 1) / kAdamTile);
-  const long long total = (long long)a.n_virtual * tiles_per;
-  const bool has_t = a.target != nullptr;
-  // tile t -> (global element offset, element count, member)
-  auto locate = [&](long long t, long long& off, int& n, int& p) {
-    const int av = (int)(t / tiles_per);
-    const int i = (int)(t - (long long)av * tiles_per);
-    const int am = av / a.nb, e = av - am * a.nb;
-    p = a.member_list[am];
-    off = ((long long)p * a.nb + e) * a.S + (long long)i * kAdamTile;
-    n = (int)min((long long)kAdamTile, a.S - (long long)i * kAdamTile);
-  };
-  if (warp == 0) {
-    if (lane == 0) {
-      const uint64_t pol = l2_policy_evict_first();   // optimizer state is touched once per step: do not let it push the
-                                                      // bf16 shadow weights (which the chains stream from L2) out
-      int s = 0;
-      uint32_t ph = 0;
-      for (long long t = blockIdx.x; t < total; t += gridDim.x) {
-        long long off; int n, p;
-        locate(t, off, n, p);
-        mbar_wait(&empty[s], ph ^ 1);
-        uint8_t* st = smem + s * kAdamStageBytes;
-        const uint32_t bytes = (uint32_t)n * 4;
-        mbar_arrive_expect_tx(&full[s], bytes * (has_t ? 5u : 4u));
-        bulk_load_hint(st, a.grad + off, bytes, &full[s], pol);
-        bulk_load_hint(st + 1 * kAdamArrayBytes, a.theta + off, bytes, &full[s], pol);
-        bulk_load_hint(st + 2 * kAdamArrayBytes, a.mu + off, bytes, &full[s], pol);
-        bulk_load_hint(st + 3 * kAdamArrayBytes, a.nu + off, bytes, &full[s], pol);
-        if (has_t) bulk_load_hint(st + 4 * kAdamArrayBytes, a.target + off, bytes, &full[s], pol);
-        if (++s == kAdamStages) { s = 0; ph ^= 1; }
-      }
-    }
-  } else {
-    const int w = warp - 1;   // 0..7: floats [256 w, 256 w + 256) of every tile, as two float4 per lane (coalesced)
-    int s = 0;
-    uint32_t ph = 0;
-    for (long long t = blockIdx.x; t < total; t += gridDim.x) {
-      long long off; int n, p;
-      locate(t, off, n, p);
-      const float ibc1 = 1.f / a.adam_bc[2 * p], ibc2 = 1.f / a.adam_bc[2 * p + 1];
-      const float4* st = reinterpret_cast<const float4*>(smem + s * kAdamStageBytes);
-      mbar_wait(&full[s], ph);
-      float4 g[2], th[2], m[2], v[2], tg[2];
-      int q[2];
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        q[u] = w * 64 + u * 32 + lane;          // float4 index within the tile
-        g[u] = st[q[u]];
-        th[u] = st[kAdamTile / 4 + q[u]];
-        m[u] = st[2 * (kAdamTile / 4) + q[u]];
-        v[u] = st[3 * (kAdamTile / 4) + q[u]];
-        tg[u] = has_t ? st[4 * (kAdamTile / 4) + q[u]] : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-      __syncwarp();                             // every lane holds its values: the stage may be refilled
-      if (lane == 0) mbar_arrive(&empty[s]);
-#pragma unroll
-      for (int u = 0; u < 2; ++u)
-        if (q[u] * 4 < n) adam_quad(a, off + 4ll * q[u], ibc1, ibc2, g[u], th[u], m[u], v[u], tg[u]);
-      if (++s == kAdamStages) { s = 0; ph ^= 1; }
-    }
-  }
-  if (tl_on) tl_record(a.timeline, tl_t0, a.tag);
-}
-
 // theta -> bf16 shadow (after importing parameters)
 __global__ void __launch_bounds__(256) to_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
                                                       long long n4) {
@@ -918,19 +821,12 @@ static void launch_adam_one(Population* P, Arena& ar, cudaStream_t s) {
   a.timeline = P->timeline;
   a.tag = (&ar == &P->critic ? 30 : (&ar == &P->bc ? 31 : 32)) | ((long long)P->g_off << 8);
   a.n_virtual = P->cur_n() * ar.L.nb;
-  // FQLPOP_ADAM_STREAM=0: the register-path kernel (32 CTAs x 1024 threads) instead of the bulk-copy streaming kernel
-  static const int stream_mode = [] { const char* e = getenv("FQLPOP_ADAM_STREAM"); return e ? atoi(e) : 1; }();
-  static const int ctas = [] { const char* e = getenv("FQLPOP_ADAM_CTAS"); return e ? atoi(e) : 0; }();
-  if (stream_mode) {
-    // CTAs in proportion to the bytes (one per ~2 virtual-member blocks), between 4 and 32: each streams at the SM's L2 port rate
-    static const int mb_per_cta = [] { const char* e = getenv("FQLPOP_ADAM_MB_PER_CTA"); return e ? atoi(e) : 16; }();
-    const long long bytes = (long long)a.n_virtual * a.S * (a.target ? 40 : 30);
-    int n = ctas > 0 ? ctas : (int)(bytes / ((long long)mb_per_cta << 20));
-    n = n < 4 ? 4 : (n > 32 ? 32 : n);
-    adam_stream_kernel<<<n, kAdamTmaThreads, kAdamTmaSmem, s>>>(a);
-  } else {
-    adam_kernel<<<ctas > 0 ? ctas : 32, kAdamThreads, 0, s>>>(a);
-  }
+  // Tried and dropped in round 2 (profiles/r02_adam_experiments.txt): a bulk-copy (cp.async.bulk) streaming variant with a
+  // small SM footprint -- it moves fewer bytes per SM and second than this register-path kernel (49 vs 68-85 GB/s per
+  // SM at 8-12 CTAs per launch), and the step time is insensitive to the CTA count / group phasing anyway: the optimizer's
+  // ~310 us per step is its HBM time (1.8 GB at ~5.8 TB/s) and adds to the chain time whatever the schedule.
+  static const int ctas = [] { const char* e = getenv("FQLPOP_ADAM_CTAS"); return e ? atoi(e) : 32; }();
+  adam_kernel<<<ctas > 0 ? ctas : 32, kAdamThreads, 0, s>>>(a);
 }
 void launch_adam(Population* P, int which, cudaStream_t s) {
   launch_adam_one(P, which == 0 ? P->critic : (which == 1 ? P->bc : P->pi), s);
@@ -994,8 +890,6 @@ int pointwise_init() {
     e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (e != cudaSuccess) return (int)e;
   }
-  e = cudaFuncSetAttribute(adam_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAdamTmaSmem);
-  if (e != cudaSuccess) return (int)e;
   return 0;
 }
 

@@ -268,16 +268,6 @@ struct Builder {
 // ---------------------------------------------------------------------------------------------------
 void record(Plan* pl, cudaEvent_t* out, cudaStream_t s);
 
-// Holds a stream for `ns` nanoseconds (one thread, sleeping): staggers the member groups of a multi-step call.
-__global__ void delay_kernel(long long ns) {
-  long long t0, t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-  do {
-    __nanosleep(2000);
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  } while (t - t0 < ns);
-}
-
 struct ChainBuilder {
   Population* P;
   std::string* err;
@@ -889,15 +879,6 @@ static int run_plan(Population* P, bool train, int n_steps, cudaStream_t stream,
   // all n_steps of group 0 first would block the host inside group 0's loop and serialise the groups for large n_steps
   // (the Trainer steps in chunks of log_interval = 5000).
   for (GroupPlan& gp : pl->groups) cudaStreamWaitEvent(gp.s[0], e_in, 0);
-  // Multi-step calls start the groups STAGGERED: groups that start together stay in phase, and then every group reaches
-  // its optimizer kernels (HBM-bound, no tensor work) at the same time while nobody runs layer chains (tensor-bound, no
-  // HBM traffic) -- measured as alternating ~450 us chain / ~400 us optimizer phases. Out of phase, one group's optimizer
-  // traffic overlaps the other groups' chains. FQLPOP_STAGGER_US = offset between consecutive groups (0 disables).
-  static const int stagger_us = [] { const char* e = getenv("FQLPOP_STAGGER_US"); return e ? atoi(e) : 200; }();
-  if (train && !eager && stagger_us > 0 && n_steps >= 8 && pl->groups.size() > 1) {
-    for (size_t g = 1; g < pl->groups.size(); ++g)
-      delay_kernel<<<1, 1, 0, pl->groups[g].s[0]>>>((long long)g * stagger_us * 1000ll);
-  }
   if (eager) {
     for (GroupPlan& gp : pl->groups) {
       if (rc) break;
