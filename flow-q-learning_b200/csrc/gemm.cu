@@ -230,7 +230,7 @@ fql_gemm_kernel(const __grid_constant__ GemmLaunch L) {
     float* part1 = epi_scratch + 4 * ncols_total;          // [4][ncols_total]
     float* part2 = epi_scratch + 8 * ncols_total;          // [4][ncols_total]
 
-    if (kind == EPI_STORE_F32 || kind == EPI_STORE_BF16 || kind == EPI_FWD || kind == EPI_DGRAD) {
+    if (kind == EPI_STORE_F32 || kind == EPI_STORE_BF16 || kind == EPI_FWD || kind == EPI_DGRAD || kind == EPI_ADAM) {
       // ---------------- single-pass epilogues ----------------
       for (int sub = 0; sub < N_SUB; ++sub) {
         const int ncols = sub_cols(sub);
@@ -246,7 +246,71 @@ fql_gemm_kernel(const __grid_constant__ GemmLaunch L) {
           float v[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          if (kind == EPI_STORE_F32) {
+          if (kind == EPI_ADAM) {
+            // Weight-gradient tile -> optimizer update in place (optax.adam + Polyak + bf16 shadow refresh),
+            // without the gradient ever travelling to HBM and back. Same transpose as the plain store below, then every
+            // lane owns 16 contiguous bytes of 8 rows: theta / mu / nu (/ target) are read and written with coalesced
+            // 16-byte accesses, 4 rows' worth of loads in flight per lane.
+            if (N_SUB == 1) {
+              const AdamTile& T = E.adam;
+              uint8_t* stg = stage_base + q * 4096;
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                *reinterpret_cast<float4*>(stg + lane * 128 + ((i ^ (lane & 7)) << 4)) =
+                    make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+              __syncwarp();
+              const int rows_valid = G.M - (mt * kBlockM + q * 32);
+              const long long base = member * E.out_f32.ms + (long long)(mt * kBlockM + q * 32) * E.out_f32.ld + col;
+              const int ch = lane & 7, rsub = lane >> 3;
+              const int pm = member / T.nb;
+              const float ibc1 = 1.f / __ldg(T.adam_bc + 2 * pm), ibc2 = 1.f / __ldg(T.adam_bc + 2 * pm + 1);
+              const bool has_t = T.target != nullptr;
+#pragma unroll
+              for (int half = 0; half < 2; ++half) {
+                float4 th[4], m[4], vv[4], tg[4];
+                long long o[4];
+                bool ok[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const int r = (half * 4 + j) * 4 + rsub;
+                  ok[j] = r < rows_valid;
+                  o[j] = base + (long long)(ok[j] ? r : 0) * E.out_f32.ld + ch * 4;
+                  th[j] = __ldcs(reinterpret_cast<const float4*>(T.theta + o[j]));
+                  m[j] = __ldcs(reinterpret_cast<const float4*>(T.mu + o[j]));
+                  vv[j] = __ldcs(reinterpret_cast<const float4*>(T.nu + o[j]));
+                  tg[j] = has_t ? __ldcs(reinterpret_cast<const float4*>(T.target + o[j])) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const int r = (half * 4 + j) * 4 + rsub;
+                  const float4 g = *reinterpret_cast<const float4*>(stg + r * 128 + ((ch ^ (r & 7)) << 4));
+                  if (!ok[j]) continue;
+#define ADAM1(c)                                                                \
+  m[j].c = T.b1 * m[j].c + (1.f - T.b1) * g.c;                                  \
+  vv[j].c = T.b2 * vv[j].c + (1.f - T.b2) * g.c * g.c;                          \
+  th[j].c = th[j].c - T.lr * (m[j].c * ibc1) / (sqrtf(vv[j].c * ibc2) + T.eps);
+                  ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
+#undef ADAM1
+                  __stcs(reinterpret_cast<float4*>(T.theta + o[j]), th[j]);
+                  __stcs(reinterpret_cast<float4*>(T.mu + o[j]), m[j]);
+                  __stcs(reinterpret_cast<float4*>(T.nu + o[j]), vv[j]);
+                  *reinterpret_cast<uint2*>(T.shadow + o[j]) =
+                      make_uint2(pack_bf16x2(th[j].x, th[j].y), pack_bf16x2(th[j].z, th[j].w));
+                  if (has_t) {
+                    tg[j].x = T.tau * th[j].x + (1.f - T.tau) * tg[j].x;
+                    tg[j].y = T.tau * th[j].y + (1.f - T.tau) * tg[j].y;
+                    tg[j].z = T.tau * th[j].z + (1.f - T.tau) * tg[j].z;
+                    tg[j].w = T.tau * th[j].w + (1.f - T.tau) * tg[j].w;
+                    __stcs(reinterpret_cast<float4*>(T.target + o[j]), tg[j]);
+                    *reinterpret_cast<uint2*>(T.tshadow + o[j]) =
+                        make_uint2(pack_bf16x2(tg[j].x, tg[j].y), pack_bf16x2(tg[j].z, tg[j].w));
+                  }
+                  if (T.keep_grad) *reinterpret_cast<float4*>(E.out_f32.p + o[j]) = g;
+                }
+              }
+              __syncwarp();
+            }
+          } else if (kind == EPI_STORE_F32) {
             if (N_SUB == 1) {
               // One tile per CTA: once the accumulator is complete the operand stages are idle. A thread owns a ROW, so
               // storing its 128 bytes directly costs 32 partial-line requests per warp instruction; transposing the

@@ -28,6 +28,20 @@ enum EpiKind : int {
   EPI_FWD_LN = 3,      // as EPI_FWD followed by LayerNorm over the full 512-wide row (needs N_SUB = 4)
   EPI_DGRAD = 4,       // dz = acc * gp; store dz (bf16); column sums of dz -> bias-gradient partials
   EPI_DGRAD_LN = 5,    // LayerNorm backward on acc, then as EPI_DGRAD; also gamma/beta gradient partials
+  EPI_ADAM = 6,        // acc = dL/dW: Adam + Polyak + bf16 shadow refresh of that weight tile, straight out of the accumulator
+                       // (the gradient itself is stored only when adam.keep_grad is set)
+};
+
+// Optimizer state of the weight tile a weight-gradient GEMM produces (EPI_ADAM). All arrays share the gradient's layout
+// (out_f32: per-virtual-member stride ms, leading dimension ld) and are already offset to the leaf.
+struct AdamTile {
+  float *theta, *mu, *nu, *target;        // target == nullptr: no Polyak copy (actor networks)
+  __nv_bfloat16 *shadow, *tshadow;
+  const float* adam_bc;                   // [population][2]: 1 - b1^t, 1 - b2^t of the current step
+  int nb;                                 // virtual members per population member (adam_bc is indexed by member / nb)
+  int keep_grad;                          // also write the gradient to out_f32 (steps whose gradients are read back)
+  float lr, b1, b2, eps, tau;
+  int _pad;
 };
 enum ActKind : int { ACT_NONE = 0, ACT_GELU = 1, ACT_RELU = 2 };
 
@@ -59,6 +73,7 @@ struct EpiParams {
   MPtr<float> out_dbias_part;      // DGRAD*: [P][m_tiles][N] column sums of dz (optional)
   MPtr<float> out_dgamma_part;     // DGRAD_LN: [P][m_tiles][N]
   MPtr<float> out_dbeta_part;      // DGRAD_LN: [P][m_tiles][N]
+  AdamTile adam;                   // EPI_ADAM
 };
 
 struct GemmGroup {

@@ -617,6 +617,32 @@ __global__ void __launch_bounds__(kAdamThreads, 1) adam_kernel(const AdamArgs a)
   if (tl_on) tl_record(a.timeline, tl_t0, a.tag);
 }
 
+// The same update for the leaves no weight-gradient GEMM produces (biases, LayerNorm scale / bias): the kernels are
+// updated inside the GEMM epilogue (gemm.cu, EPI_ADAM), these few thousand parameters per virtual member here.
+constexpr int kMaxAdamSegs = 32;
+struct AdamLeafArgs {
+  AdamArgs a;
+  long long seg_off[kMaxAdamSegs];
+  int seg_n[kMaxAdamSegs];
+};
+__global__ void __launch_bounds__(128) adam_leaves_kernel(const __grid_constant__ AdamLeafArgs L) {
+  const AdamArgs& a = L.a;
+  const int av = blockIdx.y;
+  const int am = av / a.nb, e = av - am * a.nb;
+  const int p = a.member_list[am];
+  const float ibc1 = 1.f / a.adam_bc[2 * p], ibc2 = 1.f / a.adam_bc[2 * p + 1];
+  const long long base = ((long long)p * a.nb + e) * a.S + L.seg_off[blockIdx.x];
+  for (int i = threadIdx.x; i < L.seg_n[blockIdx.x] / 4; i += 128) {
+    const long long o = base + 4ll * i;
+    const float4 g = *reinterpret_cast<const float4*>(a.grad + o);
+    const float4 th = *reinterpret_cast<const float4*>(a.theta + o);
+    const float4 m = *reinterpret_cast<const float4*>(a.mu + o);
+    const float4 v = *reinterpret_cast<const float4*>(a.nu + o);
+    const float4 tg = a.target ? *reinterpret_cast<const float4*>(a.target + o) : make_float4(0.f, 0.f, 0.f, 0.f);
+    adam_quad(a, o, ibc1, ibc2, g, th, m, v, tg);
+  }
+}
+
 // theta -> bf16 shadow (after importing parameters)
 __global__ void __launch_bounds__(256) to_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
                                                       long long n4) {
@@ -830,6 +856,31 @@ static void launch_adam_one(Population* P, Arena& ar, cudaStream_t s) {
 }
 void launch_adam(Population* P, int which, cudaStream_t s) {
   launch_adam_one(P, which == 0 ? P->critic : (which == 1 ? P->bc : P->pi), s);
+}
+
+// Adam on the bias / LayerNorm leaves only (the kernels are updated by the weight-gradient GEMM's epilogue).
+void launch_adam_leaves(Population* P, int which, cudaStream_t s) {
+  Arena& ar = which == 0 ? P->critic : (which == 1 ? P->bc : P->pi);
+  static AdamLeafArgs L;
+  AdamArgs& a = L.a;
+  a = AdamArgs{};
+  a.theta = ar.theta; a.mu = ar.mu; a.nu = ar.nu; a.grad = ar.grad; a.shadow = ar.shadow;
+  a.target = ar.target; a.tshadow = ar.tshadow;
+  a.S = ar.L.S; a.nb = ar.L.nb;
+  a.member_list = P->cur_list();
+  a.adam_bc = P->adam_bc;
+  a.lr = P->c.lr; a.b1 = P->c.adam_b1; a.b2 = P->c.adam_b2; a.eps = P->c.adam_eps; a.tau = P->c.tau;
+  a.n_virtual = P->cur_n() * ar.L.nb;
+  const NetLayout& N = ar.L;
+  int n = 0;
+  for (int l = 0; l <= N.n_hidden; ++l) {
+    L.seg_off[n] = N.offb[l]; L.seg_n[n] = N.N(l); ++n;
+    if (N.ln && l < N.n_hidden) {
+      L.seg_off[n] = N.offg[l]; L.seg_n[n] = N.H; ++n;
+      L.seg_off[n] = N.offbeta[l]; L.seg_n[n] = N.H; ++n;
+    }
+  }
+  adam_leaves_kernel<<<dim3(n, (unsigned)a.n_virtual), 128, 0, s>>>(L);
 }
 
 void launch_finish_info(Population* P, int bump, cudaStream_t s) {

@@ -37,8 +37,10 @@ struct GroupPlan {
   // low-priority twins of s[0..4]: the layer-chain launches (SM-filling, long) run here, so that whenever an SM frees
   // up the short kernels between them (heads, weight gradients, optimizer) are served first
   cudaStream_t c[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-  cudaGraph_t g_step = nullptr, g_loss = nullptr;
-  cudaGraphExec_t x_step = nullptr, x_loss = nullptr;
+  // g_step: the update whose gradients stay readable (the last step of a call: grad stats, fqlpop_leaf which = grad);
+  // g_fast: the same update without the gradient stores (every earlier step of a multi-step call)
+  cudaGraph_t g_step = nullptr, g_fast = nullptr, g_loss = nullptr;
+  cudaGraphExec_t x_step = nullptr, x_fast = nullptr, x_loss = nullptr;
   cudaEvent_t done = nullptr;
 };
 struct Plan {
@@ -248,6 +250,9 @@ struct Builder {
   }
 
   // weight gradient of layer l: dW_l = X_l^T dz_l  (fp32, written straight into the grad arena)
+  // keep_grad < 0: plain gradient store (the optimizer runs as its own kernel); 0 / 1: Adam + Polyak + shadow refresh
+  // fused into the GEMM's epilogue, the gradient itself stored only when 1
+  int fuse_adam = -1;
   void wgrad_group(PassBuf& pass, BwdBuf& bw, const Arena& ar, int l, int row0) {
     const NetLayout& N = ar.L;
     GemmGroup& g = add();
@@ -260,6 +265,16 @@ struct Builder {
     tmap(&g.mapB, dZ, Nout, bw.M, bw.V, Nout, (long long)bw.M * Nout, 64);
     g.epi.kind = EPI_STORE_F32;
     g.epi.out_f32 = {ar.grad + N.offW[l], N.S, Nout, 0};
+    if (fuse_adam >= 0) {
+      g.epi.kind = EPI_ADAM;
+      AdamTile& T = g.epi.adam;
+      T.theta = ar.theta + N.offW[l]; T.mu = ar.mu + N.offW[l]; T.nu = ar.nu + N.offW[l];
+      T.shadow = ar.shadow + N.offW[l];
+      T.target = ar.target ? ar.target + N.offW[l] : nullptr;
+      T.tshadow = ar.tshadow ? ar.tshadow + N.offW[l] : nullptr;
+      T.adam_bc = P->adam_bc; T.nb = N.nb; T.keep_grad = fuse_adam;
+      T.lr = P->c.lr; T.b1 = P->c.adam_b1; T.b2 = P->c.adam_b2; T.eps = P->c.adam_eps; T.tau = P->c.tau;
+    }
   }
 };
 
@@ -439,7 +454,7 @@ void record(Plan* pl, cudaEvent_t* out, cudaStream_t s) {
 
 // Issues one step (train = update; !train = losses only) of the members in P's current window on the group's
 // streams. Called under stream capture; s[0] is the origin stream.
-int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
+int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err, bool keep_grads = true) {
   Plan* pl = P->plan;
   // schedule knobs (measured on B200): FQLPOP_SCHED bit 0 = critic forward / actor-critic pass
   // on their own streams (s3, s4) instead of queued behind s1 / s2; bit 1 = optimizer kernels on separate streams;
@@ -457,6 +472,13 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   const PopParams& c = P->c;
   Builder b{P, err};
   b.L = new GemmLaunch;
+  // FQLPOP_FUSE_ADAM=1: the optimizer inside the weight-gradient GEMM's epilogue (gemm.cu EPI_ADAM) instead of separate
+  // kernels after plain weight-gradient GEMMs. Parity-tested, and it removes the fp32 gradient round trip (34 -> 26 bytes
+  // per parameter), but MEASURED SLOWER (16.3k vs 18.1k updates/s at 16 members): 2 CTAs x 128 epilogue threads per SM keep
+  // ~64 KB of loads in flight per SM against the 160 KB of the stand-alone adam_kernel, so the fused pass streams at
+  // ~3.2 TB/s instead of 5.8. Off by default; read at graph-capture time.
+  const int fuse = [] { const char* e = getenv("FQLPOP_FUSE_ADAM"); return e ? atoi(e) : 0; }();
+  b.fuse_adam = fuse ? (keep_grads ? 1 : 0) : -1;
   int pw = 0;  // pointwise launches
   const int B = c.B;
   const int nsub_q = P->critic.L.ln ? 4 : 1, nsub_a = P->pi.L.ln ? 4 : 1;
@@ -543,9 +565,11 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   launch_qc_head(P, s1); ++pw;
   if (train) {
     bwd_pass(P->QC, P->bQC, P->critic, nsub_q, true, nullptr, s1);
-    b.begin(c.E);
-    for (int l = 0; l <= nh_q; ++l) b.wgrad_group(P->QC, P->bQC, P->critic, l, 0);
-    if (!(dbg_skip & 2)) b.launch(1, s1);
+    if (!fuse) {
+      b.begin(c.E);
+      for (int l = 0; l <= nh_q; ++l) b.wgrad_group(P->QC, P->bQC, P->critic, l, 0);
+      if (!(dbg_skip & 2)) b.launch(1, s1);
+    }
   }
 
   // ---- s2: BC flow forward/backward, then the critic pass on (s, clip(a_pi)) -----------------------
@@ -553,9 +577,11 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   launch_bc_head(P, s2); ++pw;
   if (train) {
     bwd_pass(P->BC, P->bBC, P->bc, nsub_a, true, nullptr, s2);
-    b.begin(1);
-    for (int l = 0; l <= nh_a; ++l) b.wgrad_group(P->BC, P->bBC, P->bc, l, 0);
-    if (!(dbg_skip & 2)) b.launch(1, s2);
+    if (!fuse) {
+      b.begin(1);
+      for (int l = 0; l <= nh_a; ++l) b.wgrad_group(P->BC, P->bBC, P->bc, l, 0);
+      if (!(dbg_skip & 2)) b.launch(1, s2);
+    }
   }
   // critic pass on (s, clip(a_pi)): its own stream, as soon as the policy head is out
   cudaStreamWaitEvent(s4, e_pi, 0);
@@ -569,30 +595,44 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
   launch_pi_dout(P, s0); ++pw;
   if (train) {
     bwd_pass(P->PI, P->bPI, P->pi, nsub_a, true, nullptr, s0);
-    b.begin(1);
-    for (int l = 0; l <= nh_a; ++l) b.wgrad_group(P->PI, P->bPI, P->pi, l, 0);
-    if (!(dbg_skip & 2)) b.launch(1, s0);
     // the optimizer branches run on the low-priority streams
     cudaStream_t a0 = (sched & 2) ? gp.s[5] : s1, a1 = (sched & 2) ? gp.s[6] : s2, a2 = (sched & 2) ? gp.s[7] : s0;
     cudaEvent_t e_w0, e_w1, e_w2, e_a0, e_a1, e_a2;
+    if (!fuse) {
+      b.begin(1);
+      for (int l = 0; l <= nh_a; ++l) b.wgrad_group(P->PI, P->bPI, P->pi, l, 0);
+      if (!(dbg_skip & 2)) b.launch(1, s0);
+    }
+    // Fused mode: the weight-gradient GEMM of a network IS its optimizer step (gemm.cu EPI_ADAM), so it may only start once
+    // every reader of that network's weights is done; the biases / LayerNorm leaves follow in a small kernel.
+    auto optimizer = [&](int which, PassBuf& pass, BwdBuf& bw, Arena& ar, int nb, int nh, cudaStream_t st) {
+      if (fuse) {
+        b.begin(nb);
+        for (int l = 0; l <= nh; ++l) b.wgrad_group(pass, bw, ar, l, 0);
+        if (!(dbg_skip & 2)) b.launch(1, st);
+      }
+      if (!(dbg_skip & 4)) { launch_small_grads(P, which, st); ++pw; }
+      if (!(dbg_skip & 1)) {
+        if (fuse) launch_adam_leaves(P, which, st);
+        else launch_adam(P, which, st);
+        ++pw;
+      }
+    };
     record(pl, &e_w2, s0);
     cudaStreamWaitEvent(a2, e_w2, 0);
-    if (!(dbg_skip & 4)) { launch_small_grads(P, 2, a2); ++pw; }
-    if (!(dbg_skip & 1)) { launch_adam(P, 2, a2); ++pw; }
+    optimizer(2, P->PI, P->bPI, P->pi, 1, nh_a, a2);
     record(pl, &e_a2, a2);
     // critic optimizer: after every reader of the critic weights (QA chain on s4) is done
     record(pl, &e_w0, s1);
     cudaStreamWaitEvent(a0, e_w0, 0);
     cudaStreamWaitEvent(a0, e_qa, 0);
-    if (!(dbg_skip & 4)) { launch_small_grads(P, 0, a0); ++pw; }
-    if (!(dbg_skip & 1)) { launch_adam(P, 0, a0); ++pw; }
+    optimizer(0, P->QC, P->bQC, P->critic, c.E, nh_q, a0);
     record(pl, &e_a0, a0);
     // BC flow optimizer: after the Euler chain (s0) has stopped reading the BC weights
     record(pl, &e_w1, s2);
     cudaStreamWaitEvent(a1, e_w1, 0);
     cudaStreamWaitEvent(a1, e_euler, 0);
-    if (!(dbg_skip & 4)) { launch_small_grads(P, 1, a1); ++pw; }
-    if (!(dbg_skip & 1)) { launch_adam(P, 1, a1); ++pw; }
+    optimizer(1, P->BC, P->bBC, P->bc, 1, nh_a, a1);
     record(pl, &e_a1, a1);
     cudaStreamWaitEvent(s0, e_a0, 0);
     cudaStreamWaitEvent(s0, e_a1, 0);
@@ -614,11 +654,13 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err) {
 void destroy_graphs(Plan* pl) {
   for (GroupPlan& g : pl->groups) {
     if (g.x_step) cudaGraphExecDestroy(g.x_step);
+    if (g.x_fast) cudaGraphExecDestroy(g.x_fast);
     if (g.x_loss) cudaGraphExecDestroy(g.x_loss);
     if (g.g_step) cudaGraphDestroy(g.g_step);
+    if (g.g_fast) cudaGraphDestroy(g.g_fast);
     if (g.g_loss) cudaGraphDestroy(g.g_loss);
-    g.x_step = g.x_loss = nullptr;
-    g.g_step = g.g_loss = nullptr;
+    g.x_step = g.x_fast = g.x_loss = nullptr;
+    g.g_step = g.g_fast = g.g_loss = nullptr;
   }
   for (cudaEvent_t e : pl->ev) cudaEventDestroy(e);
   pl->ev.clear();
@@ -673,10 +715,10 @@ struct Window {  // RAII: narrows the population's launch window to one group
   ~Window() { P->g_off = off; P->g_n = n; }
 };
 
-int build_graph(Population* P, bool train, GroupPlan& gp, std::string* err) {
+int build_graph(Population* P, bool train, GroupPlan& gp, std::string* err, bool keep_grads = true) {
   Window w(P, gp);
   CK(cudaStreamBeginCapture(gp.s[0], cudaStreamCaptureModeThreadLocal));
-  const int rc = issue_step(P, train, gp, err);
+  const int rc = issue_step(P, train, gp, err, keep_grads);
   cudaGraph_t g = nullptr;
   cudaError_t e = cudaStreamEndCapture(gp.s[0], &g);
   if (rc) {
@@ -686,7 +728,8 @@ int build_graph(Population* P, bool train, GroupPlan& gp, std::string* err) {
   CK(e);
   cudaGraphExec_t x = nullptr;
   CK(cudaGraphInstantiate(&x, g, 0));
-  if (train) { gp.g_step = g; gp.x_step = x; }
+  if (train && keep_grads) { gp.g_step = g; gp.x_step = x; }
+  else if (train) { gp.g_fast = g; gp.x_fast = x; }
   else { gp.g_loss = g; gp.x_loss = x; }
   return 0;
 }
@@ -874,6 +917,13 @@ static int run_plan(Population* P, bool train, int n_steps, cudaStream_t stream,
     for (GroupPlan& gp : pl->groups)
       if (!rc) rc = build_graph(P, train, gp, err);
   }
+  // multi-step calls: every step but the last runs the variant that does not store the weight gradients
+  if (!eager && train && n_steps > 1 && !pl->groups[0].x_fast) {
+    const int keep = pl->launches_per_step;
+    for (GroupPlan& gp : pl->groups)
+      if (!rc) rc = build_graph(P, true, gp, err, false);
+    pl->launches_per_step = keep;
+  }
   // every group runs its n_steps back to back on its own streams; the groups only meet again on `stream`. The launches
   // are submitted ROUND-ROBIN over the groups: the stream launch queue is finite (~1k pending launches), so submitting
   // all n_steps of group 0 first would block the host inside group 0's loop and serialise the groups for large n_steps
@@ -889,7 +939,8 @@ static int run_plan(Population* P, bool train, int n_steps, cudaStream_t stream,
   } else {
     for (int i = 0; i < n_steps && !rc; ++i) {
       for (GroupPlan& gp : pl->groups) {
-        cudaError_t e = cudaGraphLaunch(train ? gp.x_step : gp.x_loss, gp.s[0]);
+        cudaGraphExec_t x = !train ? gp.x_loss : (i + 1 < n_steps ? gp.x_fast : gp.x_step);
+        cudaError_t e = cudaGraphLaunch(x, gp.s[0]);
         if (e != cudaSuccess) {
           if (err) *err = std::string("cudaGraphLaunch: ") + cudaGetErrorString(e);
           rc = 1;

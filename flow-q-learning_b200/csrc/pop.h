@@ -174,6 +174,7 @@ void launch_pi_dout(Population* p, cudaStream_t s);
 void launch_small_grads(Population* p, int which, cudaStream_t s);
 void launch_grad_stats(Population* p, cudaStream_t s);
 void launch_adam(Population* p, int which, cudaStream_t s);  // 0 critic, 1 bc flow, 2 one-step policy
+void launch_adam_leaves(Population* p, int which, cudaStream_t s);  // biases / LayerNorm leaves only (kernels: gemm.cu EPI_ADAM)
 void launch_finish_info(Population* p, int bump_step, cudaStream_t s);
 void launch_refresh_shadow(Population* p, cudaStream_t s);
 void launch_fill_qa_dout(Population* p, cudaStream_t s);
