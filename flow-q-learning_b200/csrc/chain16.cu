@@ -73,12 +73,22 @@ __device__ __forceinline__ float warp_colsum16(float (&v)[16], int lane) {
   return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
 }
 
+// Shared memory is addressed explicitly (32-bit shared-space addresses, st.shared / ld.shared): through generic pointers the
+// compiler emits generic ST.E / LD.E with 64-bit addresses for these (it cannot prove the address space across the Epi struct).
+__device__ __forceinline__ void sts128(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+  return v;
+}
 // 16 columns starting at `col` (multiple of 16) of row r -> ACT (two 16-byte chunks of the 128-byte-swizzled row)
-__device__ __forceinline__ void st_act16(uint8_t* act, int r, int col, const uint32_t* w) {
-  uint8_t* row = act + (col >> 6) * kActBlockBytes + r * 128;
+__device__ __forceinline__ void st_act16(uint32_t act, int r, int col, const uint32_t* w) {
+  const uint32_t row = act + (uint32_t)((col >> 6) * kActBlockBytes + r * 128);
   const int c0 = (col & 63) >> 3;
-  *reinterpret_cast<uint4*>(row + ((c0 ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
-  *reinterpret_cast<uint4*>(row + (((c0 + 1) ^ (r & 7)) << 4)) = make_uint4(w[4], w[5], w[6], w[7]);
+  sts128(row + ((c0 ^ (r & 7)) << 4), w[0], w[1], w[2], w[3]);
+  sts128(row + (((c0 + 1) ^ (r & 7)) << 4), w[4], w[5], w[6], w[7]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -87,53 +97,54 @@ __device__ __forceinline__ void st_act16(uint8_t* act, int r, int col, const uin
 //   quarter block: 32 rows x 16 bf16 (32 B per row), 1 KB; chunk c (0..1) of row r at r * 32 + ((c ^ ((r >> 2) & 1)) << 4)
 // Row-wise accesses (lane = row) and the coalesced sweeps are bank-conflict free in both.
 // ---------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void st_half16(uint8_t* blk, int lane, int cw, const uint32_t* w) {
-  uint8_t* row = blk + lane * 64;
+__device__ __forceinline__ void st_half16(uint32_t blk, int lane, int cw, const uint32_t* w) {
+  const uint32_t row = blk + lane * 64;
   const int c0 = cw >> 3, sw = (lane >> 1) & 3;
-  *reinterpret_cast<uint4*>(row + ((c0 ^ sw) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
-  *reinterpret_cast<uint4*>(row + (((c0 + 1) ^ sw) << 4)) = make_uint4(w[4], w[5], w[6], w[7]);
+  sts128(row + ((c0 ^ sw) << 4), w[0], w[1], w[2], w[3]);
+  sts128(row + (((c0 + 1) ^ sw) << 4), w[4], w[5], w[6], w[7]);
 }
 // half block -> global rows (row stride ld elements); 8 rows x 64 contiguous bytes per warp instruction
-__device__ __forceinline__ void copy_out_half(const uint8_t* blk, __nv_bfloat16* g, int ld, int lane, int rows_valid) {
+__device__ __forceinline__ void copy_out_half(uint32_t blk, __nv_bfloat16* g, int ld, int lane, int rows_valid) {
   const int ch = lane & 3, rsub = lane >> 2;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int r = i * 8 + rsub;
-    const uint4 v = *reinterpret_cast<const uint4*>(blk + r * 64 + ((ch ^ ((r >> 1) & 3)) << 4));
+    const uint4 v = lds128(blk + r * 64 + ((ch ^ ((r >> 1) & 3)) << 4));
     if (r < rows_valid) *reinterpret_cast<uint4*>(g + (long long)r * ld + ch * 8) = v;
   }
 }
 // global rows -> quarter block, asynchronously (rows that do not exist are zero-filled). One commit group.
-__device__ __forceinline__ void stage_in_quarter(uint8_t* blk, const __nv_bfloat16* g, int ld, int lane, int rows_valid) {
+__device__ __forceinline__ void stage_in_quarter(uint32_t blk, const __nv_bfloat16* g, int ld, int lane, int rows_valid) {
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     const int p = lane + 32 * i;
     const int r = p >> 1, c = p & 1;
-    uint8_t* dst = blk + r * 32 + ((c ^ ((r >> 2) & 1)) << 4);
-    if (r < rows_valid) cp_async16(dst, g + (long long)r * ld + c * 8);
-    else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+    const uint32_t dst = blk + r * 32 + ((c ^ ((r >> 2) & 1)) << 4);
+    if (r < rows_valid)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(g + (long long)r * ld + c * 8) : "memory");
+    else sts128(dst, 0u, 0u, 0u, 0u);
   }
 }
-__device__ __forceinline__ void ld_quarter16(const uint8_t* blk, int lane, uint32_t* w) {
-  const uint8_t* row = blk + lane * 32;
+__device__ __forceinline__ void ld_quarter16(uint32_t blk, int lane, uint32_t* w) {
+  const uint32_t row = blk + lane * 32;
   const int sw = (lane >> 2) & 1;
-  const uint4 a = *reinterpret_cast<const uint4*>(row + (sw << 4));
-  const uint4 b = *reinterpret_cast<const uint4*>(row + ((sw ^ 1) << 4));
+  const uint4 a = lds128(row + (sw << 4));
+  const uint4 b = lds128(row + ((sw ^ 1) << 4));
   w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
   w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
 }
 // 64-column block of ACT (this warp's 32 rows: 32 x 128 bytes) -> global; 4 rows x 128 contiguous bytes per warp instruction
-__device__ __forceinline__ void copy_out_block(const uint8_t* blk, __nv_bfloat16* g, int ld, int lane, int rows_valid) {
+__device__ __forceinline__ void copy_out_block(uint32_t blk, __nv_bfloat16* g, int ld, int lane, int rows_valid) {
   const int ch = lane & 7, rsub = lane >> 3;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int r = i * 4 + rsub;
-    const uint4 v = *reinterpret_cast<const uint4*>(blk + r * 128 + ((ch ^ (r & 7)) << 4));
+    const uint4 v = lds128(blk + r * 128 + ((ch ^ (r & 7)) << 4));
     if (r < rows_valid) *reinterpret_cast<uint4*>(g + (long long)r * ld + ch * 8) = v;
   }
 }
 // the same sweep, also summing every column over the warp's 32 rows (rows that do not exist hold zeros)
-__device__ __forceinline__ void copy_out_block_colsum(const uint8_t* blk, __nv_bfloat16* g, int ld, int lane,
+__device__ __forceinline__ void copy_out_block_colsum(uint32_t blk, __nv_bfloat16* g, int ld, int lane,
                                                       int rows_valid, float* part) {
   const int ch = lane & 7, rsub = lane >> 3;
   float acc[8];
@@ -142,7 +153,7 @@ __device__ __forceinline__ void copy_out_block_colsum(const uint8_t* blk, __nv_b
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int r = i * 4 + rsub;
-    const uint4 v = *reinterpret_cast<const uint4*>(blk + r * 128 + ((ch ^ (r & 7)) << 4));
+    const uint4 v = lds128(blk + r * 128 + ((ch ^ (r & 7)) << 4));
     if (r < rows_valid) *reinterpret_cast<uint4*>(g + (long long)r * ld + ch * 8) = v;
     acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x);
     acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
@@ -169,10 +180,13 @@ struct Epi {
   // LEADER CTA (of this CTA itself when CTAs are not paired). One arrival per WARP.
   uint32_t blk_full_a, drained_a, x0_ready_a;
   bool remote;             // those barriers live in the other CTA of the pair
-  uint8_t* act;
+  const float* pb;         // shared-memory copy of the current layer's bias | LayerNorm scale | LayerNorm bias restricted to
+                           // this column group's 128 columns ([3][128] floats), or nullptr -> read them through L1 / L2
+  float* pb_base;          // this column group's two parameter buffers (layer parity), nullptr when the X0 block is in use
+  uint32_t act;            // shared-space address of ACT
   const float* params;     // this virtual member's fp32 parameter block
   float2* ex;              // LayerNorm row-sum exchange [4 column groups][128 rows] (the X0 block, idle by then)
-  uint8_t* stg;            // this warp's staging block (nullptr in launches that keep all 5 weight stages)
+  uint32_t stg;            // shared-space address of this warp's staging block (launches that stage tensors only)
   int r, q, cg, lane, H;
   bool row_ok;
   int rows_valid;          // how many of the warp's 32 rows exist
@@ -230,6 +244,41 @@ __device__ __forceinline__ void ld_vec16(const float* p, float4 (&v)[4]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) v[i] = __ldg(reinterpret_cast<const float4*>(p) + i);
 }
+// 16 parameters of array `arr` (0 bias, 1 LayerNorm scale, 2 LayerNorm bias; element offset `off` in the parameter block)
+// at absolute column `col` of this thread's column group: from the shared-memory copy when there is one
+__device__ __forceinline__ void ld_param16(const Epi& C, int arr, long long off, int col, float4 (&v)[4]) {
+  if (C.pb) {
+    const int k = (col >= kTileN ? 64 : 0) + (col & 63);
+    const float4* p = reinterpret_cast<const float4*>(C.pb + arr * 128 + k);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = p[i];
+  } else {
+    ld_vec16(C.params + off + col, v);
+  }
+}
+// Every bias / LayerNorm vector element is used once per CTA and layer, so each read through L1 is an L2 round trip
+// (~600 cycles, a dozen of them per thread and layer in the LayerNorm passes: measured as the epilogue's main
+// long-scoreboard stall). One warp of each column group copies the group's 3 x 128 values into shared memory while
+// the group waits for its accumulator (the X0 block is idle after the first layer; two buffers alternate by layer, so
+// nobody can still be reading the one being written), then the group's four warps meet on a named barrier.
+__device__ __forceinline__ void load_layer_params(Epi& C, const ChainLayer& Ly, int layer_parity, bool need_bias, bool need_ln,
+                                                  bool need_gamma_only) {
+  if (C.pb_base == nullptr || Ly.a_from_x0) { C.pb = nullptr; return; }
+  float* buf = C.pb_base + layer_parity * (3 * 128);
+  if (C.q == 0) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const bool need = j == 0 ? need_bias : (j == 1 ? (need_ln || need_gamma_only) : need_ln);
+      if (!need) continue;
+      const long long off = j == 0 ? Ly.off_b : (j == 1 ? Ly.off_g : Ly.off_beta);
+      const int k = C.lane;                                    // float4 index within the group's 128 columns
+      const int col = (k < 16 ? 0 : kTileN) + C.cg * 64 + (k & 15) * 4;
+      reinterpret_cast<float4*>(buf + j * 128)[k] = __ldg(reinterpret_cast<const float4*>(C.params + off + col));
+    }
+  }
+  asm volatile("bar.sync %0, 128;" ::"r"(5 + C.cg) : "memory");
+  C.pb = buf;
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // forward hidden layer: h = LayerNorm?(gelu(acc + b))
@@ -264,7 +313,6 @@ __device__ __forceinline__ void fwd_pass1(const Epi& C, const ChainLayer& Ly, in
                                           float& s2) {
   const int colw = tile * kTileN + C.cg * 64;
   const uint32_t tbase = C.tmem_row + colw;
-  const float* bias = C.params + Ly.off_b + colw;
   uint32_t ra[16], rb[16];
   tmem_ld16(tbase, ra);
 #pragma unroll
@@ -272,7 +320,7 @@ __device__ __forceinline__ void fwd_pass1(const Epi& C, const ChainLayer& Ly, in
     uint32_t gpk[8];
     float4 b4[4];
     // ---- even chunk (ra) ----
-    ld_vec16(bias + c * 16, b4);
+    ld_param16(C, 0, Ly.off_b, colw + c * 16, b4);
     tmem_ld_wait();
     tmem_ld16(tbase + (c + 1) * 16, rb);
     fwd_chunk<LN, SAVE>(ra, b4, pk + 8 * c, gpk, s1, s2);
@@ -280,7 +328,7 @@ __device__ __forceinline__ void fwd_pass1(const Epi& C, const ChainLayer& Ly, in
     if (DEST == 1) st_act16(C.act, C.r, colw + c * 16, pk + 8 * c);
     if (DEST == 2) tmem_st8(tbase + c * 8, *reinterpret_cast<const uint32_t(*)[8]>(pk + 8 * c));
     // ---- odd chunk (rb) ----
-    ld_vec16(bias + (c + 1) * 16, b4);
+    ld_param16(C, 0, Ly.off_b, colw + (c + 1) * 16, b4);
     tmem_ld_wait();
     if (c + 2 < 4) tmem_ld16(tbase + (c + 2) * 16, ra);
     fwd_chunk<LN, SAVE>(rb, b4, pk + 8 * (c + 1), gpk, s1, s2);
@@ -300,8 +348,8 @@ template <bool SAVE>
 __device__ __forceinline__ void ln_chunk(const Epi& C, const ChainLayer& Ly, int col, const uint32_t* pr, float rstd,
                                          float shift, int cw, bool save_x) {
   float4 ga[4], be[4];
-  ld_vec16(C.params + Ly.off_g + col, ga);
-  ld_vec16(C.params + Ly.off_beta + col, be);
+  ld_param16(C, 1, Ly.off_g, col, ga);
+  ld_param16(C, 2, Ly.off_beta, col, be);
   uint32_t hk[8], xk[8];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -319,20 +367,43 @@ __device__ __forceinline__ void ln_chunk(const Epi& C, const ChainLayer& Ly, int
   if (SAVE && save_x) st_half16(C.stg, C.lane, cw, xk);
 }
 
+// parked tile (bf16 pairs in the drained accumulator columns) -> LayerNorm -> ACT (+ xhat -> staging -> global)
+template <bool SAVE>
+__device__ __forceinline__ void ln_flush_tile(const Epi& C, const ChainLayer& Ly, int tile, float rstd, float shift, bool save_x) {
+  const int colw = tile * kTileN + C.cg * 64;
+  uint32_t pa[8], pb[8];
+  tmem_ld8(C.tmem_row + colw, pa);
+#pragma unroll
+  for (int c = 0; c < 4; c += 2) {
+    tmem_ld_wait();
+    tmem_ld8(C.tmem_row + colw + (c + 1) * 8, pb);
+    ln_chunk<SAVE>(C, Ly, colw + c * 16, pa, rstd, shift, 0, save_x);
+    tmem_ld_wait();
+    if (c + 2 < 4) tmem_ld8(C.tmem_row + colw + (c + 2) * 8, pa);
+    ln_chunk<SAVE>(C, Ly, colw + (c + 1) * 16, pb, rstd, shift, 16, save_x);
+    if (save_x) {
+      __syncwarp();
+      copy_out_half(C.stg, Ly.out_xhat + C.wrow + colw + c * 16, C.H, C.lane, C.rows_valid);
+      __syncwarp();
+    }
+  }
+}
+
 template <bool LN, bool SAVE>
-__device__ __forceinline__ void fwd_hidden_layer(const Epi& C, const ChainLayer& Ly, uint32_t par0, uint32_t par1,
-                                                 bool pub) {
-  prefetch_params(C, Ly, true, LN);
+__device__ __forceinline__ void fwd_hidden_layer(Epi& C, const ChainLayer& Ly, uint32_t par0, uint32_t par1, bool pub,
+                                                 int layer_parity) {
+  load_layer_params(C, Ly, layer_parity, true, LN, false);
+  if (!C.pb) prefetch_params(C, Ly, true, LN);
   float s1 = 0.f, s2 = 0.f;
-  uint32_t pk0[32];
-  wait_full(C, 0, par0);
-  stamp(C, 1);
-  fwd_pass1<LN, SAVE, 0>(C, Ly, 0, pk0, s1, s2);
-  arrive_drained(C, 0);
-  stamp(C, 2);
-  wait_full(C, 1, par1);  // every MMA of the layer has retired: ACT may be overwritten
-  stamp(C, 3);
   if (!LN) {
+    uint32_t pk0[32];
+    wait_full(C, 0, par0);
+    stamp(C, 1);
+    fwd_pass1<false, SAVE, 0>(C, Ly, 0, pk0, s1, s2);
+    arrive_drained(C, 0);
+    stamp(C, 2);
+    wait_full(C, 1, par1);  // every MMA of the layer has retired: ACT may be overwritten
+    stamp(C, 3);
 #pragma unroll
     for (int c = 0; c < 4; ++c) st_act16(C.act, C.r, C.cg * 64 + c * 16, pk0 + 8 * c);
     if (pub) publish(C, C.cg);
@@ -343,8 +414,17 @@ __device__ __forceinline__ void fwd_hidden_layer(const Epi& C, const ChainLayer&
     arrive_drained(C, 1);
     stamp(C, 5);
   } else {
-    uint32_t pk1[32];
-    fwd_pass1<true, SAVE, 2>(C, Ly, 1, pk1, s1, s2);
+    // LayerNorm needs the whole row before anything can be normalised: both tiles are parked as bf16 in the accumulator
+    // columns they were drained from (holding tile 0 in registers instead costs the LayerNorm instantiation spills in
+    // its inner loops), then flushed tile by tile once the row statistics are known.
+    uint32_t pk[32];
+    wait_full(C, 0, par0);
+    stamp(C, 1);
+    fwd_pass1<true, SAVE, 2>(C, Ly, 0, pk, s1, s2);
+    stamp(C, 2);
+    wait_full(C, 1, par1);
+    stamp(C, 3);
+    fwd_pass1<true, SAVE, 2>(C, Ly, 1, pk, s1, s2);
     tmem_st_wait();
     // row statistics over all 512 columns: the four column-group warps of this lane quarter
     C.ex[C.cg * 128 + C.r] = make_float2(s1, s2);
@@ -363,36 +443,11 @@ __device__ __forceinline__ void fwd_hidden_layer(const Epi& C, const ChainLayer&
     const float shift = -mean * rstd;
     if (C.row_ok && C.cg == 0 && Ly.out_rstd) Ly.out_rstd[C.rs_off] = rstd;
     const bool save_x = SAVE && Ly.out_xhat != nullptr;
-    // tile 0 out of the registers
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      ln_chunk<SAVE>(C, Ly, C.cg * 64 + c * 16, pk0 + 8 * c, rstd, shift, (c & 1) * 16, save_x);
-      if (save_x && (c & 1)) {
-        __syncwarp();
-        copy_out_half(C.stg, Ly.out_xhat + C.wrow + C.cg * 64 + (c - 1) * 16, C.H, C.lane, C.rows_valid);
-        __syncwarp();
-      }
-    }
+    ln_flush_tile<SAVE>(C, Ly, 0, rstd, shift, save_x);
     if (pub) publish(C, C.cg);
+    arrive_drained(C, 0);
     stamp(C, 4);
-    // tile 1 out of its parked columns
-    const int colw = kTileN + C.cg * 64;
-    uint32_t pa[8], pb[8];
-    tmem_ld8(C.tmem_row + colw, pa);
-#pragma unroll
-    for (int c = 0; c < 4; c += 2) {
-      tmem_ld_wait();
-      tmem_ld8(C.tmem_row + colw + (c + 1) * 8, pb);
-      ln_chunk<SAVE>(C, Ly, colw + c * 16, pa, rstd, shift, 0, save_x);
-      tmem_ld_wait();
-      if (c + 2 < 4) tmem_ld8(C.tmem_row + colw + (c + 2) * 8, pa);
-      ln_chunk<SAVE>(C, Ly, colw + (c + 1) * 16, pb, rstd, shift, 16, save_x);
-      if (save_x) {
-        __syncwarp();
-        copy_out_half(C.stg, Ly.out_xhat + C.wrow + colw + c * 16, C.H, C.lane, C.rows_valid);
-        __syncwarp();
-      }
-    }
+    ln_flush_tile<SAVE>(C, Ly, 1, rstd, shift, save_x);
     if (pub) publish(C, 4 + C.cg);
     arrive_drained(C, 1);
     stamp(C, 5);
@@ -400,7 +455,7 @@ __device__ __forceinline__ void fwd_hidden_layer(const Epi& C, const ChainLayer&
   // h -> HBM out of ACT, off the hand-off path: these rows of the two blocks are next written by this very warp
   if (Ly.out_h) {
     __syncwarp();
-    const uint8_t* b0 = C.act + C.cg * kActBlockBytes + C.q * (32 * 128);
+    const uint32_t b0 = C.act + C.cg * kActBlockBytes + C.q * (32 * 128);
     copy_out_block(b0, Ly.out_h + C.wrow + C.cg * 64, C.H, C.lane, C.rows_valid);
     copy_out_block(b0 + 4 * kActBlockBytes, Ly.out_h + C.wrow + kTileN + C.cg * 64, C.H, C.lane, C.rows_valid);
   }
@@ -497,7 +552,6 @@ __device__ __forceinline__ void bwd_hidden_ln(const Epi& C, const ChainLayer& Ly
   const __nv_bfloat16* xsrc = Ly.xhat + C.wrow;
   const bool has_gp = Ly.gp != nullptr;
   const __nv_bfloat16* gsrc = has_gp ? Ly.gp + C.wrow : nullptr;
-  const float* gamma = C.params + Ly.off_g;
   auto prefetch_x = [&](int cc) {
     if (cc < 8) stage_in_quarter(C.stg + (cc & 1) * 1024, xsrc + chunk_col(C, cc), C.H, C.lane, C.rows_valid);
     cp_async_commit();
@@ -519,7 +573,7 @@ __device__ __forceinline__ void bwd_hidden_ln(const Epi& C, const ChainLayer& Ly
     __syncwarp();
     prefetch_x(cc + 2);
     float4 ga[4];
-    ld_vec16(gamma + col, ga);
+    ld_param16(C, 1, Ly.off_g, col, ga);
     tmem_ld_wait();
     float t0[16], t1[16];
 #pragma unroll
@@ -584,7 +638,7 @@ __device__ __forceinline__ void bwd_hidden_ln(const Epi& C, const ChainLayer& Ly
     __syncwarp();
     prefetch_xg(cc + 1);
     float4 ga[4];
-    ld_vec16(gamma + col, ga);
+    ld_param16(C, 1, Ly.off_g, col, ga);
     tmem_ld_wait();
     uint32_t pk[8];
 #pragma unroll
@@ -614,14 +668,17 @@ __device__ __forceinline__ void bwd_hidden_ln(const Epi& C, const ChainLayer& Ly
 }
 
 template <bool LN>
-__device__ __forceinline__ void bwd_hidden_layer(const Epi& C, const ChainLayer& Ly, uint32_t par0, uint32_t par1, bool pub) {
-  prefetch_params(C, Ly, false, LN);
+__device__ __forceinline__ void bwd_hidden_layer(Epi& C, const ChainLayer& Ly, uint32_t par0, uint32_t par1, bool pub,
+                                                 int layer_parity) {
+  if (LN) load_layer_params(C, Ly, layer_parity, false, false, true);
+  else C.pb = nullptr;
+  if (!C.pb) prefetch_params(C, Ly, false, LN);
   if (LN) bwd_hidden_ln(C, Ly, par0, par1, pub);
   else bwd_hidden_plain(C, Ly, par0, par1, pub);
   stamp(C, 5);
   // dz -> HBM (+ bias-gradient partial sums) out of ACT, off the hand-off path
   __syncwarp();
-  const uint8_t* b0 = C.act + C.cg * kActBlockBytes + C.q * (32 * 128);
+  const uint32_t b0 = C.act + C.cg * kActBlockBytes + C.q * (32 * 128);
 #pragma unroll
   for (int t = 0; t < 2; ++t) {
     const int col = t * kTileN + C.cg * 64;
@@ -893,7 +950,7 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
     C.blk_full_a = C.remote ? mapa_u32(smem_u32(blk_full), 0) : smem_u32(blk_full);
     C.drained_a = C.remote ? mapa_u32(smem_u32(drained), 0) : smem_u32(drained);
     C.x0_ready_a = C.remote ? mapa_u32(smem_u32(x0_ready), 0) : smem_u32(x0_ready);
-    C.act = act;
+    C.act = smem_u32(act);
     C.params = J.params + (long long)v * J.S;
     C.ex = reinterpret_cast<float2*>(x0s);
     C.r = r; C.q = q; C.cg = cg; C.lane = lane; C.H = J.H;
@@ -901,11 +958,15 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
     C.rs_off = (long long)v * J.pass_rs + grow;
     C.part_off = (long long)v * J.part_ms + (long long)(mt * 4 + q) * J.H;
     C.ln_eps = J.ln_eps;
-    C.stg = L.staged ? stage_base + kStagesStaged * kStageBytes + (warp - kFirstEpiWarp) * kStgBytes : nullptr;
+    C.stg = L.staged ? smem_u32(stage_base + kStagesStaged * kStageBytes + (warp - kFirstEpiWarp) * kStgBytes) : 0u;
     const int grow0 = mt * 128 + q * 32;
     C.wrow = (long long)v * J.pass_ms + (long long)grow0 * J.H;
     C.wdz = (long long)v * J.dz_ms + (long long)grow0 * J.H;
     C.rows_valid = min(32, max(0, J.M - grow0));
+    C.pb = nullptr;
+    // the X0 block after the first layer: [0, 4 KB) LayerNorm row-sum exchange, then per column group two parameter
+    // buffers of 3 x 128 floats (the Euler flow keeps re-using X0 as its first layer's operand: no buffers there)
+    C.pb_base = iters == 1 ? reinterpret_cast<float*>(x0s + 4096) + cg * (2 * 3 * 128) : nullptr;
     C.tr = nullptr;
 #ifdef FQLPOP_EPI_TRACE
     const bool ep_traced = L.trace && blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0;
@@ -930,10 +991,10 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
         if (Ly.kind == CL_HIDDEN) {
           const bool pub = !(it == iters - 1 && li == n_layers - 1);  // the last layer's output is consumed by nobody on chip
           if (MODE == 0) {
-            if (Ly.out_gp != nullptr) fwd_hidden_layer<LN, true>(C, Ly, par0, par1, pub);
-            else fwd_hidden_layer<LN, false>(C, Ly, par0, par1, pub);
+            if (Ly.out_gp != nullptr) fwd_hidden_layer<LN, true>(C, Ly, par0, par1, pub, lc & 1);
+            else fwd_hidden_layer<LN, false>(C, Ly, par0, par1, pub, lc & 1);
           } else {
-            bwd_hidden_layer<LN>(C, Ly, par0, par1, pub);
+            bwd_hidden_layer<LN>(C, Ly, par0, par1, pub, lc & 1);
           }
           ++tc;
         } else if (Ly.kind == CL_EULER_HEAD) {
