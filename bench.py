@@ -485,7 +485,9 @@ def sh64_bench(torch, np, dev, rank, world, dist, barrier, n_alphas=64, shape="a
                 dist.all_gather(g, t)                      # measurement only (not part of the product path)
                 busy_all = [float(x) for x in g]
             mine = sum(1 for c in now if self.owns(c))
-            rec.append({"population": len(now), "local_members": mine, "busy_s": busy_all, "gather_s": t_gather})
+            # wall time of this evaluation as this rank lived it: its own work + the time it waited in the all-gather
+            rec.append({"population": len(now), "local_members": mine, "busy_s": busy_all, "gather_s": t_gather,
+                        "wall_s": busy + t_gather})
             return out
 
     random.seed(0); np.random.seed(0)
@@ -514,13 +516,14 @@ def sh64_bench(torch, np, dev, rank, world, dist, barrier, n_alphas=64, shape="a
         g = rungs.setdefault(r["population"], {"evaluations": 0, "wall_s": 0.0, "busy_max_s": 0.0, "busy_mean_s": 0.0,
                                                 "gather_ms": []})
         g["evaluations"] += 1
-        g["wall_s"] += max(r["busy_s"]) + r["gather_s"]
+        g["wall_s"] += r["wall_s"]
         g["busy_max_s"] += max(r["busy_s"])
         g["busy_mean_s"] += sum(r["busy_s"]) / len(r["busy_s"])
         g["gather_ms"].append(1e3 * r["gather_s"])
     per_rung = [{"population": n, "evaluations": g["evaluations"], "wall_s": round(g["wall_s"], 4),
                  "member_updates_per_s": n * eval_interval * g["evaluations"] / max(g["wall_s"], 1e-9),
                  "idle_gpu_fraction": 1.0 - g["busy_mean_s"] / max(g["busy_max_s"], 1e-12),
+                 "idle_gpu_fraction_unavoidable": max(0.0, 1.0 - n / world),
                  "allgather_ms_median": sorted(g["gather_ms"])[len(g["gather_ms"]) // 2]}
                 for n, g in sorted(rungs.items(), reverse=True)]
     survivors = sorted(c.alpha for c in tr.candidates)
@@ -625,6 +628,8 @@ def main():
         block_ms.append(float(t.item()))
     ms_total = sorted(block_ms)[len(block_ms) // 2]
     info_last = pop.info()
+    free_b, total_b = torch.cuda.mem_get_info(dev)
+    hbm_used = int(total_b - free_b)   # parameters + optimiser state + pass buffers + dataset of this rank's members
 
     # ---- end to end: host batches (pinned) -> H2D -> step -> info D2H, every step ---------------------------
     row = 2 * O + A + 2
@@ -748,6 +753,7 @@ def main():
                           "adam_hbm_floor_ms_per_step": adam_b * P / (pk["hbm_gbs"] * 1e9) * 1e3},
         "clocks": sampler.summary(),
         "timed_blocks_ms": block_ms,
+        "hbm_bytes_in_use_rank0": hbm_used,
         "env_switches": env_switches,
         "last_info_member0": {k: float(v) for k, v in zip(("critic_loss", "q_mean"), info_last[0][:2])},
     }
