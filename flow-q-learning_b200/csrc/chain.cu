@@ -1603,7 +1603,7 @@ cudaError_t chain_init() {
   return chain16_init();
 }
 
-constexpr int kClusterMaxMembers = 11;
+constexpr int kClusterMaxMembers = 8;
 
 // The cluster kernel covers the production shape: every hidden layer 512 wide, reductions of 64 (first layer) or 512.
 static bool chain2_eligible(const ChainLaunch& L) {
@@ -1630,14 +1630,18 @@ static bool chain2_eligible(const ChainLaunch& L) {
 }
 
 // Which kernel generation runs a chain of this shape: the second-generation kernel (chain16.cu) unless
-// FQLPOP_CHAIN_GEN=1 (first-generation kernels: A/B measurements, parity cross-checks) or FQLPOP_CHAIN2=1/2 forces the
-// N-split cluster kernel. The builders in pop.cu ask the same question: the weight boxes of a backward chain are sized
+// FQLPOP_CHAIN_GEN=1 (first-generation kernels: A/B measurements, parity cross-checks), FQLPOP_CHAIN2=1/2 forces the
+// N-split cluster kernel, or few members are active (below). The builders in pop.cu ask the same question: the weight boxes of a backward chain are sized
 // for the kernel that will read them.
-bool chain16_selected_shape(int H, int in_pad, bool ln, int iters) {
+// Population size decides between the two cluster designs (measured on B200, profiles/r02_small_populations.txt): up to
+// kClusterMaxMembers active members the step is latency-bound and the N-split cluster kernel of the first generation
+// (two SMs work on every layer of a row tile: shortest chain latency) wins -- 1 member 2.9k vs 2.4k updates/s, 4 members
+// 10.5k vs 8.8k, 8 members 15.5k vs 14.9k; above, SM time decides and the second-generation pair kernel wins.
+bool chain16_selected_shape(int H, int in_pad, bool ln, int iters, int population_active) {
   static const int gen = [] { const char* e = getenv("FQLPOP_CHAIN_GEN"); return e ? atoi(e) : 2; }();
   if (gen < 2 || H != 512 || in_pad != 64 || (ln && iters > 1)) return false;
   const char* e = getenv("FQLPOP_CHAIN2");
-  const int m = e ? atoi(e) : 0;
+  const int m = e ? atoi(e) : ((population_active > 0 && population_active <= kClusterMaxMembers) ? 1 : 0);
   return !(m == 1 || (m == 2 && iters > 1));
 }
 
@@ -1651,7 +1655,7 @@ cudaError_t launch_chain(ChainLaunch& L, int mode, cudaStream_t stream) {
     for (int l = 0; l < L.job[i].n_layers; ++l)
       if (L.job[i].layer[l].out_gp || L.job[i].layer[l].out_xhat) staged = true;
   L.stages = staged ? kStagesStaged : kStages;
-  if (chain16_eligible(L) && chain16_selected_shape(L.job[0].H, 64, L.job[0].ln != 0, L.job[0].iters))
+  if (chain16_eligible(L) && chain16_selected_shape(L.job[0].H, 64, L.job[0].ln != 0, L.job[0].iters, L.population_active))
     return launch_chain16(L, mode, grid, stream);
   if (chain2_eligible(L)) {
     if (mode == 0) fql_chain2_kernel<0><<<2 * grid, kThreads2, kSmemBytes, stream>>>(L);

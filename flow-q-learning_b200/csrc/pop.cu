@@ -408,7 +408,7 @@ struct ChainBuilder {
     tmap(&j.mapA0, bw.dout, kHeadPad, bw.M, bw.V, kHeadPad, (long long)bw.M * kHeadPad, 128);
     const long long roff = (long long)row0 * N.H;
     // rows of a weight box = output columns one CTA stages per k step: 256, or 128 when CTAs run as cta_group::2 pairs
-    const int cap = (chain16_selected_shape(N.H, N.in_pad, N.ln != 0, 1) && chain16_pair_mode() && chain16_pairs_rows(bw.M)) ? 128 : 256;
+    const int cap = (chain16_selected_shape(N.H, N.in_pad, N.ln != 0, 1, (int)P->h_members.size()) && chain16_pair_mode() && chain16_pairs_rows(bw.M)) ? 128 : 256;
     int s = 0;
     for (int l = N.n_hidden; l >= 1; --l, ++s) {
       const int Kd = N.N(l);

@@ -31,8 +31,9 @@ constexpr int kActBlockBytes = 128 * 64 * 2;  // one 64-wide k-block of the A op
 constexpr int kActBytes = 8 * kActBlockBytes;  // 128 KB
 constexpr int kStageBytes = 32 * 256 * 2;      // (32 k) x (256 n) bf16 = 16 KB = four TMA boxes
 constexpr int kBoxBytes = 64 * 32 * 2;         // 64 n x 32 k
-constexpr int kBarBytes = 256;
+constexpr int kBarBytes = 512;
 constexpr int kSmemBytes = kActBytes + kActBlockBytes + kStages * kStageBytes + kBarBytes + 1024;
+constexpr int kMaxSlots = 2 * kStages;  // pair mode: 8 KB weight slots (each CTA stages half of every tile's columns)
 
 __device__ __forceinline__ float clip1(float x) { return fminf(fmaxf(x, -1.f), 1.f); }
 
@@ -69,6 +70,12 @@ __device__ __forceinline__ void st_volatile_s32(int* p, int v) {
   asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
 }
 
+// PAIR: CTAs run as clusters of two (adjacent 128-episode tiles of the same member) and every product is ONE
+// tcgen05.mma.cta_group::2 of M = 256 issued by the leader (cluster rank 0): each CTA stages only half of the N columns of
+// every weight stage, which halves the bytes a CTA pulls through shared memory per lockstep step (1.93 MB -> 0.97 MB; the
+// weight stream's stage round trip of ~3000 cycles is what bounds the single-CTA kernel). The pair leaves
+// the step loop together: "every episode is done" is tracked per CTA and mirrored into the peer.
+template <bool PAIR>
 __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_constant__ RoParams P) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -76,43 +83,70 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
   uint8_t* x0s = smem + kActBytes;
   uint8_t* stage_base = x0s + kActBlockBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(stage_base + kStages * kStageBytes);
-  uint64_t* full_bar = bars;              // [kStages]
-  uint64_t* empty_bar = bars + kStages;   // [kStages]
-  uint64_t* act_ready = bars + 2 * kStages;
-  uint64_t* layer_done = bars + 2 * kStages + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 2);
+  uint64_t* full_bar = bars;                // [kMaxSlots]
+  uint64_t* empty_bar = bars + kMaxSlots;   // [kMaxSlots]
+  uint64_t* act_ready = bars + 2 * kMaxSlots;
+  uint64_t* layer_done = bars + 2 * kMaxSlots + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kMaxSlots + 2);
   int* first_done = reinterpret_cast<int*>(tmem_slot + 1);  // first step at which every episode of the CTA was done
   int* steps_done = first_done + 1;                         // lockstep steps fully book-kept
-  int* warp_all = steps_done + 1;                           // [4]
+  int* peer_first_done = steps_done + 1;                    // (pair) the other CTA's two flags, written by it
+  int* peer_steps_done = peer_first_done + 1;
+  int* warp_all = peer_steps_done + 1;                      // [4]
+  constexpr int kSlotBytes = PAIR ? kStageBytes / 2 : kStageBytes;
+  constexpr int kSlots = PAIR ? kMaxSlots : kStages;
+  constexpr uint32_t kCtas = PAIR ? 2 : 1;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int tile = blockIdx.x;
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+  const bool leader = rank == 0;
+  const int tile = PAIR ? 2 * ((int)blockIdx.x >> 1) + (int)rank : (int)blockIdx.x;
   const int member = P.member_list ? __ldg(P.member_list + blockIdx.y) : (int)blockIdx.y;
   const int n_layers = P.n_layers;
   const int n_steps = P.n_steps;
 
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < n_layers; ++i) tma_prefetch_desc(&P.maps[i]);
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < kMaxSlots; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    mbar_init(act_ready, 256);
+    mbar_init(act_ready, 8 * kCtas);   // one arrival per epilogue warp (4 episode + 4 helper warps per CTA)
     mbar_init(layer_done, 1);
     *first_done = INT_MAX;
     *steps_done = 0;
+    *peer_first_done = PAIR ? INT_MAX : 0;   // unpaired: the "peer" is always done
+    *peer_steps_done = PAIR ? 0 : INT_MAX;
     fence_barrier_init();
     fence_proxy_async_smem();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, 512);
-    tmem_relinquish();
+    if (PAIR) { tmem_alloc_2sm(tmem_slot, 512); tmem_relinquish_2sm(); }
+    else { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
   }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // the pair leaves at the first step both CTAs were done at; both flags of the peer are settled once its bookkeeping of
+  // that step is (the producer checks that explicitly, everybody else is ordered behind it by the MMA barriers)
+  auto pair_first_done = [&]() { return max(ld_volatile_s32(first_done), ld_volatile_s32(peer_first_done)); };
+  // barriers both CTAs signal live in the leader
+  const uint32_t act_ready_l = (PAIR && !leader) ? mapa_u32(smem_u32(act_ready), 0) : smem_u32(act_ready);
+  const uint32_t full_bar_l = (PAIR && !leader) ? mapa_u32(smem_u32(full_bar), 0) : smem_u32(full_bar);
+  // this warp's rows of the next A operand are written (generic proxy -> async proxy fence per lane), its accumulator
+  // columns read: one arrival per warp
+  auto arrive_ready = [&]() {
+    tc_fence_before();
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      if (PAIR && !leader) mbar_arrive_cluster(act_ready_l);
+      else mbar_arrive(act_ready);
+    }
+  };
 
   if (warp == 0) {
     // ======================================= TMA producer ========================================
@@ -122,24 +156,30 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
       for (int step = 0; step < n_steps; ++step) {
         if (step >= 2) {
           const long long t0 = clock64();
-          while (ld_volatile_s32(steps_done) < step - 1) {
+          while (min(ld_volatile_s32(steps_done), ld_volatile_s32(peer_steps_done)) < step - 1) {
             __nanosleep(64);
             if (clock64() - t0 > 8000000000LL) __trap();
           }
-          if (ld_volatile_s32(first_done) <= step - 2) break;
+          if (pair_first_done() <= step - 2) break;
         }
         for (int li = 0; li < n_layers; ++li) {
           const RoLayer& Ly = P.layer[li];
           const int batch = Ly.per_member ? member : 0;
           for (int n0 = 0; n0 < Ly.n_pad; n0 += 256) {
             const int ncols = min(256, Ly.n_pad - n0);
+            // columns of this MMA tile staged by THIS CTA (a 64-column layer is issued as N = 128 in pair mode: the
+            // second CTA's half lies outside the weight tensor and is zero-filled)
+            const int mycols = PAIR ? max(ncols / 2, 64) : ncols;
+            const int c0 = n0 + (int)rank * mycols;
             for (int ks = 0; ks < Ly.k_blocks * 2; ++ks) {  // one stage = 32 k x ncols n
               mbar_wait(&empty_bar[stage], phase ^ 1);
-              uint8_t* sb = stage_base + stage * kStageBytes;
-              mbar_arrive_expect_tx(&full_bar[stage], (ncols / 64) * kBoxBytes);
-              for (int b = 0; b < ncols / 64; ++b)
-                tma_load_3d(sb + b * kBoxBytes, &P.maps[li], &full_bar[stage], n0 + 64 * b, ks * 32, batch);
-              if (++stage == kStages) { stage = 0; phase ^= 1; }
+              uint8_t* sb = stage_base + stage * kSlotBytes;
+              if (leader) mbar_arrive_expect_tx(&full_bar[stage], (mycols / 64) * kBoxBytes * kCtas);
+              for (int b = 0; b < mycols / 64; ++b) {
+                if (PAIR) tma_load_3d_2sm(sb + b * kBoxBytes, &P.maps[li], full_bar_l + 8u * (uint32_t)stage, c0 + 64 * b, ks * 32, batch);
+                else tma_load_3d(sb + b * kBoxBytes, &P.maps[li], &full_bar[stage], c0 + 64 * b, ks * 32, batch);
+              }
+              if (++stage == kSlots) { stage = 0; phase ^= 1; }
             }
           }
         }
@@ -147,39 +187,41 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
     }
   } else if (warp == 1) {
     // ======================================= MMA issuer ==========================================
-    if (lane == 0) {
+    if (lane == 0 && leader) {
       int stage = 0;
       uint32_t phase = 0;
       uint32_t it = 0;
       const uint32_t act_addr = smem_u32(act), x0_addr = smem_u32(x0s);
       for (int step = 0; step < n_steps; ++step) {
-        if (step >= 2 && ld_volatile_s32(first_done) <= step - 2) break;
+        if (step >= 2 && pair_first_done() <= step - 2) break;
         for (int li = 0; li < n_layers; ++li, ++it) {
           const RoLayer& Ly = P.layer[li];
           mbar_wait(act_ready, it & 1);
           tc_fence_after();
           const uint32_t a_base = Ly.a_from_x0 ? x0_addr : act_addr;
-          // 128 x 256 x 16 MMAs (96 % of the tensor pipe's rate against 57 % for 128 x 128, profiles/ubench): a stage holds
-          // 32 k x up to 256 n as 64n x 32k boxes
+          // 128 x 256 x 16 MMAs (256 x 256 x 16 across the pair): a stage holds 32 k x up to 256 n as 64n x 32k boxes
           for (int n0 = 0; n0 < Ly.n_pad; n0 += 256) {
             const int ncols = min(256, Ly.n_pad - n0);
-            const uint32_t idesc = make_idesc_bf16(128, (uint32_t)ncols, 0, 1);
+            const uint32_t idesc = make_idesc_bf16(PAIR ? 256 : 128, PAIR ? (uint32_t)max(ncols, 128) : (uint32_t)ncols, 0, 1);
             for (int ks = 0; ks < Ly.k_blocks * 2; ++ks) {
               mbar_wait(&full_bar[stage], phase);
               tc_fence_after();
               const uint32_t sa = a_base + (ks >> 1) * kActBlockBytes + (ks & 1) * 64;
-              const uint32_t sb = smem_u32(stage_base + stage * kStageBytes);
+              const uint32_t sb = smem_u32(stage_base + stage * kSlotBytes);
 #pragma unroll
               for (int k = 0; k < 2; ++k) {
                 const uint64_t adesc = make_smem_desc_sw128(sa + k * 32, 16, 1024);
                 const uint64_t bdesc = make_smem_desc_sw128(sb + k * 2048, kBoxBytes, 1024);
-                umma_bf16(tmem_base + n0, adesc, bdesc, idesc, (ks | k) != 0 ? 1u : 0u);
+                if (PAIR) umma_bf16_2sm(tmem_base + n0, adesc, bdesc, idesc, (ks | k) != 0 ? 1u : 0u);
+                else umma_bf16(tmem_base + n0, adesc, bdesc, idesc, (ks | k) != 0 ? 1u : 0u);
               }
-              umma_commit(&empty_bar[stage]);
-              if (++stage == kStages) { stage = 0; phase ^= 1; }
+              if (PAIR) umma_commit_2sm(&empty_bar[stage], 3);
+              else umma_commit(&empty_bar[stage]);
+              if (++stage == kSlots) { stage = 0; phase ^= 1; }
             }
           }
-          umma_commit(layer_done);
+          if (PAIR) umma_commit_2sm(layer_done, 3);
+          else umma_commit(layer_done);
         }
       }
     }
@@ -191,9 +233,9 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
     const int r = q * 32 + lane;
     const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
     uint32_t it = 0;
-    mbar_arrive(act_ready);
+    arrive_ready();
     for (int step = 0; step < n_steps; ++step) {
-      if (step >= 2 && ld_volatile_s32(first_done) <= step - 2) break;
+      if (step >= 2 && pair_first_done() <= step - 2) break;
       for (int li = 0; li < n_layers; ++li, ++it) {
         const RoLayer& Ly = P.layer[li];
         mbar_wait(layer_done, it & 1);
@@ -219,12 +261,10 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
             st_act32(act, r, c * 32, v);
           }
         }
-        tc_fence_before();
-        fence_proxy_async_smem();
-        mbar_arrive(act_ready);
+        arrive_ready();
       }
     }
-  } else {
+  } else if (warp >= 2) {
     // ======================================= epilogue ============================================
     const int q = warp & 3;
     const int r = q * 32 + lane;  // row of the tile == TMEM lane
@@ -296,11 +336,10 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
     } else {
       build_policy_input(0);
     }
-    fence_proxy_async_smem();
-    mbar_arrive(act_ready);
+    arrive_ready();
 
     for (int step = 0; step < n_steps; ++step) {
-      if (step >= 2 && ld_volatile_s32(first_done) <= step - 2) break;
+      if (step >= 2 && pair_first_done() <= step - 2) break;
       steps_executed = step + 1;
       for (int li = 0; li < n_layers; ++li, ++it) {
         const RoLayer& Ly = P.layer[li];
@@ -423,18 +462,27 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
               if (lane == 0) warp_all[q] = all;
               epi_bar_sync();
               if (r == 0) {
-                if (warp_all[0] && warp_all[1] && warp_all[2] && warp_all[3] && ld_volatile_s32(first_done) == INT_MAX)
+                int fd = ld_volatile_s32(first_done);
+                if (warp_all[0] && warp_all[1] && warp_all[2] && warp_all[3] && fd == INT_MAX) {
+                  fd = step;
                   st_volatile_s32(first_done, step);
+                }
+                if (PAIR) {  // mirror both flags into the peer, first_done before steps_done
+                  const uint32_t peer = rank ^ 1u;
+                  asm volatile("st.shared::cluster.s32 [%0], %1;" ::"r"(mapa_u32(smem_u32(peer_first_done), peer)), "r"(fd) : "memory");
+                  asm volatile("fence.acq_rel.cluster;" ::: "memory");
+                  asm volatile("st.shared::cluster.s32 [%0], %1;" ::"r"(mapa_u32(smem_u32(peer_steps_done), peer)), "r"(s1) : "memory");
+                  asm volatile("fence.acq_rel.cluster;" ::: "memory");
+                }
                 __threadfence_block();
                 st_volatile_s32(steps_done, s1);
               }
+              epi_bar_sync();  // the flags are published before any warp of this CTA arrives for the next step
               if (s1 < n_steps) build_policy_input(s1);
             }
           }
         }
-        tc_fence_before();
-        fence_proxy_async_smem();
-        mbar_arrive(act_ready);
+        arrive_ready();
       }
     }
 
@@ -464,9 +512,11 @@ __global__ void __launch_bounds__(kThreads, 1) fql_rollout_kernel(const __grid_c
 
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    if (PAIR) tmem_dealloc_2sm(tmem_base, 512);
+    else tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -499,7 +549,36 @@ __global__ void finish_rollout_kernel(const int* member_list, int n_active, int 
 }  // namespace
 
 cudaError_t rollout_init() {
-  return cudaFuncSetAttribute(fql_rollout_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  cudaError_t e = cudaFuncSetAttribute(fql_rollout_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(fql_rollout_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+}
+
+// Pair mode (tcgen05.mma.cta_group::2 over two adjacent episode tiles): FQLPOP_ROLLOUT_PAIR=1. Parity-tested, OFF by default:
+// halving the weight bytes per CTA does not speed this kernel up (165 vs 170 M env-steps/s at 16 x 4096 x 200) -- its layers
+// are serialised on the epilogue (MMA of layer l+1 waits for the 8 epilogue warps of layer l), not on the weight stream.
+static cudaError_t launch_rollout(const RoParams& R, int n_members, cudaStream_t stream) {
+  const bool pair_on = [] { const char* e = getenv("FQLPOP_ROLLOUT_PAIR"); return e ? atoi(e) != 0 : false; }();
+  bool pair_ok = pair_on && R.tiles_per_member >= 2;
+  for (int i = 0; i < R.n_layers && pair_ok; ++i) {   // every MMA tile must split into two halves of whole 64-column boxes
+    const int rem = R.layer[i].n_pad % 256;
+    pair_ok = rem == 0 || rem == 64 || rem == 128;
+  }
+  if (!pair_ok) {
+    fql_rollout_kernel<false><<<dim3(R.tiles_per_member, n_members), kThreads, kSmemBytes, stream>>>(R);
+    return cudaGetLastError();
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * ((R.tiles_per_member + 1) / 2), n_members);   // an odd last tile gets an all-invalid partner
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, fql_rollout_kernel<true>, R);
 }
 
 #define CK(call)                                                                                  \
@@ -728,7 +807,7 @@ int rollout_impl(Population* P, EnvModel* m, const RolloutArgs& a, cudaStream_t 
   CK(cudaMemsetAsync(P->ro.success_sum, 0, sizeof(float) * P->c.P, stream));
   CK(cudaMemsetAsync(P->ro.return_sum, 0, sizeof(float) * P->c.P, stream));
   CK(cudaMemsetAsync(R.steps_run, 0, sizeof(int) * P->c.P, stream));
-  fql_rollout_kernel<<<dim3(R.tiles_per_member, n_active), kThreads, kSmemBytes, stream>>>(R);
+  CK(launch_rollout(R, n_active, stream));
   CK(cudaGetLastError());
   finish_rollout_kernel<<<(n_active + 127) / 128, 128, 0, stream>>>(P->member_list, n_active, a.n_episodes,
                                                                     P->ro.success_sum, P->ro.return_sum,
@@ -767,7 +846,7 @@ int sample_actions_impl(Population* P, int member, const float* obs, int n, cons
   R.noise = noise; R.noise_ms = 0;
   R.actions_out = out;
   launch_head_image(P, stream);
-  fql_rollout_kernel<<<dim3(R.tiles_per_member, 1), kThreads, kSmemBytes, stream>>>(R);
+  CK(launch_rollout(R, 1, stream));
   CK(cudaGetLastError());
   P->ro.launches += 2;
   return 0;
@@ -794,7 +873,7 @@ int env_step_impl(EnvModel* m, const float* obs, const float* act, int n, float*
   R.env_ln_scale = m->ln_scale; R.env_ln_bias = m->ln_bias;
   R.init_obs = obs; R.actions_in = act;
   R.next_obs_out = next_obs; R.logits_out = logits;
-  fql_rollout_kernel<<<dim3(R.tiles_per_member, 1), kThreads, kSmemBytes, stream>>>(R);
+  CK(launch_rollout(R, 1, stream));
   CK(cudaGetLastError());
   return 0;
 }

@@ -2,8 +2,8 @@
 selection (no FQLPOP_* switch set):
 
   * config 2: lockstep population of 16 alpha values, cube-single shape, batch 256 (four graph groups of 4) -- one update
-    of all 16 members vs the oracle; also 11 and 12 members (the population sizes either side of the cluster-kernel
-    threshold of the first-generation kernels, groups of 2 / 4);
+    of all 16 members vs the oracle; also 8 and 9 members (either side of the population size at which the default
+    switches from the first-generation N-split cluster kernel to the second-generation pair kernel) and 12;
   * per-step losses over 200 updates of two members vs the fp32 oracle fed the same batches and noise (north_star:
     "per-step losses ... within a stated fp tolerance"): the envelope is written below;
   * config 3: 4096 episodes x 200 steps, antsoccer shape, termination bias calibrated so that about half of the episodes
@@ -25,7 +25,7 @@ def _default_kernel_selection(monkeypatch):
         monkeypatch.delenv(k, raising=False)
 
 
-@pytest.mark.parametrize("P,fuse", [(16, 0), (11, 0), (12, 0), (5, 1)])
+@pytest.mark.parametrize("P,fuse", [(16, 0), (8, 0), (9, 0), (12, 0), (5, 1)])
 def test_population_update_default_kernels_matches_oracle(P, fuse, monkeypatch):
     from fqlpop.population import INFO_KEYS, Population
     monkeypatch.setenv("FQLPOP_FUSE_ADAM", str(fuse))   # 1: Adam + Polyak inside the weight-gradient GEMM's epilogue

@@ -120,8 +120,9 @@ def test_env_step_matches_oracle(shape, hidden):
     dem.close()
 
 
-@pytest.mark.parametrize("shape", [(42, 8), (28, 5)])
-def test_rollout_matches_oracle_fixed_horizon(shape):
+@pytest.mark.parametrize("shape,pair", [((42, 8), 0), ((28, 5), 0), ((42, 8), 1)], ids=["antsoccer", "cube", "antsoccer_cta_pair"])
+def test_rollout_matches_oracle_fixed_horizon(shape, pair, monkeypatch):
+    monkeypatch.setenv("FQLPOP_ROLLOUT_PAIR", str(pair))   # 1: tcgen05.mma.cta_group::2 over two episode tiles (off by default)
     O, A = shape
     cfg = orc.FQLConfig(ob_dim=O, action_dim=A, batch_size=128)
     alphas, seeds = [3.0, 30.0, 300.0], [5, 6, 7]
