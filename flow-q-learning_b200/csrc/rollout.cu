@@ -551,7 +551,9 @@ __global__ void finish_rollout_kernel(const int* member_list, int n_active, int 
 cudaError_t rollout_init() {
   cudaError_t e = cudaFuncSetAttribute(fql_rollout_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(fql_rollout_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  e = cudaFuncSetAttribute(fql_rollout_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  if (e != cudaSuccess) return e;
+  return rollout16_init();
 }
 
 // Pair mode (tcgen05.mma.cta_group::2 over two adjacent episode tiles): FQLPOP_ROLLOUT_PAIR=1. Parity-tested, OFF by default:
@@ -559,6 +561,9 @@ cudaError_t rollout_init() {
 // are serialised on the epilogue (MMA of layer l+1 waits for the 8 epilogue warps of layer l), not on the weight stream.
 static cudaError_t launch_rollout(const RoParams& R, int n_members, cudaStream_t stream) {
   const bool pair_on = [] { const char* e = getenv("FQLPOP_ROLLOUT_PAIR"); return e ? atoi(e) != 0 : false; }();
+  // FQLPOP_ROLLOUT_GEN=1 keeps whole rollouts on this file's kernel; default: rollout16.cu where it applies
+  const int gen = [] { const char* e = getenv("FQLPOP_ROLLOUT_GEN"); return e ? atoi(e) : 2; }();
+  if (gen >= 2 && rollout16_eligible(R)) return launch_rollout16(R, n_members, pair_on, stream);
   bool pair_ok = pair_on && R.tiles_per_member >= 2;
   for (int i = 0; i < R.n_layers && pair_ok; ++i) {   // every MMA tile must split into two halves of whole 64-column boxes
     const int rem = R.layer[i].n_pad % 256;

@@ -120,5 +120,9 @@ int sample_actions_impl(Population* P, int member, const float* obs, int n, cons
 int env_step_impl(EnvModel* m, const float* obs, const float* act, int n, float* next_obs, float* logits,
                   cudaStream_t stream, std::string* err);
 cudaError_t rollout_init();
+// rollout16.cu: second-generation whole-rollout kernel (16 epilogue warps)
+cudaError_t rollout16_init();
+bool rollout16_eligible(const RoParams& R);
+cudaError_t launch_rollout16(const RoParams& R, int n_members, bool pair, cudaStream_t stream);
 
 }  // namespace fqlpop
