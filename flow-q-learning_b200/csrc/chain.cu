@@ -1657,6 +1657,10 @@ cudaError_t launch_chain(ChainLaunch& L, int mode, cudaStream_t stream) {
   L.stages = staged ? kStagesStaged : kStages;
   if (chain16_eligible(L) && chain16_selected_shape(L.job[0].H, 64, L.job[0].ln != 0, L.job[0].iters, L.population_active))
     return launch_chain16(L, mode, grid, stream);
+  if (mode == 0)  // wide-box weight maps are read by chain16.cu only
+    for (int i = 0; i < L.num_jobs; ++i)
+      for (int l = 0; l < L.job[i].n_layers; ++l)
+        if (L.job[i].layer[l].b_box_rows != 0) return cudaErrorInvalidValue;
   if (chain2_eligible(L)) {
     if (mode == 0) fql_chain2_kernel<0><<<2 * grid, kThreads2, kSmemBytes, stream>>>(L);
     else fql_chain2_kernel<1><<<2 * grid, kThreads2, kSmemBytes, stream>>>(L);

@@ -32,7 +32,8 @@ struct ChainLayer {
   int k_blocks;    // reduction length / 64
   int n_pad;       // output columns (multiple of 64, <= 512)
   int a_from_x0;   // A operand = the 128 x 64 input block instead of the activation buffer
-  int b_box_rows;  // backward: rows of the weight TMA box (min(256, output columns)); forward: unused
+  int b_box_rows;  // backward: rows of the weight TMA box (min(256, output columns)); forward: 0 = weight map with 64 n x
+                   // 32 k boxes, else a wide map whose box spans this many 64-column blocks (chain16.cu only)
   int _pad0;
   long long off_b, off_g, off_beta;  // element offsets of bias / LayerNorm scale / LayerNorm bias in `params`
   // forward outputs (nullptr = not stored). Row-major [V][pass rows][H] bf16, already offset to the job's row 0.

@@ -814,9 +814,10 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
                 if (leader) mbar_arrive_expect_tx(&full_bar[stage], my_bytes * kCtas);
                 if (MODE == 0) {
                   // W[k][n], n contiguous: boxes of 64 n x 32 k
-                  for (int b = 0; b < mycols / 64; ++b) {
-                    if (PAIR) tma_load_3d_2sm(sb + b * kFwdBoxBytes, &J.mapW[li], fb, c0 + 64 * b, ks * kStageK, v);
-                    else tma_load_3d(sb + b * kFwdBoxBytes, &J.mapW[li], &full_bar[stage], c0 + 64 * b, ks * kStageK, v);
+                  const int wb = Ly.b_box_rows;   // 64-column blocks per TMA instruction
+                  for (int b = 0; b < mycols / 64; b += wb) {
+                    if (PAIR) tma_load_4d_2sm(sb + b * kFwdBoxBytes, &J.mapW[li], fb, 0, ks * kStageK, (c0 >> 6) + b, v);
+                    else tma_load_4d(sb + b * kFwdBoxBytes, &J.mapW[li], &full_bar[stage], 0, ks * kStageK, (c0 >> 6) + b, v);
                   }
                 } else {
                   // the same array read as B^T: rows = output columns of this GEMM, 32 reduction elements per 64-byte row
@@ -1123,6 +1124,19 @@ bool chain16_eligible(const ChainLaunch& L) {
   }
   return true;
 }
+// ... whose forward weight maps were encoded with wide boxes (pop.cu wide_boxes)
+static bool chain16_maps_ok(const ChainLaunch& L, int mode, bool pair) {
+  if (mode != 0) return true;
+  for (int i = 0; i < L.num_jobs; ++i) {
+    const ChainJob& j = L.job[i];
+    for (int l = 0; l < j.n_layers; ++l) {
+      const int wb = j.layer[l].b_box_rows;
+      const int per_cta = j.layer[l].n_pad >= 256 ? (pair ? 2 : 4) : 1;
+      if (wb < 1 || per_cta % wb != 0) return false;
+    }
+  }
+  return true;
+}
 
 template <int MODE, bool LN>
 static cudaError_t launch_variant(ChainLaunch& L, bool pair, int units, cudaStream_t stream) {
@@ -1152,6 +1166,7 @@ cudaError_t launch_chain16(ChainLaunch& L, int mode, int grid, cudaStream_t stre
   for (int i = 0; i < L.num_jobs; ++i)
     units += (pair ? (L.job[i].m_tiles + 1) / 2 : L.job[i].m_tiles) * L.n_virtual;
   // weight slots: 16 KB each (8 KB in pair mode); launches that stage tensors through shared memory give up the last 32 KB
+  if (!chain16_maps_ok(L, mode, pair)) return cudaErrorInvalidValue;
   L.staged = L.stages != kStages;
   L.stages = (L.staged ? kStagesStaged : kStages) * (pair ? 2 : 1);
   if (mode == 0) return ln ? launch_variant<0, true>(L, pair, units, stream) : launch_variant<0, false>(L, pair, units, stream);

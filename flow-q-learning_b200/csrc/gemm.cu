@@ -589,6 +589,42 @@ int encode_tmap_bf16(CUtensorMap* out, const void* base, long long inner, long l
   return r == CUDA_SUCCESS ? 0 : (int)r;
 }
 
+// One box = n_boxes adjacent 64-column blocks x box_rows rows, landing in shared memory as n_boxes consecutive
+// [box_rows][64] 128-byte-swizzled tiles -- the layout n_boxes separate encode_tmap_bf16 boxes would give, for ONE
+// cp.async.bulk.tensor instruction. Coordinates: (0, row, column block, batch). `inner` must be a multiple of 64.
+int encode_tmap_bf16_wide(CUtensorMap* out, const void* base, long long inner, long long rows, long long batch,
+                          long long ld, long long batch_stride, int box_rows, int n_boxes) {
+  PFN_encodeTiled fn = get_encode_fn();
+  if (!fn || inner % 64 != 0) return -1;
+  cuuint64_t dims[4] = {64, (cuuint64_t)rows, (cuuint64_t)(inner / 64), (cuuint64_t)(batch < 1 ? 1 : batch)};
+  cuuint64_t strides[3] = {(cuuint64_t)ld * 2, 128, (cuuint64_t)batch_stride * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)box_rows, (cuuint32_t)n_boxes, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  if (batch <= 1) strides[2] = (cuuint64_t)ld * 2 * (cuuint64_t)rows;
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : (int)r;
+}
+
+// Weights re-tiled as [K / ks][N / 64][ks k][64 n] (every 64 n x ks k box a contiguous run, the boxes of one k-slab
+// adjacent; ks = 32 or 64): a box of n_boxes * ks rows is one CTA's weight stage, fetched from consecutive addresses.
+// Coordinates: (0, (k_slab * (N / 64) + column block) * ks, batch).
+int encode_tmap_bf16_tiled(CUtensorMap* out, const void* base, long long K, long long N, long long batch,
+                           long long batch_stride, int n_boxes, int ks) {
+  PFN_encodeTiled fn = get_encode_fn();
+  if (!fn || N % 64 != 0 || K % ks != 0 || ks * n_boxes > 256) return -1;
+  cuuint64_t dims[3] = {64, (cuuint64_t)(K * (N / 64)), (cuuint64_t)(batch < 1 ? 1 : batch)};
+  cuuint64_t strides[2] = {128, (cuuint64_t)batch_stride * 2};
+  cuuint32_t box[3] = {64, (cuuint32_t)(ks * n_boxes), 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  if (batch <= 1) strides[1] = (cuuint64_t)K * N * 2;
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : (int)r;
+}
+
 int encode_tmap_bf16_sw64(CUtensorMap* out, const void* base, long long inner, long long rows, long long batch,
                           long long ld, long long batch_stride, int box_rows) {
   PFN_encodeTiled fn = get_encode_fn();

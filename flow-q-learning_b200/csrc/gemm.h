@@ -112,6 +112,10 @@ int encode_tmap_bf16(CUtensorMap* out, const void* base, long long inner, long l
                      long long ld, long long batch_stride, int box_rows);
 
 // Same tensor, 64-byte swizzle and a (32, box_rows, 1) box: K-major operand stages of 32 reduction elements per row.
+int encode_tmap_bf16_wide(CUtensorMap* out, const void* base, long long inner, long long rows, long long batch,
+                          long long ld, long long batch_stride, int box_rows, int n_boxes);
+int encode_tmap_bf16_tiled(CUtensorMap* out, const void* base, long long K, long long N, long long batch,
+                           long long batch_stride, int n_boxes, int ks);
 int encode_tmap_bf16_sw64(CUtensorMap* out, const void* base, long long inner, long long rows, long long batch,
                           long long ld, long long batch_stride, int box_rows);
 

@@ -106,10 +106,12 @@ struct Plan;  // captured step (streams, events, CUDA graph)
 struct RolloutScratch {
   __nv_bfloat16* head_w = nullptr;  // [P][H][64] one-step-policy head, action j in column O + j
   float* head_b = nullptr;          // [P][64]
+  __nv_bfloat16* pi_tiled = nullptr;  // [P][S] hidden-layer kernels of the one-step policy, tiled [K/32][H/64][32][64]
   float *obs_work = nullptr, *success_sum = nullptr, *return_sum = nullptr;
   int* steps_run = nullptr;
   unsigned char* success = nullptr;
   int* length = nullptr;
+  float* noise_next = nullptr;  // [P][2][ep_cap][A] policy noise of the next lockstep step (rollout16.cu draws it early)
   int* identity = nullptr;  // [P] = 0..P-1 (a one-entry member list for single-member launches)
   long long ep_cap = 0;
   long long launches = 0;   // kernels launched by rollout / sample_actions calls so far

@@ -537,6 +537,20 @@ __global__ void build_head_image_kernel(const float* __restrict__ theta, long lo
   }
 }
 
+// hidden-layer kernel [K][H] (bf16 shadow) -> tiled [K / ks][H / 64][ks][64], ks = 32 << ks_shift; grid.y = member
+__global__ void tile_policy_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long S,
+                                   long long offW, int K, int H, const int* member_list, int ks_shift) {
+  const int p = member_list ? member_list[blockIdx.y] : (int)blockIdx.y;
+  const uint4* s = reinterpret_cast<const uint4*>(src + (long long)p * S + offW);
+  uint4* d = reinterpret_cast<uint4*>(dst + (long long)p * S + offW);
+  const int NB = H / 64, per_row = H / 8;   // 16-byte chunks
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < K * per_row; i += gridDim.x * blockDim.x) {
+    const int k = i / per_row, c = i % per_row;   // chunk c = columns [8 c, 8 c + 8)
+    const int sh = 5 + ks_shift, ks = 1 << sh;
+    d[((long long)((k >> sh) * NB + (c >> 3)) * ks + (k & (ks - 1))) * 8 + (c & 7)] = s[i];
+  }
+}
+
 __global__ void finish_rollout_kernel(const int* member_list, int n_active, int n, const float* success_sum,
                                       const float* return_sum, float* success_rate, float* return_mean) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -556,14 +570,19 @@ cudaError_t rollout_init() {
   return rollout16_init();
 }
 
-// Pair mode (tcgen05.mma.cta_group::2 over two adjacent episode tiles): FQLPOP_ROLLOUT_PAIR=1. Parity-tested, OFF by default:
-// halving the weight bytes per CTA does not speed this kernel up (165 vs 170 M env-steps/s at 16 x 4096 x 200) -- its layers
-// are serialised on the epilogue (MMA of layer l+1 waits for the 8 epilogue warps of layer l), not on the weight stream.
+// FQLPOP_ROLLOUT_PAIR: clusters of two CTAs on adjacent episode tiles (tcgen05.mma.cta_group::2). Unset: on for the
+// second-generation kernel (348 vs 327 M env-steps/s at 16 x 4096 x 200), off for this file's (165 vs 170).
+static bool rollout_pair_mode(bool gen2) {
+  static const int v = [] { const char* e = getenv("FQLPOP_ROLLOUT_PAIR"); return e ? (atoi(e) != 0 ? 1 : 0) : -1; }();
+  return v < 0 ? gen2 : v != 0;
+}
+// FQLPOP_ROLLOUT_GEN=1 keeps whole rollouts on this file's kernel; default: rollout16.cu where it applies
+static int rollout_gen() {
+  static const int gen = [] { const char* e = getenv("FQLPOP_ROLLOUT_GEN"); return e ? atoi(e) : 2; }();
+  return gen;
+}
 static cudaError_t launch_rollout(const RoParams& R, int n_members, cudaStream_t stream) {
-  const bool pair_on = [] { const char* e = getenv("FQLPOP_ROLLOUT_PAIR"); return e ? atoi(e) != 0 : false; }();
-  // FQLPOP_ROLLOUT_GEN=1 keeps whole rollouts on this file's kernel; default: rollout16.cu where it applies
-  const int gen = [] { const char* e = getenv("FQLPOP_ROLLOUT_GEN"); return e ? atoi(e) : 2; }();
-  if (gen >= 2 && rollout16_eligible(R)) return launch_rollout16(R, n_members, pair_on, stream);
+  const bool pair_on = rollout_pair_mode(false);
   bool pair_ok = pair_on && R.tiles_per_member >= 2;
   for (int i = 0; i < R.n_layers && pair_ok; ++i) {   // every MMA tile must split into two halves of whole 64-column boxes
     const int rem = R.layer[i].n_pad % 256;
@@ -608,9 +627,24 @@ static int upload_layer(EnvModel* m, EnvModel::Layer& L, int K, int N, const flo
   for (int k = 0; k < K; ++k)
     for (int n = 0; n < N; ++n) w[(size_t)k * L.N_pad + n] = __float2bfloat16(kernel[(size_t)k * N + n]);
   for (int n = 0; n < N; ++n) b[n] = bias[n];
-  void *dw = nullptr, *db = nullptr;
+  std::vector<__nv_bfloat16> wt(w.size()), wt64(w.size());
+  const int NB = L.N_pad / 64;
+  for (int k = 0; k < L.K_pad; ++k)
+    for (int n = 0; n < L.N_pad; ++n) {
+      wt[((size_t)((k / 32) * NB + n / 64) * 32 + k % 32) * 64 + n % 64] = w[(size_t)k * L.N_pad + n];
+      wt64[((size_t)((k / 64) * NB + n / 64) * 64 + k % 64) * 64 + n % 64] = w[(size_t)k * L.N_pad + n];
+    }
+  void *dw = nullptr, *db = nullptr, *dwt = nullptr, *dwt64 = nullptr;
   CK(cudaMalloc(&dw, w.size() * sizeof(__nv_bfloat16)));
   m->allocs.push_back(dw);
+  CK(cudaMalloc(&dwt, wt.size() * sizeof(__nv_bfloat16)));
+  m->allocs.push_back(dwt);
+  CK(cudaMemcpy(dwt, wt.data(), wt.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
+  L.wt = (__nv_bfloat16*)dwt;
+  CK(cudaMalloc(&dwt64, wt64.size() * sizeof(__nv_bfloat16)));
+  m->allocs.push_back(dwt64);
+  CK(cudaMemcpy(dwt64, wt64.data(), wt64.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
+  L.wt64 = (__nv_bfloat16*)dwt64;
   CK(cudaMalloc(&db, b.size() * sizeof(float)));
   m->allocs.push_back(db);
   CK(cudaMemcpy(dw, w.data(), w.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
@@ -695,14 +729,33 @@ struct Program {
   RoParams* R;
   std::string* err;
   bool ok = true;
+  struct MapArgs { const void* w; const void* wt; const void* wt64; int K_pad, N_pad, batch; long long ms; };
+  MapArgs margs[kRoMaxLayers];
+  // rollout16.cu fetches a whole weight stage (the 64-column boxes of one CTA's share of an accumulator tile x 32 k) with
+  // one TMA instruction from the TILED copy of the weights, where that stage is one contiguous run: re-encode every map
+  bool widen(bool pair) {
+    for (int i = 0; i < R->n_layers; ++i) {
+      const MapArgs& a = margs[i];
+      const int ncols = a.N_pad < 256 ? a.N_pad : 256;
+      const int mycols = pair ? (ncols / 2 > 64 ? ncols / 2 : 64) : ncols;
+      const void* img = pair ? a.wt64 : a.wt;   // pair mode: 64-k weight stages
+      if (!img || encode_tmap_bf16_tiled(&R->maps[i], img, a.K_pad, a.N_pad, a.batch, a.ms, mycols / 64, pair ? 64 : 32) != 0) {
+        if (err) *err = "rollout: cuTensorMapEncodeTiled (tiled weights) failed";
+        return ok = false;
+      }
+    }
+    return true;
+  }
   int add(const void* w, int K_pad, int N_pad, int n_true, int batch, long long ms, int kind, int act, int ln,
-          int a_from_x0, const float* bias, long long bias_ms, int per_member) {
+          int a_from_x0, const float* bias, long long bias_ms, int per_member, const void* wt = nullptr,
+          const void* wt64 = nullptr) {
     if (R->n_layers >= kRoMaxLayers) {
       ok = false;
       if (err) *err = "rollout: too many layers";
       return -1;
     }
     const int i = R->n_layers++;
+    margs[i] = MapArgs{w, wt, wt64 ? wt64 : wt, K_pad, N_pad, batch, ms};
     if (encode_tmap_bf16(&R->maps[i], w, N_pad, K_pad, batch, N_pad, ms, 32) != 0) {
       ok = false;
       if (err) *err = "rollout: cuTensorMapEncodeTiled failed";
@@ -722,6 +775,7 @@ int ensure_scratch(Population* P, int n, std::string* err) {
     void* p = nullptr;
     CK(cudaMalloc(&p, (size_t)Pn * P->pi.L.H * 64 * sizeof(__nv_bfloat16))); P->allocs.push_back(p); S.head_w = (__nv_bfloat16*)p;
     CK(cudaMalloc(&p, (size_t)Pn * 64 * sizeof(float))); P->allocs.push_back(p); S.head_b = (float*)p;
+    CK(cudaMalloc(&p, (size_t)Pn * P->pi.L.S * sizeof(__nv_bfloat16))); P->allocs.push_back(p); S.pi_tiled = (__nv_bfloat16*)p;
     CK(cudaMalloc(&p, (size_t)Pn * sizeof(float))); P->allocs.push_back(p); S.success_sum = (float*)p;
     CK(cudaMalloc(&p, (size_t)Pn * sizeof(float))); P->allocs.push_back(p); S.return_sum = (float*)p;
     CK(cudaMalloc(&p, (size_t)Pn * sizeof(int))); P->allocs.push_back(p); S.steps_run = (int*)p;
@@ -735,6 +789,7 @@ int ensure_scratch(Population* P, int n, std::string* err) {
     CK(cudaMalloc(&p, (size_t)Pn * n * P->c.O * sizeof(float))); P->allocs.push_back(p); S.obs_work = (float*)p;
     CK(cudaMalloc(&p, (size_t)Pn * n)); P->allocs.push_back(p); S.success = (unsigned char*)p;
     CK(cudaMalloc(&p, (size_t)Pn * n * sizeof(int))); P->allocs.push_back(p); S.length = (int*)p;
+    CK(cudaMalloc(&p, (size_t)Pn * 2 * n * P->c.A * sizeof(float))); P->allocs.push_back(p); S.noise_next = (float*)p;
     S.ep_cap = n;
   }
   return 0;
@@ -745,24 +800,26 @@ void add_policy(Program& pg, Population* P) {
   const NetLayout& N = ar.L;
   for (int l = 0; l < N.n_hidden; ++l) {
     const int i = pg.add(ar.shadow + N.offW[l], N.K(l), N.H, N.H, ar.V, N.S, RO_HIDDEN, ACT_GELU, N.ln, l == 0,
-                         ar.theta + N.offb[l], N.S, 1);
+                         ar.theta + N.offb[l], N.S, 1, P->ro.pi_tiled ? P->ro.pi_tiled + N.offW[l] : nullptr);
     if (i >= 0 && N.ln) {
       pg.R->layer[i].gamma = ar.theta + N.offg[l];
       pg.R->layer[i].beta = ar.theta + N.offbeta[l];
     }
   }
-  pg.add(P->ro.head_w, N.H, 64, N.out_dim, ar.V, (long long)N.H * 64, RO_PI_HEAD, ACT_NONE, 0, 0, P->ro.head_b, 64, 1);
+  // (a 64-column kernel is its own tiled image)
+  pg.add(P->ro.head_w, N.H, 64, N.out_dim, ar.V, (long long)N.H * 64, RO_PI_HEAD, ACT_NONE, 0, 0, P->ro.head_b, 64, 1,
+         P->ro.head_w, P->ro.head_w);
 }
 void add_env(Program& pg, const EnvModel* m) {
   for (size_t i = 0; i < m->state.size(); ++i) {
     const EnvModel::Layer& L = m->state[i];
     const bool last = i + 1 == m->state.size();
-    pg.add(L.w, L.K_pad, L.N_pad, L.N, 1, 0, last ? RO_STATE_OUT : RO_HIDDEN, ACT_RELU, 0, i == 0, L.b, 0, 0);
+    pg.add(L.w, L.K_pad, L.N_pad, L.N, 1, 0, last ? RO_STATE_OUT : RO_HIDDEN, ACT_RELU, 0, i == 0, L.b, 0, 0, L.wt, L.wt64);
   }
   for (size_t i = 0; i < m->term.size(); ++i) {
     const EnvModel::Layer& L = m->term[i];
     const bool last = i + 1 == m->term.size();
-    pg.add(L.w, L.K_pad, L.N_pad, L.N, 1, 0, last ? RO_TERM_OUT : RO_HIDDEN, ACT_RELU, 0, i == 0, L.b, 0, 0);
+    pg.add(L.w, L.K_pad, L.N_pad, L.N, 1, 0, last ? RO_TERM_OUT : RO_HIDDEN, ACT_RELU, 0, i == 0, L.b, 0, 0, L.wt, L.wt64);
   }
 }
 void launch_head_image(Population* P, cudaStream_t s) {
@@ -803,6 +860,7 @@ int rollout_impl(Population* P, EnvModel* m, const RolloutArgs& a, cudaStream_t 
   R.init_obs = a.init_obs; R.init_obs_ms = a.init_obs_ms;
   R.noise = a.noise; R.noise_ms = a.noise_ms;
   R.obs_work = P->ro.obs_work;
+  R.noise_next = P->ro.noise_next;
   R.success = a.success ? a.success : P->ro.success;
   R.length = a.length ? a.length : P->ro.length;
   R.success_sum = P->ro.success_sum; R.return_sum = P->ro.return_sum;
@@ -812,7 +870,18 @@ int rollout_impl(Population* P, EnvModel* m, const RolloutArgs& a, cudaStream_t 
   CK(cudaMemsetAsync(P->ro.success_sum, 0, sizeof(float) * P->c.P, stream));
   CK(cudaMemsetAsync(P->ro.return_sum, 0, sizeof(float) * P->c.P, stream));
   CK(cudaMemsetAsync(R.steps_run, 0, sizeof(int) * P->c.P, stream));
-  CK(launch_rollout(R, n_active, stream));
+  if (rollout_gen() >= 2 && rollout16_eligible(R)) {
+    const bool pair = rollout_pair_mode(true) && R.tiles_per_member >= 2;
+    if (!pg.widen(pair)) return 1;
+    const NetLayout& N = P->pi.L;
+    for (int l = 0; l < N.n_hidden; ++l)
+      tile_policy_kernel<<<dim3(16, n_active), 256, 0, stream>>>(P->pi.shadow, P->ro.pi_tiled, N.S, N.offW[l], N.K(l), N.H,
+                                                               P->member_list, pair ? 1 : 0);
+    P->ro.launches += N.n_hidden;
+    CK(launch_rollout16(R, n_active, pair, stream));
+  } else {
+    CK(launch_rollout(R, n_active, stream));
+  }
   CK(cudaGetLastError());
   finish_rollout_kernel<<<(n_active + 127) / 128, 128, 0, stream>>>(P->member_list, n_active, a.n_episodes,
                                                                     P->ro.success_sum, P->ro.return_sum,

@@ -68,6 +68,7 @@ struct RoParams {
   const float* actions_in;                        // RO_MODE_ENV: [n][A]
   // state + outputs (all indexed by member id)
   float* obs_work;         // [P][n][O] fp32 current observations (scratch, also the final observations)
+  float* noise_next;       // [P][2][n][A] scratch: Philox policy noise of step s at [s & 1], drawn during step s - 1
   unsigned char* success;  // [P][n]
   int* length;             // [P][n] step of the first termination / truncation (0 = never within n_steps)
   float* success_sum;      // [P] sum of success flags   (host divides by n)
@@ -79,6 +80,7 @@ struct RoParams {
   float* actions_out;      // RO_MODE_POLICY: [n][A]
   float* next_obs_out;     // RO_MODE_ENV: [n][O]
   float* logits_out;       // RO_MODE_ENV: [n]
+  int debug_flags;         // (make TRACE=1, rollout16.cu) 1: no MMAs, 2: no weight TMA -- timing only, results are garbage
 };
 
 // Device-resident world model (shared by every member): bf16 padded kernels for the tensor cores, fp32 biases.
@@ -91,6 +93,8 @@ struct EnvModel {
   struct Layer {
     int K = 0, N = 0, K_pad = 0, N_pad = 0;
     __nv_bfloat16* w = nullptr;  // [K_pad][N_pad]
+    __nv_bfloat16* wt = nullptr;   // the same, tiled [K_pad / 32][N_pad / 64][32][64] (rollout16.cu)
+    __nv_bfloat16* wt64 = nullptr; // ... and tiled [K_pad / 64][N_pad / 64][64][64] (rollout16.cu, pair mode)
     float* b = nullptr;          // [N_pad]
   };
   std::vector<Layer> state, term;

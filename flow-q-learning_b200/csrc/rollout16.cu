@@ -41,6 +41,21 @@ constexpr int kBoxBytes = 64 * 32 * 2;
 constexpr int kBarBytes = 1024;   // barriers and flags
 constexpr int kSmemBytesR = kActBytes + kActBlockBytes + kStages * kStageBytes + kBarBytes + 1024;
 
+#ifdef FQLPOP_EPI_TRACE
+// (make TRACE=1) CTA (0,0): [0,2048) MMA issuer, 8 words per layer: start, cycles waited for drained / A operand / weight
+// stages, end; [2048,4096) epilogue lane 0 of the cg = 0 and cg = 3 warps of quarter 0: enter, tile 0 ready, layer done
+__device__ long long g_ro16_trace[4096];
+// weight stages of lockstep step 1, policy layers 1-2 (64 stages): producer saw the slot empty / issued the TMA, MMA
+// issuer saw the stage full / issued its MMAs
+__device__ long long g_ro16_stage[4 * 64];
+__device__ long long g_ro16_stage_peer[4 * 64];   // the same two producer stamps for CTA (1,0): the peer of a pair
+#define RT_T0() const long long rt_t0 = clock64()
+#define RT_ACC(x) x += clock64() - rt_t0
+#else
+#define RT_T0()
+#define RT_ACC(x)
+#endif
+
 __device__ __forceinline__ float clip1(float x) { return fminf(fmaxf(x, -1.f), 1.f); }
 __device__ __forceinline__ void sts128(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
@@ -121,6 +136,8 @@ __device__ __forceinline__ void act_chunk(const uint32_t (&rr)[16], const float4
   }
 }
 // this thread's 64 columns of accumulator tile `tile`: DEST 0 keep in pk[32], 1 write to ACT
+// (measured: handing every block of a tile over as soon as all 16 warps have written their 16 columns of it -- blocks
+// completing one after the other -- costs more in fences than the earlier MMA start gains: 324 vs 328 M env-steps/s)
 template <int ACT, int DEST>
 __device__ __forceinline__ void hidden_pass(const REpi& C, const float* bias, int tile, uint32_t (&pk)[32]) {
   const int colw = tile * 256 + C.cg * 64;
@@ -187,8 +204,12 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
   int* peer_first_done = steps_done + 1;                    // (pair) the other CTA's two flags, written by it
   int* peer_steps_done = peer_first_done + 1;
   int* warp_all = peer_steps_done + 1;                      // [4]
-  constexpr int kSlotBytes = PAIR ? kStageBytes / 2 : kStageBytes;
-  constexpr int kSlots = PAIR ? kMaxSlots : kStages;
+  // a weight stage: 32 k x 256 n; in pair mode 64 k x this CTA's 128 n (half as many waits and commits per MMA for the one
+  // thread that feeds the M = 256 products)
+  constexpr int kSlotBytes = kStageBytes;
+  constexpr int kSlots = kStages;
+  constexpr int kStageK = PAIR ? 64 : 32;
+  constexpr int kBoxB = kStageK * 128;          // one 64-column box of a stage
   constexpr uint32_t kCtas = PAIR ? 2 : 1;
 
   const int warp = threadIdx.x >> 5;
@@ -228,8 +249,8 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
   if (PAIR) cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  auto pair_first_done = [&]() { return max(ld_volatile_s32(first_done), ld_volatile_s32(peer_first_done)); };
   const uint32_t full_bar_l = (PAIR && !leader) ? mapa_u32(smem_u32(full_bar), 0) : smem_u32(full_bar);
+  auto pair_first_done = [&]() { return max(ld_volatile_s32(first_done), ld_volatile_s32(peer_first_done)); };
 
   if (warp == 0) {
     // ======================================= TMA producer ========================================
@@ -252,14 +273,31 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
             const int ncols = min(256, Ly.n_pad - n0);
             const int mycols = PAIR ? max(ncols / 2, 64) : ncols;
             const int c0 = n0 + (int)rank * mycols;
-            for (int ks = 0; ks < Ly.k_blocks * 2; ++ks) {  // one stage = 32 k x ncols n
+            for (int ks = 0; ks < Ly.k_blocks * (64 / kStageK); ++ks) {  // one stage = kStageK k x mycols n
               mbar_wait(&empty_bar[stage], phase ^ 1);
+#ifdef FQLPOP_EPI_TRACE
+              const bool st_tr = blockIdx.x <= 1 && blockIdx.y == 0 && step == 1 && (li == 1 || li == 2);
+              const int st_idx = (li - 1) * 32 + (n0 / 256) * 16 + ks;
+              long long* st_log = blockIdx.x == 0 ? g_ro16_stage : g_ro16_stage_peer;
+              if (st_tr) st_log[4 * st_idx] = clock64();
+#endif
               uint8_t* sb = stage_base + stage * kSlotBytes;
-              if (leader) mbar_arrive_expect_tx(&full_bar[stage], (mycols / 64) * kBoxBytes * kCtas);
-              for (int b = 0; b < mycols / 64; ++b) {
-                if (PAIR) tma_load_3d_2sm(sb + b * kBoxBytes, &P.maps[li], full_bar_l + 8u * (uint32_t)stage, c0 + 64 * b, ks * 32, batch);
-                else tma_load_3d(sb + b * kBoxBytes, &P.maps[li], &full_bar[stage], c0 + 64 * b, ks * 32, batch);
+#ifdef FQLPOP_DEBUG_SWITCHES
+              if (P.debug_flags & 2) {
+                if (leader) mbar_arrive(&full_bar[stage]);
+                if (++stage == kSlots) { stage = 0; phase ^= 1; }
+                continue;
               }
+#endif
+              if (leader) mbar_arrive_expect_tx(&full_bar[stage], (mycols / 64) * kBoxB * kCtas);
+              // one instruction per stage: the weights are tiled [K / kStageK][N / 64][kStageK][64] and the map's box is this CTA's
+              // mycols / 64 adjacent boxes (Program::widen) -- one contiguous run of global memory
+              const int row = (ks * (Ly.n_pad >> 6) + (c0 >> 6)) * kStageK;
+              if (PAIR) tma_load_3d_2sm(sb, &P.maps[li], full_bar_l + 8u * (uint32_t)stage, 0, row, batch);
+              else tma_load_3d(sb, &P.maps[li], &full_bar[stage], 0, row, batch);
+#ifdef FQLPOP_EPI_TRACE
+              if (st_tr) st_log[4 * st_idx + 1] = clock64();
+#endif
               if (++stage == kSlots) { stage = 0; phase ^= 1; }
             }
           }
@@ -279,10 +317,16 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
         for (int li = 0; li < n_layers; ++li, ++lc) {
           const RoLayer& Ly = P.layer[li];
           const bool from_act = !Ly.a_from_x0;
+#ifdef FQLPOP_EPI_TRACE
+          long long w_dr = 0, w_a = 0, w_wt = 0;
+          const long long t_begin = clock64();
+#endif
           if (!from_act) {
+            RT_T0();
             mbar_wait(x0_ready, xc & 1);
             ++xc;
             tc_fence_after();
+            RT_ACC(w_a);
           }
           const uint32_t a_base = from_act ? act_addr : x0_addr;
           const bool two = Ly.n_pad > 256;
@@ -290,29 +334,56 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
           for (int n0 = 0; n0 < Ly.n_pad; n0 += 256, ++t) {
             const int ncols = min(256, Ly.n_pad - n0);
             const uint32_t idesc = make_idesc_bf16(PAIR ? 256 : 128, PAIR ? (uint32_t)max(ncols, 128) : (uint32_t)ncols, 0, 1);
-            if (t == 0) {
-              if (lc > 0) mbar_wait(&drained[0], (lc - 1) & 1);
-            } else if (tc > 0) {
-              mbar_wait(&drained[1], (tc - 1) & 1);
+            {
+              RT_T0();
+              if (t == 0) {
+                if (lc > 0) mbar_wait(&drained[0], (lc - 1) & 1);
+              } else if (tc > 0) {
+                mbar_wait(&drained[1], (tc - 1) & 1);
+              }
+              tc_fence_after();
+              RT_ACC(w_dr);
             }
-            tc_fence_after();
             for (int kb = 0; kb < Ly.k_blocks; ++kb) {
               if (from_act && t == 0) {
+                RT_T0();
                 mbar_wait(&blk_full[kb], (blk_par >> kb) & 1u);
                 blk_par ^= 1u << kb;
                 tc_fence_after();
+                RT_ACC(w_a);
               }
-              for (int h = 0; h < 2; ++h) {
-                mbar_wait(&full_bar[stage], phase);
-                tc_fence_after();
+              for (int h = 0; h < 64 / kStageK; ++h) {
+                {
+                  RT_T0();
+                  mbar_wait(&full_bar[stage], phase);
+                  tc_fence_after();
+                  RT_ACC(w_wt);
+                }
+#ifdef FQLPOP_EPI_TRACE
+                const bool st_tr = blockIdx.x == 0 && blockIdx.y == 0 && step == 1 && (li == 1 || li == 2) && lane == 0;
+                const int st_idx = (li - 1) * 32 + t * 16 + kb * 2 + h;
+                if (st_tr) g_ro16_stage[4 * st_idx + 2] = clock64();
+#endif
+#ifdef FQLPOP_DEBUG_SWITCHES
+                if (P.debug_flags & 1) {   // free the slot (both CTAs) without reading it
+                  if (lane == 0) {
+                    mbar_arrive(&empty_bar[stage]);
+                    if (PAIR) mbar_arrive_cluster(mapa_u32(smem_u32(&empty_bar[stage]), 1));
+                    if (kb == Ly.k_blocks - 1 && h == 64 / kStageK - 1) {
+                      if (PAIR) umma_commit_2sm(&tmem_full[t], 3);
+                      else umma_commit(&tmem_full[t]);
+                    }
+                  }
+                } else
+#endif
                 if (elect_one()) {
                   const uint32_t sa = a_base + kb * kActBlockBytes + h * 64;
                   const uint32_t sb = smem_u32(stage_base + stage * kSlotBytes);
-                  const bool last = kb == Ly.k_blocks - 1 && h == 1;
+                  const bool last = kb == Ly.k_blocks - 1 && h == 64 / kStageK - 1;
 #pragma unroll
-                  for (int k = 0; k < 2; ++k) {
+                  for (int k = 0; k < kStageK / 16; ++k) {
                     const uint64_t adesc = make_smem_desc_sw128(sa + k * 32, 16, 1024);
-                    const uint64_t bdesc = make_smem_desc_sw128(sb + k * 2048, kBoxBytes, 1024);
+                    const uint64_t bdesc = make_smem_desc_sw128(sb + k * 2048, kBoxB, 1024);
                     const uint32_t acc = (kb | h | k) != 0 ? 1u : 0u;
                     if (PAIR) umma_bf16_2sm(tmem_base + n0, adesc, bdesc, idesc, acc);
                     else umma_bf16(tmem_base + n0, adesc, bdesc, idesc, acc);
@@ -326,11 +397,20 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
                   }
                 }
                 __syncwarp();
+#ifdef FQLPOP_EPI_TRACE
+                if (st_tr) g_ro16_stage[4 * st_idx + 3] = clock64();
+#endif
                 if (++stage == kSlots) { stage = 0; phase ^= 1; }
               }
             }
           }
           if (two) ++tc;
+#ifdef FQLPOP_EPI_TRACE
+          if (blockIdx.x == 0 && blockIdx.y == 0 && lane == 0 && lc < 256) {
+            long long* o = g_ro16_trace + 8 * lc;
+            o[0] = t_begin; o[1] = w_dr; o[2] = w_a; o[3] = w_wt; o[4] = clock64();
+          }
+#endif
         }
       }
     }
@@ -365,10 +445,23 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
     bool done_once = false, success = false;   // (cg == 0 thread) episode bookkeeping
     int length = 0, steps_executed = 0;
 
+    // Philox policy noise is drawn one lockstep step ahead, while this warp would otherwise wait for the tensor core, and
+    // parked in global scratch (L2): thread (row, cg) draws action slots cg, cg + 4, ... of its row, one share per policy
+    // layer. Step 0's is drawn inline.
+    int pi_head = 0;
+    while (pi_head < n_layers - 1 && P.layer[pi_head].kind != RO_PI_HEAD) ++pi_head;
+    float* nz_next = P.noise_next + ((long long)member * 2 * P.n + e) * A;   // + (step & 1) * n * A
+    auto draw_ahead = [&](int step, int li) {   // called on entry to policy layer li of lockstep step `step`
+      if (P.noise || !row_ok || li < 1 || li > pi_head || step + 1 >= n_steps) return;
+      float* dst = nz_next + (long long)((step + 1) & 1) * P.n * A;
+      for (int j = cg + 4 * (li - 1); j < A; j += 4 * pi_head)
+        __stcg(dst + j, philox_normal(seed, P.eval_counter + (unsigned long long)(step + 1), (uint32_t)e, (uint32_t)j));
+    };
     // policy input [o, z_step] -> X0 (this thread's 16 columns)
     auto build_policy_input = [&](int step) {
       float x[16];
       const float* nz = P.noise ? P.noise + (long long)member * P.noise_ms + ((long long)step * P.n + e) * A : nullptr;
+      const float* nzs = nz_next + (long long)(step & 1) * P.n * A;
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
         const int k = k0 + i;
@@ -376,7 +469,8 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
         if (k >= O && k < OA) {
           if (!row_ok) v = 0.f;
           else if (nz) v = __ldg(nz + (k - O));
-          else v = philox_normal(seed, P.eval_counter + (unsigned long long)step, (uint32_t)e, (uint32_t)(k - O));
+          else if (step > 0) v = __ldcg(nzs + (k - O));
+          else v = philox_normal(seed, P.eval_counter, (uint32_t)e, (uint32_t)(k - O));
         }
         x[i] = v;
       }
@@ -399,14 +493,26 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
         const RoLayer& Ly = P.layer[li];
         const uint32_t par0 = lc & 1, par1 = tc & 1;
         const float* bias = Ly.bias + (Ly.per_member ? (long long)member * Ly.bias_ms : 0);
+#ifdef FQLPOP_EPI_TRACE
+        long long* tr = (blockIdx.x == 0 && blockIdx.y == 0 && q == 0 && lane == 0 && (cg == 0 || cg == 3) && lc < 256)
+                            ? g_ro16_trace + 2048 + 8 * lc + (cg ? 4 : 0) : nullptr;
+        if (tr) tr[0] = clock64();
+#endif
+        draw_ahead(step, li);
         if (Ly.kind == RO_HIDDEN) {
           if (Ly.act == ACT_GELU) hidden_layer<ACT_GELU>(C, bias, Ly.n_pad, par0, par1);
           else hidden_layer<ACT_RELU>(C, bias, Ly.n_pad, par0, par1);
           if (Ly.n_pad > 256) ++tc;
+#ifdef FQLPOP_EPI_TRACE
+          if (tr) tr[2] = clock64();
+#endif
           continue;
         }
         // head layers: 64 accumulator columns, 16 per thread
         wait_full(C, 0, par0);
+#ifdef FQLPOP_EPI_TRACE
+        if (tr) tr[1] = clock64();
+#endif
         float x[16];
         {
           uint32_t rr[16];
@@ -496,11 +602,17 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
             }
             asm volatile("bar.sync 9, 128;" ::: "memory");
           }
+#ifdef FQLPOP_EPI_TRACE
+          if (tr) tr[3] = clock64();
+#endif
           if (s1 < n_steps) {
             build_policy_input(s1);
             publish(C, C.x0_ready_a);
           }
         }
+#ifdef FQLPOP_EPI_TRACE
+        if (tr) tr[2] = clock64();
+#endif
       }
     }
 
@@ -565,7 +677,11 @@ bool rollout16_eligible(const RoParams& R) {
   return true;
 }
 
-cudaError_t launch_rollout16(const RoParams& R, int n_members, bool pair, cudaStream_t stream) {
+cudaError_t launch_rollout16(const RoParams& R_in, int n_members, bool pair, cudaStream_t stream) {
+  RoParams R = R_in;
+#ifdef FQLPOP_DEBUG_SWITCHES
+  if (const char* e = getenv("FQLPOP_RO_DEBUG")) R.debug_flags = atoi(e);
+#endif
   if (!pair || R.tiles_per_member < 2) {
     fql_rollout16_kernel<false><<<dim3(R.tiles_per_member, n_members), kThreadsR, kSmemBytesR, stream>>>(R);
     return cudaGetLastError();
@@ -584,3 +700,15 @@ cudaError_t launch_rollout16(const RoParams& R, int n_members, bool pair, cudaSt
 }
 
 }  // namespace fqlpop
+
+#ifdef FQLPOP_EPI_TRACE
+extern "C" int fqlpop_debug_rollout_trace(long long* host_out, int n) {
+  cudaDeviceSynchronize();
+  return cudaMemcpyFromSymbol(host_out, fqlpop::g_ro16_trace, sizeof(long long) * (n < 4096 ? n : 4096)) == cudaSuccess ? 0 : -1;
+}
+extern "C" int fqlpop_debug_rollout_stage_trace(long long* host_out) {
+  cudaDeviceSynchronize();
+  return cudaMemcpyFromSymbol(host_out, fqlpop::g_ro16_stage, sizeof(long long) * 256) == cudaSuccess &&
+         cudaMemcpyFromSymbol(host_out + 256, fqlpop::g_ro16_stage_peer, sizeof(long long) * 256) == cudaSuccess ? 0 : -1;
+}
+#endif

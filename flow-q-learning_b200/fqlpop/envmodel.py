@@ -72,6 +72,8 @@ class EnvModel:
         if not torch.cuda.is_available():
             raise _lib.FqlPopError("no CUDA device: the world-model rollout has no CPU fallback")
         self.device = torch.device(device) if device is not None else _lib.default_device()
+        if self.device.index is None:   # a bare "cuda" means the current device
+            self.device = torch.device("cuda", torch.cuda.current_device())
         torch.cuda.set_device(self.device)
         sl, tl = _dense_layers(state), _dense_layers(termination)
         if len(sl) < 2 or len(tl) < 2:

@@ -85,6 +85,8 @@ class Population:
         if not torch.cuda.is_available():
             raise _lib.FqlPopError("no CUDA device: the population hot path has no CPU fallback")
         self.device = torch.device(device) if device is not None else _lib.default_device()
+        if self.device.index is None:   # a bare "cuda" means the current device
+            self.device = torch.device("cuda", torch.cuda.current_device())
         torch.cuda.set_device(self.device)
         ha, nha = _uniform_width(get("actor_hidden_dims", (512,) * 4), "actor_hidden_dims")
         hv, nhv = _uniform_width(get("value_hidden_dims", (512,) * 4), "value_hidden_dims")
