@@ -307,6 +307,16 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&rr)[16], const float4
   }
 }
 
+// 16 bf16 values (one 32-byte sector) of this thread's row straight to global memory: one 256-bit store. Used for act'(z) of
+// the LayerNorm-free forward passes, which then need no staging area and keep all five weight slots (with three, the
+// policy pass spent 60 % of its MMA issuer's time waiting for weights).
+__device__ __forceinline__ void st_row32(__nv_bfloat16* dst, const uint32_t (&w)[8], bool ok) {
+  if (ok)
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst), "r"(w[0]), "r"(w[1]), "r"(w[2]),
+                 "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+                 : "memory");
+}
+
 // DEST: 0 = keep the 64 bf16 results in pk[32]; 1 = write them to ACT; 2 = park them in the drained TMEM columns
 template <bool LN, bool SAVE, int DEST>
 __device__ __forceinline__ void fwd_pass1(const Epi& C, const ChainLayer& Ly, int tile, uint32_t (&pk)[32], float& s1,
@@ -324,7 +334,10 @@ __device__ __forceinline__ void fwd_pass1(const Epi& C, const ChainLayer& Ly, in
     tmem_ld_wait();
     tmem_ld16(tbase + (c + 1) * 16, rb);
     fwd_chunk<LN, SAVE>(ra, b4, pk + 8 * c, gpk, s1, s2);
-    if (SAVE) st_half16(C.stg, C.lane, 0, gpk);
+    if (SAVE) {
+      if (LN) st_half16(C.stg, C.lane, 0, gpk);
+      else st_row32(Ly.out_gp + C.wrow + (long long)C.lane * C.H + colw + c * 16, gpk, C.row_ok);
+    }
     if (DEST == 1) st_act16(C.act, C.r, colw + c * 16, pk + 8 * c);
     if (DEST == 2) tmem_st8(tbase + c * 8, *reinterpret_cast<const uint32_t(*)[8]>(pk + 8 * c));
     // ---- odd chunk (rb) ----
@@ -333,10 +346,14 @@ __device__ __forceinline__ void fwd_pass1(const Epi& C, const ChainLayer& Ly, in
     if (c + 2 < 4) tmem_ld16(tbase + (c + 2) * 16, ra);
     fwd_chunk<LN, SAVE>(rb, b4, pk + 8 * (c + 1), gpk, s1, s2);
     if (SAVE) {
-      st_half16(C.stg, C.lane, 16, gpk);
-      __syncwarp();
-      copy_out_half(C.stg, Ly.out_gp + C.wrow + colw + c * 16, C.H, C.lane, C.rows_valid);
-      __syncwarp();
+      if (LN) {
+        st_half16(C.stg, C.lane, 16, gpk);
+        __syncwarp();
+        copy_out_half(C.stg, Ly.out_gp + C.wrow + colw + c * 16, C.H, C.lane, C.rows_valid);
+        __syncwarp();
+      } else {
+        st_row32(Ly.out_gp + C.wrow + (long long)C.lane * C.H + colw + (c + 1) * 16, gpk, C.row_ok);
+      }
     }
     if (DEST == 1) st_act16(C.act, C.r, colw + (c + 1) * 16, pk + 8 * (c + 1));
     if (DEST == 2) tmem_st8(tbase + (c + 1) * 8, *reinterpret_cast<const uint32_t(*)[8]>(pk + 8 * (c + 1)));
@@ -713,7 +730,13 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
   uint64_t* a0_full = drained + 2;
   uint64_t* x0_ready = a0_full + 1;             // Euler: the X0 block holds the next step's input
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(x0_ready + 1);
-  constexpr int kSlotBytes = PAIR ? kStageBytes / 2 : kStageBytes;
+  // weight slot = one stage of THIS CTA: 32 k x 256 n; pair mode, backward: 32 k x this CTA's 128 rows (8 KB slots, twice
+  // as many); pair mode, forward: 64 k x this CTA's 128 n -- four MMAs per wait / commit of the one issuing thread, whose
+  // loop overhead is what bounds a pair (measured in rollout16.cu: 310 -> 348 M env-steps/s)
+  constexpr bool kDeep = PAIR && MODE == 0;
+  constexpr int kSlotBytes = (PAIR && MODE == 1) ? kStageBytes / 2 : kStageBytes;
+  constexpr int kStgK = kDeep ? 64 : kStageK;       // reduction elements per weight stage
+  constexpr int kFwdBox = 64 * kStgK * 2;           // forward weight box: 64 n x kStgK k
   constexpr uint32_t kCtas = PAIR ? 2 : 1;
 
   const int warp = threadIdx.x >> 5;
@@ -792,14 +815,14 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
       for (int it = 0; it < iters; ++it) {
         for (int li = 0; li < n_layers; ++li) {
           const ChainLayer& Ly = J.layer[li];
-          const int k_steps = Ly.k_blocks * 2;
+          const int k_steps = Ly.k_blocks * (64 / kStgK);
           for (int n0 = 0; n0 < Ly.n_pad; n0 += kTileN) {
             const int ncols = min(kTileN, Ly.n_pad - n0);
             // columns of this MMA tile staged by THIS CTA: [c0, c0 + mycols). A narrow layer (64 columns) is issued as an
             // N = 128 product in pair mode: the second CTA's half lies outside the weight tensor and is zero-filled.
             const int mycols = PAIR ? max(ncols / 2, 64) : ncols;
             const int c0 = n0 + (int)rank * mycols;
-            const uint32_t my_bytes = MODE == 0 ? (uint32_t)mycols * kStageK * 2
+            const uint32_t my_bytes = MODE == 0 ? (uint32_t)mycols * kStgK * 2
                                                 : (uint32_t)(PAIR ? mycols : Ly.b_box_rows) * kStageK * 2;
             for (int ks = 0; ks < k_steps; ++ks) {
               mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -816,8 +839,8 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
                   // W[k][n], n contiguous: boxes of 64 n x 32 k
                   const int wb = Ly.b_box_rows;   // 64-column blocks per TMA instruction
                   for (int b = 0; b < mycols / 64; b += wb) {
-                    if (PAIR) tma_load_4d_2sm(sb + b * kFwdBoxBytes, &J.mapW[li], fb, 0, ks * kStageK, (c0 >> 6) + b, v);
-                    else tma_load_4d(sb + b * kFwdBoxBytes, &J.mapW[li], &full_bar[stage], 0, ks * kStageK, (c0 >> 6) + b, v);
+                    if (PAIR) tma_load_4d_2sm(sb + b * kFwdBox, &J.mapW[li], fb, 0, ks * kStgK, (c0 >> 6) + b, v);
+                    else tma_load_4d(sb + b * kFwdBox, &J.mapW[li], &full_bar[stage], 0, ks * kStgK, (c0 >> 6) + b, v);
                   }
                 } else {
                   // the same array read as B^T: rows = output columns of this GEMM, 32 reduction elements per 64-byte row
@@ -842,7 +865,7 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
     int tc = 0;  // two-tile layers issued so far
     int pc = 0;  // ACT productions consumed so far
     const uint32_t act_addr = smem_u32(act), x0_addr = smem_u32(x0s);
-    const uint64_t bdesc0 = MODE == 0 ? make_smem_desc(smem_u32(stage_base), kFwdBoxBytes, 1024, 2)
+    const uint64_t bdesc0 = MODE == 0 ? make_smem_desc(smem_u32(stage_base), kFwdBox, 1024, 2)
                                       : make_smem_desc(smem_u32(stage_base), 16, 512, 4);
     constexpr uint32_t kBStep = (MODE == 0 ? 2048u : 32u) >> 4;  // descriptor units (16 B) per K = 16 step
 #ifdef FQLPOP_EPI_TRACE
@@ -897,7 +920,7 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
               tc_fence_after();
               TR_ACC(w_blk);
             }
-            for (int h = 0; h < 2; ++h) {
+            for (int h = 0; h < 64 / kStgK; ++h) {
               {
                 TR_T0();
                 mbar_wait(&full_bar[stage], phase);
@@ -908,10 +931,14 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
                 const uint64_t ad = adesc0 + (uint64_t)(kb * (kActBlockBytes >> 4) + h * 4);
                 const uint64_t bd = bdesc0 + (uint64_t)(stage * (kSlotBytes >> 4));
                 const uint32_t acc = (kb != 0 || h != 0) ? 1u : 0u;
-                const bool last = kb == nkb - 1 && h == 1;
+                const bool last = kb == nkb - 1 && h == 64 / kStgK - 1;
                 if (PAIR) {
                   umma_bf16_2sm(tmem_d, ad, bd, idesc, acc);
                   umma_bf16_2sm(tmem_d, ad + 2, bd + kBStep, idesc, 1u);
+                  if (kDeep) {
+                    umma_bf16_2sm(tmem_d, ad + 4, bd + 2 * kBStep, idesc, 1u);
+                    umma_bf16_2sm(tmem_d, ad + 6, bd + 3 * kBStep, idesc, 1u);
+                  }
                   umma_commit_2sm(&empty_bar[stage], 3);
                   if (last) umma_commit_2sm(&tmem_full[tile], 3);
                 } else {
@@ -1132,7 +1159,7 @@ static bool chain16_maps_ok(const ChainLaunch& L, int mode, bool pair) {
     for (int l = 0; l < j.n_layers; ++l) {
       const int wb = j.layer[l].b_box_rows;
       const int per_cta = j.layer[l].n_pad >= 256 ? (pair ? 2 : 4) : 1;
-      if (wb < 1 || per_cta % wb != 0) return false;
+      if (wb != per_cta) return false;   // (the box is also 64 k deep in pair mode, 32 otherwise: ChainBuilder::launch)
     }
   }
   return true;
@@ -1167,8 +1194,9 @@ cudaError_t launch_chain16(ChainLaunch& L, int mode, int grid, cudaStream_t stre
     units += (pair ? (L.job[i].m_tiles + 1) / 2 : L.job[i].m_tiles) * L.n_virtual;
   // weight slots: 16 KB each (8 KB in pair mode); launches that stage tensors through shared memory give up the last 32 KB
   if (!chain16_maps_ok(L, mode, pair)) return cudaErrorInvalidValue;
+  if (mode == 0 && !ln) L.stages = kStages;   // LayerNorm-free forward passes store act'(z) from registers: nothing staged
   L.staged = L.stages != kStages;
-  L.stages = (L.staged ? kStagesStaged : kStages) * (pair ? 2 : 1);
+  L.stages = (L.staged ? kStagesStaged : kStages) * ((pair && mode == 1) ? 2 : 1);
   if (mode == 0) return ln ? launch_variant<0, true>(L, pair, units, stream) : launch_variant<0, false>(L, pair, units, stream);
   return ln ? launch_variant<1, true>(L, pair, units, stream) : launch_variant<1, false>(L, pair, units, stream);
 }

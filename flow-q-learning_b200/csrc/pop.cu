@@ -315,6 +315,7 @@ struct ChainBuilder {
     }
   }
   void launch(int mode, cudaStream_t s) {
+    if (mode == 0) encode_forward_maps();
     finalize_chain(L);
     L->timeline = P->timeline;
     L->tag = (long long)count | ((long long)P->g_off << 8);
@@ -357,34 +358,52 @@ struct ChainBuilder {
 
   // forward pass over rows [row0, row0 + M): every hidden layer; the last hidden activations always go to HBM
   // (the head kernels read them), the others only when the backward pass needs them
-  // Weight maps of a forward chain. When the second-generation kernel (chain16.cu) will run the launch, a weight stage is
-  // fetched by one TMA instruction whose box spans `boxes` 64-column blocks (encode_tmap_bf16_wide): 4 = a whole
-  // 256-column accumulator tile, 2 = one CTA's half of it in pair mode (a launch that ends up unpaired issues two).
-  int wide_boxes(const NetLayout& N, int iters, int M) const {
-    if (!chain16_selected_shape(N.H, N.in_pad, N.ln != 0, iters, (int)P->h_members.size())) return 0;
-    return (chain16_pair_mode() && chain16_pairs_rows(M)) ? 2 : 4;
+  // Weight maps of a forward chain are encoded when the launch is complete (launch()): the second-generation kernel
+  // (chain16.cu) fetches a weight stage with one TMA instruction whose box spans the CTA's 64-column blocks -- 4 blocks x
+  // 32 k for a whole 256-column accumulator tile, 2 blocks x 64 k for one CTA's half in pair mode, 1 block for the narrow
+  // layers (encode_tmap_bf16_wide) -- and whether it runs, paired or not, depends on every job of the launch.
+  struct WArgs { const void* base; long long inner, rows, batch, ms; };
+  WArgs wargs[kChainMaxJobs][kChainMaxLayers];
+  void wmap_later(int layer, const void* base, long long inner, long long rows, long long batch, long long ms) {
+    wargs[L->num_jobs - 1][layer] = WArgs{base, inner, rows, batch, ms};
   }
-  void wmap(CUtensorMap* m, const void* base, long long inner, long long rows, long long batch, long long ms, int boxes) {
-    if (boxes == 0) return tmap(m, base, inner, rows, batch, inner, ms, 32);
-    const int rc = encode_tmap_bf16_wide(m, base, inner, rows, batch, inner, ms, 32, boxes);
-    if (rc != 0 && ok) {
-      ok = false;
-      if (err) *err = "cuTensorMapEncodeTiled (wide box) failed rc=" + std::to_string(rc);
+  void encode_forward_maps() {
+    const ChainJob& j0 = L->job[0];
+    const bool c16 = chain16_eligible(*L) &&
+                     chain16_selected_shape(j0.H, 64, j0.ln != 0, j0.iters, (int)P->h_members.size());
+    bool pair = c16 && chain16_pair_mode();
+    for (int i = 0; i < L->num_jobs; ++i) pair = pair && chain16_pairs_rows(L->job[i].M);
+    for (int i = 0; i < L->num_jobs; ++i) {
+      ChainJob& j = L->job[i];
+      for (int l = 0; l < j.n_layers; ++l) {
+        const WArgs& a = wargs[i][l];
+        int rc;
+        if (c16) {
+          const int boxes = j.layer[l].n_pad >= 256 ? (pair ? 2 : 4) : 1;
+          rc = encode_tmap_bf16_wide(&j.mapW[l], a.base, a.inner, a.rows, a.batch, a.inner, a.ms, pair ? 64 : 32, boxes);
+          j.layer[l].b_box_rows = boxes;
+        } else {
+          rc = encode_tmap_bf16(&j.mapW[l], a.base, a.inner, a.rows, a.batch, a.inner, a.ms, 32);
+          j.layer[l].b_box_rows = 0;
+        }
+        if (rc != 0 && ok) {
+          ok = false;
+          if (err) *err = "cuTensorMapEncodeTiled (forward weights) failed rc=" + std::to_string(rc);
+        }
+      }
     }
   }
   ChainJob& fwd_job(PassBuf& pass, const Arena& ar, const float* params, const __nv_bfloat16* wsh, int row0, int M,
-                    bool save, int iters = 1) {
+                    bool save) {
     const NetLayout& N = ar.L;
     ChainJob& j = common(pass, ar, params, row0, M);
     j.n_layers = N.n_hidden;
-    const int boxes = wide_boxes(N, iters, M);
     tmap(&j.mapA0, pass.X0, N.in_pad, pass.M, pass.V, N.in_pad, (long long)pass.M * N.in_pad, 128);
     const long long roff = (long long)row0 * N.H;
     for (int l = 0; l < N.n_hidden; ++l) {
-      wmap(&j.mapW[l], wsh + N.offW[l], N.H, N.K(l), ar.V, N.S, boxes);
+      wmap_later(l, wsh + N.offW[l], N.H, N.K(l), ar.V, N.S);
       ChainLayer& y = j.layer[l];
       y.kind = CL_HIDDEN; y.k_blocks = N.K(l) / 64; y.n_pad = N.H; y.a_from_x0 = l == 0;
-      y.b_box_rows = boxes;
       y.off_b = N.offb[l]; y.off_g = N.offg[l]; y.off_beta = N.offbeta[l];
       if (save || l == N.n_hidden - 1) y.out_h = pass.hl(l) + roff;
       if (save) {
@@ -402,13 +421,11 @@ struct ChainBuilder {
   void euler_job() {
     const Arena& ar = P->bc;
     const NetLayout& N = ar.L;
-    ChainJob& j = fwd_job(P->EU, ar, ar.theta, ar.shadow, 0, P->c.B, false, P->c.F);
+    ChainJob& j = fwd_job(P->EU, ar, ar.theta, ar.shadow, 0, P->c.B, false);
     j.layer[N.n_hidden - 1].out_h = nullptr;
     const int l = N.n_hidden;
-    const int boxes = wide_boxes(N, P->c.F, P->c.B) ? 1 : 0;
-    wmap(&j.mapW[l], ar.shadow + N.offW[l], kHeadPad, N.H, ar.V, N.S, boxes);
+    wmap_later(l, ar.shadow + N.offW[l], kHeadPad, N.H, ar.V, N.S);
     ChainLayer& y = j.layer[l];
-    y.b_box_rows = boxes;
     y.kind = CL_EULER_HEAD; y.k_blocks = N.H / 64; y.n_pad = kHeadPad; y.a_from_x0 = 0;
     y.off_b = N.offb[l];
     j.n_layers = N.n_hidden + 1;

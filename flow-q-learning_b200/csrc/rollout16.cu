@@ -485,6 +485,34 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
     build_policy_input(0);
     publish(C, C.x0_ready_a);
 
+    // The CTA's done / progress flags of lockstep step s are published by ONE thread, off the critical path: the other
+    // three bookkeeping warps only arrive on named barrier 9 after the termination layer; the first one completes the
+    // barrier and stores the flags on entry to layer 1 of step s + 1 -- before its next mbarrier arrival, which every role's
+    // check of the flags (two steps after they were set) is ordered after.
+    int pending_step = -1;
+    auto publish_flags = [&]() {
+      asm volatile("bar.sync 9, 128;" ::: "memory");
+      if (r == 0) {
+        const int s1 = pending_step + 1;
+        int fd = ld_volatile_s32(first_done);
+        if (warp_all[0] && warp_all[1] && warp_all[2] && warp_all[3] && fd == INT_MAX) {
+          fd = pending_step;
+          st_volatile_s32(first_done, fd);
+        }
+        if (PAIR) {  // mirror both flags into the peer, first_done before steps_done
+          const uint32_t peer = rank ^ 1u;
+          asm volatile("st.shared::cluster.s32 [%0], %1;" ::"r"(mapa_u32(smem_u32(peer_first_done), peer)), "r"(fd) : "memory");
+          asm volatile("fence.acq_rel.cluster;" ::: "memory");
+          asm volatile("st.shared::cluster.s32 [%0], %1;" ::"r"(mapa_u32(smem_u32(peer_steps_done), peer)), "r"(s1) : "memory");
+          asm volatile("fence.acq_rel.cluster;" ::: "memory");
+        }
+        __threadfence_block();
+        st_volatile_s32(steps_done, s1);
+      }
+      __syncwarp();
+      pending_step = -1;
+    };
+
     uint32_t lc = 0, tc = 0;
     for (int step = 0; step < n_steps; ++step) {
       if (step >= 2 && pair_first_done() <= step - 2) break;
@@ -498,6 +526,7 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
                             ? g_ro16_trace + 2048 + 8 * lc + (cg ? 4 : 0) : nullptr;
         if (tr) tr[0] = clock64();
 #endif
+        if (li == 1 && pending_step >= 0) publish_flags();
         draw_ahead(step, li);
         if (Ly.kind == RO_HIDDEN) {
           if (Ly.act == ACT_GELU) hidden_layer<ACT_GELU>(C, bias, Ly.n_pad, par0, par1);
@@ -583,24 +612,13 @@ __global__ void __launch_bounds__(kThreadsR, 1) fql_rollout16_kernel(const __gri
             done_once = done_once || term || trunc;
             const int all = __all_sync(0xffffffffu, done_once || !row_ok);
             if (lane == 0) warp_all[q] = all;
-            asm volatile("bar.sync 9, 128;" ::: "memory");   // the four cg = 0 warps
-            if (r == 0) {
-              int fd = ld_volatile_s32(first_done);
-              if (warp_all[0] && warp_all[1] && warp_all[2] && warp_all[3] && fd == INT_MAX) {
-                fd = step;
-                st_volatile_s32(first_done, step);
-              }
-              if (PAIR) {  // mirror both flags into the peer, first_done before steps_done
-                const uint32_t peer = rank ^ 1u;
-                asm volatile("st.shared::cluster.s32 [%0], %1;" ::"r"(mapa_u32(smem_u32(peer_first_done), peer)), "r"(fd) : "memory");
-                asm volatile("fence.acq_rel.cluster;" ::: "memory");
-                asm volatile("st.shared::cluster.s32 [%0], %1;" ::"r"(mapa_u32(smem_u32(peer_steps_done), peer)), "r"(s1) : "memory");
-                asm volatile("fence.acq_rel.cluster;" ::: "memory");
-              }
+            if (q != 0) {
               __threadfence_block();
-              st_volatile_s32(steps_done, s1);
+              __syncwarp();
+              asm volatile("bar.arrive 9, 128;" ::: "memory");
+            } else {
+              pending_step = step;   // publish_flags() on entry to layer 1 of the next step
             }
-            asm volatile("bar.sync 9, 128;" ::: "memory");
           }
 #ifdef FQLPOP_EPI_TRACE
           if (tr) tr[3] = clock64();
