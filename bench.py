@@ -316,8 +316,11 @@ def rollout_bench(torch, np, dev, P, world, barrier, dist, n=4096, T=200, reps=3
                 "mean_success_rate": sr, "lockstep_steps_per_member": steps / max(P, 1),
                 "algorithmic_tflops": env_steps / world * flop_step / (ms * 1e-3) / 1e12}
 
+    from fqlpop._lib import lib as _lib
+    l0 = int(_lib.fqlpop_rollout_launches(pop._h))
     half = run(em_half)
     none = run(em_none)
+    launches = int(_lib.fqlpop_rollout_launches(pop._h)) - l0   # kernels of the 2 x (2 reps + 1) evaluations above
     pop.close()
     out = dict(half)
     out["config"] = {"workload": f"simulated evaluation, antsoccer shape (O={O}, A={A}), {P} members x {n} episodes x {T} steps per GPU, "
@@ -325,7 +328,8 @@ def rollout_bench(torch, np, dev, P, world, barrier, dist, n=4096, T=200, reps=3
                                  f"episodes terminating before T (member 0: {rate0:.2f})"}
     out["no_termination"] = none
     out["flop_per_env_step"] = flop_step
-    out["gpu_launches"] = 2 * (2 * reps + 1)
+    out["gpu_launches"] = launches
+    out["launches_per_evaluation"] = launches // (2 * (2 * reps + 1))
     if with_cpu:
         n_cpu = 512
         v, threads, steps = cpu_rollout_env_steps_per_sec(O, A, n_cpu, T, bias)
