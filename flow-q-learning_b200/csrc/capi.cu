@@ -201,6 +201,14 @@ extern "C" int fqlpop_philox_fill(uint64_t seed, uint64_t step, int32_t rows, in
   if (fqlpop::philox_fill(seed, step, rows, slots, kind, n, out_host)) return fail("philox_fill: CUDA error");
   return 0;
 }
+extern "C" int fqlpop_philox_fill_noalloc(uint64_t seed, uint64_t step, int32_t rows, int32_t slots, int32_t kind, uint32_t n,
+                                          void* out_host) {
+  if (!out_host || rows < 1 || slots < 1 || kind < 0 || kind > 3) return fail("philox_fill_noalloc: bad arguments");
+  std::string err;
+  if (fqlpop::philox_fill_noalloc(seed, step, rows, slots, kind, n, out_host, &err)) return fail(err);
+  return 0;
+}
+extern "C" int32_t fqlpop_philox_fill_noalloc_max_words(void) { return fqlpop::kPhiloxNoAllocMaxWords; }
 extern "C" int fqlpop_debug_chain_trace(void* h, long long* host_out, int32_t n) {
   POP(h);
   if (!P->chain_trace) return fail("chain trace disabled (set FQLPOP_CHAIN_TRACE=1 before fqlpop_create)");

@@ -8,6 +8,8 @@
 #include <cfloat>
 
 #include "philox.cuh"
+#include <string>
+
 #include "pop.h"
 #include "ptx_sm100.cuh"
 
@@ -930,6 +932,48 @@ int philox_fill(unsigned long long seed, unsigned long long step, int rows, int 
   cudaError_t e = cudaMemcpy(out_host, d, count * 4, cudaMemcpyDeviceToHost);
   cudaFree(d);
   return e == cudaSuccess ? 0 : 1;
+}
+
+// ---- fqlpop_philox_fill_noalloc: the same kernel, staging through a fixed file-scope device array -------------------
+// (no counterpart in the reference; added for callers that must not allocate:
+// code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc.) Every GPU that loads the
+// library holds kPhiloxNoAllocMaxWords * 4 bytes = 1 MiB until exit. Every call shares the array and it keeps the last
+// call's contents: the kernel writes each of the `count` words a call copies out, so nothing has to start at zero, but
+// two calls that overlap on one GPU (different host threads / streams) race on it.
+static __device__ __align__(256) unsigned int g_philox_scratch[kPhiloxNoAllocMaxWords];
+
+int philox_fill_noalloc(unsigned long long seed, unsigned long long step, int rows, int slots, int kind, unsigned int n,
+                        void* out_host, std::string* err) {
+  auto bad = [&](const std::string& m) {
+    if (err) *err = m;
+    return 1;
+  };
+  const unsigned long long count = (unsigned long long)rows * (unsigned long long)slots * (kind == 0 ? 4ull : 1ull);
+  if (count > (unsigned long long)kPhiloxNoAllocMaxWords)
+    return bad("philox_fill_noalloc: " + std::to_string(count) + " output words exceed the fixed scratch of " +
+               std::to_string(kPhiloxNoAllocMaxWords) + " words (use fqlpop_philox_fill)");
+  // the array's name is a host-side stand-in in host code: ask the runtime for its device address, once per device,
+  // with that device current
+  constexpr int kMaxDevices = 64;
+  static unsigned int* dev_ptr[kMaxDevices] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return bad(std::string("philox_fill_noalloc: cudaGetDevice: ") + cudaGetErrorString(e));
+  if (dev < 0 || dev >= kMaxDevices) return bad("philox_fill_noalloc: device ordinal out of range");
+  if (!dev_ptr[dev]) {
+    unsigned int* ptr = nullptr;
+    e = cudaGetSymbolAddress((void**)&ptr, g_philox_scratch);
+    if (e != cudaSuccess || !ptr)
+      return bad(std::string("philox_fill_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    dev_ptr[dev] = ptr;
+  }
+  unsigned int* d = dev_ptr[dev];
+  philox_fill_kernel<<<(rows * slots + 255) / 256, 256>>>(seed, step, rows, slots, kind, n, (float*)d, d);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return bad(std::string("philox_fill_noalloc: launch: ") + cudaGetErrorString(e));
+  e = cudaMemcpy(out_host, d, (size_t)count * 4, cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) return bad(std::string("philox_fill_noalloc: copy: ") + cudaGetErrorString(e));
+  return 0;
 }
 
 int pointwise_init() {

@@ -183,5 +183,9 @@ void launch_fill_qa_dout(Population* p, cudaStream_t s);
 int pointwise_init();
 int philox_fill(unsigned long long seed, unsigned long long step, int rows, int slots, int kind, unsigned int n,
                 void* out_host);
+// the same through a fixed file-scope device array instead of cudaMalloc / cudaFree (pointwise.cu)
+constexpr int kPhiloxNoAllocMaxWords = 262144;  // 1 MiB of uint32 / fp32 outputs per call
+int philox_fill_noalloc(unsigned long long seed, unsigned long long step, int rows, int slots, int kind, unsigned int n,
+                        void* out_host, std::string* err);
 
 }  // namespace fqlpop

@@ -100,6 +100,16 @@ int fqlpop_last_batch(void* handle, float* rewards_host, float* masks_host);
  * [0, n) as uint32; 3: normal fp32. out_host: [rows][slots] (x4 words for kind 0).                           */
 int fqlpop_philox_fill(uint64_t seed, uint64_t step, int32_t rows, int32_t slots, int32_t kind, uint32_t n,
                        void* out_host);
+/* fqlpop_philox_fill without any allocation -- no counterpart in the reference; added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it). Same arguments, same output; the device staging buffer is a fixed 1 MiB file-scope device array
+ * (fqlpop_philox_fill_noalloc_max_words() = 262144 output words: rows * slots, x4 for kind 0), which every GPU that
+ * loads the library holds until exit. A larger request fails with a clear fqlpop_last_error(); nothing is truncated. The
+ * entry point calls no cudaMalloc / cudaFree or allocating library routine. All calls share the array (it keeps the last
+ * call's contents; each call overwrites every word it returns): calls that overlap on one GPU race -- serialise them. */
+int fqlpop_philox_fill_noalloc(uint64_t seed, uint64_t step, int32_t rows, int32_t slots, int32_t kind, uint32_t n,
+                               void* out_host);
+int32_t fqlpop_philox_fill_noalloc_max_words(void);
 /* Debug: clock64 stamps of CTA 0 of the Euler layer-chain kernel (needs FQLPOP_CHAIN_TRACE=1 at create time):
  * [0,4096) MMA thread (layer start, after each sub-tile's last MMA issue), [4096,8192) first epilogue thread.  */
 int fqlpop_debug_chain_trace(void* handle, long long* host_out, int32_t n);
