@@ -4,6 +4,8 @@
 
 #include <cmath>
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -441,6 +443,11 @@ struct WmTrainer {
   unsigned int* ticket = nullptr;
   int* step = nullptr;
   int rows = 0;  // batch * sequence length
+  // multistep: persistent scan kernels (wm_scan.cuh)
+  float* wt = nullptr;        // transposed kernels for the backward scan
+  bool scan_ok = false;
+  unsigned scan_mask = 0;     // layers whose kernel the scan kernels keep in shared memory
+  int scan_smem = 0, scan_maxdim = 0;
   // resident dataset + sampled batch
   const float *ds_obs = nullptr, *ds_act = nullptr, *ds_next = nullptr, *ds_rew = nullptr;
   long long ds_rows = 0;
@@ -616,6 +623,8 @@ void wm_issue(WmTrainer* t, Launcher& L, int train, int gather, const float* obs
 }
 
 
+#include "wm_scan.cuh"
+
 constexpr int kWmLossCtas = 128, kWmSplits = 64;
 constexpr int kWmEpisodeLen = 1000;  // OGBench episodes (stride 1000 at utils/data_loader.py:16,30)
 
@@ -641,16 +650,29 @@ void wm_issue_multistep(WmTrainer* t, Launcher& L, int train, int gather, const 
   }
   wm_take_first_kernel<<<(B * O + 255) / 256, 256, 0, s>>>(obs, B, T, O, t->ocur);
   ++L.n;
-  for (int ti = 0; ti < T; ++ti) {
-    float* act_l[kWmMaxLayers + 1];
-    for (int l = 0; l < nl; ++l) act_l[l] = t->x[l] + (long long)ti * B * net.dims[l];
-    float* o_t = t->ocur + (long long)ti * B * O;
-    act_l[nl] = o_t + (long long)B * O;  // o_{t+1}: prediction of this step, input of the next
-    wm_ln_concat_kernel<<<(B * 32 + 255) / 256, 256, 0, s>>>(o_t, act + (long long)ti * A, T * A, O, A, B, scale,
-                                                            t->params + net.off_ln_bias, c.ln_eps, act_l[0],
-                                                            t->xhat + (long long)ti * B * D0, t->rstd + ti * B);
+  // FQLPOP_WM_SCAN=0 keeps the per-step launches (2 x T x 5 dependent small kernels) for A/B runs
+  static const bool scan_on = [] { const char* e = getenv("FQLPOP_WM_SCAN"); return e ? atoi(e) != 0 : true; }();
+  const bool scan = scan_on && t->scan_ok;
+  ScanArgs sa{};
+  if (scan) {
+    sa.net = net; sa.params = t->params; sa.wt = t->wt;
+    for (int l = 0; l <= nl; ++l) { sa.x[l] = t->x[l]; sa.gx[l] = t->gx[l]; }
+    sa.ocur = t->ocur; sa.xhat = t->xhat; sa.rstd = t->rstd; sa.act = act;
+    sa.B = B; sa.T = T; sa.O = O; sa.A = A; sa.maxdim = t->scan_maxdim; sa.eps = c.ln_eps; sa.cache_mask = t->scan_mask;
+    wm_scan_fwd_kernel<<<(B + kScanRB - 1) / kScanRB, kScanThreads, t->scan_smem, s>>>(sa);
     ++L.n;
-    wm_forward(L, net, t->params, act_l, B, o_t, O);
+  } else {
+    for (int ti = 0; ti < T; ++ti) {
+      float* act_l[kWmMaxLayers + 1];
+      for (int l = 0; l < nl; ++l) act_l[l] = t->x[l] + (long long)ti * B * net.dims[l];
+      float* o_t = t->ocur + (long long)ti * B * O;
+      act_l[nl] = o_t + (long long)B * O;  // o_{t+1}: prediction of this step, input of the next
+      wm_ln_concat_kernel<<<(B * 32 + 255) / 256, 256, 0, s>>>(o_t, act + (long long)ti * A, T * A, O, A, B, scale,
+                                                              t->params + net.off_ln_bias, c.ln_eps, act_l[0],
+                                                              t->xhat + (long long)ti * B * D0, t->rstd + ti * B);
+      ++L.n;
+      wm_forward(L, net, t->params, act_l, B, o_t, O);
+    }
   }
   float* pred = t->ocur + (long long)B * O;  // [T][B][O]
   if (with_term) wm_forward(L, t->term, t->term_params, t->tx, R, nullptr, 0);  // tx[0] aliases pred
@@ -671,21 +693,32 @@ void wm_issue_multistep(WmTrainer* t, Launcher& L, int train, int gather, const 
       gt = out;
     }
   }
-  // back-propagation through time: input-gradient chain of step ti, then LayerNorm backward + residual into step ti-1
-  for (int ti = T - 1; ti >= 0; --ti) {
-    const float* g = t->gx[nl] + (long long)ti * B * O;
-    for (int l = nl - 1; l >= 0; --l) {
-      const int din = net.dims[l], dout = net.dims[l + 1];
-      float* out = t->gx[l] + (long long)ti * B * din;
-      L.gemm(false, true, g, dout, t->params + net.offW[l], dout, out, din, B, din, dout, l > 0 ? WE_MASK : WE_NONE, nullptr,
-             l > 0 ? t->x[l] + (long long)ti * B * din : nullptr, din, 0);
-      g = out;
-    }
-    if (ti > 0) {
-      wm_ln_bwd_kernel<<<(B * 32 + 255) / 256, 256, 0, s>>>(g, t->xhat + (long long)ti * B * D0, t->rstd + ti * B, scale, O,
-                                                           D0, B, t->gx[nl] + (long long)ti * B * O,
-                                                           t->gx[nl] + (long long)(ti - 1) * B * O);
+  if (scan) {
+    for (int l = 0; l < nl; ++l) {
+      const int n = net.dims[l] * net.dims[l + 1];
+      wm_transpose_kernel<<<(n + 255) / 256, 256, 0, s>>>(t->params + net.offW[l], t->wt + net.offW[l], net.dims[l],
+                                                         net.dims[l + 1]);
       ++L.n;
+    }
+    wm_scan_bwd_kernel<<<(B + kScanRB - 1) / kScanRB, kScanThreads, t->scan_smem, s>>>(sa);
+    ++L.n;
+  } else {
+    // back-propagation through time: input-gradient chain of step ti, then LayerNorm backward + residual into step ti-1
+    for (int ti = T - 1; ti >= 0; --ti) {
+      const float* g = t->gx[nl] + (long long)ti * B * O;
+      for (int l = nl - 1; l >= 0; --l) {
+        const int din = net.dims[l], dout = net.dims[l + 1];
+        float* out = t->gx[l] + (long long)ti * B * din;
+        L.gemm(false, true, g, dout, t->params + net.offW[l], dout, out, din, B, din, dout, l > 0 ? WE_MASK : WE_NONE, nullptr,
+               l > 0 ? t->x[l] + (long long)ti * B * din : nullptr, din, 0);
+        g = out;
+      }
+      if (ti > 0) {
+        wm_ln_bwd_kernel<<<(B * 32 + 255) / 256, 256, 0, s>>>(g, t->xhat + (long long)ti * B * D0, t->rstd + ti * B, scale, O,
+                                                             D0, B, t->gx[nl] + (long long)ti * B * O,
+                                                             t->gx[nl] + (long long)(ti - 1) * B * O);
+        ++L.n;
+      }
     }
   }
   // parameter gradients over all T*B rows at once
@@ -792,6 +825,33 @@ int wm_create_impl(const WmConfig& cfg, const float* params_host, const float* t
     rc |= wm_alloc(t, &t->ocur, (R + B) * cfg.O, err) || wm_alloc(t, &t->wpart, kWmSplits * maxw, err) ||
           wm_alloc(t, &t->cpart, 2LL * kWmSplits * maxdim, err);
     t->x[nl] = t->ocur ? t->ocur + (long long)B * cfg.O : nullptr;
+    // persistent scan kernels: widths up to kScanMaxDim; the largest kernels that fit stay in shared memory
+    if (!rc && maxdim <= kScanMaxDim && t->net.dims[0] <= kScanMaxIn) {
+      rc |= wm_alloc(t, &t->wt, n, err);
+      t->scan_maxdim = scan_round32(maxdim);
+      const int base = scan_base_floats(t->scan_maxdim, cfg.O);
+      int budget = (220 * 1024) / 4 - base;   // floats left of the opt-in shared memory of one SM
+      // a cached kernel is padded to a multiple of 4 columns in BOTH orientations (the backward kernel holds its transpose)
+      auto padded = [&](int l) {
+        const int K = t->net.dims[l], N = t->net.dims[l + 1];
+        return std::max(K * scan_round4(N), N * scan_round4(K));
+      };
+      bool used[kWmMaxLayers] = {};
+      for (int pick = 0; pick < nl; ++pick) {
+        int best = -1;
+        for (int l = 0; l < nl; ++l)
+          if (!used[l] && padded(l) <= budget && (best < 0 || padded(l) > padded(best))) best = l;
+        if (best < 0) break;
+        used[best] = true;
+        t->scan_mask |= 1u << best;
+        budget -= padded(best);
+      }
+      t->scan_smem = ((220 * 1024) / 4 - budget) * 4;
+      if (!rc && (cudaFuncSetAttribute(wm_scan_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, t->scan_smem) != cudaSuccess ||
+                  cudaFuncSetAttribute(wm_scan_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, t->scan_smem) != cudaSuccess))
+        rc = bad("world model: raising the scan kernels' shared-memory limit failed");
+      t->scan_ok = !rc;
+    }
   }
   if (!rc && with_term) {
     t->term = wm_layout(cfg.O, cfg.term_n_hidden, cfg.term_hidden, 1, false);

