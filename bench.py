@@ -256,7 +256,7 @@ def cpu_rollout_env_steps_per_sec(O, A, n, T, term_bias):
     init = torch.randn(n, O, generator=g)
     noise = torch.randn(T, n, A, generator=g)
     t0 = time.perf_counter()
-    out = orc.rollout(st["params"]["actor_onestep_flow"], env, init, noise, cfg, T)
+    out = orc.rollout(st["params"], env, init, noise, cfg, T)
     dt = time.perf_counter() - t0
     steps = int(out["steps"])
     return steps * n / dt, torch.get_num_threads(), steps
