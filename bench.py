@@ -155,8 +155,8 @@ def run_reference(args, rank, world):
 
 
 # DRAM traffic of the roofline launch by (shape, members, batch), from the committed ncu --set full capture of that launch
-ROOFLINE_TRAFFIC = {("cube-single", 16, 256): 28415232 + 4670464}
-ROOFLINE_TRAFFIC_SOURCE = "profiles/r02_chain_ncu_full_summary.txt"
+ROOFLINE_TRAFFIC = {("cube-single", 16, 256): 28017408 + 3933184}
+ROOFLINE_TRAFFIC_SOURCE = "profiles/r03_chain_ncu_full_summary.txt"
 
 
 def chain_launch_roofline(torch, pop, P, O, A, B, which, iters=50):
