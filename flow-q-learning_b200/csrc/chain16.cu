@@ -470,6 +470,8 @@ __device__ __forceinline__ void fwd_hidden_layer(Epi& C, const ChainLayer& Ly, u
     stamp(C, 5);
   }
   // h -> HBM out of ACT, off the hand-off path: these rows of the two blocks are next written by this very warp
+  // (measured: storing h from the registers like act'(z), one 32-byte sector per thread and chunk, makes the policy pass
+  // slower -- 59.7 vs 54.1 us; the copy-out writes whole 128-byte row segments)
   if (Ly.out_h) {
     __syncwarp();
     const uint32_t b0 = C.act + C.cg * kActBlockBytes + C.q * (32 * 128);

@@ -12,7 +12,8 @@ for k in ("bench", "bench_nopair"):
     try:
         d = json.loads([l for l in open("gpurun_out/${tag}_%s.json" % k) if l.startswith("{")][-1])
         print(k, round(d["value"]), "updates/s e2e", round(d["e2e"]["value"]), "ms/step", d["ms_per_step"], "roofline", d["roofline"]["frac"], d["roofline"].get("launch_us"))
-        for r in d.get("roofline_other_launches", []): print("   ", r.get("launch"), r.get("launch_us"), r.get("frac"))
+        print("    policy pass launch_ms", d["roofline"]["launch_ms"])
+        for k, r in d.get("roofline_other_launches", {}).items(): print("   ", k, round(r["launch_ms"], 4), round(r["frac"], 3))
     except Exception as e: print(k, "FAILED", e)
 P
 tail -3 gpurun_out/${tag}_bench.err
