@@ -152,7 +152,10 @@ typedef struct {
   int64_t init_obs_member_stride;
   const float* noise;           /* (dev) [T][n][action_dim] policy noise (+ member * stride) or NULL=Philox */
   int64_t noise_member_stride;
-  uint64_t eval_seed;           /* Philox stream of this evaluation when noise == NULL                      */
+  uint64_t eval_seed;           /* Philox stream of this evaluation when noise == NULL: the noise of member m,
+                                   lockstep step t, episode e, action slot j is the normal draw (fqlpop_philox_fill
+                                   kind 3) of key = member seed, counter = (2^63 | (eval_seed & 0x7FFFFFFF) << 32) + t,
+                                   row e, slot j                                                            */
   uint8_t* out_success;         /* (dev, optional) [P][n] terminated at the first done step                 */
   int32_t* out_length;          /* (dev, optional) [P][n] step index of the first done step, 0 = none       */
   float* out_success_rate;      /* (dev, optional) [P]  == stats["success"] of evaluate_actor_fn            */

@@ -120,14 +120,21 @@ def test_env_step_matches_oracle(shape, hidden):
     dem.close()
 
 
-@pytest.mark.parametrize("shape,pair", [((42, 8), 0), ((28, 5), 0), ((42, 8), 1)], ids=["antsoccer", "cube", "antsoccer_cta_pair"])
-def test_rollout_matches_oracle_fixed_horizon(shape, pair, monkeypatch):
-    monkeypatch.setenv("FQLPOP_ROLLOUT_PAIR", str(pair))   # 1: tcgen05.mma.cta_group::2 over two episode tiles (off by default)
+@pytest.mark.parametrize("shape,pair,hidden", [((42, 8), 0, (128, 256, 128)), ((28, 5), 0, (128, 256, 128)),
+                                               ((42, 8), 1, (128, 256, 128)), ((28, 5), 1, (100, 72)),
+                                               ((42, 8), 1, (512, 256)), ((28, 5), 0, (64, 64))],
+                         ids=["antsoccer", "cube", "antsoccer_cta_pair", "padded_widths_100_72", "wide_512_256",
+                              "narrow_64_64_first_generation_kernel"])
+def test_rollout_matches_oracle_fixed_horizon(shape, pair, hidden, monkeypatch):
+    # pair 1: tcgen05.mma.cta_group::2 over two episode tiles. World models of other widths than the reference's default walk
+    # the other layer shapes of the second-generation kernel (two-tile relu layers, widths padded to 128); 64-wide hidden
+    # layers are outside its range and take the first-generation kernel.
+    monkeypatch.setenv("FQLPOP_ROLLOUT_PAIR", str(pair))
     O, A = shape
     cfg = orc.FQLConfig(ob_dim=O, action_dim=A, batch_size=128)
     alphas, seeds = [3.0, 30.0, 300.0], [5, 6, 7]
     pop, states = _population(cfg, alphas, seeds)
-    em = _envmodel(O, A, term_bias=-0.6)
+    em = _envmodel(O, A, hidden=hidden, term_bias=-0.6)
     dem = _device_envmodel(em, O, A)
     n, T = 200, 12
     g = torch.Generator().manual_seed(4)
@@ -206,6 +213,37 @@ def test_rollout_truncation_early_exit_and_active_members():
     assert int(lengths.min()) >= 1 and int(lengths.max()) <= T
     trunc = (lengths == T) & (o1["success"].cpu() == 0)
     assert bool(((o1["success"].cpu() == 1) | trunc).all())
+    pop.close()
+    dem.close()
+
+
+@pytest.mark.parametrize("pair", [0, 1], ids=["single_cta", "cta_pair"])
+def test_rollout_policy_noise_is_the_documented_philox_stream(pair, monkeypatch):
+    """The policy noise of an evaluation with eval_seed s is Philox(member seed, 2^63 | s << 32 + lockstep step, episode,
+    action slot) -> Box-Muller (include/fqlpop.h, FqlRolloutArgs.eval_seed). The second-generation kernel draws it one step ahead, in shares spread
+    over its policy layers: an evaluation with the same numbers passed as explicit noise must give the same trajectory bit
+    for bit, every step, every action slot."""
+    from fqlpop.population import philox_fill
+    monkeypatch.setenv("FQLPOP_ROLLOUT_PAIR", str(pair))
+    O, A = 42, 8
+    cfg = orc.FQLConfig(ob_dim=O, action_dim=A, batch_size=128)
+    seeds = [5, 2**40 + 6, 7]
+    pop, _ = _population(cfg, [3.0, 30.0, 300.0], seeds)
+    dem = _device_envmodel(_envmodel(O, A, term_bias=-0.5), O, A)
+    n, T, eval_seed = 300, 9, 5
+    init = torch.randn(n, O, generator=torch.Generator().manual_seed(8))
+    counter = (1 << 63) | (eval_seed << 32)
+    noise = torch.stack([torch.stack([torch.from_numpy(philox_fill(sd, counter + t, n, A, 3)) for t in range(T)]) for sd in seeds])
+    a = pop.rollout(dem, init, max_episode_steps=T, eval_seed=eval_seed, trajectory=True)
+    b = pop.rollout(dem, init, max_episode_steps=T, noise=noise, trajectory=True)
+    torch.cuda.synchronize()
+    assert torch.equal(a["steps"], b["steps"])
+    for p in range(3):
+        t_run = int(a["steps"][p])
+        assert t_run >= 2
+        for k in ("traj_act", "traj_obs", "traj_logit"):
+            assert torch.equal(a[k][p, :t_run], b[k][p, :t_run]), (p, k)
+    assert torch.equal(a["length"], b["length"]) and torch.equal(a["success"], b["success"])
     pop.close()
     dem.close()
 
