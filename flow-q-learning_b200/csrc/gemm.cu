@@ -252,63 +252,72 @@ fql_gemm_kernel(const __grid_constant__ GemmLaunch L) {
             // lane owns 16 contiguous bytes of 8 rows: theta / mu / nu (/ target) are read and written with coalesced
             // 16-byte accesses, 4 rows' worth of loads in flight per lane.
             if (N_SUB == 1) {
+              // The warp's whole 32 x ncols block is staged first (16 KB of the idle operand stages per warp, 16-byte chunks
+              // XOR-swizzled by row), then walked ROW by row: every load / store instruction of the update covers one
+              // contiguous row segment of up to 512 bytes (lane = 16-byte chunk) instead of four 128-byte pieces of four
+              // rows -- DRAM pages are touched once, not once per 32-column chunk.
               const AdamTile& T = E.adam;
-              uint8_t* stg = stage_base + q * 4096;
+              uint8_t* stg = stage_base + q * 16384;
 #pragma unroll
               for (int i = 0; i < 8; ++i)
-                *reinterpret_cast<float4*>(stg + lane * 128 + ((i ^ (lane & 7)) << 4)) =
+                *reinterpret_cast<float4*>(stg + lane * 512 + (((c * 8 + i) ^ lane) & 31) * 16) =
                     make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-              __syncwarp();
-              const int rows_valid = G.M - (mt * kBlockM + q * 32);
-              const long long base = member * E.out_f32.ms + (long long)(mt * kBlockM + q * 32) * E.out_f32.ld + col;
-              const int ch = lane & 7, rsub = lane >> 3;
-              const int pm = member / T.nb;
-              const float ibc1 = 1.f / __ldg(T.adam_bc + 2 * pm), ibc2 = 1.f / __ldg(T.adam_bc + 2 * pm + 1);
-              const bool has_t = T.target != nullptr;
+              if (c == ncols / 32 - 1) {
+                __syncwarp();
+                const int nch = ncols >> 2;   // 16-byte chunks per row of this tile
+                const int rows_valid = G.M - (mt * kBlockM + q * 32);
+                const long long base = member * E.out_f32.ms + (long long)(mt * kBlockM + q * 32) * E.out_f32.ld + n_base +
+                                       sub * kBlockN + lane * 4;
+                const int pm = member / T.nb;
+                const float ibc1 = 1.f / __ldg(T.adam_bc + 2 * pm), ibc2 = 1.f / __ldg(T.adam_bc + 2 * pm + 1);
+                const bool has_t = T.target != nullptr;
+                if (lane < nch) {
+#pragma unroll 1
+                  for (int r0 = 0; r0 < 32; r0 += 4) {
+                    float4 th[4], m[4], vv[4], tg[4];
+                    long long o[4];
+                    bool ok[4];
 #pragma unroll
-              for (int half = 0; half < 2; ++half) {
-                float4 th[4], m[4], vv[4], tg[4];
-                long long o[4];
-                bool ok[4];
+                    for (int j = 0; j < 4; ++j) {
+                      const int r = r0 + j;
+                      ok[j] = r < rows_valid;
+                      o[j] = base + (long long)(ok[j] ? r : 0) * E.out_f32.ld;
+                      th[j] = __ldcs(reinterpret_cast<const float4*>(T.theta + o[j]));
+                      m[j] = __ldcs(reinterpret_cast<const float4*>(T.mu + o[j]));
+                      vv[j] = __ldcs(reinterpret_cast<const float4*>(T.nu + o[j]));
+                      tg[j] = has_t ? __ldcs(reinterpret_cast<const float4*>(T.target + o[j])) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  const int r = (half * 4 + j) * 4 + rsub;
-                  ok[j] = r < rows_valid;
-                  o[j] = base + (long long)(ok[j] ? r : 0) * E.out_f32.ld + ch * 4;
-                  th[j] = __ldcs(reinterpret_cast<const float4*>(T.theta + o[j]));
-                  m[j] = __ldcs(reinterpret_cast<const float4*>(T.mu + o[j]));
-                  vv[j] = __ldcs(reinterpret_cast<const float4*>(T.nu + o[j]));
-                  tg[j] = has_t ? __ldcs(reinterpret_cast<const float4*>(T.target + o[j])) : make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  const int r = (half * 4 + j) * 4 + rsub;
-                  const float4 g = *reinterpret_cast<const float4*>(stg + r * 128 + ((ch ^ (r & 7)) << 4));
-                  if (!ok[j]) continue;
+                    for (int j = 0; j < 4; ++j) {
+                      const int r = r0 + j;
+                      const float4 g = *reinterpret_cast<const float4*>(stg + r * 512 + ((lane ^ r) & 31) * 16);
+                      if (!ok[j]) continue;
 #define ADAM1(c)                                                                \
   m[j].c = T.b1 * m[j].c + (1.f - T.b1) * g.c;                                  \
   vv[j].c = T.b2 * vv[j].c + (1.f - T.b2) * g.c * g.c;                          \
   th[j].c = th[j].c - T.lr * (m[j].c * ibc1) / (sqrtf(vv[j].c * ibc2) + T.eps);
-                  ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
+                      ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
 #undef ADAM1
-                  __stcs(reinterpret_cast<float4*>(T.theta + o[j]), th[j]);
-                  __stcs(reinterpret_cast<float4*>(T.mu + o[j]), m[j]);
-                  __stcs(reinterpret_cast<float4*>(T.nu + o[j]), vv[j]);
-                  *reinterpret_cast<uint2*>(T.shadow + o[j]) =
-                      make_uint2(pack_bf16x2(th[j].x, th[j].y), pack_bf16x2(th[j].z, th[j].w));
-                  if (has_t) {
-                    tg[j].x = T.tau * th[j].x + (1.f - T.tau) * tg[j].x;
-                    tg[j].y = T.tau * th[j].y + (1.f - T.tau) * tg[j].y;
-                    tg[j].z = T.tau * th[j].z + (1.f - T.tau) * tg[j].z;
-                    tg[j].w = T.tau * th[j].w + (1.f - T.tau) * tg[j].w;
-                    __stcs(reinterpret_cast<float4*>(T.target + o[j]), tg[j]);
-                    *reinterpret_cast<uint2*>(T.tshadow + o[j]) =
-                        make_uint2(pack_bf16x2(tg[j].x, tg[j].y), pack_bf16x2(tg[j].z, tg[j].w));
+                      __stcs(reinterpret_cast<float4*>(T.theta + o[j]), th[j]);
+                      __stcs(reinterpret_cast<float4*>(T.mu + o[j]), m[j]);
+                      __stcs(reinterpret_cast<float4*>(T.nu + o[j]), vv[j]);
+                      *reinterpret_cast<uint2*>(T.shadow + o[j]) =
+                          make_uint2(pack_bf16x2(th[j].x, th[j].y), pack_bf16x2(th[j].z, th[j].w));
+                      if (has_t) {
+                        tg[j].x = T.tau * th[j].x + (1.f - T.tau) * tg[j].x;
+                        tg[j].y = T.tau * th[j].y + (1.f - T.tau) * tg[j].y;
+                        tg[j].z = T.tau * th[j].z + (1.f - T.tau) * tg[j].z;
+                        tg[j].w = T.tau * th[j].w + (1.f - T.tau) * tg[j].w;
+                        __stcs(reinterpret_cast<float4*>(T.target + o[j]), tg[j]);
+                        *reinterpret_cast<uint2*>(T.tshadow + o[j]) =
+                            make_uint2(pack_bf16x2(tg[j].x, tg[j].y), pack_bf16x2(tg[j].z, tg[j].w));
+                      }
+                      if (T.keep_grad) *reinterpret_cast<float4*>(E.out_f32.p + o[j]) = g;
+                    }
                   }
-                  if (T.keep_grad) *reinterpret_cast<float4*>(E.out_f32.p + o[j]) = g;
                 }
+                __syncwarp();
               }
-              __syncwarp();
             }
           } else if (kind == EPI_STORE_F32) {
             if (N_SUB == 1) {

@@ -510,9 +510,11 @@ int issue_step(Population* P, bool train, GroupPlan& gp, std::string* err, bool 
   b.L = new GemmLaunch;
   // FQLPOP_FUSE_ADAM=1: the optimizer inside the weight-gradient GEMM's epilogue (gemm.cu EPI_ADAM) instead of separate
   // kernels after plain weight-gradient GEMMs. Parity-tested, and it removes the fp32 gradient round trip (34 -> 26 bytes
-  // per parameter), but MEASURED SLOWER (16.3k vs 18.1k updates/s at 16 members): 2 CTAs x 128 epilogue threads per SM keep
-  // ~64 KB of loads in flight per SM against the 160 KB of the stand-alone adam_kernel, so the fused pass streams at
-  // ~3.2 TB/s instead of 5.8. Off by default; read at graph-capture time.
+  // per parameter), but MEASURED SLOWER: 17.1k vs 18.4k updates/s at 16 members (16.3k before the epilogue walked its tile
+  // row by row in 512-byte segments). 2 CTAs x 128 epilogue threads per SM keep at most 64 KB of loads in flight per SM, and
+  // only half of the time (a batch of rows is loaded, waited for, updated, stored), against the 160 KB of the stand-alone
+  // adam_kernel; double-buffering the batches needs ~64 more registers than the 168 two resident CTAs leave.
+  // Off by default; read at graph-capture time.
   const int fuse = [] { const char* e = getenv("FQLPOP_FUSE_ADAM"); return e ? atoi(e) : 0; }();
   b.fuse_adam = fuse ? (keep_grads ? 1 : 0) : -1;
   int pw = 0;  // pointwise launches
