@@ -307,9 +307,9 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&rr)[16], const float4
   }
 }
 
-// 16 bf16 values (one 32-byte sector) of this thread's row straight to global memory: one 256-bit store. Used for act'(z) of
-// the LayerNorm-free forward passes, which then need no staging area and keep all five weight slots (with three, the
-// policy pass spent 60 % of its MMA issuer's time waiting for weights).
+// 16 bf16 values (one 32-byte sector) of this thread's row straight to global memory: one 256-bit store. Used for the
+// tensors a forward pass saves for the backward pass (act'(z), the LayerNorm's xhat): forward launches then need no staging
+// area and keep all five weight slots (with three, the policy pass spent 60 % of its MMA issuer's time waiting for weights).
 __device__ __forceinline__ void st_row32(__nv_bfloat16* dst, const uint32_t (&w)[8], bool ok) {
   if (ok)
     asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst), "r"(w[0]), "r"(w[1]), "r"(w[2]),
@@ -334,10 +334,7 @@ __device__ __forceinline__ void fwd_pass1(const Epi& C, const ChainLayer& Ly, in
     tmem_ld_wait();
     tmem_ld16(tbase + (c + 1) * 16, rb);
     fwd_chunk<LN, SAVE>(ra, b4, pk + 8 * c, gpk, s1, s2);
-    if (SAVE) {
-      if (LN) st_half16(C.stg, C.lane, 0, gpk);
-      else st_row32(Ly.out_gp + C.wrow + (long long)C.lane * C.H + colw + c * 16, gpk, C.row_ok);
-    }
+    if (SAVE) st_row32(Ly.out_gp + C.wrow + (long long)C.lane * C.H + colw + c * 16, gpk, C.row_ok);
     if (DEST == 1) st_act16(C.act, C.r, colw + c * 16, pk + 8 * c);
     if (DEST == 2) tmem_st8(tbase + c * 8, *reinterpret_cast<const uint32_t(*)[8]>(pk + 8 * c));
     // ---- odd chunk (rb) ----
@@ -345,22 +342,13 @@ __device__ __forceinline__ void fwd_pass1(const Epi& C, const ChainLayer& Ly, in
     tmem_ld_wait();
     if (c + 2 < 4) tmem_ld16(tbase + (c + 2) * 16, ra);
     fwd_chunk<LN, SAVE>(rb, b4, pk + 8 * (c + 1), gpk, s1, s2);
-    if (SAVE) {
-      if (LN) {
-        st_half16(C.stg, C.lane, 16, gpk);
-        __syncwarp();
-        copy_out_half(C.stg, Ly.out_gp + C.wrow + colw + c * 16, C.H, C.lane, C.rows_valid);
-        __syncwarp();
-      } else {
-        st_row32(Ly.out_gp + C.wrow + (long long)C.lane * C.H + colw + (c + 1) * 16, gpk, C.row_ok);
-      }
-    }
+    if (SAVE) st_row32(Ly.out_gp + C.wrow + (long long)C.lane * C.H + colw + (c + 1) * 16, gpk, C.row_ok);
     if (DEST == 1) st_act16(C.act, C.r, colw + (c + 1) * 16, pk + 8 * (c + 1));
     if (DEST == 2) tmem_st8(tbase + (c + 1) * 8, *reinterpret_cast<const uint32_t(*)[8]>(pk + 8 * (c + 1)));
   }
 }
 
-// LayerNorm of 16 held / parked bf16 values: x = (g - mean) rstd, h = x gamma + beta -> ACT (+ xhat -> staging)
+// LayerNorm of 16 held / parked bf16 values: x = (g - mean) rstd, h = x gamma + beta -> ACT (+ xhat -> global)
 template <bool SAVE>
 __device__ __forceinline__ void ln_chunk(const Epi& C, const ChainLayer& Ly, int col, const uint32_t* pr, float rstd,
                                          float shift, int cw, bool save_x) {
@@ -381,10 +369,10 @@ __device__ __forceinline__ void ln_chunk(const Epi& C, const ChainLayer& Ly, int
     hk[2 * i + 1] = pack_bf16x2(fmaf(x2, ga[i].z, be[i].z), fmaf(x3, ga[i].w, be[i].w));
   }
   st_act16(C.act, C.r, col, hk);
-  if (SAVE && save_x) st_half16(C.stg, C.lane, cw, xk);
+  if (SAVE && save_x) st_row32(Ly.out_xhat + C.wrow + (long long)C.lane * C.H + col, xk, C.row_ok);
 }
 
-// parked tile (bf16 pairs in the drained accumulator columns) -> LayerNorm -> ACT (+ xhat -> staging -> global)
+// parked tile (bf16 pairs in the drained accumulator columns) -> LayerNorm -> ACT (+ xhat -> global)
 template <bool SAVE>
 __device__ __forceinline__ void ln_flush_tile(const Epi& C, const ChainLayer& Ly, int tile, float rstd, float shift, bool save_x) {
   const int colw = tile * kTileN + C.cg * 64;
@@ -398,11 +386,6 @@ __device__ __forceinline__ void ln_flush_tile(const Epi& C, const ChainLayer& Ly
     tmem_ld_wait();
     if (c + 2 < 4) tmem_ld8(C.tmem_row + colw + (c + 2) * 8, pa);
     ln_chunk<SAVE>(C, Ly, colw + (c + 1) * 16, pb, rstd, shift, 16, save_x);
-    if (save_x) {
-      __syncwarp();
-      copy_out_half(C.stg, Ly.out_xhat + C.wrow + colw + c * 16, C.H, C.lane, C.rows_valid);
-      __syncwarp();
-    }
   }
 }
 
@@ -1196,7 +1179,7 @@ cudaError_t launch_chain16(ChainLaunch& L, int mode, int grid, cudaStream_t stre
     units += (pair ? (L.job[i].m_tiles + 1) / 2 : L.job[i].m_tiles) * L.n_virtual;
   // weight slots: 16 KB each (8 KB in pair mode); launches that stage tensors through shared memory give up the last 32 KB
   if (!chain16_maps_ok(L, mode, pair)) return cudaErrorInvalidValue;
-  if (mode == 0 && !ln) L.stages = kStages;   // LayerNorm-free forward passes store act'(z) from registers: nothing staged
+  if (mode == 0) L.stages = kStages;   // forward passes store what they save from registers: nothing is staged
   L.staged = L.stages != kStages;
   L.stages = (L.staged ? kStagesStaged : kStages) * ((pair && mode == 1) ? 2 : 1);
   if (mode == 0) return ln ? launch_variant<0, true>(L, pair, units, stream) : launch_variant<0, false>(L, pair, units, stream);
