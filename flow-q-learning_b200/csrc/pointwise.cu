@@ -583,38 +583,38 @@ __global__ void __launch_bounds__(kAdamThreads, 1) adam_kernel(const AdamArgs a)
   long long tl_t0 = 0;
   const bool tl_on = a.timeline && threadIdx.x == 0;
   if (tl_on) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
+  // virtual member by virtual member: the element index needs no 64-bit division (a grid-stride walk over
+  // n_virtual x S / 4 quads spent most of its issue slots -- 63-67 % busy, ncu -- on `idx / n4`), and the member's
+  // pointers and bias corrections are computed once per member instead of once per quad
   const int n4 = (int)(a.S >> 2);
-  const long long total = (long long)a.n_virtual * n4;
-  const long long stride = (long long)gridDim.x * kAdamThreads;
-  for (long long idx0 = (long long)blockIdx.x * kAdamThreads + threadIdx.x; idx0 < total; idx0 += kAdamUnroll * stride) {
-    long long o[kAdamUnroll];
-    float ibc1[kAdamUnroll], ibc2[kAdamUnroll];
-    float4 g[kAdamUnroll], th[kAdamUnroll], m[kAdamUnroll], v[kAdamUnroll], tg[kAdamUnroll];
-    bool ok[kAdamUnroll];
+  const int stride = (int)gridDim.x * kAdamThreads;
+  for (int av = 0; av < a.n_virtual; ++av) {
+    const int am = av / a.nb, e = av - am * a.nb;
+    const int p = a.member_list[am];
+    const long long base = ((long long)p * a.nb + e) * a.S;
+    const float ibc1 = 1.f / a.adam_bc[2 * p], ibc2 = 1.f / a.adam_bc[2 * p + 1];
+    for (int i0 = (int)blockIdx.x * kAdamThreads + (int)threadIdx.x; i0 < n4; i0 += kAdamUnroll * stride) {
+      long long o[kAdamUnroll];
+      float4 g[kAdamUnroll], th[kAdamUnroll], m[kAdamUnroll], v[kAdamUnroll], tg[kAdamUnroll];
+      bool ok[kAdamUnroll];
 #pragma unroll
-    for (int u = 0; u < kAdamUnroll; ++u) {
-      const long long idx = idx0 + u * stride;
-      ok[u] = idx < total;
-      const long long id = ok[u] ? idx : idx0;
-      const int av = (int)(id / n4);
-      const int i = (int)(id - (long long)av * n4);
-      const int am = av / a.nb, e = av - am * a.nb;
-      const int p = a.member_list[am];
-      o[u] = ((long long)p * a.nb + e) * a.S + 4ll * i;
-      ibc1[u] = 1.f / a.adam_bc[2 * p];
-      ibc2[u] = 1.f / a.adam_bc[2 * p + 1];
+      for (int u = 0; u < kAdamUnroll; ++u) {
+        const int i = i0 + u * stride;
+        ok[u] = i < n4;
+        o[u] = base + 4ll * (ok[u] ? i : i0);
+      }
+#pragma unroll
+      for (int u = 0; u < kAdamUnroll; ++u) {
+        g[u] = __ldcs(reinterpret_cast<const float4*>(a.grad + o[u]));
+        th[u] = __ldcs(reinterpret_cast<const float4*>(a.theta + o[u]));
+        m[u] = __ldcs(reinterpret_cast<const float4*>(a.mu + o[u]));
+        v[u] = __ldcs(reinterpret_cast<const float4*>(a.nu + o[u]));
+        tg[u] = a.target ? __ldcs(reinterpret_cast<const float4*>(a.target + o[u])) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < kAdamUnroll; ++u)
+        if (ok[u]) adam_quad(a, o[u], ibc1, ibc2, g[u], th[u], m[u], v[u], tg[u]);
     }
-#pragma unroll
-    for (int u = 0; u < kAdamUnroll; ++u) {
-      g[u] = __ldcs(reinterpret_cast<const float4*>(a.grad + o[u]));
-      th[u] = __ldcs(reinterpret_cast<const float4*>(a.theta + o[u]));
-      m[u] = __ldcs(reinterpret_cast<const float4*>(a.mu + o[u]));
-      v[u] = __ldcs(reinterpret_cast<const float4*>(a.nu + o[u]));
-      tg[u] = a.target ? __ldcs(reinterpret_cast<const float4*>(a.target + o[u])) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-#pragma unroll
-    for (int u = 0; u < kAdamUnroll; ++u)
-      if (ok[u]) adam_quad(a, o[u], ibc1[u], ibc2[u], g[u], th[u], m[u], v[u], tg[u]);
   }
   if (tl_on) tl_record(a.timeline, tl_t0, a.tag);
 }
