@@ -88,6 +88,79 @@ __global__ void __launch_bounds__(256) wm_gemm_kernel(const float* __restrict__ 
   }
 }
 
+// The same product for the LARGE problems (the multistep trainer's products over all T*B rows: the frozen termination
+// predictor forward / backward and the split-K weight gradients): 64 x 64 tiles, 4 x 4 outputs per thread, 16-deep k slabs
+// with the next slab's global loads in flight while the current one is multiplied -- 16 FMAs per two 16-byte shared-memory
+// loads instead of 4 per two scalar ones. Same arguments and epilogues as wm_gemm_kernel.
+constexpr int kWmTile64 = 64;
+constexpr int kWmBK64 = 16;
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(256) wm_gemm64_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B,
+                                                        int ldb, float* __restrict__ C, int ldc, int M, int N, int K,
+                                                        int epi, const float* __restrict__ bias,
+                                                        const float* __restrict__ aux, int ldaux, int accumulate,
+                                                        int k_chunk, long long c_split_stride) {
+  __shared__ __align__(16) float As[kWmBK64][kWmTile64 + 4];  // [k][m]
+  __shared__ __align__(16) float Bs[kWmBK64][kWmTile64 + 4];  // [k][n]
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.y * kWmTile64, n0 = blockIdx.x * kWmTile64;
+  const int kbeg = blockIdx.z * k_chunk;
+  K = min(K, kbeg + k_chunk);
+  C += blockIdx.z * c_split_stride;
+  float acc[4][4] = {};
+  float ra[4], rb[4];
+  auto load_round = [&](int k0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int e = tid + i * 256;
+      const int am = TA ? (e & 63) : (e >> 4), ak = TA ? (e >> 6) : (e & 15);
+      const int bk = TB ? (e & 15) : (e >> 6), bn = TB ? (e >> 4) : (e & 63);
+      const int gm = m0 + am, gka = k0 + ak, gkb = k0 + bk, gn = n0 + bn;
+      ra[i] = (gm < M && gka < K) ? (TA ? A[(long long)gka * lda + gm] : A[(long long)gm * lda + gka]) : 0.f;
+      rb[i] = (gkb < K && gn < N) ? (TB ? B[(long long)gn * ldb + gkb] : B[(long long)gkb * ldb + gn]) : 0.f;
+    }
+  };
+  if (kbeg < K) load_round(kbeg);
+  for (int k0 = kbeg; k0 < K; k0 += kWmBK64) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int e = tid + i * 256;
+      As[TA ? (e >> 6) : (e & 15)][TA ? (e & 63) : (e >> 4)] = ra[i];
+      Bs[TB ? (e & 15) : (e >> 6)][TB ? (e >> 4) : (e & 63)] = rb[i];
+    }
+    __syncthreads();
+    if (k0 + kWmBK64 < K) load_round(k0 + kWmBK64);
+#pragma unroll
+    for (int k = 0; k < kWmBK64; ++k) {
+      const float4 a4 = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+      const float4 b4 = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+      const float av[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int gm = m0 + ty * 4 + i;
+    if (gm >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int gn = n0 + tx * 4 + j;
+      if (gn >= N) continue;
+      float r = acc[i][j];
+      if (epi == WE_BIAS || epi == WE_BIAS_RELU || epi == WE_BIAS_RESID) r += bias[gn];
+      if (epi == WE_BIAS_RELU) r = fmaxf(r, 0.f);
+      if (epi == WE_BIAS_RESID) r += aux[(long long)gm * ldaux + gn];
+      if (epi == WE_MASK) r = aux[(long long)gm * ldaux + gn] > 0.f ? r : 0.f;
+      float* c = C + (long long)gm * ldc + gn;
+      *c = accumulate ? *c + r : r;
+    }
+  }
+}
+
 // out[n] = sum_m X[m][n] (* Y[m][n]): bias gradients and the LayerNorm scale / bias gradients. One thread per column.
 // (both at once for the LayerNorm: out = sum X, out_xy = sum X * Y). blockIdx.y = row slice (rows_per_slice rows each,
 // its sums go to out + y * N: partials for wm_reduce_kernel when gridDim.y > 1).
@@ -506,9 +579,21 @@ struct Launcher {
   // splits > 1: slice z of the k range goes to C + z * M * N (ldc must be N); wm_reduce adds the slices
   void gemm(bool ta, bool tb, const float* A, int lda, const float* B, int ldb, float* C, int ldc, int M, int N, int K,
             int epi, const float* bias, const float* aux, int ldaux, int accumulate, int splits = 1) {
-    dim3 grid((N + kWmTile - 1) / kWmTile, (M + kWmTile - 1) / kWmTile, splits);
     const int kc = splits > 1 ? ((K + splits - 1) / splits + kWmBK - 1) / kWmBK * kWmBK : K;
     const long long cs = splits > 1 ? (long long)M * N : 0;
+    // enough 64 x 64 tiles for every SM: the register-tiled kernel (the small per-step products keep the 32 x 32 one,
+    // whose finer tiles give a latency-bound step more CTAs)
+    const long long tiles64 = (long long)((N + kWmTile64 - 1) / kWmTile64) * ((M + kWmTile64 - 1) / kWmTile64) * splits;
+    static const bool big_on = [] { const char* e = getenv("FQLPOP_WM_GEMM64"); return e ? atoi(e) != 0 : true; }();
+    if (big_on && tiles64 >= 148) {
+      dim3 g64((N + kWmTile64 - 1) / kWmTile64, (M + kWmTile64 - 1) / kWmTile64, splits);
+      if (ta) wm_gemm64_kernel<true, false><<<g64, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate, kc, cs);
+      else if (tb) wm_gemm64_kernel<false, true><<<g64, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate, kc, cs);
+      else wm_gemm64_kernel<false, false><<<g64, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate, kc, cs);
+      ++n;
+      return;
+    }
+    dim3 grid((N + kWmTile - 1) / kWmTile, (M + kWmTile - 1) / kWmTile, splits);
     if (ta) wm_gemm_kernel<true, false><<<grid, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate, kc, cs);
     else if (tb) wm_gemm_kernel<false, true><<<grid, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate, kc, cs);
     else wm_gemm_kernel<false, false><<<grid, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate, kc, cs);

@@ -18,7 +18,7 @@
 // ([out][in], rebuilt once per optimiser step by wm_transpose_kernel) so that its products have the same access pattern.
 //
 // Measured (T = 256, B = 256, antsoccer shape, 64 CTAs): 6.9 ms per optimiser step against 14.6 ms for the per-step
-// launches (5.5 ms with termination_weight = 0, the reference scripts' setting). The per-step critical path is a chain of
+// launches (5.5 ms with termination_weight = 0, the reference scripts' setting); 6.0 / 5.3 ms with wm_gemm64_kernel. The per-step critical path is a chain of
 // 9 short phases whose latencies (barrier, shared-memory round trips, L2 for the one kernel that does not fit) are paid in
 // full at 2 warps per scheduler: issue slots 24 % busy. Tried and dropped: 512 / 1024 threads with finer reduction
 // slices (7.4 / 9.0 ms: more partial sums to add, same latencies); clusters of 2 or 4 CTAs that split every layer's
