@@ -122,21 +122,26 @@ def test_env_step_matches_oracle(shape, hidden):
 
 @pytest.mark.parametrize("shape,pair,hidden", [((42, 8), 0, (128, 256, 128)), ((28, 5), 0, (128, 256, 128)),
                                                ((42, 8), 1, (128, 256, 128)), ((28, 5), 1, (100, 72)),
-                                               ((42, 8), 1, (512, 256)), ((28, 5), 0, (64, 64))],
+                                               ((42, 8), 1, (512, 256)), ((28, 5), 0, (64, 64)),
+                                               ((42, 8), -50, (128, 256, 128))],
                          ids=["antsoccer", "cube", "antsoccer_cta_pair", "padded_widths_100_72", "wide_512_256",
-                              "narrow_64_64_first_generation_kernel"])
+                              "narrow_64_64_first_generation_kernel", "default_50_episodes_one_tile"])
 def test_rollout_matches_oracle_fixed_horizon(shape, pair, hidden, monkeypatch):
+    n = 200
+    if pair < 0:   # the reference's default eval_episodes = 50: one episode tile per member, default kernel choice
+        n, pair = -pair, None
     # pair 1: tcgen05.mma.cta_group::2 over two episode tiles. World models of other widths than the reference's default walk
     # the other layer shapes of the second-generation kernel (two-tile relu layers, widths padded to 128); 64-wide hidden
     # layers are outside its range and take the first-generation kernel.
-    monkeypatch.setenv("FQLPOP_ROLLOUT_PAIR", str(pair))
+    if pair is not None:
+        monkeypatch.setenv("FQLPOP_ROLLOUT_PAIR", str(pair))
     O, A = shape
     cfg = orc.FQLConfig(ob_dim=O, action_dim=A, batch_size=128)
     alphas, seeds = [3.0, 30.0, 300.0], [5, 6, 7]
     pop, states = _population(cfg, alphas, seeds)
     em = _envmodel(O, A, hidden=hidden, term_bias=-0.6)
     dem = _device_envmodel(em, O, A)
-    n, T = 200, 12
+    T = 12
     g = torch.Generator().manual_seed(4)
     init = torch.randn(n, O, generator=g)
     noise = torch.randn(3, T, n, A, generator=g)
