@@ -1060,8 +1060,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1) fql_ch
               uint8_t* sb = stage_base + stage * kStageBytes;
               if (MODE == 0) {
                 mbar_arrive_expect_tx(&full_bar[stage], ncols * kStageK * 2);
-                for (int b = 0; b < ncols / 64; ++b)
-                  tma_load_3d(sb + b * kFwdBoxBytes, &J.mapW[li], &full_bar[stage], n0 + 64 * b, ks * kStageK, v);
+                if (Ly.b_box_rows > 0) {
+                  // wide-box weight map (pop.cu encode_forward_maps): the whole stage is ONE TMA instruction -- four
+                  // separate 4 KB box requests deliver their first bytes thousands of cycles later (measured in
+                  // rollout16.cu / chain16.cu: weight waits per layer 9 k -> 2 k cycles)
+                  tma_load_4d(sb, &J.mapW[li], &full_bar[stage], 0, ks * kStageK, n0 >> 6, v);
+                } else {
+                  for (int b = 0; b < ncols / 64; ++b)
+                    tma_load_3d(sb + b * kFwdBoxBytes, &J.mapW[li], &full_bar[stage], n0 + 64 * b, ks * kStageK, v);
+                }
               } else {
                 mbar_arrive_expect_tx(&full_bar[stage], (split ? 256 : Ly.b_box_rows) * kStageK * 2);
                 tma_load_3d(sb, &J.mapW[li], &full_bar[stage], ks * kStageK, n0, v);
@@ -1606,6 +1613,14 @@ cudaError_t chain_init() {
 constexpr int kClusterMaxMembers = 8;
 
 // The cluster kernel covers the production shape: every hidden layer 512 wide, reductions of 64 (first layer) or 512.
+static bool chain2_eligible(const ChainLaunch& L);
+// (pop.cu) true when launch_chain will run this forward launch on the N-split cluster kernel: its weight maps may then be
+// wide-box maps (4 column blocks per hidden-layer stage, 1 for the narrow layers)
+bool chain2_will_run(const ChainLaunch& L) {
+  if (chain16_eligible(L) && chain16_selected_shape(L.job[0].H, 64, L.job[0].ln != 0, L.job[0].iters, L.population_active))
+    return false;
+  return chain2_eligible(L);
+}
 static bool chain2_eligible(const ChainLaunch& L) {
   // FQLPOP_CHAIN2 = 0: single-CTA kernel; 1: cluster kernel for every chain; 2: cluster kernel for the Euler chain only;
   // unset: by population size. The cluster kernel cuts a chain's latency 1.4-1.7x but costs ~20 % more SM time: with few
@@ -1657,11 +1672,15 @@ cudaError_t launch_chain(ChainLaunch& L, int mode, cudaStream_t stream) {
   L.stages = staged ? kStagesStaged : kStages;
   if (chain16_eligible(L) && chain16_selected_shape(L.job[0].H, 64, L.job[0].ln != 0, L.job[0].iters, L.population_active))
     return launch_chain16(L, mode, grid, stream);
-  if (mode == 0)  // wide-box weight maps are read by chain16.cu only
+  const bool c2 = chain2_eligible(L);
+  if (mode == 0)  // wide-box weight maps are read by chain16.cu and the cluster kernel only, each with its own box shape
     for (int i = 0; i < L.num_jobs; ++i)
-      for (int l = 0; l < L.job[i].n_layers; ++l)
-        if (L.job[i].layer[l].b_box_rows != 0) return cudaErrorInvalidValue;
-  if (chain2_eligible(L)) {
+      for (int l = 0; l < L.job[i].n_layers; ++l) {
+        const int wb = L.job[i].layer[l].b_box_rows;
+        if (wb != 0 && !(c2 && wb == (L.job[i].layer[l].kind == CL_HIDDEN ? 4 : L.job[i].layer[l].n_pad / 64)))
+          return cudaErrorInvalidValue;
+      }
+  if (c2) {
     if (mode == 0) fql_chain2_kernel<0><<<2 * grid, kThreads2, kSmemBytes, stream>>>(L);
     else fql_chain2_kernel<1><<<2 * grid, kThreads2, kSmemBytes, stream>>>(L);
     return cudaGetLastError();

@@ -98,6 +98,7 @@ int finalize_chain(ChainLaunch* L);
 // launch has the production shape (chain16_eligible).
 cudaError_t chain16_init();
 bool chain16_eligible(const ChainLaunch& L);
+bool chain2_will_run(const ChainLaunch& L);  // the N-split cluster kernel will take this forward launch
 bool chain16_selected_shape(int H, int in_pad, bool ln, int iters, int population_active);
 bool chain16_pair_mode();
 bool chain16_pairs_rows(int M);  // ... and only for jobs with an even number of 128-row tiles  // clusters of two CTAs, tcgen05.mma.cta_group::2 (default; FQLPOP_CHAIN_PAIR=0 disables)

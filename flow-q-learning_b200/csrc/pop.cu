@@ -377,6 +377,10 @@ struct ChainBuilder {
                      chain16_selected_shape(j0.H, 64, j0.ln != 0, j0.iters, (int)P->h_members.size());
     bool pair = c16 && chain16_pair_mode();
     for (int i = 0; i < L->num_jobs; ++i) pair = pair && chain16_pairs_rows(L->job[i].M);
+    L->population_active = (int)P->h_members.size();
+    for (int i = 0; i < L->num_jobs; ++i)      // (chain2_will_run looks at the layer shapes only)
+      for (int l = 0; l < L->job[i].n_layers; ++l) L->job[i].layer[l].b_box_rows = 0;
+    const bool c2 = !c16 && chain2_will_run(*L);
     for (int i = 0; i < L->num_jobs; ++i) {
       ChainJob& j = L->job[i];
       for (int l = 0; l < j.n_layers; ++l) {
@@ -385,6 +389,10 @@ struct ChainBuilder {
         if (c16) {
           const int boxes = j.layer[l].n_pad >= 256 ? (pair ? 2 : 4) : 1;
           rc = encode_tmap_bf16_wide(&j.mapW[l], a.base, a.inner, a.rows, a.batch, a.inner, a.ms, pair ? 64 : 32, boxes);
+          j.layer[l].b_box_rows = boxes;
+        } else if (c2) {   // N-split cluster kernel: one CTA stages 256 columns of a hidden layer, all of a narrow one
+          const int boxes = j.layer[l].kind == CL_HIDDEN ? 4 : j.layer[l].n_pad / 64;
+          rc = encode_tmap_bf16_wide(&j.mapW[l], a.base, a.inner, a.rows, a.batch, a.inner, a.ms, 32, boxes);
           j.layer[l].b_box_rows = boxes;
         } else {
           rc = encode_tmap_bf16(&j.mapW[l], a.base, a.inner, a.rows, a.batch, a.inner, a.ms, 32);
