@@ -92,27 +92,11 @@ __device__ __forceinline__ void st_act16(uint32_t act, int r, int col, const uin
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Staging blocks (per warp, 2 KB).
-//   half block   : 32 rows x 32 bf16 (64 B per row); 16-byte chunk c (0..3) of row r at r * 64 + ((c ^ ((r >> 1) & 3)) << 4)
+// Staging blocks of the BACKWARD chains (per warp, 2 KB = two quarter blocks; the forward passes store what they save
+// straight from registers and stage nothing).
 //   quarter block: 32 rows x 16 bf16 (32 B per row), 1 KB; chunk c (0..1) of row r at r * 32 + ((c ^ ((r >> 2) & 1)) << 4)
-// Row-wise accesses (lane = row) and the coalesced sweeps are bank-conflict free in both.
+// Row-wise accesses (lane = row) and the coalesced sweeps are bank-conflict free.
 // ---------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void st_half16(uint32_t blk, int lane, int cw, const uint32_t* w) {
-  const uint32_t row = blk + lane * 64;
-  const int c0 = cw >> 3, sw = (lane >> 1) & 3;
-  sts128(row + ((c0 ^ sw) << 4), w[0], w[1], w[2], w[3]);
-  sts128(row + (((c0 + 1) ^ sw) << 4), w[4], w[5], w[6], w[7]);
-}
-// half block -> global rows (row stride ld elements); 8 rows x 64 contiguous bytes per warp instruction
-__device__ __forceinline__ void copy_out_half(uint32_t blk, __nv_bfloat16* g, int ld, int lane, int rows_valid) {
-  const int ch = lane & 3, rsub = lane >> 2;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int r = i * 8 + rsub;
-    const uint4 v = lds128(blk + r * 64 + ((ch ^ ((r >> 1) & 3)) << 4));
-    if (r < rows_valid) *reinterpret_cast<uint4*>(g + (long long)r * ld + ch * 8) = v;
-  }
-}
 // global rows -> quarter block, asynchronously (rows that do not exist are zero-filled). One commit group.
 __device__ __forceinline__ void stage_in_quarter(uint32_t blk, const __nv_bfloat16* g, int ld, int lane, int rows_valid) {
 #pragma unroll
