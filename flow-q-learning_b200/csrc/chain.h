@@ -34,7 +34,7 @@ struct ChainLayer {
   int a_from_x0;   // A operand = the 128 x 64 input block instead of the activation buffer
   int b_box_rows;  // backward: rows of the weight TMA box (min(256, output columns)); forward: 0 = weight map with 64 n x
                    // 32 k boxes, else a wide map whose box spans this many 64-column blocks (chain16.cu only)
-  int _pad0;
+  int h_tma;       // (chain16.cu, forward) out_h is written by TMA stores through ChainJob::mapH of this layer
   long long off_b, off_g, off_beta;  // element offsets of bias / LayerNorm scale / LayerNorm bias in `params`
   // forward outputs (nullptr = not stored). Row-major [V][pass rows][H] bf16, already offset to the job's row 0.
   __nv_bfloat16* out_h;
@@ -58,6 +58,7 @@ struct ChainJob {
   CUtensorMap mapA0;                   // first A operand: dims (64, pass rows, V), box 64 x 128
   CUtensorMap mapW[kChainMaxLayers];   // forward: [K][N] n-contiguous, box 64n x 32k; backward: same array read
                                        // as B^T, 64-byte swizzle, box 32 k x min(256, n) rows
+  CUtensorMap mapH[kChainMaxLayers];   // (chain16.cu, forward) the layer's h buffer: dims (H, row0 + M, V), box 64 x 32
   ChainLayer layer[kChainMaxLayers];
   int tile_begin, m_tiles, M, row0;    // rows [row0, row0 + M) of the pass buffers
   int n_layers, iters, ln, H;

@@ -179,6 +179,9 @@ struct Epi {
   long long rs_off;        // offset of this thread's row in the rstd buffers
   long long part_off;      // offset of this (row tile, lane quarter) row in the partial-sum buffers
   float ln_eps;
+  const CUtensorMap* map_h;  // this layer's h store map (ChainLayer::h_tma)
+  int h_row, h_v;          // first row of this warp in the pass buffers, virtual member (TMA store coordinates)
+  bool h_pending;          // this warp has TMA stores in flight that read its rows of ACT
   long long* tr;           // (make TRACE=1) stamp log of the traced epilogue thread, 8 slots per layer
 };
 __device__ __forceinline__ void stamp(const Epi& C, int slot) {
@@ -376,6 +379,13 @@ __device__ __forceinline__ void ln_flush_tile(const Epi& C, const ChainLayer& Ly
 template <bool LN, bool SAVE>
 __device__ __forceinline__ void fwd_hidden_layer(Epi& C, const ChainLayer& Ly, uint32_t par0, uint32_t par1, bool pub,
                                                  int layer_parity) {
+  // the previous layer's h stores (TMA, below) must have read this warp's rows of ACT before they are rewritten; they
+  // were issued a whole layer of MMAs ago, so this wait does not wait
+  if (C.h_pending) {
+    if (C.lane == 0) bulk_wait_group_read0();
+    __syncwarp();
+    C.h_pending = false;
+  }
   load_layer_params(C, Ly, layer_parity, true, LN, false);
   if (!C.pb) prefetch_params(C, Ly, true, LN);
   float s1 = 0.f, s2 = 0.f;
@@ -440,10 +450,24 @@ __device__ __forceinline__ void fwd_hidden_layer(Epi& C, const ChainLayer& Ly, u
   // (measured: storing h from the registers like act'(z), one 32-byte sector per thread and chunk, makes the policy pass
   // slower -- 59.7 vs 54.1 us; the copy-out writes whole 128-byte row segments)
   if (Ly.out_h) {
-    __syncwarp();
     const uint32_t b0 = C.act + C.cg * kActBlockBytes + C.q * (32 * 128);
-    copy_out_block(b0, Ly.out_h + C.wrow + C.cg * 64, C.H, C.lane, C.rows_valid);
-    copy_out_block(b0 + 4 * kActBlockBytes, Ly.out_h + C.wrow + kTileN + C.cg * 64, C.H, C.lane, C.rows_valid);
+    if (Ly.h_tma) {
+      // the warp's 32 rows of its two 64-column blocks are two 4 KB boxes in the 128-byte-swizzled layout TMA knows: one
+      // lane hands them to the copy engine (rows beyond the job's last row are clipped by the map) -- no epilogue
+      // instructions for the copy-out (it was ~5 k cycles per layer of a saving pass)
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (C.lane == 0 && C.rows_valid > 0) {
+        tma_store_3d(C.map_h, b0, C.cg * 64, C.h_row, C.h_v);
+        tma_store_3d(C.map_h, b0 + 4 * kActBlockBytes, kTileN + C.cg * 64, C.h_row, C.h_v);
+        bulk_commit_group();
+      }
+      C.h_pending = true;
+    } else {
+      __syncwarp();
+      copy_out_block(b0, Ly.out_h + C.wrow + C.cg * 64, C.H, C.lane, C.rows_valid);
+      copy_out_block(b0 + 4 * kActBlockBytes, Ly.out_h + C.wrow + kTileN + C.cg * 64, C.H, C.lane, C.rows_valid);
+    }
   }
   stamp(C, 6);
 }
@@ -965,6 +989,7 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
     // buffers of 3 x 128 floats (the Euler flow keeps re-using X0 as its first layer's operand: no buffers there)
     C.pb_base = iters == 1 ? reinterpret_cast<float*>(x0s + 4096) + cg * (2 * 3 * 128) : nullptr;
     C.tr = nullptr;
+    C.map_h = nullptr; C.h_row = J.row0 + grow0; C.h_v = v; C.h_pending = false;
 #ifdef FQLPOP_EPI_TRACE
     const bool ep_traced = L.trace && blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0;
 #endif
@@ -985,6 +1010,7 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
         C.tr = (ep_traced && lc < 400) ? L.trace + 4096 + 8 * lc : nullptr;
 #endif
         stamp(C, 0);
+        C.map_h = &J.mapH[li];
         if (Ly.kind == CL_HIDDEN) {
           const bool pub = !(it == iters - 1 && li == n_layers - 1);  // the last layer's output is consumed by nobody on chip
           if (MODE == 0) {
@@ -1052,6 +1078,8 @@ __global__ void __launch_bounds__(kThreads16, 1) fql_chain16_kernel(const __grid
         }
       }
     }
+    // the h stores of the last layer complete before the CTA (and its shared memory) goes away
+    if (C.h_pending && lane == 0) bulk_wait_group0();
   }
 
   tc_fence_before();

@@ -368,6 +368,8 @@ struct ChainBuilder {
   // layers (encode_tmap_bf16_wide) -- and whether it runs, paired or not, depends on every job of the launch.
   struct WArgs { const void* base; long long inner, rows, batch, ms; };
   WArgs wargs[kChainMaxJobs][kChainMaxLayers];
+  struct HArgs { const void* base; long long pass_rows, V; };   // the layer's h buffer [V][pass rows][H] (out_h set)
+  HArgs hargs[kChainMaxJobs][kChainMaxLayers];
   void wmap_later(int layer, const void* base, long long inner, long long rows, long long batch, long long ms) {
     wargs[L->num_jobs - 1][layer] = WArgs{base, inner, rows, batch, ms};
   }
@@ -386,6 +388,14 @@ struct ChainBuilder {
       for (int l = 0; l < j.n_layers; ++l) {
         const WArgs& a = wargs[i][l];
         int rc;
+        j.layer[l].h_tma = 0;
+        if (c16 && j.layer[l].out_h && l < kChainMaxLayers && j.layer[l].kind == CL_HIDDEN) {
+          // chain16.cu writes h with TMA stores: box 64 columns x 32 rows (one epilogue warp's rows of one ACT block),
+          // rows clipped at the job's last row
+          const HArgs& h = hargs[i][l];
+          const int hrc = encode_tmap_bf16(&j.mapH[l], h.base, j.H, j.row0 + j.M, h.V, j.H, h.pass_rows * j.H, 32);
+          if (hrc == 0) j.layer[l].h_tma = 1;
+        }
         if (c16) {
           const int boxes = j.layer[l].n_pad >= 256 ? (pair ? 2 : 4) : 1;
           rc = encode_tmap_bf16_wide(&j.mapW[l], a.base, a.inner, a.rows, a.batch, a.inner, a.ms, pair ? 64 : 32, boxes);
@@ -418,6 +428,7 @@ struct ChainBuilder {
       y.kind = CL_HIDDEN; y.k_blocks = N.K(l) / 64; y.n_pad = N.H; y.a_from_x0 = l == 0;
       y.off_b = N.offb[l]; y.off_g = N.offg[l]; y.off_beta = N.offbeta[l];
       if (save || l == N.n_hidden - 1) y.out_h = pass.hl(l) + roff;
+      hargs[L->num_jobs - 1][l] = HArgs{pass.hl(l), pass.M, pass.V};
       if (save) {
         y.out_gp = pass.gp[l] + roff;
         if (N.ln) {
