@@ -138,7 +138,7 @@ __device__ __forceinline__ void copy_out_block_colsum(uint32_t blk, __nv_bfloat1
   for (int i = 0; i < 8; ++i) {
     const int r = i * 4 + rsub;
     const uint4 v = lds128(blk + r * 128 + ((ch ^ (r & 7)) << 4));
-    if (r < rows_valid) *reinterpret_cast<uint4*>(g + (long long)r * ld + ch * 8) = v;
+    if (g != nullptr && r < rows_valid) *reinterpret_cast<uint4*>(g + (long long)r * ld + ch * 8) = v;  // (nullptr: TMA stores it)
     acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x);
     acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
     acc[4] += bf16_lo(v.z); acc[5] += bf16_hi(v.z);
@@ -680,22 +680,39 @@ __device__ __forceinline__ void bwd_hidden_ln(const Epi& C, const ChainLayer& Ly
 template <bool LN>
 __device__ __forceinline__ void bwd_hidden_layer(Epi& C, const ChainLayer& Ly, uint32_t par0, uint32_t par1, bool pub,
                                                  int layer_parity) {
+  if (C.h_pending) {   // the previous layer's dz stores (TMA, below) have read this warp's rows of ACT
+    if (C.lane == 0) bulk_wait_group_read0();
+    __syncwarp();
+    C.h_pending = false;
+  }
   if (LN) load_layer_params(C, Ly, layer_parity, false, false, true);
   else C.pb = nullptr;
   if (!C.pb) prefetch_params(C, Ly, false, LN);
   if (LN) bwd_hidden_ln(C, Ly, par0, par1, pub);
   else bwd_hidden_plain(C, Ly, par0, par1, pub);
   stamp(C, 5);
-  // dz -> HBM (+ bias-gradient partial sums) out of ACT, off the hand-off path
-  __syncwarp();
+  // dz -> HBM (+ bias-gradient partial sums) out of ACT, off the hand-off path. With a store map (ChainLayer::h_tma) the
+  // copy engine moves the warp's two 4 KB boxes (as the forward passes' h) and only the column sums are left to the warp.
   const uint32_t b0 = C.act + C.cg * kActBlockBytes + C.q * (32 * 128);
+  if (Ly.h_tma) {
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (C.lane == 0 && C.rows_valid > 0) {
+      tma_store_3d(C.map_h, b0, C.cg * 64, C.h_row, C.h_v);
+      tma_store_3d(C.map_h, b0 + 4 * kActBlockBytes, kTileN + C.cg * 64, C.h_row, C.h_v);
+      bulk_commit_group();
+    }
+    C.h_pending = true;
+  } else {
+    __syncwarp();
+  }
 #pragma unroll
   for (int t = 0; t < 2; ++t) {
     const int col = t * kTileN + C.cg * 64;
+    __nv_bfloat16* dst = Ly.h_tma ? nullptr : Ly.out_dz + C.wdz + col;
     if (Ly.dbias_part)
-      copy_out_block_colsum(b0 + t * 4 * kActBlockBytes, Ly.out_dz + C.wdz + col, C.H, C.lane, C.rows_valid,
-                            Ly.dbias_part + C.part_off + col);
-    else copy_out_block(b0 + t * 4 * kActBlockBytes, Ly.out_dz + C.wdz + col, C.H, C.lane, C.rows_valid);
+      copy_out_block_colsum(b0 + t * 4 * kActBlockBytes, dst, C.H, C.lane, C.rows_valid, Ly.dbias_part + C.part_off + col);
+    else if (dst) copy_out_block(b0 + t * 4 * kActBlockBytes, dst, C.H, C.lane, C.rows_valid);
   }
   stamp(C, 6);
 }

@@ -318,8 +318,25 @@ struct ChainBuilder {
       if (err) *err = "cuTensorMapEncodeTiled (64B swizzle) failed rc=" + std::to_string(rc);
     }
   }
+  // backward chains on chain16.cu: dz leaves through TMA stores too (box 64 columns x 32 rows of the [V][M][H] buffer)
+  void encode_backward_maps() {
+    const ChainJob& j0 = L->job[0];
+    L->population_active = (int)P->h_members.size();
+    const bool c16 = chain16_eligible(*L) &&
+                     chain16_selected_shape(j0.H, 64, j0.ln != 0, j0.iters, (int)P->h_members.size());
+    for (int i = 0; i < L->num_jobs; ++i) {
+      ChainJob& j = L->job[i];
+      for (int l = 0; l < j.n_layers; ++l) {
+        j.layer[l].h_tma = 0;
+        if (!c16 || j.layer[l].kind != CL_HIDDEN || !j.layer[l].out_dz) continue;
+        const HArgs& h = hargs[i][l];
+        if (encode_tmap_bf16(&j.mapH[l], h.base, j.H, j.row0 + j.M, h.V, j.H, h.pass_rows * j.H, 32) == 0) j.layer[l].h_tma = 1;
+      }
+    }
+  }
   void launch(int mode, cudaStream_t s) {
     if (mode == 0) encode_forward_maps();
+    else encode_backward_maps();
     finalize_chain(L);
     L->timeline = P->timeline;
     L->tag = (long long)count | ((long long)P->g_off << 8);
@@ -482,6 +499,7 @@ struct ChainBuilder {
         y.rstd = pass.rstd[l - 1] + row0;
       }
       y.out_dz = bw.dz[l - 1];
+      hargs[L->num_jobs - 1][s] = HArgs{bw.dz[l - 1], bw.M, bw.V};
       if (partials) {
         y.dbias_part = bw.dbias_part[l - 1];
         if (N.ln) {
