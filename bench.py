@@ -155,7 +155,7 @@ def run_reference(args, rank, world):
 
 
 # DRAM traffic of the roofline launch by (shape, members, batch), from the committed ncu --set full capture of that launch
-ROOFLINE_TRAFFIC = {("cube-single", 16, 256): 28017408 + 3933184}
+ROOFLINE_TRAFFIC = {("cube-single", 16, 256): 28017664 + 3474944}
 ROOFLINE_TRAFFIC_SOURCE = "profiles/r03_chain_ncu_full_summary.txt"
 
 
