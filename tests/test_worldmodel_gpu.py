@@ -292,7 +292,8 @@ def test_initial_observation_decoder_matches_oracle_and_loads_from_reference_fil
     assert torch.equal(a, b) and not torch.equal(a, d.sample(n, seed=79))
 
 
-@pytest.mark.parametrize("T,rows", [(6, 64), (40, 256), (5, 30)], ids=["T6_B64", "T40_B256", "T5_B30_ragged_row_tile"])
+@pytest.mark.parametrize("T,rows", [(6, 64), (40, 256), (5, 30), (37, 250)],
+                         ids=["T6_B64", "T40_B256", "T5_B30_ragged_row_tile", "T37_B250_ragged_rows_in_the_64x64_gemm"])
 def test_multistep_predictor_steps_match_oracle(T, rows):
     """Back-propagation through time of the scanned cell (envmodel/multistep.py) against torch autograd in float64:
     logs, every gradient leaf of the first step, parameters after three Adam steps, and a forward-only evaluation."""
