@@ -25,11 +25,15 @@ def _default_kernel_selection(monkeypatch):
         monkeypatch.delenv(k, raising=False)
 
 
-@pytest.mark.parametrize("P,fuse", [(16, 0), (8, 0), (9, 0), (12, 0), (5, 1)])
-def test_population_update_default_kernels_matches_oracle(P, fuse, monkeypatch):
+# B (a multiple of 64): 256 is the benchmark's batch; 192 gives the pair kernel a half-empty second tile (its TMA stores
+# must be clipped by the tensor map), 320 an odd number of 128-row tiles (one CTA per tile then) with a ragged last one;
+# 1024 is config 5's batch.
+@pytest.mark.parametrize("P,fuse,B", [(16, 0, 256), (8, 0, 256), (9, 0, 256), (12, 0, 256), (5, 1, 256),
+                                      (12, 0, 192), (10, 0, 320), (10, 0, 1024)])
+def test_population_update_default_kernels_matches_oracle(P, fuse, B, monkeypatch):
     from fqlpop.population import INFO_KEYS, Population
     monkeypatch.setenv("FQLPOP_FUSE_ADAM", str(fuse))   # 1: Adam + Polyak inside the weight-gradient GEMM's epilogue
-    cfg = orc.FQLConfig(ob_dim=28, action_dim=5, batch_size=256)
+    cfg = orc.FQLConfig(ob_dim=28, action_dim=5, batch_size=B)
     alphas = list(np.logspace(np.log10(3), np.log10(1000), P))
     seeds = list(range(100, 100 + P))
     states = [orc.init_state(s, cfg) for s in seeds]
