@@ -411,9 +411,10 @@ def worldmodel_bench(torch, np, dev, steps=2000, cpu_steps=100, with_cpu=True):
 def sh64_bench(torch, np, dev, rank, world, dist, barrier, n_alphas=64, shape="antsoccer", batch=256, eval_interval=100,
                total_evaluations=50, episodes=256, T=200):
     """BASELINE config 4: successive halving (f=0.5, h=2, total_evaluations=50) over 64 alpha values of a LIVE population
-    sharded over the ranks (member i -> rank i mod world), antsoccer shape, batch 256 -- the real Trainer +
-    SuccessiveHalving + fused simulated evaluation, evaluation scores all-gathered (NCCL) after every evaluation so that
-    every rank prunes identically. eval_interval is shortened (the reference trains 20 000 steps between evaluations);
+    sharded over the ranks (member i starts on rank i mod world; after every pruning the survivors are spread over the
+    GPUs again, one NCCL send / recv of the member's state per move -- FQLPOP_REBALANCE=0 keeps them where they are),
+    antsoccer shape, batch 256 -- the real Trainer + SuccessiveHalving + fused simulated evaluation, evaluation scores
+    all-gathered (NCCL) after every evaluation so that every rank prunes identically. eval_interval is shortened (the reference trains 20 000 steps between evaluations);
     the schedule of population sizes is the reference's (64 -> 32 -> 16 -> 8 -> 4 -> 2 -> 1 at
     evaluations 2, 3, 5, 8, 14, 26). STRONG scaling: the job is fixed, ranks only split it.
     Reports whole-job member-updates/s, per-evaluation wall time by population size, all-gather latency and the idle-GPU
@@ -531,14 +532,20 @@ def sh64_bench(torch, np, dev, rank, world, dist, barrier, n_alphas=64, shape="a
                  "allgather_ms_median": sorted(g["gather_ms"])[len(g["gather_ms"]) // 2]}
                 for n, g in sorted(rungs.items(), reverse=True)]
     survivors = sorted(c.alpha for c in tr.candidates)
+    member_mb = round(4e-6 * tr.population.member_state_words(), 1) if tr.population is not None else None
     if tr.population is not None:
         tr.population.close()
     return {"value": updates / total_s, "unit": "updates/s", "scaling": "strong", "total_s": total_s,
             "member_updates": updates, "evaluations": len(rec), "n_gpus": world,
+            "survivor_migration": {"enabled": tr.rebalance, "members_moved": tr.migrations,
+                                   "seconds": round(tr.migration_seconds, 4),
+                                   **{k: round(v, 4) for k, v in tr.migration_breakdown.items()},
+                                   "mb_per_member": member_mb},
             "config": {"workload": f"successive halving f=0.5 h=2 over {n_alphas} alpha values, {shape} shape (O={O}, A={A}), "
                                    f"batch {batch}, {total_evaluations} evaluations of {episodes} episodes x {T} steps, "
-                                   f"eval_interval {eval_interval} steps (shortened), members placed i mod {world}, "
-                                   "scores all-gathered over NCCL after every evaluation"},
+                                   f"eval_interval {eval_interval} steps (shortened), members placed i mod {world}"
+                                   + (", survivors migrated after every pruning" if tr.rebalance else "")
+                                   + ", scores all-gathered over NCCL after every evaluation"},
             "population_sizes": [r["population"] for r in rec], "per_rung": per_rung, "survivor_alphas": survivors}
 
 

@@ -170,6 +170,22 @@ extern "C" int fqlpop_refresh_shadow(void* h, void* stream) {
   if (fqlpop::pop_refresh_shadow_impl(P, (cudaStream_t)stream, &err)) return fail(err);
   return 0;
 }
+extern "C" int64_t fqlpop_member_state_words(void* h) {
+  if (!h) return -1;
+  return fqlpop::pop_member_state_words(static_cast<fqlpop::Population*>(h));
+}
+extern "C" int fqlpop_member_export(void* h, int32_t member, float* blob_dev, void* stream) {
+  POP(h);
+  std::string err;
+  if (fqlpop::pop_member_io(P, member, blob_dev, 0, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_member_import(void* h, int32_t member, const float* blob_dev, void* stream) {
+  POP(h);
+  std::string err;
+  if (fqlpop::pop_member_io(P, member, const_cast<float*>(blob_dev), 1, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
 extern "C" int fqlpop_counters(void* h, int32_t* adam_steps, uint64_t* step_counter, int32_t set) {
   POP(h);
   cudaDeviceSynchronize();

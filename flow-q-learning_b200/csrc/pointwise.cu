@@ -900,6 +900,10 @@ void launch_refresh_shadow(Population* P, cudaStream_t s) {
   }
 }
 
+void launch_to_bf16(const float* src, __nv_bfloat16* dst, long long n4, cudaStream_t s) {
+  to_bf16_kernel<<<(unsigned)min(1184LL, (n4 + 255) / 256), 256, 0, s>>>(src, dst, n4);
+}
+
 void launch_fill_qa_dout(Population* P, cudaStream_t s) {
   const long long rows = (long long)P->bQA.V * P->bQA.M;
   const float v = -1.f / (float)(P->c.E * P->c.B);

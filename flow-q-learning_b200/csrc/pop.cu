@@ -1107,6 +1107,79 @@ int pop_debug_chain_launch(Population* P, int which, int iters, cudaStream_t str
   return 0;
 }
 
+// ---- member migration (survivors of a successive-halving rung are spread over the GPUs again) ------------
+// One member's whole training state as ONE contiguous device blob of 32-bit words, so that the host side can hand it to
+// a single NCCL send / recv: an 8-word header {adam_step, alpha (fp32 bits), seed lo/hi, Philox step counter lo/hi,
+// blob words, layout check} followed by critic theta / mu / nu / target (E blocks each), BC-flow theta / mu / nu and
+// one-step-policy theta / mu / nu, each exactly as it lies in its arena (padded kernels included: padding is zero on
+// both sides). Gradients, bf16 shadows and activations are not state: the shadows are rebuilt on import.
+constexpr int kMemberHeaderWords = 8;
+static unsigned member_layout_check(const Population* P) {
+  // two populations exchange members only if their arenas have the same shape
+  unsigned long long h = 1469598103934665603ull;
+  for (const Arena* ar : {&P->critic, &P->bc, &P->pi})
+    for (long long v : {(long long)ar->L.nb, ar->L.S, (long long)ar->L.in_pad, (long long)ar->L.H, (long long)ar->L.n_hidden,
+                        (long long)ar->L.out_dim, (long long)ar->L.ln})
+      h = (h ^ (unsigned long long)v) * 1099511628211ull;
+  return (unsigned)(h ^ (h >> 32));
+}
+long long pop_member_state_words(const Population* P) {
+  long long n = kMemberHeaderWords;
+  for (const Arena* ar : {&P->critic, &P->bc, &P->pi}) n += (long long)ar->L.nb * ar->L.S * (ar->target ? 4 : 3);
+  return n;
+}
+__global__ void member_header_kernel(unsigned* blob, int* adam_step, float* alphas, unsigned long long* seeds,
+                                     unsigned long long* step_counter, int member, unsigned words, unsigned check,
+                                     int import) {
+  if (threadIdx.x || blockIdx.x) return;
+  if (!import) {
+    blob[0] = (unsigned)adam_step[member];
+    blob[1] = __float_as_uint(alphas[member]);
+    blob[2] = (unsigned)seeds[member]; blob[3] = (unsigned)(seeds[member] >> 32);
+    blob[4] = (unsigned)step_counter[member]; blob[5] = (unsigned)(step_counter[member] >> 32);
+    blob[6] = words; blob[7] = check;
+  } else {
+    adam_step[member] = (int)blob[0];
+    alphas[member] = __uint_as_float(blob[1]);
+    seeds[member] = (unsigned long long)blob[2] | ((unsigned long long)blob[3] << 32);
+    step_counter[member] = (unsigned long long)blob[4] | ((unsigned long long)blob[5] << 32);
+  }
+}
+int pop_member_io(Population* P, int member, float* blob, int import, cudaStream_t stream, std::string* err) {
+  if (member < 0 || member >= P->c.P || !blob) {
+    if (err) *err = "member_io: bad member or null buffer";
+    return 1;
+  }
+  const unsigned words = (unsigned)pop_member_state_words(P), check = member_layout_check(P);
+  if (import) {   // the header is checked on the host before a single word of the arenas is touched
+    unsigned head[kMemberHeaderWords];
+    CK(cudaMemcpyAsync(head, blob, sizeof(head), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    if (head[6] != words || head[7] != check) {
+      if (err) *err = "member_import: the blob was not exported by a population of the same network shapes";
+      return 1;
+    }
+  }
+  member_header_kernel<<<1, 32, 0, stream>>>(reinterpret_cast<unsigned*>(blob), P->adam_step, P->alphas, P->seeds,
+                                             P->step_counter, member, words, check, import);
+  float* w = blob + kMemberHeaderWords;
+  for (Arena* ar : {&P->critic, &P->bc, &P->pi}) {
+    const long long n = (long long)ar->L.nb * ar->L.S, off = (long long)member * n;
+    for (float* base : {ar->theta, ar->mu, ar->nu, ar->target}) {
+      if (!base) continue;
+      CK(cudaMemcpyAsync(import ? base + off : w, import ? w : base + off, sizeof(float) * (size_t)n,
+                         cudaMemcpyDeviceToDevice, stream));
+      w += n;
+    }
+    if (import) {
+      launch_to_bf16(ar->theta + off, ar->shadow + off, n / 4, stream);
+      if (ar->target) launch_to_bf16(ar->target + off, ar->tshadow + off, n / 4, stream);
+    }
+  }
+  CK(cudaGetLastError());
+  return 0;
+}
+
 // leaf I/O: kind 0 kernel [nb][K_true][N_true], 1 bias [nb][N_true], 2 LayerNorm scale, 3 LayerNorm bias [nb][H];
 // which 0 theta, 1 mu, 2 nu, 3 target, 4 grad. Host buffers are unpadded fp32.
 int pop_leaf_io(Population* P, int net, int layer, int kind, int which, int member, float* host, int to_host,

@@ -163,6 +163,9 @@ int pop_launches_per_step(const Population* p);
 int pop_debug_chain_launch(Population* p, int which, int iters, cudaStream_t stream, std::string* err);
 int pop_leaf_io(Population* p, int net, int layer, int kind, int which, int member, float* host, int to_host,
                 std::string* err);
+// one member's training state as one contiguous device blob (survivor migration between GPUs)
+long long pop_member_state_words(const Population* p);
+int pop_member_io(Population* p, int member, float* blob_dev, int import, cudaStream_t stream, std::string* err);
 
 // ---- pointwise.cu launchers (all take the population and a stream; grid covers the active members) ----
 void launch_prep(Population* p, cudaStream_t s, int bump_adam);
@@ -179,6 +182,7 @@ void launch_adam(Population* p, int which, cudaStream_t s);  // 0 critic, 1 bc f
 void launch_adam_leaves(Population* p, int which, cudaStream_t s);  // biases / LayerNorm leaves only (kernels: gemm.cu EPI_ADAM)
 void launch_finish_info(Population* p, int bump_step, cudaStream_t s);
 void launch_refresh_shadow(Population* p, cudaStream_t s);
+void launch_to_bf16(const float* src, __nv_bfloat16* dst, long long n4, cudaStream_t s);  // n4 = float4 groups
 void launch_fill_qa_dout(Population* p, cudaStream_t s);
 int pointwise_init();
 int philox_fill(unsigned long long seed, unsigned long long step, int rows, int slots, int kind, unsigned int n,

@@ -60,8 +60,12 @@ lib.fqlpop_philox_fill.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_in
                                    ctypes.c_uint32, _vp]
 lib.fqlpop_philox_fill.restype = ctypes.c_int
 for _f in ("create", "destroy", "set_dataset", "set_noise", "set_active", "step", "total_loss", "info", "leaf",
-           "refresh_shadow", "counters", "launches_per_step"):
+           "refresh_shadow", "counters", "launches_per_step", "member_export", "member_import"):
     getattr(lib, "fqlpop_" + _f).restype = ctypes.c_int
+lib.fqlpop_member_state_words.argtypes = [_vp]
+lib.fqlpop_member_state_words.restype = ctypes.c_int64
+lib.fqlpop_member_export.argtypes = [_vp, ctypes.c_int32, _vp, _vp]
+lib.fqlpop_member_import.argtypes = [_vp, ctypes.c_int32, _vp, _vp]
 
 
 def _uniform_width(dims, what):
@@ -277,6 +281,33 @@ class Population:
             np.broadcast_to(np.asarray(step_counter, np.uint64), (self.P,)))
         check(lib.fqlpop_counters(self._h, None if steps is None else steps.ctypes.data,
                                   None if ctr is None else ctr.ctypes.data, 1), "fqlpop_counters")
+
+
+    # ---- survivor migration (include/fqlpop.h: fqlpop_member_export / _import) -----------------------------------
+    def member_state_words(self) -> int:
+        return int(lib.fqlpop_member_state_words(self._h))
+
+    def export_member(self, member: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Slot `member`'s whole training state as one float32 device tensor (a bit container: the header words are
+        integers), ready for torch.distributed.send / recv. Stream-ordered on the current stream."""
+        n = self.member_state_words()
+        if out is None:
+            out = torch.empty(n, dtype=torch.float32, device=self.device)
+        assert out.is_cuda and out.dtype == torch.float32 and out.numel() == n and out.is_contiguous()
+        check(lib.fqlpop_member_export(self._h, int(member), out.data_ptr(),
+                                       torch.cuda.current_stream(self.device).cuda_stream), "fqlpop_member_export")
+        return out
+
+    def import_member(self, member: int, blob: torch.Tensor):
+        """Overwrites slot `member` with a state exported by a population of the same network shapes (alpha, seed, Adam
+        step and Philox position travel with it)."""
+        assert blob.is_cuda and blob.dtype == torch.float32 and blob.is_contiguous()
+        assert blob.numel() == self.member_state_words(), "blob of another population shape"
+        check(lib.fqlpop_member_import(self._h, int(member), blob.data_ptr(),
+                                       torch.cuda.current_stream(self.device).cuda_stream), "fqlpop_member_import")
+        head = blob[:4].view(torch.int32).cpu().numpy().view(np.uint32)
+        self.alphas[member] = head[1:2].view(np.float32)[0]
+        self.seeds[member] = np.uint64(head[2]) | (np.uint64(head[3]) << np.uint64(32))
 
 
 def philox_fill(seed: int, step: int, rows: int, slots: int, kind: int, n: int = 0) -> np.ndarray:

@@ -43,7 +43,11 @@ class Experiment:
             self.experiment_name = f"{name}_{datetime.now().strftime('%Y%m%d_%H%M%S')}"
             self.current_step = 0
         else:
-            self.agent = from_state_dict(self.agent, state_dict["agent"])
+            # "agent": None = the member's device state is already in its slot (Trainer._migrate moved it GPU to GPU)
+            if state_dict.get("agent") is not None:
+                self.agent = from_state_dict(self.agent, state_dict["agent"])
+            if "agent_rng" in state_dict:
+                self.agent.rng = state_dict["agent_rng"].copy()
             self.experiment_name = state_dict["experiment_name"]
             self.current_step = state_dict["current_step"]
         self.logger = Logger(trainer_config.save_directory, trainer_config.env_name, self.experiment_name, agent_config,

@@ -92,6 +92,17 @@ int fqlpop_refresh_shadow(void* handle, void* stream);
 /* Adam step counts [population] and the per-member step counters [population] (position of each member's Philox
  * stream: batch indices and noise of its next update); set != 0 writes. NULL skips an array.                   */
 int fqlpop_counters(void* handle, int32_t* adam_steps, uint64_t* step_counter, int32_t set);
+/* Survivor migration (the reference is single-process and has no counterpart: after a successive-halving
+ * rung, /root/reference/hpo/successive_halving.py:64-100, the members that go on may sit on a few GPUs only).
+ * A member's whole training state -- parameters, Adam moments, target critic, Adam step count, alpha, seed and the
+ * position of its Philox stream -- as ONE device buffer of fqlpop_member_state_words() 32-bit words, so that the host
+ * side moves it with one NCCL send / recv (or cudaMemcpyPeer). export reads slot `member`; import overwrites slot
+ * `member` of a population with the same network shapes (checked: a foreign blob fails and writes nothing) and
+ * rebuilds its bf16 GEMM copies. Both are stream-ordered on `stream`; a member continues on the importing GPU with
+ * exactly the batches and noise it would have drawn where it was.                                          */
+int64_t fqlpop_member_state_words(void* handle);
+int fqlpop_member_export(void* handle, int32_t member, float* blob_dev, void* stream);
+int fqlpop_member_import(void* handle, int32_t member, const float* blob_dev, void* stream);
 /* Rewards / masks [population][batch] (host) of the batch the last step gathered: lets a test recover the row
  * indices the on-device uniform gather drew (Dataset.sample, task/offline_task_simulated.py:53-58).         */
 int fqlpop_last_batch(void* handle, float* rewards_host, float* masks_host);

@@ -53,6 +53,12 @@ def main(out_dir, n_alphas=8):
     sh = SuccessiveHalving(set(pop), total_evaluations=3, fraction=0.5, history_length=1)
     tr = Trainer(task, sh, cfg)
     assert tr.world == world and tr.rank == rank
+    if world == 2:
+        # survivor migration over NCCL, exercised whatever the scores turn out to be: ship one of rank 0's members to
+        # rank 1 before training starts (3 / 5); the first rebalancing after a rung sends members the other way
+        first = next(c for c in tr._ordered(tr._order) if tr._owner[c] == 0)
+        tr._migrate([(first, 0, 1)])
+        assert tr._owner[first] == 1 and (first in tr.experiments) == (rank == 1)
     t0 = time.perf_counter()
     tr.train(max_evaluations=1000)
     torch.cuda.synchronize()
@@ -61,7 +67,8 @@ def main(out_dir, n_alphas=8):
            "local_members": len(tr.experiments), "candidates": sorted(c.alpha for c in tr.candidates),
            "scores": {repr(c.alpha): [float(x) for x in v] for c, v in sh.candidate_scores.items()},
            "steps": {repr(c.alpha): e.current_step for c, e in tr.experiments.items()}, "seconds": dt,
-           "backend": (torch.distributed.get_backend() if world > 1 else None)}
+           "backend": (torch.distributed.get_backend() if world > 1 else None),
+           "migrations": tr.migrations, "migration_seconds": tr.migration_seconds}
     with open(os.path.join(out_dir, f"w{world}r{rank}.json"), "w") as f:
         json.dump(out, f)
     if tr.population is not None:

@@ -23,20 +23,38 @@ def main(rank, world, port, out_dir, mode="plain"):
     from trainer.trainer import Trainer
     cfg = TrainerConfig(steps=40, eval_interval=10, log_interval=5, save_directory=Path(out_dir) / f"rank{rank}",
                         env_name="cube-test", agent=AgentConfig(batch_size=8))
-    pop = [ExperimentConfig(seed=i, alpha=a) for i, a in enumerate(np.logspace(np.log10(3), 3, 8).tolist())]
+    alphas = np.logspace(np.log10(3), 3, 8).tolist()
+    migrate = mode.startswith("migrate")
+    if mode in ("static", "migrate", "migrate_resume"):
+        # FakeTask ranks by |log10(alpha) - 2|: make the best four all start on rank 0 and the rest on rank 1. Placement
+        # follows the iteration order of the strategy's candidate SET, so pick alphas whose set order does that
+        # (hashes of float / int dataclasses are the same in every process).
+        import itertools
+        good = (100.0, 90.0, 120.0, 70.0)
+        for alphas in itertools.permutations(good + (3.0, 5.0, 7.0, 1000.0)):
+            order = list({ExperimentConfig(seed=i, alpha=a) for i, a in enumerate(alphas)})
+            if all((c.alpha in good) == (i % 2 == 0) for i, c in enumerate(order)):
+                break
+        else:
+            raise AssertionError("no ordering puts the best four on rank 0")
+    pop = [ExperimentConfig(seed=i, alpha=a) for i, a in enumerate(alphas)]
     sh = SuccessiveHalving(set(pop), total_evaluations=4, fraction=0.5, history_length=1)
-    tr = Trainer(FakeTask(), sh, cfg, population_factory=FakePopulation)
-    if mode == "resume":
+    tr = Trainer(FakeTask(), sh, cfg, population_factory=FakePopulation, rebalance=migrate)
+    if mode.endswith("resume"):
         # stop after the first sweep + half of the second, write this rank's shard, rebuild everything from it
         import pickle
         tr.train(max_evaluations=10)
         shard = pickle.loads(pickle.dumps({"trainer": tr.state_dict(), "strategy": tr.strategy.state_dict()}))
         sh = SuccessiveHalving(set(pop), total_evaluations=4, fraction=0.5, history_length=1, state_dict=shard["strategy"])
-        tr = Trainer(FakeTask(), sh, cfg, state_dict=shard["trainer"], population_factory=FakePopulation)
+        tr = Trainer(FakeTask(), sh, cfg, state_dict=shard["trainer"], population_factory=FakePopulation,
+                     rebalance=migrate)
     tr.train(max_evaluations=100)
     out = {"rank": rank, "local_members": len(tr.experiments), "candidates": sorted(c.alpha for c in tr.candidates),
            "scores": {str(c.alpha): v for c, v in sh.candidate_scores.items()},
-           "steps": {str(c.alpha): e.current_step for c, e in tr.experiments.items()}}
+           "steps": {str(c.alpha): e.current_step for c, e in tr.experiments.items()},
+           "migrations": tr.migrations, "owner": {str(c.alpha): r for c, r in tr._owner.items()},
+           "imports": [c for c in (tr.population.calls if tr.population else []) if c[0] == "import"],
+           "device_steps": {str(c.alpha): int(tr.population.steps_done[tr._slot[c]]) for c in tr.experiments}}
     with open(os.path.join(out_dir, f"rank{rank}.json"), "w") as f:
         json.dump(out, f)
     dist.destroy_process_group()

@@ -62,6 +62,25 @@ class FakePopulation:
     def set_counters(self, adam_steps=None, step_counter=None):
         pass
 
+    # survivor migration: the fake member state is (steps trained, alpha, seed)
+    def member_state_words(self):
+        return 4
+
+    def export_member(self, member, out=None):
+        import torch
+        blob = torch.tensor([float(self.steps_done[member]), float(self.alphas[member]), float(self.seeds[member]), 7.0])
+        if out is not None:
+            out.copy_(blob)
+            return out
+        return blob
+
+    def import_member(self, member, blob):
+        assert blob.numel() == 4 and float(blob[3]) == 7.0
+        self.steps_done[member] = int(blob[0])
+        self.alphas[member] = float(blob[1])
+        self.seeds[member] = int(blob[2])
+        self.calls.append(("import", member))
+
     def close(self):
         pass
 

@@ -45,3 +45,33 @@ def test_two_rank_trainer_agrees_on_pruning(tmp_path):
     # same decisions as the single-process run
     best = sorted((float(a) for a in trained), key=lambda a: abs(__import__("math").log10(a) - 2))[:2]
     assert sorted(best) == r0["candidates"]
+
+
+def test_two_rank_survivor_migration_changes_placement_not_results(tmp_path):
+    """The four best candidates all start on rank 0. Without migration rank 1 idles from the second rung on; with it the
+    survivors are spread again (two per rank, then one per rank), every member keeps training from the state it had --
+    the device step counts travel with it -- and scores, survivors and step totals equal the static run's."""
+    (tmp_path / "s").mkdir(); (tmp_path / "m").mkdir(); (tmp_path / "r").mkdir()
+    static = _run_two_ranks(tmp_path / "s", "static")
+    moved = _run_two_ranks(tmp_path / "m", "migrate")
+    assert static[0]["migrations"] == 0 and moved[0]["migrations"] == moved[1]["migrations"] >= 2
+    assert sorted(static[0]["steps"]) == sorted(["100.0", "90.0", "120.0", "70.0"])     # the premise: all on rank 0
+    assert moved[0]["owner"] == moved[1]["owner"]                                        # replicated bookkeeping
+    assert moved[1]["imports"] and not static[1]["imports"]
+    for run in (static, moved):
+        assert run[0]["candidates"] == run[1]["candidates"] and run[0]["scores"] == run[1]["scores"]
+        assert not set(run[0]["steps"]) & set(run[1]["steps"])                           # one home per member
+    assert moved[0]["candidates"] == static[0]["candidates"]
+    assert moved[0]["scores"] == static[0]["scores"]
+    assert {**moved[0]["steps"], **moved[1]["steps"]} == {**static[0]["steps"], **static[1]["steps"]}
+    # the migrants' device state came along: what the population holds equals what the host believes
+    for r in moved:
+        assert r["device_steps"] == r["steps"]
+    # survivors end up one per rank
+    final = [a for a in moved[0]["candidates"]]
+    assert len(final) == 2 and {moved[0]["owner"][str(a)] for a in final} == {0, 1}
+    # save-then-resume across a migration ends where the uninterrupted run does
+    resumed = _run_two_ranks(tmp_path / "r", "migrate_resume")
+    for m, r in zip(moved, resumed):
+        assert m["candidates"] == r["candidates"] and m["steps"] == r["steps"] and m["scores"] == r["scores"]
+        assert m["owner"] == r["owner"] and r["device_steps"] == r["steps"]

@@ -1,6 +1,6 @@
 """BASELINE config 4 in miniature on real GPUs: successive halving over a live population sharded over 2 ranks
-(torchrun, one process per GPU), evaluation scores all-gathered over NCCL, identical pruning on every rank and equal to
-the single-process run. Needs >= 2 GPUs (skipped otherwise)."""
+(torchrun, one process per GPU), evaluation scores all-gathered over NCCL, members migrated between the GPUs (one NCCL
+send / recv of the member's state each), identical pruning on every rank and equal to the single-process run. Needs >= 2 GPUs (skipped otherwise)."""
 import json
 import os
 import socket
@@ -33,7 +33,10 @@ def test_two_gpu_successive_halving_matches_single_process(tmp_path):
     s = json.load(open(tmp_path / "w1r0.json"))
     r0, r1 = (json.load(open(tmp_path / f"w2r{r}.json")) for r in range(2))
     assert r0["backend"] == "nccl" and {r0["device"], r1["device"]} == {0, 1}
-    assert r0["local_members"] == 4 and r1["local_members"] == 4 and s["local_members"] == 8   # member i -> rank i mod 2
+    # member i starts on rank i mod 2; the worker then ships one member 0 -> 1 over NCCL before training, and the
+    # Trainer's rebalancing may move more after each rung: wherever they live, all 8 are somewhere, once
+    assert r0["local_members"] + r1["local_members"] == 8 and s["local_members"] == 8
+    assert r0["migrations"] == r1["migrations"] >= 1 and s["migrations"] == 0
     assert not set(r0["steps"]) & set(r1["steps"])                                             # nobody trained twice
     assert r0["candidates"] == r1["candidates"]                                                # same decision everywhere
     assert r0["scores"] == r1["scores"] and len(r0["scores"]) == 8                             # every rank saw every score
