@@ -420,3 +420,62 @@ extern "C" int fqlpop_decoder_sample(void* h, int32_t n, const float* noise, uin
   if (fqlpop::wm_decoder_sample_impl((fqlpop::WmDecoder*)h, n, noise, seed, out, (cudaStream_t)stream, &err)) return fail(err);
   return 0;
 }
+
+// initial-observation VAE training (wm_vae.cuh)
+static fqlpop::VaeConfig vae_cfg(const fqlpop_vae_config_t* c) {
+  fqlpop::VaeConfig v{};
+  v.O = c->ob_dim; v.L = c->latent_dim; v.batch = c->batch;
+  v.n_hidden = c->n_hidden;   // (range-checked by the callers below)
+  for (int i = 0; i < v.n_hidden && i < fqlpop::kWmMaxLayers; ++i) v.hidden[i] = c->hidden[i];
+  v.decay_steps = c->decay_steps; v.lr = c->lr; v.reconstruction_weight = c->reconstruction_weight; v.seed = c->seed;
+  return v;
+}
+extern "C" int64_t fqlpop_vae_num_params(const fqlpop_vae_config_t* c) {
+  if (!c || c->n_hidden < 1 || c->n_hidden >= fqlpop::kWmMaxLayers || c->ob_dim < 1 || c->latent_dim < 1) return -1;
+  return fqlpop::vae_num_params(vae_cfg(c));
+}
+extern "C" int fqlpop_vae_create(const fqlpop_vae_config_t* c, const float* params_host, void** out) {
+  if (!c || !out) return fail("null argument");
+  if (c->n_hidden < 1 || c->n_hidden >= fqlpop::kWmMaxLayers) return fail("VAE: between 1 and 7 hidden layers");
+  fqlpop::WmVae* t = nullptr;
+  std::string err;
+  if (fqlpop::vae_create_impl(vae_cfg(c), params_host, &t, &err)) return fail(err);
+  *out = t;
+  return 0;
+}
+extern "C" int fqlpop_vae_destroy(void* h) {
+  fqlpop::vae_destroy_impl((fqlpop::WmVae*)h);
+  return 0;
+}
+#define VAE(h)                                \
+  fqlpop::WmVae* T = (fqlpop::WmVae*)(h);     \
+  if (!T) return fail("null VAE handle");     \
+  std::string err
+extern "C" int fqlpop_vae_step(void* h, int32_t train, const float* obs, const float* eps, void* stream) {
+  VAE(h);
+  if (fqlpop::vae_step_impl(T, train, obs, eps, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_vae_set_dataset(void* h, const float* obs, int64_t n_rows) {
+  VAE(h);
+  if (fqlpop::vae_set_dataset_impl(T, obs, n_rows, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_vae_train(void* h, int32_t n_steps, void* stream) {
+  VAE(h);
+  if (fqlpop::vae_train_impl(T, n_steps, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_vae_logs(void* h, float* out_host, void* stream) {
+  VAE(h);
+  if (!out_host) return fail("null output");
+  if (fqlpop::vae_logs_impl(T, out_host, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int fqlpop_vae_export(void* h, int32_t which, float* out_host, int64_t n, void* stream) {
+  VAE(h);
+  if (!out_host) return fail("null output");
+  if (fqlpop::vae_export_impl(T, which, out_host, n, (cudaStream_t)stream, &err)) return fail(err);
+  return 0;
+}
+extern "C" int64_t fqlpop_vae_launches(void* h) { return h ? fqlpop::vae_launches((fqlpop::WmVae*)h) : 0; }

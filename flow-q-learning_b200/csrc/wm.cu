@@ -1106,4 +1106,6 @@ int wm_decoder_sample_impl(WmDecoder* d, int n, const float* noise, unsigned lon
   return 0;
 }
 
+#include "wm_vae.cuh"
+
 }  // namespace fqlpop

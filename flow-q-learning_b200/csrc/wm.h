@@ -39,6 +39,7 @@ enum WmLog : int {
   WL_F1 = 9,
   WL_LR = 10,               // learning rate the last train step used
   WL_STEP = 11,             // optimiser steps taken (as float)
+  WL_KL = 12,               // VAE: KL term (WL_RECON_LOSS holds its reconstruction loss)
 };
 
 struct WmNet {
@@ -92,5 +93,27 @@ void wm_decoder_destroy_impl(WmDecoder* d);
 int wm_decoder_sample_impl(WmDecoder* d, int n, const float* noise, unsigned long long seed, float* out,
                            cudaStream_t stream, std::string* err);
 long long wm_launches(const WmTrainer* t);
+
+// Training of the initial-observation VAE (/root/reference/envmodel/initial_observation.py:9-78; wm_vae.cuh).
+// Flat parameter vector: encoder hidden layers, ONE head layer of 2 * L columns (mean | logvar), then the decoder
+// (hidden dims reversed).
+struct VaeConfig {
+  int O, L, batch;
+  int n_hidden, hidden[kWmMaxLayers];   // encoder order, as the reference's config stores them
+  int decay_steps;
+  float lr, reconstruction_weight;
+  unsigned long long seed;              // Philox stream of the resident-dataset sampler and of the latent noise
+};
+struct WmVae;
+long long vae_num_params(const VaeConfig& c);
+int vae_create_impl(const VaeConfig& c, const float* params_host, WmVae** out, std::string* err);
+void vae_destroy_impl(WmVae* t);
+// explicit device batch obs[batch][O]; eps[batch][L] (dev) or nullptr -> Philox normal
+int vae_step_impl(WmVae* t, int train, const float* obs, const float* eps, cudaStream_t stream, std::string* err);
+int vae_set_dataset_impl(WmVae* t, const float* obs, long long n_rows, std::string* err);
+int vae_train_impl(WmVae* t, int n_steps, cudaStream_t stream, std::string* err);
+int vae_logs_impl(WmVae* t, float* out_host, cudaStream_t stream, std::string* err);
+int vae_export_impl(WmVae* t, int which, float* out_host, long long n, cudaStream_t stream, std::string* err);
+long long vae_launches(const WmVae* t);
 
 }  // namespace fqlpop

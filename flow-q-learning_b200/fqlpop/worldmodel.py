@@ -294,3 +294,190 @@ class Decoder:
             self.close()
         except Exception:
             pass
+
+
+# ---- initial-observation VAE training (include/fqlpop.h: fqlpop_vae_*) ------------------------------------------------
+class VaeConfig(ctypes.Structure):
+    _fields_ = [("ob_dim", ctypes.c_int32), ("latent_dim", ctypes.c_int32), ("batch", ctypes.c_int32),
+                ("n_hidden", ctypes.c_int32), ("hidden", ctypes.c_int32 * 8), ("decay_steps", ctypes.c_int32),
+                ("lr", ctypes.c_float), ("reconstruction_weight", ctypes.c_float), ("seed", ctypes.c_uint64)]
+
+
+lib.fqlpop_vae_num_params.argtypes = [ctypes.POINTER(VaeConfig)]
+lib.fqlpop_vae_num_params.restype = ctypes.c_int64
+lib.fqlpop_vae_create.argtypes = [ctypes.POINTER(VaeConfig), ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+lib.fqlpop_vae_destroy.argtypes = [ctypes.c_void_p]
+lib.fqlpop_vae_step.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+lib.fqlpop_vae_set_dataset.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]
+lib.fqlpop_vae_train.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p]
+lib.fqlpop_vae_logs.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+lib.fqlpop_vae_export.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
+lib.fqlpop_vae_launches.argtypes = [ctypes.c_void_p]
+lib.fqlpop_vae_launches.restype = ctypes.c_int64
+
+_VAE_LOGS = {"reconstruction_loss": 5, "kl": 12, "loss": 0}   # the keys of vae_loss's logs (initial_observation.py:71-75)
+
+
+def vae_dims(ob_dim: int, latent_dim: int, hidden: Sequence[int]):
+    hidden = [int(h) for h in hidden]
+    return [ob_dim, *hidden, 2 * latent_dim], [latent_dim, *hidden[::-1], ob_dim]
+
+
+def _dense_tree(rng, dims):
+    tree = {}
+    for i in range(len(dims) - 1):
+        z = rng.standard_normal(dims[i] * dims[i + 1])
+        while True:  # LeCun normal truncated at two standard deviations (flax's nn.Dense default), by resampling
+            bad = np.abs(z) > 2.0
+            if not bad.any():
+                break
+            z[bad] = rng.standard_normal(int(bad.sum()))
+        std = np.sqrt(1.0 / dims[i]) / 0.87962566103423978
+        tree[f"Dense_{i}"] = {"kernel": (z * std).astype(np.float32).reshape(dims[i], dims[i + 1]),
+                              "bias": np.zeros(dims[i + 1], np.float32)}
+    return tree
+
+
+def init_vae_params(seed: int, ob_dim: int, latent_dim: int, hidden: Sequence[int]) -> Dict:
+    """{"encoder": Dense_0 .. Dense_{h-1}, Dense_h (mean), Dense_{h+1} (logvar); "decoder": Dense_0 .. Dense_h} with flax's
+    defaults for nn.Dense (envmodel/initial_observation.py:15-18, 27-29). numpy's random stream, not JAX's."""
+    rng = np.random.default_rng(seed)
+    enc_dims, dec_dims = vae_dims(ob_dim, latent_dim, hidden)
+    h = len(hidden)
+    enc = _dense_tree(rng, enc_dims[:-1] + [latent_dim])                        # hidden layers + the mean head
+    enc[f"Dense_{h + 1}"] = _dense_tree(rng, [enc_dims[-2], latent_dim])["Dense_0"]   # the logvar head
+    return {"encoder": enc, "decoder": _dense_tree(rng, dec_dims)}
+
+
+def flatten_vae_params(tree: Dict, n_hidden: int) -> np.ndarray:
+    """flax tree -> the flat vector of include/fqlpop.h: the mean and logvar heads become ONE layer of 2 L columns."""
+    enc, dec, parts = tree["encoder"], tree["decoder"], []
+    for i in range(n_hidden):
+        parts += [_np32(enc[f"Dense_{i}"]["kernel"]).ravel(), _np32(enc[f"Dense_{i}"]["bias"]).ravel()]
+    mean, logvar = enc[f"Dense_{n_hidden}"], enc[f"Dense_{n_hidden + 1}"]
+    parts += [np.concatenate([_np32(mean["kernel"]), _np32(logvar["kernel"])], axis=1).ravel(),
+              np.concatenate([_np32(mean["bias"]), _np32(logvar["bias"])])]
+    for i in range(n_hidden + 1):
+        parts += [_np32(dec[f"Dense_{i}"]["kernel"]).ravel(), _np32(dec[f"Dense_{i}"]["bias"]).ravel()]
+    return np.ascontiguousarray(np.concatenate(parts))
+
+
+def unflatten_vae_params(flat: np.ndarray, ob_dim: int, latent_dim: int, hidden: Sequence[int]) -> Dict:
+    enc_dims, dec_dims = vae_dims(ob_dim, latent_dim, hidden)
+    off = 0
+
+    def take(*shape):
+        nonlocal off
+        n = int(np.prod(shape))
+        out = flat[off:off + n].reshape(shape).copy()
+        off += n
+        return out
+
+    h, L = len(hidden), latent_dim
+    enc = {}
+    for i in range(h):
+        enc[f"Dense_{i}"] = {"kernel": take(enc_dims[i], enc_dims[i + 1]), "bias": take(enc_dims[i + 1])}
+    k, b = take(enc_dims[h], 2 * L), take(2 * L)
+    enc[f"Dense_{h}"] = {"kernel": np.ascontiguousarray(k[:, :L]), "bias": b[:L].copy()}
+    enc[f"Dense_{h + 1}"] = {"kernel": np.ascontiguousarray(k[:, L:]), "bias": b[L:].copy()}
+    dec = {f"Dense_{i}": {"kernel": take(dec_dims[i], dec_dims[i + 1]), "bias": take(dec_dims[i + 1])}
+           for i in range(h + 1)}
+    assert off == flat.size
+    return {"encoder": enc, "decoder": dec}
+
+
+class VaeTrainer:
+    """Device-resident trainer of the initial-observation VAE (envmodel/initial_observation.py:32-78). `step` takes an
+    explicit batch (and, for parity tests, the reparameterisation noise); `set_dataset` + `train(n)` keep the observations
+    in HBM and sample batches and noise on the device."""
+
+    def __init__(self, ob_dim: int, latent_dim: int, hidden_dims: Sequence[int], batch_size: int, steps: int,
+                 init_learning_rate: float = 1e-3, reconstruction_weight: float = 1.0, params: Optional[Dict] = None,
+                 seed: int = 0, device=None):
+        self.device = torch.device(device) if device is not None else default_device()
+        self.ob_dim, self.latent_dim = int(ob_dim), int(latent_dim)
+        self.hidden_dims, self.batch_size = tuple(int(h) for h in hidden_dims), int(batch_size)
+        c = VaeConfig()
+        c.ob_dim, c.latent_dim, c.batch, c.n_hidden = self.ob_dim, self.latent_dim, self.batch_size, len(self.hidden_dims)
+        if not 1 <= c.n_hidden <= 7:
+            raise ValueError("the VAE needs between 1 and 7 hidden layers")
+        for i, h in enumerate(self.hidden_dims):
+            c.hidden[i] = h
+        c.decay_steps, c.lr, c.reconstruction_weight, c.seed = int(steps), init_learning_rate, reconstruction_weight, seed
+        self._cfg = c
+        self.n_params = int(lib.fqlpop_vae_num_params(ctypes.byref(c)))
+        if params is None:
+            params = init_vae_params(seed, self.ob_dim, self.latent_dim, self.hidden_dims)
+        flat = flatten_vae_params(params, len(self.hidden_dims))
+        if flat.size != self.n_params:
+            raise ValueError(f"parameter tree has {flat.size} values, the VAE needs {self.n_params}")
+        self._h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            check(lib.fqlpop_vae_create(ctypes.byref(c), flat.ctypes.data, ctypes.byref(self._h)), "fqlpop_vae_create")
+        self._keep = {}
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.fqlpop_vae_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _dev(self, x):
+        return torch.as_tensor(np.array(x, dtype=np.float32) if not torch.is_tensor(x) else x,
+                               dtype=torch.float32).to(self.device).contiguous()
+
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def logs(self) -> np.ndarray:
+        out = np.zeros(LOG_SLOTS, np.float32)
+        check(lib.fqlpop_vae_logs(self._h, out.ctypes.data, self._stream()), "fqlpop_vae_logs")
+        return out
+
+    def named_logs(self) -> Dict[str, float]:
+        raw = self.logs()
+        return {k: float(raw[i]) for k, i in _VAE_LOGS.items()}
+
+    def step(self, observations, eps=None, train: bool = True) -> Dict[str, float]:
+        with torch.cuda.device(self.device):
+            o = self._dev(observations)
+            if tuple(o.shape) != (self.batch_size, self.ob_dim):
+                raise ValueError(f"batch must be [{self.batch_size}, {self.ob_dim}], got {tuple(o.shape)}")
+            e = self._dev(eps) if eps is not None else None
+            if e is not None and tuple(e.shape) != (self.batch_size, self.latent_dim):
+                raise ValueError(f"eps must be [{self.batch_size}, {self.latent_dim}]")
+            self._keep["step"] = (o, e)   # the captured graph holds these pointers until the call has run
+            check(lib.fqlpop_vae_step(self._h, 1 if train else 0, o.data_ptr(), e.data_ptr() if e is not None else None,
+                                      self._stream()), "fqlpop_vae_step")
+            return self.named_logs()
+
+    def set_dataset(self, observations):
+        with torch.cuda.device(self.device):
+            self._keep["ds"] = self._dev(observations)
+            check(lib.fqlpop_vae_set_dataset(self._h, self._keep["ds"].data_ptr(), self._keep["ds"].shape[0]),
+                  "fqlpop_vae_set_dataset")
+
+    def train(self, n_steps: int):
+        """n_steps optimiser steps on batches (and latent noise) drawn on the device (asynchronous)."""
+        with torch.cuda.device(self.device):
+            check(lib.fqlpop_vae_train(self._h, int(n_steps), self._stream()), "fqlpop_vae_train")
+
+    def export(self, which: int = 0) -> np.ndarray:
+        out = np.zeros(self.n_params, np.float32)
+        check(lib.fqlpop_vae_export(self._h, which, out.ctypes.data, self.n_params, self._stream()), "fqlpop_vae_export")
+        return out
+
+    def params(self) -> Dict:
+        return unflatten_vae_params(self.export(0), self.ob_dim, self.latent_dim, self.hidden_dims)
+
+    def grads(self) -> Dict:
+        return unflatten_vae_params(self.export(3), self.ob_dim, self.latent_dim, self.hidden_dims)
+
+    @property
+    def launches(self) -> int:
+        return int(lib.fqlpop_vae_launches(self._h))

@@ -1,6 +1,10 @@
 """World-model training entry point: same command line, model selection, loss wiring and output files as the reference's
 /root/reference/train_env_model.py:20-130 (`--model baseline | multistep | termination_predictor`), with the trainers
-running on the device (envmodel/*_trainer.py -> libfqlpop.so). Differences: datasets come from
+running on the device (envmodel/*_trainer.py -> libfqlpop.so). One model more than the reference wires:
+`--model initial_observation` trains the VAE of envmodel/initial_observation.py on the episode-start observations
+(InitialObservationLoader) with the flags the reference's parser already has for it (--model.latent_dim,
+--reconstruction_weight) and leaves initial_observation.pt / _config.yaml where distribution_visualizer.py:61-94 reads
+them. Differences: datasets come from
 fql.envs.env_utils.make_env_and_datasets (ogbench files if present in --data_directory, synthetic otherwise; ogbench itself
 is not installed here), and wandb is optional (`--use_wandb`)."""
 from dataclasses import asdict
@@ -8,12 +12,13 @@ from functools import partial
 
 from argparser import build_env_model_config_from_args, get_env_model_argparser
 from envmodel.baseline import BaselineStatePredictor, TerminationPredictor
+from envmodel.initial_observation import InitialObservationEnvModel, InitialObservationTrainer, vae_loss
 from envmodel.loss import focal_loss, state_prediction_loss
 from envmodel.multistep import MultistepStatePredictor
 from envmodel.state_predictor_trainer import StatePredictorTrainer
 from envmodel.termination_predictor_trainer import TerminationPredictorTrainer
 from fql.envs.env_utils import make_env_and_datasets
-from utils.data_loader import MultistepLoader, StepLoader
+from utils.data_loader import InitialObservationLoader, MultistepLoader, StepLoader
 from utils.envmodel import save_model
 
 
@@ -48,13 +53,20 @@ def main(argv=None):
         sample = train_loader.sample(config.batch_size)
         model = TerminationPredictor(sample["observations"].shape[-1], tuple(config.model_config["hidden_dims"]))
         loss_fn = focal_loss
+    elif config.model == "initial_observation":
+        train_loader, val_loader = InitialObservationLoader(train_dataset), InitialObservationLoader(val_dataset)
+        sample = train_loader.sample(config.batch_size)
+        model = InitialObservationEnvModel(sample["observations"].shape[-1], int(config.model_config["latent_dim"]),
+                                           tuple(config.model_config["hidden_dims"]))
+        loss_fn = partial(vae_loss, reconstruction_weight=config.reconstruction_weight)
     else:
         raise ValueError(f"Unknown model type: {config.model}")
     logger = None
     if use_wandb:
         import wandb
         logger = wandb.init(name=f"{config.env_name}_{config.model}", project="fql_env_model", config=asdict(config), dir="exp/")
-    cls = TerminationPredictorTrainer if config.model == "termination_predictor" else StatePredictorTrainer
+    cls = {"termination_predictor": TerminationPredictorTrainer,
+           "initial_observation": InitialObservationTrainer}.get(config.model, StatePredictorTrainer)
     trainer = cls(model=model, train_loader=train_loader, val_loader=val_loader, loss_fn=loss_fn, config=config,
                   logger=logger, device_sampling=device_sampling)
     trainer.train()

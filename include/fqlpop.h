@@ -248,6 +248,40 @@ int fqlpop_decoder_destroy(void* decoder);
 /* out[n][out_dim] (dev) = decoder(z); z = noise[n][latent_dim] (dev) or Philox normal(seed, 0, row, col) when NULL. */
 int fqlpop_decoder_sample(void* decoder, int32_t n, const float* noise, uint64_t seed, float* out, void* stream);
 
+/* Training of that VAE: InitialObservationEnvModel.__call__ + vae_loss (envmodel/initial_observation.py:32-78) --
+ *   mu, logvar = encoder(obs); z = mu + eps * exp(logvar / 2); recon = decoder(z);
+ *   loss = (reconstruction_weight * mean((obs - recon)^2) + kl) / (reconstruction_weight + 1),
+ *   kl = -0.5 * mean(1 + logvar - mu^2 - exp(logvar))
+ * -- with backward pass and optimiser on the device. The reference ships the model and the loss but no trainer for it
+ * (train_env_model.py does not know the model): the optimiser is the one of its other world-model trainers,
+ * optax.adam over optax.cosine_decay_schedule(lr, decay_steps) (envmodel/state_predictor_trainer.py:57-61).
+ * Flat parameter vector (params_host, fqlpop_vae_export), fp32, kernel [in][out] then bias per Dense layer: encoder
+ * hidden layers, ONE head layer of 2 * latent_dim columns (columns [0, L) = the reference's mean head Dense_h, columns
+ * [L, 2L) = its logvar head Dense_{h+1}), then the decoder (hidden dims reversed, output ob_dim), which is exactly the
+ * vector fqlpop_decoder_create takes.                                                                              */
+typedef struct {
+  int32_t ob_dim, latent_dim, batch;
+  int32_t n_hidden, hidden[8];          /* encoder order, as initial_observation_config.yaml stores hidden_dims */
+  int32_t decay_steps;
+  float lr, reconstruction_weight;
+  uint64_t seed;                        /* Philox stream of the resident-dataset sampler and of the latent noise */
+} fqlpop_vae_config_t;
+int64_t fqlpop_vae_num_params(const fqlpop_vae_config_t* cfg);
+int fqlpop_vae_create(const fqlpop_vae_config_t* cfg, const float* params_host, void** out_handle);
+int fqlpop_vae_destroy(void* vae);
+/* One optimiser step (train != 0) or a forward-only evaluation on obs[batch][ob_dim] (dev). eps[batch][latent_dim]
+ * (dev) is the reparameterisation noise; NULL draws it from Philox normal(seed, step, row, 1 + column).          */
+int fqlpop_vae_step(void* vae, int32_t train, const float* obs, const float* eps, void* stream);
+/* Resident observations (borrowed device pointer, n_rows rows) + n_steps optimiser steps, each on `batch` rows drawn
+ * uniformly with replacement (Philox(seed, step, row, 0)).                                                       */
+int fqlpop_vae_set_dataset(void* vae, const float* obs, int64_t n_rows);
+int fqlpop_vae_train(void* vae, int32_t n_steps, void* stream);
+/* out_host[16]: 0 loss, 5 reconstruction_loss, 12 kl, 10 learning rate of the last step, 11 steps taken.         */
+int fqlpop_vae_logs(void* vae, float* out_host, void* stream);
+/* which: 0 parameters, 1 Adam m, 2 Adam v, 3 gradients of the last training step; n = fqlpop_vae_num_params.     */
+int fqlpop_vae_export(void* vae, int32_t which, float* out_host, int64_t n, void* stream);
+int64_t fqlpop_vae_launches(void* vae);
+
 #ifdef __cplusplus
 }
 #endif

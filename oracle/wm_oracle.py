@@ -7,6 +7,7 @@ What it restates (every function cites the reference lines it follows):
   * losses                     /root/reference/envmodel/loss.py:7-111
   * state-predictor step       /root/reference/envmodel/state_predictor_trainer.py:70-125
   * termination-predictor step /root/reference/envmodel/termination_predictor_trainer.py:58-126
+  * initial-observation VAE    /root/reference/envmodel/initial_observation.py:9-78 (model + vae_loss; no trainer there)
   * optimiser                  optax.adam(optax.cosine_decay_schedule(init_learning_rate, steps))
                                (state_predictor_trainer.py:57-61, termination_predictor_trainer.py:46-50);
                                optax is a third-party dependency absent here -- its published algorithm: Adam with
@@ -198,6 +199,53 @@ def multistep_step(params, opt, batch, term_params, *, lr0, decay_steps, true_te
                                        batch["observations"], true_termination_weight, termination_weight,
                                        reconstruction_weight)
     logs = {k: float(v.detach()) if torch.is_tensor(v) else float(v) for k, v in logs.items()}
+    if not train:
+        return params, logs, None
+    loss.backward()
+    g = _grads(p)
+    new = _detach(p)
+    logs["learning_rate"] = _adam(new, g, opt, lr0, decay_steps)
+    return new, logs, g
+
+
+# ---- initial-observation VAE (/root/reference/envmodel/initial_observation.py:9-78) ----------------------------------
+def vae_encoder_apply(p, x):
+    """Encoder.__call__ (initial_observation.py:13-18): [Dense, relu] per hidden dim, then the mean head (the next
+    Dense flax names) and the logvar head (the one after)."""
+    n = sum(1 for k in p if k.startswith("Dense_"))
+    for i in range(n - 2):
+        x = torch.relu(x @ p[f"Dense_{i}"]["kernel"] + p[f"Dense_{i}"]["bias"])
+    mean = x @ p[f"Dense_{n - 2}"]["kernel"] + p[f"Dense_{n - 2}"]["bias"]
+    logvar = x @ p[f"Dense_{n - 1}"]["kernel"] + p[f"Dense_{n - 1}"]["bias"]
+    return mean, logvar
+
+
+def vae_decoder_apply(p, z):
+    """Decoder.__call__ (initial_observation.py:25-29)."""
+    n = sum(1 for k in p if k.startswith("Dense_"))
+    for i in range(n - 1):
+        z = torch.relu(z @ p[f"Dense_{i}"]["kernel"] + p[f"Dense_{i}"]["bias"])
+    return z @ p[f"Dense_{n - 1}"]["kernel"] + p[f"Dense_{n - 1}"]["bias"]
+
+
+def vae_loss(params, observations, eps, reconstruction_weight):
+    """InitialObservationEnvModel.__call__ + vae_loss (initial_observation.py:41-78). `eps` is the reparameterisation
+    noise jax.random.normal(key, std.shape) of :43, an explicit argument here (JAX threefry bits cannot be reproduced)."""
+    mu, logvar = vae_encoder_apply(params["encoder"], observations)
+    z = mu + eps * torch.exp(0.5 * logvar)
+    recon = vae_decoder_apply(params["decoder"], z)
+    reconstruction_loss = torch.mean((observations - recon) ** 2)
+    kl = -0.5 * torch.mean(1 + logvar - mu ** 2 - torch.exp(logvar))
+    loss = (reconstruction_weight * reconstruction_loss + kl) / (reconstruction_weight + 1)
+    return loss, {"reconstruction_loss": reconstruction_loss, "kl": kl, "loss": loss}
+
+
+def vae_step(params, opt, observations, eps, *, reconstruction_weight, lr0, decay_steps, train=True):
+    """One optimiser step on vae_loss. The reference has no trainer for this model; the optimiser is the one of its other
+    world-model trainers (state_predictor_trainer.py:57-61). Returns (new params, logs, grads)."""
+    p = _with_grad(params) if train else params
+    loss, logs = vae_loss(p, observations, eps, reconstruction_weight)
+    logs = {k: float(v.detach()) for k, v in logs.items()}
     if not train:
         return params, logs, None
     loss.backward()

@@ -68,6 +68,19 @@ def test_argument_errors_come_back_as_status_and_message():
     c = WmConfig()
     c.n_hidden = 0
     assert lib.fqlpop_wm_num_params(ctypes.byref(c)) == -1
+    # VAE trainer: null handles, a configuration without hidden layers
+    from fqlpop.worldmodel import VaeConfig
+    lib.fqlpop_vae_step.argtypes = [vp, ctypes.c_int32, vp, vp, vp]
+    assert lib.fqlpop_vae_step(None, 1, None, None, None) != 0 and b"handle" in lib.fqlpop_last_error()
+    lib.fqlpop_vae_train.argtypes = [vp, ctypes.c_int32, vp]
+    assert lib.fqlpop_vae_train(None, 1, None) != 0
+    lib.fqlpop_vae_num_params.argtypes = [ctypes.POINTER(VaeConfig)]
+    lib.fqlpop_vae_num_params.restype = ctypes.c_int64
+    v = VaeConfig()
+    v.ob_dim, v.latent_dim, v.batch, v.n_hidden = 28, 4, 64, 0
+    assert lib.fqlpop_vae_num_params(ctypes.byref(v)) == -1
+    lib.fqlpop_vae_create.argtypes = [ctypes.POINTER(VaeConfig), vp, ctypes.POINTER(vp)]
+    assert lib.fqlpop_vae_create(ctypes.byref(v), None, ctypes.byref(out)) != 0 and b"hidden" in lib.fqlpop_last_error()
     c.kind, c.ob_dim, c.action_dim, c.n_hidden = 2, 42, 8, 3
     for i, h in enumerate((128, 256, 128)):
         c.hidden[i] = h

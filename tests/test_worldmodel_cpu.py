@@ -78,6 +78,58 @@ def test_flat_layout_round_trip_and_count():
     assert not tree["Dense_0"]["bias"].any() and (tree["LayerNorm_0"]["scale"] == 1).all()
 
 
+def test_vae_parameter_layout_and_oracle_loss():
+    """Flat VAE layout <-> flax tree (the mean and logvar heads share one device layer), the parameter count the library
+    reports, and the oracle's vae_loss against the closed forms of envmodel/initial_observation.py:66-71 on a case whose
+    answer is known: with every parameter zero, mu = logvar = 0, the reconstruction is 0, so kl = 0 and the
+    reconstruction loss is mean(obs^2)."""
+    import torch
+    from oracle import wm_oracle as wmo
+    from envmodel.initial_observation import InitialObservationEnvModel, vae_loss
+    from fqlpop._lib import lib
+    from fqlpop.worldmodel import VaeConfig, flatten_vae_params, init_vae_params, unflatten_vae_params, vae_dims
+    O, L, hidden = 28, 4, (128, 64)
+    tree = init_vae_params(0, O, L, hidden)
+    assert sorted(tree["encoder"]) == ["Dense_0", "Dense_1", "Dense_2", "Dense_3"]      # two hidden, mean, logvar
+    assert tree["encoder"]["Dense_2"]["kernel"].shape == (64, L) == tree["encoder"]["Dense_3"]["kernel"].shape
+    assert [tree["decoder"][f"Dense_{i}"]["kernel"].shape for i in range(3)] == [(L, 64), (64, 128), (128, O)]
+    assert vae_dims(O, L, hidden) == ([O, 128, 64, 2 * L], [L, 64, 128, O])
+    m = InitialObservationEnvModel(O, L, hidden)
+    assert m.encoder.hidden_dims == hidden and m.decoder.hidden_dims == hidden[::-1] and m.decoder.output_dimension == O
+    flat = flatten_vae_params(tree, len(hidden))
+    c = VaeConfig()
+    c.ob_dim, c.latent_dim, c.batch, c.n_hidden = O, L, 64, len(hidden)
+    for i, h in enumerate(hidden):
+        c.hidden[i] = h
+    lib.fqlpop_vae_num_params.argtypes = [ctypes.POINTER(VaeConfig)]
+    lib.fqlpop_vae_num_params.restype = ctypes.c_int64
+    assert lib.fqlpop_vae_num_params(ctypes.byref(c)) == flat.size
+    back = unflatten_vae_params(flat, O, L, hidden)
+    for part in tree:
+        for layer in tree[part]:
+            for leaf in tree[part][layer]:
+                assert np.array_equal(back[part][layer][leaf], tree[part][layer][leaf]), (part, layer, leaf)
+    t64 = lambda t: {k: (t64(v) if isinstance(v, dict) else torch.as_tensor(v, dtype=torch.float64)) for k, v in t.items()}
+    g = torch.Generator().manual_seed(0)
+    obs, eps = torch.randn(16, O, generator=g, dtype=torch.float64), torch.randn(16, L, generator=g, dtype=torch.float64)
+    zero = t64({p: {l: {k: np.zeros_like(v) for k, v in leaves.items()} for l, leaves in tree[p].items()} for p in tree})
+    _, logs = wmo.vae_loss(zero, obs, eps, 3.0)
+    assert float(logs["kl"]) == 0.0
+    assert float(logs["reconstruction_loss"]) == pytest.approx(float((obs ** 2).mean()))
+    assert float(logs["loss"]) == pytest.approx(3.0 * float((obs ** 2).mean()) / 4.0)
+    # the host-side numpy vae_loss agrees with the oracle on a random model
+    p = t64(tree)
+    mu, logvar = wmo.vae_encoder_apply(p["encoder"], obs)
+    recon = wmo.vae_decoder_apply(p["decoder"], mu + eps * torch.exp(0.5 * logvar))
+    loss, logs = wmo.vae_loss(p, obs, eps, 2.0)
+    hl, hlogs = vae_loss(obs.numpy(), recon.numpy(), mu.numpy(), logvar.numpy(), 2.0)
+    assert hl == pytest.approx(float(loss), rel=1e-5) and hlogs["kl"] == pytest.approx(float(logs["kl"]), rel=1e-5)
+    # one oracle step moves the parameters and reports the cosine schedule's first learning rate
+    new, slog, grads = wmo.vae_step(p, wmo.new_opt_state(p), obs, eps, reconstruction_weight=2.0, lr0=1e-3, decay_steps=10)
+    assert slog["learning_rate"] == pytest.approx(1e-3)
+    assert float((new["decoder"]["Dense_2"]["bias"] - p["decoder"]["Dense_2"]["bias"]).abs().max()) == pytest.approx(1e-3, rel=1e-3)
+
+
 def test_initial_observation_loader_errors_like_the_reference(tmp_path):
     """Missing files raise FileNotFoundError with the reference's messages (distribution_visualizer.py:68-75,84-91)."""
     from envmodel.initial_observation import load_initial_observation_decoder

@@ -391,3 +391,81 @@ def test_resident_window_sampling_matches_explicit_windows():
         b.step({k: v[idx] for k, v in data.items()}, train=True)
     assert np.array_equal(a.export(0), b.export(0))
     assert a.logs()[11] == 3.0
+
+
+@pytest.mark.parametrize("latent,hidden,rw,rows", [(8, (128, 64), 1.0, 256), (4, (128,), 10.0, 64), (3, (33, 50, 20), 0.0, 37)],
+                         ids=["two_hidden", "reference_default_one_hidden", "odd_widths_ragged_batch_kl_only"])
+def test_vae_steps_match_oracle(latent, hidden, rw, rows):
+    """InitialObservationEnvModel + vae_loss (envmodel/initial_observation.py:32-78) with the backward pass and Adam on
+    the device, against the float64 torch restatement fed the same batches and the same reparameterisation noise:
+    logs to 2e-5, gradients of the first step to 2e-5 of each leaf's scale, parameters after 3 steps as the other
+    world-model trainers; then an eval step leaves the parameters untouched."""
+    from fqlpop.worldmodel import VaeTrainer, init_vae_params
+    p0 = init_vae_params(3, O, latent, hidden)
+    g = torch.Generator().manual_seed(9)
+    for part in p0.values():                      # non-zero biases so that their gradients matter
+        for layer in part.values():
+            layer["bias"] = (0.05 * torch.randn(layer["bias"].shape, generator=g)).numpy().astype(np.float32)
+    tr = VaeTrainer(O, latent, hidden, rows, steps=100, init_learning_rate=1e-3, reconstruction_weight=rw, params=p0)
+    params = _t64(p0)
+    opt = wmo.new_opt_state(params)
+    for step in range(3):
+        obs = torch.randn(rows, O, generator=g, dtype=torch.float64)
+        eps = torch.randn(rows, latent, generator=g, dtype=torch.float64)
+        params, want, grads = wmo.vae_step(params, opt, obs, eps, reconstruction_weight=rw, lr0=1e-3, decay_steps=100)
+        got = tr.step(obs.to(torch.float32), eps.to(torch.float32), train=True)
+        _logs_close(got, want, ["loss", "reconstruction_loss", "kl"])
+        if step == 0:
+            _check_tree(tr.grads(), grads, 2e-5, "grad")
+        assert tr.logs()[10] == pytest.approx(want["learning_rate"], rel=1e-5)
+    _check_params(tr.params(), params, 1e-3)
+    before = tr.export(0)
+    obs = torch.randn(rows, O, generator=g, dtype=torch.float64)
+    eps = torch.randn(rows, latent, generator=g, dtype=torch.float64)
+    _, want, _ = wmo.vae_step(params, opt, obs, eps, reconstruction_weight=rw, lr0=1e-3, decay_steps=100, train=False)
+    _logs_close(tr.step(obs.to(torch.float32), eps.to(torch.float32), train=False), want, ["loss", "reconstruction_loss", "kl"])
+    assert np.array_equal(before, tr.export(0)) and tr.logs()[11] == 3
+    tr.close()
+
+
+def test_vae_trains_on_the_device_and_its_decoder_generates_initial_observations(tmp_path):
+    """train_env_model's `initial_observation` path end to end on synthetic episode starts drawn from a 2-dimensional
+    manifold: resident dataset, batches and latent noise sampled on the device, loss falling, the files written where the
+    reference's analysis script reads them, and the saved decoder (loaded through load_initial_observation_decoder, i.e.
+    the rollout's source of initial observations) reproducing what the trainer's own decoder parameters give."""
+    from functools import partial
+    from envmodel.config import TrainerConfig
+    from envmodel.initial_observation import (InitialObservationEnvModel, InitialObservationTrainer,
+                                              load_initial_observation_decoder, vae_loss)
+    from utils.data_loader import InitialObservationLoader
+    from utils.envmodel import save_model
+    rng = np.random.default_rng(0)
+    n_eps = 300
+    basis = rng.standard_normal((2, O)).astype(np.float32)
+    starts = (rng.standard_normal((n_eps, 2)).astype(np.float32) @ basis + 0.01 * rng.standard_normal((n_eps, O))).astype(np.float32)
+    obs = np.repeat(starts, 1000, axis=0)          # InitialObservationLoader keeps every 1000th row
+    obs[np.arange(len(obs)) % 1000 != 0] += 5.0    # (rows that are not episode starts must not be sampled)
+    loader = InitialObservationLoader({"observations": obs})
+    assert loader.dataset["observations"].shape == (n_eps, O)
+    cfg = TrainerConfig(env_name="synthetic-env", model="initial_observation", model_config={"hidden_dims": (64, 32), "latent_dim": 4},
+                        steps=600, batch_size=128, init_learning_rate=3e-3, reconstruction_weight=50.0, val_batches=2,
+                        save_directory=tmp_path)
+    model = InitialObservationEnvModel(O, 4, (64, 32))
+    tr = InitialObservationTrainer(model, loader, loader, partial(vae_loss, reconstruction_weight=50.0), cfg,
+                                   device_sampling=True)
+    first = tr.eval_step(loader.sample(128))
+    tr.train()
+    last = tr.last_validation
+    assert tr.state.step == 600
+    assert last["reconstruction_loss"] < 0.2 * first["reconstruction_loss"], (first, last)
+    assert np.isfinite(list(last.values())).all()
+    save_model(tr.state.params, tmp_path, "synthetic-env", "initial_observation", cfg.model_config)
+    dec = load_initial_observation_decoder(tmp_path, "synthetic-env", O)
+    z = torch.randn(50, 4, generator=torch.Generator().manual_seed(1))
+    want = wmo.vae_decoder_apply(_t64(tr.state.params["params"]["decoder"]), z.to(torch.float64)).numpy()
+    np.testing.assert_allclose(dec.sample(50, noise=z).cpu().numpy(), want, rtol=1e-4, atol=1e-4)
+    # samples land near the data's 2-dimensional subspace: the residual off the span of `basis` is small against the data scale
+    gen = dec.sample(512, seed=3).cpu().numpy()
+    q, _ = np.linalg.qr(basis.T)
+    off = gen - (gen @ q) @ q.T
+    assert np.sqrt((off ** 2).mean()) < 0.35 * np.sqrt((starts ** 2).mean())
