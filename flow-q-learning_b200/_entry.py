@@ -25,6 +25,9 @@ def sweep_parser(extra: Sequence[tuple]):
                        help="Evaluate in the learned world model (real ogbench/MuJoCo evaluation is unavailable here).")
     group.add_argument("--model", type=str, default="baseline", help="World-model kind of the simulated task.")
     group.add_argument("--max_episode_steps", type=int, default=1000, help="Truncation of simulated episodes.")
+    group.add_argument("--generated_initial_observations", action="store_true",
+                       help="Simulated episodes start from samples of the trained initial-observation VAE "
+                            "(train_env_model.py --model initial_observation) instead of environment resets.")
     group.add_argument("--strategy", choices=("identity", "successive_halving"), default="identity")
     group.add_argument("--fraction", type=float, default=0.5)
     group.add_argument("--history_length", type=int, default=1)
@@ -45,7 +48,9 @@ def make_task(args, config):
     if args.simulated_evaluations:
         from task.offline_task_simulated import OfflineTaskWithSimulatedEvaluations
         return OfflineTaskWithSimulatedEvaluations(config.env_name, model=args.model, save_directory=config.save_directory,
-                                                   max_episode_steps=args.max_episode_steps, **common)
+                                                   max_episode_steps=args.max_episode_steps,
+                                                   generated_initial_observations=args.generated_initial_observations,
+                                                   **common)
     from task.offline_task_real import OfflineTaskWithRealEvaluations
     return OfflineTaskWithRealEvaluations(config.env_name, **common)
 

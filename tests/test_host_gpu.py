@@ -176,11 +176,18 @@ def test_scripts_train_env_models_then_tune_alpha(tmp_path, monkeypatch):
     root = tmp_path / ENV / "env_models"
     assert sorted(p.name for p in root.iterdir()) == ["baseline.pt", "baseline_config.yaml", "termination_predictor.pt",
                                                       "termination_predictor_config.yaml"]
+    # the initial-observation VAE on the episode starts; the sweep below starts its simulated episodes from its samples
+    v = train_env_model.main(["--model", "initial_observation", "--device_sampling", "--model.latent_dim", "4",
+                              "--reconstruction_weight", "10.0"] + wm)
+    assert v.state.step == 60 and set(v.last_validation) == {"loss", "reconstruction_loss", "kl"}
+    assert (root / "initial_observation.pt").exists() and (root / "initial_observation_config.yaml").exists()
     trainer = tune_alpha.main(["--number_of_alphas", "3", "--number_of_seeds", "1", "--max_evaluations", "6",
                                "--steps", "40", "--eval_interval", "20", "--log_interval", "20", "--eval_episodes", "32",
                                "--agent.layer_norm", "--simulated_evaluations", "--max_episode_steps", "20",
+                               "--generated_initial_observations",
                                "--strategy", "successive_halving", "--total_evaluations", "6", "--history_length", "1"]
                               + common)
+    assert trainer.task.initial_observation_decoder is not None
     with open(tmp_path / ENV / "checkpoint.pkl", "rb") as f:
         ck = pickle.load(f)
     assert set(ck) == {"trainer", "strategy"}
