@@ -405,6 +405,49 @@ def worldmodel_bench(torch, np, dev, steps=2000, cpu_steps=100, with_cpu=True):
         out["cpu_baseline"] = {"value": cpu_steps / (time.perf_counter() - t0), "unit": "optimiser steps/s",
                                "cores": torch.get_num_threads(), "kind": "port",
                                "sample": f"{cpu_steps} steps of the same configuration, torch CPU fp32 oracle"}
+    out["vae"] = vae_bench(torch, np, dev, obs, O, with_cpu=with_cpu)
+    return out
+
+
+def vae_bench(torch, np, dev, obs, O, steps=1000, cpu_steps=50, with_cpu=True):
+    """training of the initial-observation VAE (envmodel/initial_observation.py:32-78) on the episode-start
+    rows of the same synthetic dataset: O -> 128 -> (4 | 4) -> 128 -> O, batch 256, batches and latent noise drawn on the
+    device. cpu_baseline: the torch-CPU fp32 oracle of the same step."""
+    from fqlpop.worldmodel import VaeTrainer, init_vae_params
+    L, hid, B = 4, (128,), 256
+    starts = obs[::1000].contiguous()
+    tr = VaeTrainer(O, L, hid, B, steps=steps, reconstruction_weight=1.0, params=init_vae_params(0, O, L, hid), device=dev)
+    tr.set_dataset(starts)
+    tr.train(50)
+    torch.cuda.synchronize()
+    l0 = tr.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    tr.train(steps)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    out = {"value": steps / (ms * 1e-3), "unit": "optimiser steps/s", "ms_per_step": ms / steps,
+           "launches_per_step": int((tr.launches - l0) // steps), "last_loss": tr.named_logs()["loss"],
+           "config": {"workload": f"VAE {O} -> {hid} -> 2 x {L} -> {hid[::-1]} -> {O}, batch {B}, {starts.shape[0]} resident "
+                                  "episode-start rows, fp32"}}
+    tr.close()
+    if with_cpu:
+        from oracle import wm_oracle as wmo   # checker / CPU baseline only
+        t32 = lambda t: {k: (t32(v) if isinstance(v, dict) else torch.as_tensor(v, dtype=torch.float32)) for k, v in t.items()}
+        params = t32(init_vae_params(0, O, L, hid))
+        opt = wmo.new_opt_state(params)
+        g = torch.Generator().manual_seed(1)
+        t0 = None
+        for i in range(cpu_steps + 5):
+            if i == 5:
+                t0 = time.perf_counter()
+            batch = starts[torch.randint(0, starts.shape[0], (B,), generator=g)]
+            params, _, _ = wmo.vae_step(params, opt, batch, torch.randn(B, L, generator=g), reconstruction_weight=1.0,
+                                        lr0=1e-3, decay_steps=steps)
+        out["cpu_baseline"] = {"value": cpu_steps / (time.perf_counter() - t0), "unit": "optimiser steps/s",
+                               "cores": torch.get_num_threads(), "kind": "port",
+                               "sample": f"{cpu_steps} steps of the same configuration, torch CPU fp32 oracle"}
     return out
 
 
@@ -412,7 +455,7 @@ def sh64_bench(torch, np, dev, rank, world, dist, barrier, n_alphas=64, shape="a
                total_evaluations=50, episodes=256, T=200):
     """BASELINE config 4: successive halving (f=0.5, h=2, total_evaluations=50) over 64 alpha values of a LIVE population
     sharded over the ranks (member i starts on rank i mod world; after every pruning the survivors are spread over the
-    GPUs again, one NCCL send / recv of the member's state per move -- FQLPOP_REBALANCE=0 keeps them where they are),
+    GPUs again, one NCCL broadcast of the member's state per move -- FQLPOP_REBALANCE=0 keeps them where they are),
     antsoccer shape, batch 256 -- the real Trainer + SuccessiveHalving + fused simulated evaluation, evaluation scores
     all-gathered (NCCL) after every evaluation so that every rank prunes identically. eval_interval is shortened (the reference trains 20 000 steps between evaluations);
     the schedule of population sizes is the reference's (64 -> 32 -> 16 -> 8 -> 4 -> 2 -> 1 at

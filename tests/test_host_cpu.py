@@ -147,3 +147,45 @@ def test_missing_dataset_raises_unless_synthetic_is_opted_in(tmp_path, monkeypat
     assert len(train["observations"]) == n - 2 and train["next_observations"].shape == train["observations"].shape
     _, _, train, _ = env_utils.make_env_and_datasets("cube-single-y", None)
     assert len(train["observations"]) == 2000
+
+
+def _planner(world, owner_of, free):
+    """A Trainer shell holding only what `_plan_moves` reads (the plan is a pure function of replicated state)."""
+    t = object.__new__(Trainer)
+    t.world = world
+    cands = list(owner_of)
+    t._order = {c: i for i, c in enumerate(cands)}
+    t._owner = dict(owner_of)
+    t._free_count = list(free)
+    return t
+
+
+def test_survivor_migration_plan():
+    """Trainer._plan_moves: evens out the live candidates per rank with as few moves as possible, never into a rank
+    without a free slot, never when ranks differ by at most one, and deterministically (every rank computes the plan)."""
+    held = lambda t, moves, cands: [sum(1 for c in cands if dict((m[0], m[2]) for m in moves).get(c, t._owner[c]) == r)
+                                    for r in range(t.world)]
+    # 8 survivors on 4 of 8 GPUs (the 8-member rung of config 4): four moves, one member per GPU afterwards
+    owner = {f"c{i}": i % 4 for i in range(8)}
+    t = _planner(8, owner, [4] * 8)
+    moves = t._plan_moves(list(owner))
+    assert len(moves) == 4 and held(t, moves, list(owner)) == [1] * 8
+    assert all(src < 4 <= dst for _, src, dst in moves)
+    assert moves == _planner(8, owner, [4] * 8)._plan_moves(list(reversed(list(owner))))     # order of the set is irrelevant
+    # only the candidates passed in count: pruned ones stay where they are and do not weigh
+    assert t._plan_moves(["c0", "c5"]) == []                                    # ranks 0 and 1: already one each
+    assert t._plan_moves(["c0", "c4"]) == [("c4", 0, 1)]                        # both on rank 0
+    # a difference of one is left alone (5 members on 2 ranks as 3 + 2)
+    t = _planner(2, {"a": 0, "b": 0, "c": 0, "d": 1, "e": 1}, [2, 2])
+    assert t._plan_moves(list("abcde")) == []
+    # no free slot anywhere else: nothing moves; one free slot: exactly one move, into it
+    t = _planner(2, {"a": 0, "b": 0, "c": 0, "d": 0}, [0, 0])
+    assert t._plan_moves(list("abcd")) == []
+    t = _planner(3, {"a": 0, "b": 0, "c": 0, "d": 0}, [0, 0, 1])
+    assert t._plan_moves(list("abcd")) == [("d", 0, 2)]
+    # a slot freed by a departure can be refilled later in the same plan, and the free counts are not mutated
+    t = _planner(2, {"a": 0, "b": 0, "c": 0, "d": 0}, [0, 4])
+    moves = t._plan_moves(list("abcd"))
+    assert held(t, moves, list("abcd")) == [2, 2] and t._free_count == [0, 4]
+    # the last candidates in slot order are the ones that leave
+    assert [m[0] for m in moves] == ["d", "c"]
