@@ -512,7 +512,9 @@ struct WmTrainer {
   float* tx[kWmMaxLayers + 1] = {};   // frozen termination predictor on the prediction (tx[0] aliases the prediction)
   float *xhat = nullptr, *pred = nullptr, *dbuf[2] = {nullptr, nullptr}, *dlogit = nullptr;
   float* gx[kWmMaxLayers + 1] = {};   // gx[l] = d loss / d x[l], one buffer per layer (side streams read them late)
-  float *logs = nullptr, *loss_part = nullptr, *rstd = nullptr, *ocur = nullptr, *wpart = nullptr, *cpart = nullptr;
+  float *logs = nullptr, *loss_part = nullptr, *rstd = nullptr, *ocur = nullptr, *carry = nullptr;
+  float* wparts[kWmMaxLayers] = {};      // multistep: [kWmSplits][din][dout] partial weight gradients, one buffer per layer
+  float* cparts[kWmMaxLayers + 1] = {};  // [kWmSplits][dout] partial bias sums; [nl]: LayerNorm bias / scale, 2 x [kWmSplits][D0]
   unsigned int* ticket = nullptr;
   int* step = nullptr;
   int rows = 0;  // batch * sequence length
@@ -578,14 +580,15 @@ struct Launcher {
   }
   // splits > 1: slice z of the k range goes to C + z * M * N (ldc must be N); wm_reduce adds the slices
   void gemm(bool ta, bool tb, const float* A, int lda, const float* B, int ldb, float* C, int ldc, int M, int N, int K,
-            int epi, const float* bias, const float* aux, int ldaux, int accumulate, int splits = 1) {
+            int epi, const float* bias, const float* aux, int ldaux, int accumulate, int splits = 1,
+            int min_tiles64 = 148) {
     const int kc = splits > 1 ? ((K + splits - 1) / splits + kWmBK - 1) / kWmBK * kWmBK : K;
     const long long cs = splits > 1 ? (long long)M * N : 0;
     // enough 64 x 64 tiles for every SM: the register-tiled kernel (the small per-step products keep the 32 x 32 one,
     // whose finer tiles give a latency-bound step more CTAs)
     const long long tiles64 = (long long)((N + kWmTile64 - 1) / kWmTile64) * ((M + kWmTile64 - 1) / kWmTile64) * splits;
     static const bool big_on = [] { const char* e = getenv("FQLPOP_WM_GEMM64"); return e ? atoi(e) != 0 : true; }();
-    if (big_on && tiles64 >= 148) {
+    if (big_on && tiles64 >= min_tiles64) {
       dim3 g64((N + kWmTile64 - 1) / kWmTile64, (M + kWmTile64 - 1) / kWmTile64, splits);
       if (ta) wm_gemm64_kernel<true, false><<<g64, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate, kc, cs);
       else if (tb) wm_gemm64_kernel<false, true><<<g64, 256, 0, cur>>>(A, lda, B, ldb, C, ldc, M, N, K, epi, bias, aux, ldaux, accumulate, kc, cs);
@@ -738,14 +741,54 @@ void wm_issue_multistep(WmTrainer* t, Launcher& L, int train, int gather, const 
   // FQLPOP_WM_SCAN=0 keeps the per-step launches (2 x T x 5 dependent small kernels) for A/B runs
   static const bool scan_on = [] { const char* e = getenv("FQLPOP_WM_SCAN"); return e ? atoi(e) != 0 : true; }();
   const bool scan = scan_on && t->scan_ok;
+  // Time chunks. The scans occupy (B / 4) SMs (64 of 148 at batch 256) and are latency-bound; everything else of the step
+  // is products over ALL T*B rows. Rows are time-major, so a chunk of time steps is a contiguous slab of rows: the
+  // window is cut into C chunks, the scans run chunk after chunk on the main stream, and the work over a chunk's rows
+  // runs beside the NEXT chunk's scan on the idle SMs -- forward: the frozen termination predictor; backward: its
+  // input-gradient chain (one chunk ahead) and the split-K weight-gradient / bias / LayerNorm sums (one chunk behind,
+  // every chunk filling its own slices of the partial-sum buffers, added in slice order at the end: deterministic).
+  // FQLPOP_WM_CHUNKS = 1 / 2 / 4 / 8 (default 4; windows shorter than 16 steps are not cut).
+  static const int chunks_env = [] { const char* e = getenv("FQLPOP_WM_CHUNKS"); const int v = e ? atoi(e) : 4; return v >= 8 ? 8 : (v >= 4 ? 4 : (v >= 2 ? 2 : 1)); }();
+  const int C = (scan && T >= 16) ? chunks_env : 1;
+  const int Tc = (T + C - 1) / C, Sc = kWmSplits / C;
+  auto t_lo = [&](int ch) { return std::min(T, ch * Tc); };
+  auto t_hi = [&](int ch) { return std::min(T, (ch + 1) * Tc); };
+  auto after = [&](cudaStream_t waiter, cudaStream_t done) {
+    cudaEvent_t e = L.ev();
+    cudaEventRecord(e, done);
+    cudaStreamWaitEvent(waiter, e, 0);
+  };
   ScanArgs sa{};
   if (scan) {
     sa.net = net; sa.params = t->params; sa.wt = t->wt;
     for (int l = 0; l <= nl; ++l) { sa.x[l] = t->x[l]; sa.gx[l] = t->gx[l]; }
     sa.ocur = t->ocur; sa.xhat = t->xhat; sa.rstd = t->rstd; sa.act = act;
     sa.B = B; sa.T = T; sa.O = O; sa.A = A; sa.maxdim = t->scan_maxdim; sa.eps = c.ln_eps; sa.cache_mask = t->scan_mask;
-    wm_scan_fwd_kernel<<<(B + kScanRB - 1) / kScanRB, kScanThreads, t->scan_smem, s>>>(sa);
-    ++L.n;
+    sa.carry_g = t->carry;
+  }
+  // frozen termination predictor over the rows of chunk ch (tx[0] aliases the predictions)
+  auto term_forward = [&](int ch) {
+    const long long r0 = (long long)t_lo(ch) * B;
+    const int rows = (t_hi(ch) - t_lo(ch)) * B;
+    if (rows <= 0) return;
+    float* tx[kWmMaxLayers + 1];
+    for (int l = 0; l <= t->term.n_layers; ++l) tx[l] = t->tx[l] + r0 * t->term.dims[l];
+    wm_forward(L, t->term, t->term_params, tx, rows, nullptr, 0);
+  };
+  if (scan) {
+    for (int ch = 0; ch < C; ++ch) {
+      sa.t0 = t_lo(ch); sa.t1 = t_hi(ch);
+      if (sa.t1 > sa.t0) {
+        wm_scan_fwd_kernel<<<(B + kScanRB - 1) / kScanRB, kScanThreads, t->scan_smem, s>>>(sa);
+        ++L.n;
+      }
+      if (with_term) {
+        if (C > 1) { after(L.w, s); L.cur = L.w; }
+        term_forward(ch);
+        L.cur = s;
+      }
+    }
+    if (with_term && C > 1) after(s, L.w);
   } else {
     for (int ti = 0; ti < T; ++ti) {
       float* act_l[kWmMaxLayers + 1];
@@ -758,9 +801,9 @@ void wm_issue_multistep(WmTrainer* t, Launcher& L, int train, int gather, const 
       ++L.n;
       wm_forward(L, net, t->params, act_l, B, o_t, O);
     }
+    if (with_term) term_forward(0);   // (C == 1: all rows)
   }
   float* pred = t->ocur + (long long)B * O;  // [T][B][O]
-  if (with_term) wm_forward(L, t->term, t->term_params, t->tx, R, nullptr, 0);  // tx[0] aliases pred
   wm_state_loss_kernel<<<kWmLossCtas, 256, 0, s>>>(pred, next_obs, with_term ? t->tx[t->term.n_layers] : nullptr, rew, R, B,
                                                   T, O, c.true_termination_weight, c.termination_weight,
                                                   c.reconstruction_weight, train ? t->gx[nl] : nullptr,
@@ -768,16 +811,47 @@ void wm_issue_multistep(WmTrainer* t, Launcher& L, int train, int gather, const 
                                                   t->loss_part, t->ticket);
   ++L.n;
   if (!train) return;
-  if (with_term) {
+  // d loss / d prediction through the frozen termination predictor, rows of chunk ch, added onto the squared-error part
+  auto term_backward = [&](int ch) {
+    const long long r0 = (long long)t_lo(ch) * B;
+    const int rows = (t_hi(ch) - t_lo(ch)) * B;
+    if (rows <= 0) return;
     const WmNet& tn = t->term;
-    const float* gt = t->dlogit;
+    const float* gt = t->dlogit + r0;
     for (int l = tn.n_layers - 1; l >= 0; --l) {
-      float* out = l == 0 ? t->gx[nl] : t->dbuf[l & 1];
-      L.gemm(false, true, gt, tn.dims[l + 1], t->term_params + tn.offW[l], tn.dims[l + 1], out, tn.dims[l], R, tn.dims[l],
-             tn.dims[l + 1], l == 0 ? WE_NONE : WE_MASK, nullptr, l == 0 ? nullptr : t->tx[l], tn.dims[l], l == 0);
+      float* out = (l == 0 ? t->gx[nl] : t->dbuf[l & 1]) + r0 * tn.dims[l];
+      L.gemm(false, true, gt, tn.dims[l + 1], t->term_params + tn.offW[l], tn.dims[l + 1], out, tn.dims[l], rows, tn.dims[l],
+             tn.dims[l + 1], l == 0 ? WE_NONE : WE_MASK, nullptr, l == 0 ? nullptr : t->tx[l] + r0 * tn.dims[l], tn.dims[l],
+             l == 0);
       gt = out;
     }
-  }
+  };
+  // parameter-gradient partial sums over the rows of chunk ch: slices [ch * Sc, (ch + 1) * Sc) of every layer's buffers
+  auto weight_grads = [&](int ch) {
+    const long long r0 = (long long)t_lo(ch) * B;
+    const int rows = (t_hi(ch) - t_lo(ch)) * B;
+    for (int l = nl - 1; l >= 0; --l) {
+      const int din = net.dims[l], dout = net.dims[l + 1];
+      float* wp = t->wparts[l] + (long long)ch * Sc * din * dout;
+      float* cp = t->cparts[l] + (long long)ch * Sc * dout;
+      if (rows <= 0) {   // (a window shorter than the chunk grid: this chunk's slices are zero)
+        cudaMemsetAsync(wp, 0, sizeof(float) * (size_t)Sc * din * dout, L.cur);
+        cudaMemsetAsync(cp, 0, sizeof(float) * (size_t)Sc * dout, L.cur);
+        continue;
+      }
+      // (a chunk's products run beside a scan on the ~84 SMs it leaves idle: fewer 64 x 64 tiles are enough)
+      L.gemm(true, false, t->x[l] + r0 * din, din, t->gx[l + 1] + r0 * dout, dout, wp, dout, din, dout, rows, WE_NONE, nullptr,
+             nullptr, 0, 0, Sc, C > 1 ? 84 : 148);
+      L.colsum(t->gx[l + 1] + r0 * dout, nullptr, dout, rows, dout, cp, nullptr, Sc);
+    }
+    float* lp = t->cparts[nl] + (long long)ch * Sc * D0;
+    if (rows <= 0) {
+      cudaMemsetAsync(lp, 0, sizeof(float) * (size_t)Sc * D0, L.cur);
+      cudaMemsetAsync(lp + (long long)kWmSplits * D0, 0, sizeof(float) * (size_t)Sc * D0, L.cur);
+    } else {
+      L.colsum(t->gx[0] + r0 * D0, t->xhat + r0 * D0, D0, rows, D0, lp, lp + (long long)kWmSplits * D0, Sc);
+    }
+  };
   if (scan) {
     for (int l = 0; l < nl; ++l) {
       const int n = net.dims[l] * net.dims[l + 1];
@@ -785,9 +859,34 @@ void wm_issue_multistep(WmTrainer* t, Launcher& L, int train, int gather, const 
                                                          net.dims[l + 1]);
       ++L.n;
     }
-    wm_scan_bwd_kernel<<<(B + kScanRB - 1) / kScanRB, kScanThreads, t->scan_smem, s>>>(sa);
-    ++L.n;
+    cudaEvent_t tb_done[8] = {};
+    if (with_term) {
+      term_backward(C - 1);              // the top chunk's rows first, on the main stream: the backward scan starts there
+      if (C > 1) {
+        after(L.w, s);                   // (the side stream has seen the loss kernel through this)
+        L.cur = L.w;
+        for (int ch = C - 2; ch >= 0; --ch) {
+          term_backward(ch);
+          tb_done[ch] = L.ev();
+          cudaEventRecord(tb_done[ch], L.w);
+        }
+        L.cur = s;
+      }
+    }
+    for (int ch = C - 1; ch >= 0; --ch) {
+      if (with_term && ch < C - 1) cudaStreamWaitEvent(s, tb_done[ch], 0);
+      sa.t0 = t_lo(ch); sa.t1 = t_hi(ch);
+      if (sa.t1 > sa.t0) {
+        wm_scan_bwd_kernel<<<(B + kScanRB - 1) / kScanRB, kScanThreads, t->scan_smem, s>>>(sa);
+        ++L.n;
+      }
+      if (C > 1) { after(L.c, s); L.cur = L.c; }
+      weight_grads(ch);
+      L.cur = s;
+    }
+    if (C > 1) L.cur = L.c;
   } else {
+    if (with_term) term_backward(0);
     // back-propagation through time: input-gradient chain of step ti, then LayerNorm backward + residual into step ti-1
     for (int ti = T - 1; ti >= 0; --ti) {
       const float* g = t->gx[nl] + (long long)ti * B * O;
@@ -805,19 +904,21 @@ void wm_issue_multistep(WmTrainer* t, Launcher& L, int train, int gather, const 
         ++L.n;
       }
     }
+    weight_grads(0);
   }
-  // parameter gradients over all T*B rows at once
+  // the slices of every buffer, added in slice order
   for (int l = nl - 1; l >= 0; --l) {
     const int din = net.dims[l], dout = net.dims[l + 1];
-    L.gemm(true, false, t->x[l], din, t->gx[l + 1], dout, t->wpart, dout, din, dout, R, WE_NONE, nullptr, nullptr, 0, 0,
-           kWmSplits);
-    L.reduce(t->wpart, kWmSplits, (long long)din * dout, t->grads + net.offW[l]);
-    L.colsum(t->gx[l + 1], nullptr, dout, R, dout, t->cpart, nullptr, kWmSplits);
-    L.reduce(t->cpart, kWmSplits, dout, t->grads + net.offB[l]);
+    L.reduce(t->wparts[l], kWmSplits, (long long)din * dout, t->grads + net.offW[l]);
+    L.reduce(t->cparts[l], kWmSplits, dout, t->grads + net.offB[l]);
   }
-  L.colsum(t->gx[0], t->xhat, D0, R, D0, t->cpart, t->cpart + (long long)kWmSplits * D0, kWmSplits);
-  L.reduce(t->cpart, kWmSplits, D0, t->grads + net.off_ln_bias);
-  L.reduce(t->cpart + (long long)kWmSplits * D0, kWmSplits, D0, t->grads + net.off_ln_scale);
+  L.reduce(t->cparts[nl], kWmSplits, D0, t->grads + net.off_ln_bias);
+  L.reduce(t->cparts[nl] + (long long)kWmSplits * D0, kWmSplits, D0, t->grads + net.off_ln_scale);
+  L.cur = s;
+  if (scan && C > 1) {
+    after(s, L.c);
+    if (with_term) after(s, L.w);   // (already ordered through tb_done; joins the side stream into the capture's end)
+  }
   wm_adam_kernel<<<(int)((net.n_params + 255) / 256), 256, 0, s>>>(t->params, t->m, t->v, t->grads, net.n_params, t->step,
                                                                   c.lr, c.decay_steps, t->logs);
   ++L.n;
@@ -895,9 +996,7 @@ int wm_create_impl(const WmConfig& cfg, const float* params_host, const float* t
   const long long R = (long long)B * t->cfg.seq_len;  // rows every per-row buffer holds (time-major slabs for multistep)
   t->rows = (int)R;
   int maxdim = 1;
-  long long maxw = 1;
   for (int l = 0; l <= nl; ++l) maxdim = std::max(maxdim, t->net.dims[l]);
-  for (int l = 0; l < nl; ++l) maxw = std::max(maxw, (long long)t->net.dims[l] * t->net.dims[l + 1]);
   int rc = 0;
   rc |= wm_alloc(t, &t->params, n, err) || wm_alloc(t, &t->m, n, err) || wm_alloc(t, &t->v, n, err) ||
         wm_alloc(t, &t->grads, n, err);
@@ -907,8 +1006,11 @@ int wm_create_impl(const WmConfig& cfg, const float* params_host, const float* t
   }
   if (!rc && state) rc |= wm_alloc(t, &t->xhat, R * t->net.dims[0], err) || wm_alloc(t, &t->rstd, R, err);
   if (!rc && multi) {
-    rc |= wm_alloc(t, &t->ocur, (R + B) * cfg.O, err) || wm_alloc(t, &t->wpart, kWmSplits * maxw, err) ||
-          wm_alloc(t, &t->cpart, 2LL * kWmSplits * maxdim, err);
+    rc |= wm_alloc(t, &t->ocur, (R + B) * cfg.O, err) || wm_alloc(t, &t->carry, (long long)B * cfg.O, err);
+    for (int l = 0; l < nl && !rc; ++l)
+      rc |= wm_alloc(t, &t->wparts[l], (long long)kWmSplits * t->net.dims[l] * t->net.dims[l + 1], err) ||
+            wm_alloc(t, &t->cparts[l], (long long)kWmSplits * t->net.dims[l + 1], err);
+    if (!rc) rc |= wm_alloc(t, &t->cparts[nl], 2LL * kWmSplits * t->net.dims[0], err);
     t->x[nl] = t->ocur ? t->ocur + (long long)B * cfg.O : nullptr;
     // persistent scan kernels: widths up to kScanMaxDim; the largest kernels that fit stay in shared memory
     if (!rc && maxdim <= kScanMaxDim && t->net.dims[0] <= kScanMaxIn) {

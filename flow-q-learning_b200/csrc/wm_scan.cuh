@@ -18,7 +18,9 @@
 // ([out][in], rebuilt once per optimiser step by wm_transpose_kernel) so that its products have the same access pattern.
 //
 // Measured (T = 256, B = 256, antsoccer shape, 64 CTAs): 6.9 ms per optimiser step against 14.6 ms for the per-step
-// launches (5.5 ms with termination_weight = 0, the reference scripts' setting); 6.0 / 5.3 ms with wm_gemm64_kernel. The per-step critical path is a chain of
+// launches (5.5 ms with termination_weight = 0, the reference scripts' setting); 6.0 / 5.3 ms with wm_gemm64_kernel;
+// 5.6 / 5.3 ms with the window cut into 4 time chunks (wm.cu: the products over a chunk's rows overlap the next chunk's
+// scan). The per-step critical path is a chain of
 // 9 short phases whose latencies (barrier, shared-memory round trips, L2 for the one kernel that does not fit) are paid in
 // full at 2 warps per scheduler: issue slots 24 % busy. Tried and dropped: 512 / 1024 threads with finer reduction
 // slices (7.4 / 9.0 ms: more partial sums to add, same latencies); clusters of 2 or 4 CTAs that split every layer's
@@ -49,6 +51,12 @@ struct ScanArgs {
   int maxdim;            // widest layer, rounded up to 32
   float eps;
   unsigned cache_mask;   // bit l: kernel l is copied into shared memory at kernel start
+  // One launch walks the time steps [t0, t1) (forward: upwards from o_{t0} = ocur slab t0; backward: downwards, the
+  // residual carry of step t1 arriving in / the one for step t0 - 1 leaving through carry_g [B][O]): the host cuts the
+  // window into chunks so that the work over a chunk's rows (termination predictor, weight gradients) overlaps the
+  // next chunk's scan on the SMs the scan leaves idle.
+  int t0, t1;
+  float* carry_g;
 };
 
 __host__ __device__ inline int scan_round4(int n) { return (n + 3) & ~3; }
@@ -269,7 +277,7 @@ __global__ void __launch_bounds__(kScanThreads) wm_scan_fwd_kernel(const __grid_
   float* ob = S.rowst;  // [RB][O] current observation of the rows
   for (int i = tid; i < kScanRB * O; i += kScanThreads) {
     const int r = scan_div(i, O), row = row0 + r;
-    ob[i] = row < B ? a.ocur[(long long)row * O + (i - r * O)] : 0.f;
+    ob[i] = row < B ? a.ocur[((long long)a.t0 * B + row) * O + (i - r * O)] : 0.f;
   }
   __syncthreads();
   const float* ln_scale = a.params + a.net.off_ln_scale;
@@ -285,9 +293,9 @@ __global__ void __launch_bounds__(kScanThreads) wm_scan_fwd_kernel(const __grid_
       a_pre[i] = (ln_ok && ti < T && j >= O && j < D) ? __ldg(a.act + ((long long)ln_row * T + ti) * A + (j - O)) : 0.f;
     }
   };
-  fetch_actions(0);
+  fetch_actions(a.t0);
   SCAN_TR_DECL;
-  for (int ti = 0; ti < T; ++ti) {
+  for (int ti = a.t0; ti < a.t1; ++ti) {
     // ---- x0 = LayerNorm(concat(o_t, a_t)) * scale + bias: one warp per row (as wm_ln_concat_kernel) ----
     if (warp < kScanRB) {
       const int row = ln_row;
@@ -403,7 +411,10 @@ __global__ void __launch_bounds__(kScanThreads) wm_scan_bwd_kernel(const __grid_
   const float* w[kWmMaxLayers];
   scan_load_weights<true>(a, a.wt, S.cache, w);
   float* carry = S.rowst;  // [RB][O]: what step t hands to the prediction of step t - 1
-  for (int i = tid; i < kScanRB * O; i += kScanThreads) carry[i] = 0.f;
+  for (int i = tid; i < kScanRB * O; i += kScanThreads) {
+    const int r = scan_div(i, O), row = row0 + r;
+    carry[i] = (a.t1 < T && row < B) ? a.carry_g[(long long)row * O + (i - r * O)] : 0.f;
+  }
   __syncthreads();
   const float* ln_scale = a.params + a.net.off_ln_scale;
   // global operands are fetched ahead of the phase that needs them: the loss gradient of step t - 1 during step t, the
@@ -416,14 +427,14 @@ __global__ void __launch_bounds__(kScanThreads) wm_scan_bwd_kernel(const __grid_
     for (int e = 0; e < kHeadPer; ++e) {
       const int i = tid + e * kScanThreads;
       const int r = scan_div(i, O), c = i - r * O, row = row0 + r;
-      g_pre[e] = (ti >= 0 && i < kScanRB * O && row < B) ? a.gx[nl][((long long)ti * B + row) * O + c] : 0.f;
+      g_pre[e] = (ti >= a.t0 && i < kScanRB * O && row < B) ? a.gx[nl][((long long)ti * B + row) * O + c] : 0.f;
     }
   };
-  fetch_loss_grad(T - 1);
+  fetch_loss_grad(a.t1 - 1);
   const int ln_row = row0 + warp;
   const bool ln_ok = warp < kScanRB && ln_row < B;
   SCAN_TR_DECL;
-  for (int ti = T - 1; ti >= 0; --ti) {
+  for (int ti = a.t1 - 1; ti >= a.t0; --ti) {
     // d loss / d o_{t+1}: the loss kernel's gradient plus the carry of step t + 1; the total goes back to gx[nl] (the
     // last layer's weight gradient reads it) and stays in `carry` for the residual path
     float *cur = S.xa, *nxt = S.xb;
@@ -536,6 +547,11 @@ __global__ void __launch_bounds__(kScanThreads) wm_scan_bwd_kernel(const __grid_
     __syncthreads();
     SCAN_TR(1);
   }
+  if (a.t0 > 0)
+    for (int i = tid; i < kScanRB * O; i += kScanThreads) {
+      const int r = scan_div(i, O), row = row0 + r;
+      if (row < B) a.carry_g[(long long)row * O + (i - r * O)] = carry[i];
+    }
   SCAN_TR_PRINT("wm_scan_bwd", nl);
 }
 
