@@ -1,6 +1,6 @@
 """Worker of tests/test_dist_gpu.py: one rank (torchrun) -- or the single-process reference run -- of the real Trainer +
 SuccessiveHalving + OfflineTaskWithSimulatedEvaluations.rollout_population over device populations, scores all-gathered
-over NCCL. Usage: [torchrun --nproc-per-node N] dist_gpu_worker.py <out_dir> [n_alphas]"""
+over NCCL. Usage: [torchrun --nproc-per-node N] dist_gpu_worker.py <out_dir> [n_alphas [resume]]"""
 import json
 import os
 import sys
@@ -16,7 +16,7 @@ os.environ.setdefault("FQLPOP_SYNTHETIC_ROWS", "20000")
 ENV = "cube-single-play-singletask-task2-v0"
 
 
-def main(out_dir, n_alphas=8):
+def main(out_dir, n_alphas=8, resume=0):
     from pathlib import Path
 
     import numpy as np
@@ -60,6 +60,18 @@ def main(out_dir, n_alphas=8):
         tr._migrate([(first, 0, 1)])
         assert tr._owner[first] == 1 and (first in tr.experiments) == (rank == 1)
     t0 = time.perf_counter()
+    if resume:
+        # stop after the first sweep + a part of the second (i.e. after the first rebalancing), write this rank's shard,
+        # throw everything away and rebuild population, experiments and strategy from the shard
+        import pickle
+        tr.train(max_evaluations=n_alphas + 2)
+        shard = pickle.loads(pickle.dumps({"trainer": tr.state_dict(), "strategy": sh.state_dict()}))
+        moved = tr.migrations
+        if tr.population is not None:
+            tr.population.close()
+        sh = SuccessiveHalving(set(pop), total_evaluations=3, fraction=0.5, history_length=1, state_dict=shard["strategy"])
+        tr = Trainer(task, sh, cfg, state_dict=shard["trainer"])
+        tr.migrations = moved
     tr.train(max_evaluations=1000)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
@@ -69,7 +81,7 @@ def main(out_dir, n_alphas=8):
            "steps": {repr(c.alpha): e.current_step for c, e in tr.experiments.items()}, "seconds": dt,
            "backend": (torch.distributed.get_backend() if world > 1 else None),
            "migrations": tr.migrations, "migration_seconds": tr.migration_seconds}
-    with open(os.path.join(out_dir, f"w{world}r{rank}.json"), "w") as f:
+    with open(os.path.join(out_dir, f"w{world}r{rank}{'_resumed' if resume else ''}.json"), "w") as f:
         json.dump(out, f)
     if tr.population is not None:
         tr.population.close()
@@ -78,4 +90,4 @@ def main(out_dir, n_alphas=8):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1], *(int(x) for x in sys.argv[2:3]))
+    main(sys.argv[1], *(int(x) for x in sys.argv[2:4]))

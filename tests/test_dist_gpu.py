@@ -45,3 +45,14 @@ def test_two_gpu_successive_halving_matches_single_process(tmp_path):
     assert {**r0["steps"], **r1["steps"]} == s["steps"]
     for a, v in s["scores"].items():
         assert r0["scores"][a] == pytest.approx(v, abs=1e-6), a
+    # save-then-resume in the middle of the second sweep, after members have moved: every rank rebuilds its population
+    # (spare slots included), its experiments and the owner map from its own shard and ends where the uninterrupted job did
+    again = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), worker, str(tmp_path), "8", "1"],
+                           env=env, capture_output=True, text=True, timeout=600)
+    assert again.returncode == 0, again.stdout[-2000:] + again.stderr[-2000:]
+    q0, q1 = (json.load(open(tmp_path / f"w2r{r}_resumed.json")) for r in range(2))
+    assert q0["candidates"] == q1["candidates"] == r0["candidates"]
+    assert q0["steps"] == r0["steps"] and q1["steps"] == r1["steps"]            # same members in the same places
+    for a, v in r0["scores"].items():
+        assert q0["scores"][a] == pytest.approx(v, abs=1e-6) and q1["scores"][a] == pytest.approx(v, abs=1e-6), a
