@@ -39,7 +39,17 @@ def main(rank, world, port, out_dir, mode="plain"):
             raise AssertionError("no ordering puts the best four on rank 0")
     pop = [ExperimentConfig(seed=i, alpha=a) for i, a in enumerate(alphas)]
     sh = SuccessiveHalving(set(pop), total_evaluations=4, fraction=0.5, history_length=1)
-    tr = Trainer(FakeTask(), sh, cfg, population_factory=FakePopulation, rebalance=migrate)
+    if mode.startswith("churn"):
+        # 24 members on `world` ranks, scores that reshuffle every evaluation, only two spare slots per rank: many plans,
+        # moves in both directions, re-entries of pruned members, moves skipped for want of a free slot
+        from fakes import ChurnTask
+        cfg = TrainerConfig(steps=160, eval_interval=10, log_interval=5, save_directory=Path(out_dir) / f"rank{rank}",
+                            env_name="cube-test", agent=AgentConfig(batch_size=8))
+        pop = [ExperimentConfig(seed=i, alpha=a) for i, a in enumerate(np.logspace(np.log10(3), 3, 24).tolist())]
+        sh = SuccessiveHalving(set(pop), total_evaluations=16, fraction=0.25, history_length=1)
+        tr = Trainer(ChurnTask(), sh, cfg, population_factory=FakePopulation, rebalance=mode == "churn_migrate", spare_slots=2)
+    else:
+        tr = Trainer(FakeTask(), sh, cfg, population_factory=FakePopulation, rebalance=migrate)
     if mode.endswith("resume"):
         # stop after the first sweep + half of the second, write this rank's shard, rebuild everything from it
         import pickle
@@ -53,6 +63,8 @@ def main(rank, world, port, out_dir, mode="plain"):
            "scores": {str(c.alpha): v for c, v in sh.candidate_scores.items()},
            "steps": {str(c.alpha): e.current_step for c, e in tr.experiments.items()},
            "migrations": tr.migrations, "owner": {str(c.alpha): r for c, r in tr._owner.items()},
+           "slots": {str(c.alpha): s for c, s in tr._slot.items()}, "free_count": list(tr._free_count),
+           "capacity": list(tr._capacity), "free_slots": sorted(tr._free_slots),
            "imports": [c for c in (tr.population.calls if tr.population else []) if c[0] == "import"],
            "device_steps": {str(c.alpha): int(tr.population.steps_done[tr._slot[c]]) for c in tr.experiments}}
     with open(os.path.join(out_dir, f"rank{rank}.json"), "w") as f:

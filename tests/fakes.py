@@ -119,3 +119,17 @@ class FakeTask(Task):
 
     def close(self):
         pass
+
+
+class ChurnTask(FakeTask):
+    """Scores that reshuffle from evaluation to evaluation (a fixed pseudo-random function of alpha and of the steps trained),
+    so that SuccessiveHalving's survivors change owners often and pruned candidates re-enter (its ranking covers every
+    candidate ever scored)."""
+
+    def rollout_population(self, population, seed=None, trajectory=False):
+        self.rollouts += 1
+        rate = np.full(population.P, np.nan, np.float32)
+        for m in population.active:
+            key = int(round(float(population.alphas[m]) * 1000)) * 7919 + int(population.steps_done[m]) * 104729
+            rate[m] = ((key * 2654435761) % 2 ** 32) / 2 ** 32
+        return {"success_rate": rate}

@@ -13,13 +13,18 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _run_two_ranks(tmp_path, mode="plain"):
+def _run_ranks(tmp_path, mode="plain", world=2):
     port = _free_port()
     worker = os.path.join(os.path.dirname(__file__), "dist_worker.py")
-    procs = [subprocess.Popen([sys.executable, worker, str(r), "2", str(port), str(tmp_path), mode]) for r in range(2)]
+    procs = [subprocess.Popen([sys.executable, worker, str(r), str(world), str(port), str(tmp_path), mode])
+             for r in range(world)]
     for p in procs:
         assert p.wait(timeout=240) == 0
-    return tuple(json.load(open(tmp_path / f"rank{r}.json")) for r in range(2))
+    return tuple(json.load(open(tmp_path / f"rank{r}.json")) for r in range(world))
+
+
+def _run_two_ranks(tmp_path, mode="plain"):
+    return _run_ranks(tmp_path, mode, 2)
 
 
 def test_two_rank_save_then_resume_matches_uninterrupted_run(tmp_path):
@@ -75,3 +80,30 @@ def test_two_rank_survivor_migration_changes_placement_not_results(tmp_path):
     for m, r in zip(moved, resumed):
         assert m["candidates"] == r["candidates"] and m["steps"] == r["steps"] and m["scores"] == r["scores"]
         assert m["owner"] == r["owner"] and r["device_steps"] == r["steps"]
+
+
+def test_three_rank_migration_under_churning_scores_keeps_the_books_straight(tmp_path):
+    """24 members on 3 ranks, successive halving by quarters, scores that reshuffle every evaluation (survivors change, pruned members re-enter), two spare
+    slots per rank (a rank that has used them takes no more migrants). Whatever the plans were: every rank holds the same owner map, every member
+    lives in exactly one slot of exactly one rank, the free-slot counts every rank keeps for the others are the truth, the
+    members' device state (steps trained) followed them, and scores / survivors / step totals equal the static run's."""
+    (tmp_path / "s").mkdir(); (tmp_path / "m").mkdir()
+    static = _run_ranks(tmp_path / "s", "churn_static", 3)
+    moved = _run_ranks(tmp_path / "m", "churn_migrate", 3)
+    assert moved[0]["migrations"] >= 3 and all(r["migrations"] == moved[0]["migrations"] for r in moved)
+    assert all(r["owner"] == moved[0]["owner"] and r["free_count"] == moved[0]["free_count"] for r in moved)
+    seen = {}
+    for rank, r in enumerate(moved):
+        assert set(r["steps"]) == {a for a, o in r["owner"].items() if o == rank} == set(r["slots"])
+        slots = sorted(r["slots"].values())
+        assert len(set(slots)) == len(slots) and all(0 <= s < r["capacity"][rank] for s in slots)
+        assert sorted(slots + r["free_slots"]) == list(range(r["capacity"][rank]))
+        assert r["free_count"][rank] == len(r["free_slots"])
+        assert r["device_steps"] == r["steps"]
+        for a in r["steps"]:
+            assert a not in seen
+            seen[a] = rank
+    assert len(seen) == 24
+    assert moved[0]["candidates"] == static[0]["candidates"] and moved[0]["scores"] == static[0]["scores"]
+    merged = lambda run: {a: n for r in run for a, n in r["steps"].items()}
+    assert merged(moved) == merged(static)
