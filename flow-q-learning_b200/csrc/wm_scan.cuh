@@ -20,7 +20,7 @@
 // Measured (T = 256, B = 256, antsoccer shape, 64 CTAs): 6.9 ms per optimiser step against 14.6 ms for the per-step
 // launches (5.5 ms with termination_weight = 0, the reference scripts' setting); 6.0 / 5.3 ms with wm_gemm64_kernel;
 // 5.6 / 5.3 ms with the window cut into 4 time chunks (wm.cu: the products over a chunk's rows overlap the next chunk's
-// scan). The per-step critical path is a chain of
+// scan); 5.5 / 5.2 ms with the LayerNorm scale / bias of a lane's inputs read once instead of on every step. The per-step critical path is a chain of
 // 9 short phases whose latencies (barrier, shared-memory round trips, L2 for the one kernel that does not fit) are paid in
 // full at 2 warps per scheduler: issue slots 24 % busy. Tried and dropped: 512 / 1024 threads with finer reduction
 // slices (7.4 / 9.0 ms: more partial sums to add, same latencies); clusters of 2 or 4 CTAs that split every layer's
@@ -294,6 +294,14 @@ __global__ void __launch_bounds__(kScanThreads) wm_scan_fwd_kernel(const __grid_
     }
   };
   fetch_actions(a.t0);
+  // this lane's LayerNorm scale / bias: read once, not on every step's critical path
+  float ln_s[kScanLnPer], ln_b[kScanLnPer];
+#pragma unroll
+  for (int i = 0; i < kScanLnPer; ++i) {
+    const int j = lane + 32 * i;
+    ln_s[i] = j < D ? __ldg(ln_scale + j) : 0.f;
+    ln_b[i] = j < D ? __ldg(ln_bias + j) : 0.f;
+  }
   SCAN_TR_DECL;
   for (int ti = a.t0; ti < a.t1; ++ti) {
     // ---- x0 = LayerNorm(concat(o_t, a_t)) * scale + bias: one warp per row (as wm_ln_concat_kernel) ----
@@ -323,7 +331,7 @@ __global__ void __launch_bounds__(kScanThreads) wm_scan_fwd_kernel(const __grid_
         const int j = lane + 32 * i;
         if (j < D) {
           const float h = (vin[i] - mean) * rstd;
-          const float x0 = ok ? h * ln_scale[j] + ln_bias[j] : 0.f;
+          const float x0 = ok ? h * ln_s[i] + ln_b[i] : 0.f;
           if (ok) {
             a.xhat[base + j] = h;
             a.x[0][base + j] = x0;
@@ -433,6 +441,9 @@ __global__ void __launch_bounds__(kScanThreads) wm_scan_bwd_kernel(const __grid_
   fetch_loss_grad(a.t1 - 1);
   const int ln_row = row0 + warp;
   const bool ln_ok = warp < kScanRB && ln_row < B;
+  float ln_s[kScanLnPer];   // this lane's LayerNorm scales, read once
+#pragma unroll
+  for (int i = 0; i < kScanLnPer; ++i) ln_s[i] = (lane + 32 * i) < D ? __ldg(ln_scale + lane + 32 * i) : 0.f;
   SCAN_TR_DECL;
   for (int ti = a.t1 - 1; ti >= a.t0; --ti) {
     // d loss / d o_{t+1}: the loss kernel's gradient plus the carry of step t + 1; the total goes back to gx[nl] (the
@@ -528,7 +539,7 @@ __global__ void __launch_bounds__(kScanThreads) wm_scan_bwd_kernel(const __grid_
 #pragma unroll
       for (int i = 0; i < kScanLnPer; ++i) {
         const int j = lane + 32 * i;
-        d[i] = j < D ? cur[j * kScanRB + warp] * ln_scale[j] : 0.f;
+        d[i] = j < D ? cur[j * kScanRB + warp] * ln_s[i] : 0.f;
         s1 += d[i];
         s2 += d[i] * xh_pre[i];
       }
