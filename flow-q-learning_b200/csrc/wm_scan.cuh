@@ -20,7 +20,8 @@
 // Measured (T = 256, B = 256, antsoccer shape, 64 CTAs): 6.9 ms per optimiser step against 14.6 ms for the per-step
 // launches (5.5 ms with termination_weight = 0, the reference scripts' setting); 6.0 / 5.3 ms with wm_gemm64_kernel;
 // 5.6 / 5.3 ms with the window cut into 4 time chunks (wm.cu: the products over a chunk's rows overlap the next chunk's
-// scan); 5.5 / 5.2 ms with the LayerNorm scale / bias of a lane's inputs read once instead of on every step. The per-step critical path is a chain of
+// scan); 5.4 / 5.1 ms with the LayerNorm scale / bias of a lane's inputs read once instead of on every step and the
+// slices' partial sums fetched four loads at a time. The per-step critical path is a chain of
 // 9 short phases whose latencies (barrier, shared-memory round trips, L2 for the one kernel that does not fit) are paid in
 // full at 2 warps per scheduler: issue slots 24 % busy. Tried and dropped: 512 / 1024 threads with finer reduction
 // slices (7.4 / 9.0 ms: more partial sums to add, same latencies); clusters of 2 or 4 CTAs that split every layer's
@@ -212,9 +213,20 @@ __device__ __forceinline__ void scan_product(const float* __restrict__ W, bool c
 __device__ __forceinline__ float4 scan_gather4(const float* part, int N, int r, int cg) {
   const int Np = scan_round4(N), G = scan_slices(N);
   const uint32_t a = scan_saddr(part) + (uint32_t)(r * Np + 4 * cg) * 4u;
+  // the slices' loads are issued back to back (four at a time), then added in slice order
   float4 v = scan_lds4(a);
-  for (int g = 1; g < G; ++g) {
-    const float4 p = scan_lds4(a + (uint32_t)(g * kScanRB * Np) * 4u);
+  const uint32_t step = (uint32_t)(kScanRB * Np) * 4u;
+  int g = 1;
+  for (; g + 3 < G; g += 4) {
+    const float4 p0 = scan_lds4(a + (uint32_t)g * step), p1 = scan_lds4(a + (uint32_t)(g + 1) * step);
+    const float4 p2 = scan_lds4(a + (uint32_t)(g + 2) * step), p3 = scan_lds4(a + (uint32_t)(g + 3) * step);
+    v.x += p0.x; v.y += p0.y; v.z += p0.z; v.w += p0.w;
+    v.x += p1.x; v.y += p1.y; v.z += p1.z; v.w += p1.w;
+    v.x += p2.x; v.y += p2.y; v.z += p2.z; v.w += p2.w;
+    v.x += p3.x; v.y += p3.y; v.z += p3.z; v.w += p3.w;
+  }
+  for (; g < G; ++g) {
+    const float4 p = scan_lds4(a + (uint32_t)g * step);
     v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
   }
   return v;
