@@ -27,7 +27,8 @@
 // slices (7.4 / 9.0 ms: more partial sums to add, same latencies); clusters of 2 or 4 CTAs that split every layer's
 // columns, keep the whole network shared-memory resident and broadcast their outputs with st.shared::cluster + one
 // barrier.cluster per layer (products 2x faster, but the cluster barrier and the remote stores cost ~1.5 k cycles per
-// layer: 8.0 ms).
+// layer: 8.0 ms); rotating the epilogues' four [column][row] activation stores per lane pair so that a warp's store
+// spreads over 8 banks instead of 2 (the bank-conflict replays ncu shows): the selects cost more than the replays (6.1 ms).
 #pragma once
 
 constexpr int kScanRB = 4;         // batch rows per CTA
